@@ -1,0 +1,664 @@
+// qex_oracle.cpp -- CPU ORACLE (TEST INFRASTRUCTURE ONLY, NOT PRODUCT CODE)
+//
+// A plain C++17/OpenMP restatement of the arithmetic of QEX's staggered
+// Dslash + CG hot path.  Only tests/, __graft_entry__.smoke() and the
+// cpu_baseline / --impl reference legs of bench.py may load this library, and
+// only as the checker or the timed CPU baseline.  The product
+// (qex_b200/csrc) never links, imports or calls anything in oracle/.
+//
+// Parity pin: the input generator (RngMilc6 seeding + Box-Muller gaussian +
+// projectSU + plaq) is pinned against the reference's own known-answer test
+// tests/reprod/trandgauge.nim:14-17 (six plaquettes of g.random on 8^4, default
+// seed 17^7) -- see tests/test_oracle_golden.py.  The reference publishes no
+// golden Dslash vector or stand-alone CG iteration count, so the
+// operator/solver restatement is additionally pinned by analytic identities
+// (free-field eigenvalues, anti-Hermiticity, D^+D block identity, solve(Dx)=x).
+// The reference itself (Nim + MPI + QMP) cannot be built in this image.
+//
+// Field memory layout used by the oracle == QEX's own layout for a single rank
+// with V=1 (innerGeom = 1,1,1,1): site index i = lex(x)/2 (+ nSites/2 for odd
+// sites), lex with x[0] fastest (layout/qlayout.nim:110-131); a colour vector
+// is double[3][2] per site, a colour matrix double[3][3][2] row-major
+// (maths/matrixConcept.nim:117-123, maths/complexType.nim:11-13).
+//
+// All file:line citations are relative to /root/reference.
+
+#include <cmath>
+#include <cstdint>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+#include <complex>
+#include <omp.h>
+
+typedef std::complex<double> cplx;
+
+extern "C" {
+
+// ---------------------------------------------------------------------------
+// Layout index maps  (src/layout/qlayout.nim:10-185)
+// ---------------------------------------------------------------------------
+struct OrcLayout {
+  int nd;
+  int phys[4], rankg[4], inner[4], local[4], outer[4];
+  int nSites, nEven, nOdd, nSitesOuter, nEvenOuter, nOddOuter, nSitesInner;
+  int innerCb, innerCbDir;
+};
+
+// layoutSetupQ, qlayout.nim:10-64.  returns 0 on success.
+int orc_layout_setup(OrcLayout* l, const int* phys, const int* rankg, const int* inner) {
+  l->nd = 4;
+  long pvol = 1, lvol = 1, ovol = 1;
+  int icb = 0, icbd = -1;
+  for (int i = 0; i < 4; i++) {
+    l->phys[i] = phys[i]; l->rankg[i] = rankg[i]; l->inner[i] = inner[i];
+    l->local[i] = phys[i] / rankg[i];
+    l->outer[i] = l->local[i] / inner[i];
+    pvol *= phys[i]; lvol *= l->local[i]; ovol *= l->outer[i];
+    if (inner[i] > 1 && (l->outer[i] & 1) == 1) icb++;
+    if (inner[i] == 1 && (l->outer[i] & 1) == 0) icbd = i;
+  }
+  if (icb == 0) icbd = 0;
+  else {
+    if (icbd < 0) return -1;
+    icb = l->outer[icbd] / 2;
+    if ((icb & 1) == 0) return -2;
+  }
+  l->nSites = (int)lvol;
+  l->nOdd = (int)(lvol / 2);
+  l->nEven = (int)(lvol - l->nOdd);
+  l->nSitesOuter = (int)ovol;
+  l->nOddOuter = (int)(ovol / 2);
+  l->nEvenOuter = (int)(ovol - l->nOddOuter);
+  l->nSitesInner = l->nSites / l->nSitesOuter;
+  l->innerCb = icb;
+  l->innerCbDir = icbd;
+  return 0;
+}
+
+// layoutIndexQ, qlayout.nim:110-131.  coords are GLOBAL lattice coordinates.
+void orc_layout_index(const OrcLayout* l, const int* coords_in, int* rank, int* index) {
+  int c[4];
+  for (int i = 0; i < 4; i++) c[i] = coords_in[i];
+  int ri = 0;   // lexr_i: x[0] slowest (qlayout.nim:94-104)
+  for (int i = 0; i < 4; i++) ri = ri * l->rankg[i] + ((c[i] / l->local[i]) % l->rankg[i]);
+  int ii = 0;   // lex_i: x[0] fastest (qlayout.nim:80-91)
+  for (int i = 3; i >= 0; i--) ii = ii * l->inner[i] + ((c[i] / l->outer[i]) % l->inner[i]);
+  int ib = 0;
+  for (int i = 0; i < 4; i++) {
+    int xi = c[i] / l->outer[i];
+    int xli = xi % l->inner[i];
+    ib += xli * l->outer[i];
+  }
+  ib &= 1;
+  c[l->innerCbDir] += l->innerCb * ib;
+  int oi = 0;
+  for (int i = 3; i >= 0; i--) oi = oi * l->outer[i] + (c[i] % l->outer[i]);
+  c[l->innerCbDir] -= l->innerCb * ib;
+  int p = 0;
+  for (int i = 0; i < 4; i++) p += c[i];
+  int oi2 = oi / 2;
+  if (p & 1) oi2 = (oi + l->nSitesOuter) / 2;
+  *rank = ri;
+  *index = oi2 * l->nSitesInner + ii;
+}
+
+// layoutCoordQ, qlayout.nim:133-185 (inverse map), restated as a search-free
+// closed form and checked against orc_layout_index by the tests.
+void orc_layout_coord(const OrcLayout* l, int rank, int index, int* coords) {
+  int cr[4];
+  { int r = rank; for (int i = 3; i >= 0; i--) { cr[i] = r % l->rankg[i]; r /= l->rankg[i]; } }
+  int p = 0;
+  int ll = index % l->nSitesInner;
+  int ib = 0;
+  for (int i = 0; i < 4; i++) {
+    int w = l->inner[i], wl = l->outer[i];
+    int k = ll % w;
+    int c = l->local[i] * cr[i] + k * wl;
+    cr[i] = c; p += c; ll /= w; ib += k * wl;
+  }
+  ib &= 1;
+  int ii = index / l->nSitesInner;
+  if (ii >= l->nEvenOuter) { ii -= l->nEvenOuter; p++; }
+  ii *= 2;
+  for (int i = 0; i < 4; i++) {
+    int wl = l->outer[i];
+    int k = ii % wl;
+    if (i == l->innerCbDir) k = (k + l->innerCb * ib) % wl;
+    coords[i] = k; p += k; ii /= wl;
+  }
+  if (p & 1) {
+    for (int i = 0; i < 4; i++) {
+      int wl = l->outer[i];
+      if (i == l->innerCbDir) coords[i] = (coords[i] + l->innerCb * ib) % wl;
+      coords[i]++;
+      if (coords[i] >= wl) {
+        coords[i] = 0;
+        if (i == l->innerCbDir) coords[i] = (coords[i] + l->innerCb * ib) % wl;
+      } else {
+        if (i == l->innerCbDir) coords[i] = (coords[i] + l->innerCb * ib) % wl;
+        break;
+      }
+    }
+  }
+  for (int i = 0; i < 4; i++) coords[i] += cr[i];
+}
+
+// ---------------------------------------------------------------------------
+// The oracle's working lattice: single rank, V=1.
+// ---------------------------------------------------------------------------
+struct Lat {
+  int L[4];
+  int vol, half;
+  std::vector<int> fwd[4][2];  // fwd[mu][h==1?0:1][i] = index of x + h*mu
+  std::vector<int> bwd[4][2];
+  std::vector<short> x[4];     // coords of site i
+};
+
+static inline int lat_index(const int* L, const int* x) {
+  int lex = ((x[3] * L[2] + x[2]) * L[1] + x[1]) * L[0] + x[0];
+  int p = (x[0] + x[1] + x[2] + x[3]) & 1;
+  int vol = L[0] * L[1] * L[2] * L[3];
+  return p ? (lex + vol) / 2 : lex / 2;
+}
+
+void* orc_lat_new(const int* L) {
+  Lat* l = new Lat;
+  for (int i = 0; i < 4; i++) l->L[i] = L[i];
+  l->vol = L[0] * L[1] * L[2] * L[3];
+  l->half = l->vol / 2;
+  for (int mu = 0; mu < 4; mu++) {
+    l->x[mu].resize(l->vol);
+    for (int h = 0; h < 2; h++) { l->fwd[mu][h].resize(l->vol); l->bwd[mu][h].resize(l->vol); }
+  }
+  int x[4];
+  for (x[3] = 0; x[3] < L[3]; x[3]++)
+  for (x[2] = 0; x[2] < L[2]; x[2]++)
+  for (x[1] = 0; x[1] < L[1]; x[1]++)
+  for (x[0] = 0; x[0] < L[0]; x[0]++) {
+    int i = lat_index(L, x);
+    for (int mu = 0; mu < 4; mu++) l->x[mu][i] = (short)x[mu];
+    for (int mu = 0; mu < 4; mu++) for (int h = 0; h < 2; h++) {
+      int hop = h ? 3 : 1;
+      int y[4] = {x[0], x[1], x[2], x[3]};
+      y[mu] = (x[mu] + hop) % L[mu];
+      l->fwd[mu][h][i] = lat_index(L, y);
+      y[mu] = ((x[mu] - hop) % L[mu] + L[mu]) % L[mu];
+      l->bwd[mu][h][i] = lat_index(L, y);
+    }
+  }
+  return l;
+}
+void orc_lat_free(void* p) { delete (Lat*)p; }
+int orc_lat_vol(void* p) { return ((Lat*)p)->vol; }
+void orc_lat_coords(void* p, short* out) {  // out[4][vol]
+  Lat* l = (Lat*)p;
+  for (int mu = 0; mu < 4; mu++) memcpy(out + (size_t)mu * l->vol, l->x[mu].data(), sizeof(short) * l->vol);
+}
+
+// ---------------------------------------------------------------------------
+// RngMilc6  (src/rng/milcrng.nim:12-188, non-FUELCompat branch)
+// ---------------------------------------------------------------------------
+struct Rng { uint32_t r0, r1, r2, r3, r4, r5, r6, ic, mult; };
+
+static const uint32_t INDX1 = 69607u, INDX2 = 8u, ADDEND = 12345u, MASK = 0x00FFFFFFu;
+
+// seedX, milcrng.nim:92-111
+static void rng_seed(Rng* p, uint32_t seed0, uint32_t index) {
+  uint32_t seed = seed0;
+  uint32_t* r[7] = {&p->r0, &p->r1, &p->r2, &p->r3, &p->r4, &p->r5, &p->r6};
+  for (int k = 0; k < 7; k++) {
+    seed = (INDX1 + INDX2 * index) * seed + ADDEND;
+    *r[k] = (seed >> 8) & MASK;
+  }
+  seed = (INDX1 + INDX2 * index) * seed + ADDEND;
+  p->ic = seed;
+  p->mult = 100005u + 8u * index;
+}
+// nextI, milcrng.nim:121-134
+static inline uint32_t rng_next(Rng* p) {
+  uint32_t t = (((p->r5 >> 7) | (p->r6 << 17)) ^ ((p->r4 >> 1) | (p->r5 << 23))) & MASK;
+  p->r6 = p->r5; p->r5 = p->r4; p->r4 = p->r3; p->r3 = p->r2; p->r2 = p->r1; p->r1 = p->r0; p->r0 = t;
+  uint32_t s = p->ic * p->mult + ADDEND;
+  p->ic = s;
+  return t ^ ((s >> 8) & MASK);
+}
+// uniform, milcrng.nim:150-154: float32 result
+static inline float rng_uniform(Rng* p) {
+  const float SCALE = 1.0f / (float)0x01000000;
+  return SCALE * (float)rng_next(p);
+}
+// gaussian, milcrng.nim:158-188 (non-FUELCompat): Box-Muller, one deviate per
+// two uniforms.  The source mixes float32 uniforms with float64 maths
+// (`var p = prn.uniform * 2.0 * PI`), and which products Nim takes in which
+// precision is not obvious from the text.  It was settled EMPIRICALLY against the
+// reference's known-answer plaquettes (tests/reprod/trandgauge.nim:14-17): of 18
+// candidate readings exactly one reproduces all six to sum-diff^2 = 1.4e-31
+// (bar: 1e-30): radius and phase in float64, the DEVIATE rounded to float32.
+// gauss_variant 0 keeps the all-float64 reading (misses the golden at 1e-20) so
+// the test can show the pin discriminates.
+static int gauss_variant = 8;
+void orc_set_gauss_variant(int v) { gauss_variant = v; }
+int orc_get_gauss_variant() { return gauss_variant; }
+static inline double rng_gaussian(Rng* p) {
+  const double TINY = 9.999999999999999e-308;
+  const double PI = 3.1415926535897932384626433;
+  double v = (double)rng_uniform(p);
+  float u = rng_uniform(p);
+  double r = sqrt(-2.0 * log(v + TINY));
+  double ph = (double)u * 2.0 * PI;
+  double g = r * cos(ph);
+  return gauss_variant == 0 ? g : (double)(float)g;
+}
+
+// newRNGField, distributionUtils.nim:306-331: one generator per site, seeded
+// with the lexicographic index (x[0] fastest, x[nd-1] slowest) of its coords.
+void* orc_rng_new(void* lat, uint64_t seed) {
+  Lat* l = (Lat*)lat;
+  Rng* r = (Rng*)malloc(sizeof(Rng) * l->vol);
+  for (int i = 0; i < l->vol; i++) {
+    long li = l->x[3][i];
+    for (int d = 2; d >= 0; d--) li = li * l->L[d] + l->x[d][i];
+    rng_seed(&r[i], (uint32_t)seed, (uint32_t)li);
+  }
+  return r;
+}
+void orc_rng_free(void* r) { free(r); }
+uint32_t orc_rng_next_site(void* r, int site) { return rng_next(&((Rng*)r)[site]); }
+
+// gaussian(Field, RNGField): distributionUtils.nim:13-24,65-97 -- every real
+// component of the site object in row-major order, re then im.
+void orc_gaussian(void* lat, void* rng, double* f, int nreal) {
+  Lat* l = (Lat*)lat; Rng* r = (Rng*)rng;
+  for (int i = 0; i < l->vol; i++)
+    for (int k = 0; k < nreal; k++) f[(size_t)i * nreal + k] = rng_gaussian(&r[i]);
+}
+
+// ---------------------------------------------------------------------------
+// 3x3 complex algebra
+// ---------------------------------------------------------------------------
+struct M3 { cplx e[3][3]; };
+struct V3 { cplx e[3]; };
+
+static inline M3 m3_load(const double* p) {
+  M3 m; for (int a = 0; a < 3; a++) for (int b = 0; b < 3; b++) m.e[a][b] = cplx(p[(a * 3 + b) * 2], p[(a * 3 + b) * 2 + 1]); return m;
+}
+static inline void m3_store(double* p, const M3& m) {
+  for (int a = 0; a < 3; a++) for (int b = 0; b < 3; b++) { p[(a * 3 + b) * 2] = m.e[a][b].real(); p[(a * 3 + b) * 2 + 1] = m.e[a][b].imag(); }
+}
+static inline cplx cmul(cplx a, cplx b) {  // plain complex product (no inf/nan fix-ups)
+  return cplx(a.real() * b.real() - a.imag() * b.imag(), a.real() * b.imag() + a.imag() * b.real());
+}
+static inline M3 m3_mul(const M3& a, const M3& b) {
+  M3 r; for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) { cplx s = 0; for (int k = 0; k < 3; k++) s += cmul(a.e[i][k], b.e[k][j]); r.e[i][j] = s; } return r;
+}
+static inline M3 m3_adj(const M3& a) {
+  M3 r; for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) r.e[i][j] = std::conj(a.e[j][i]); return r;
+}
+// determinant, matrixFunctions.nim:66-77
+static inline cplx m3_det(const M3& x) {
+  return cmul(cmul(x.e[0][0], x.e[1][1]) - cmul(x.e[0][1], x.e[1][0]), x.e[2][2]) +
+         cmul(cmul(x.e[0][2], x.e[1][0]) - cmul(x.e[0][0], x.e[1][2]), x.e[2][1]) +
+         cmul(cmul(x.e[0][1], x.e[1][2]) - cmul(x.e[0][2], x.e[1][1]), x.e[2][0]);
+}
+// eigs3, matrixFunctions.nim:79-111
+static inline void eigs3(double& e0, double& e1, double& e2, double tr, double p2, double det) {
+  double tr3 = (1.0 / 3.0) * tr;
+  double p23 = (1.0 / 3.0) * p2;
+  double tr32 = tr3 * tr3;
+  double q = fabs(0.5 * (p23 - tr32));
+  double r = 0.25 * tr3 * (5 * tr32 - p2) - 0.5 * det;
+  double sq = sqrt(q);
+  double sq3 = q * sq;
+  double isq3 = 1.0 / sq3;
+  double isq3c = fmin(3e38, fmax(-3e38, isq3));
+  double rsq3c = r * isq3c;
+  double rsq3 = fmin(1.0, fmax(-1.0, rsq3c));
+  double t = (1.0 / 3.0) * acos(rsq3);
+  double st = sin(t), ct = cos(t);
+  double sqc = sq * ct;
+  double sqs = 1.73205080756887729352 * sq * st;
+  double ll = tr3 + sqc;
+  e0 = tr3 - 2 * sqc; e1 = ll + sqs; e2 = ll - sqs;
+}
+// rsqrtPHM3f + rsqrtPHM3, matrixFunctions.nim:126-181
+static inline M3 rsqrtPH3(const M3& x) {
+  double tr = (x.e[0][0] + x.e[1][1] + x.e[2][2]).real();
+  M3 x2 = m3_mul(x, x);
+  double p2 = (x2.e[0][0] + x2.e[1][1] + x2.e[2][2]).real();
+  double det = m3_det(x).real();
+  double l0, l1, l2;
+  eigs3(l0, l1, l2, tr, p2, det);
+  double sl0 = sqrt(fabs(l0)), sl1 = sqrt(fabs(l1)), sl2 = sqrt(fabs(l2));
+  double u = sl0 + sl1 + sl2;
+  double w = sl0 * sl1 * sl2;
+  double d = w * (sl0 + sl1) * (sl0 + sl2) * (sl1 + sl2);
+  double di = 1 / d;
+  double c0 = (w * u * u + l0 * sl0 * (l1 + l2) + l1 * sl1 * (l0 + l2) + l2 * sl2 * (l0 + l1)) * di;
+  double c1 = -(tr * u + w) * di;
+  double c2 = u * di;
+  M3 r;
+  for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) {
+    r.e[i][j] = c1 * x.e[i][j] + c2 * x2.e[i][j];
+    if (i == j) r.e[i][j] += c0;
+  }
+  return r;
+}
+// projectU, matrixFunctions.nim:301-312: x (x^+ x + eps)^{-1/2}
+static inline M3 projectU(const M3& x) {
+  M3 t = m3_mul(m3_adj(x), x);
+  for (int i = 0; i < 3; i++) t.e[i][i] += 1e-20;
+  return m3_mul(x, rsqrtPH3(t));
+}
+// projectSU, matrixFunctions.nim:359-370
+static inline M3 projectSU(const M3& x) {
+  M3 m = projectU(x);
+  cplx d = m3_det(m);
+  double p = (1.0 / -3.0) * atan2(d.imag(), d.real());
+  cplx ph(cos(p), sin(p));
+  M3 r; for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) r.e[i][j] = cmul(ph, m.e[i][j]);
+  return r;
+}
+void orc_projectU(const double* in, double* out) { m3_store(out, projectU(m3_load(in))); }
+void orc_projectSU(const double* in, double* out) { m3_store(out, projectSU(m3_load(in))); }
+
+// random(g, r): gaugeUtils.nim:1424-1429 -> randomSU :1352-1354, mu by mu on the
+// continuing per-site streams.  g = nmu contiguous fields [mu][vol][18].
+void orc_random_gauge(void* lat, void* rng, double* g, int nmu) {
+  Lat* l = (Lat*)lat;
+  for (int mu = 0; mu < nmu; mu++) {
+    double* gm = g + (size_t)mu * l->vol * 18;
+    orc_gaussian(lat, rng, gm, 18);
+#pragma omp parallel for
+    for (int i = 0; i < l->vol; i++) m3_store(gm + (size_t)i * 18, projectSU(m3_load(gm + (size_t)i * 18)));
+  }
+}
+
+// plaq, gaugeUtils.nim:213-284: pl[ip(mu,nu)] = sum_x Re tr[(U_mu(x)U_nu(x+mu))^+ (U_nu(x)U_mu(x+nu))] / (vol*6*3)
+void orc_plaq(void* lat, const double* g, double* pl) {
+  Lat* l = (Lat*)lat;
+  size_t fs = (size_t)l->vol * 18;
+  for (int mu = 1; mu < 4; mu++) for (int nu = 0; nu < mu; nu++) {
+    double s = 0;
+#pragma omp parallel for reduction(+ : s)
+    for (int i = 0; i < l->vol; i++) {
+      M3 unumu = m3_mul(m3_load(g + nu * fs + (size_t)i * 18), m3_load(g + mu * fs + (size_t)l->fwd[nu][0][i] * 18));
+      M3 umunu = m3_mul(m3_load(g + mu * fs + (size_t)i * 18), m3_load(g + nu * fs + (size_t)l->fwd[mu][0][i] * 18));
+      double d = 0;
+      for (int a = 0; a < 3; a++) for (int b = 0; b < 3; b++)
+        d += umunu.e[a][b].real() * unumu.e[a][b].real() + umunu.e[a][b].imag() * unumu.e[a][b].imag();
+      s += d;
+    }
+    pl[(mu * (mu - 1)) / 2 + nu] = s / ((double)l->vol * 6.0 * 3.0);
+  }
+}
+
+// setBC, gaugeUtils.nim:124-131: U_3 *= -1 on the last time slice
+void orc_setbc(void* lat, double* g) {
+  Lat* l = (Lat*)lat;
+  double* gt = g + (size_t)3 * l->vol * 18;
+  for (int i = 0; i < l->vol; i++)
+    if (l->x[3][i] == l->L[3] - 1) for (int k = 0; k < 18; k++) gt[(size_t)i * 18 + k] *= -1;
+}
+// stagPhase, stagD.nim:509-522 with phases [8,9,11,0]
+void orc_stagphase(void* lat, double* g) {
+  Lat* l = (Lat*)lat;
+  const int phases[4] = {8, 9, 11, 0};
+  for (int mu = 0; mu < 4; mu++) {
+    double* gm = g + (size_t)mu * l->vol * 18;
+    for (int i = 0; i < l->vol; i++) {
+      int s = 0;
+      for (int k = 0; k < 4; k++) s += (phases[mu] >> k) & l->x[k][i];
+      if (s & 1) for (int k = 0; k < 18; k++) gm[(size_t)i * 18 + k] *= -1;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Staggered operator  (src/physics/stagD.nim)
+// g = nd contiguous link fields [k][vol][18]; nd==4: hop 1 in dir k;
+// nd==8: g[2mu] hop 1, g[2mu+1] hop 3 in dir mu  (stagD.nim:36-49,552-564).
+// ---------------------------------------------------------------------------
+static inline void mv_acc(double* acc, const double* u, const double* v, double sgn) {
+  // acc += sgn * U v
+  for (int a = 0; a < 3; a++) {
+    double re = 0, im = 0;
+    for (int b = 0; b < 3; b++) {
+      double ur = u[(a * 3 + b) * 2], ui = u[(a * 3 + b) * 2 + 1];
+      re += ur * v[2 * b] - ui * v[2 * b + 1];
+      im += ur * v[2 * b + 1] + ui * v[2 * b];
+    }
+    acc[2 * a] += sgn * re; acc[2 * a + 1] += sgn * im;
+  }
+}
+static inline void mv_adj_acc(double* acc, const double* u, const double* v, double sgn) {
+  // acc += sgn * U^+ v
+  for (int a = 0; a < 3; a++) {
+    double re = 0, im = 0;
+    for (int b = 0; b < 3; b++) {
+      double ur = u[(b * 3 + a) * 2], ui = -u[(b * 3 + a) * 2 + 1];
+      re += ur * v[2 * b] - ui * v[2 * b + 1];
+      im += ur * v[2 * b + 1] + ui * v[2 * b];
+    }
+    acc[2 * a] += sgn * re; acc[2 * a + 1] += sgn * im;
+  }
+}
+
+// stagD2 on one parity, stagD.nim:348-395:
+//   r[s] = a*r[s] + b*x[s] + sum_k [ g_k(s) x(s+h_k) - g_k(s-h_k)^+ x(s-h_k) ]
+// sgn=-1 gives the stagDM flavour (stagD.nim:278-313).  parity 0=even, 1=odd.
+static void stag_sweep(Lat* l, int nd, const double* g, double* r, const double* x,
+                       double a, const double* bx, double b, int parity, double sgn) {
+  size_t fs = (size_t)l->vol * 18;
+  int lo = parity ? l->half : 0, hi = parity ? l->vol : l->half;
+#pragma omp parallel for schedule(static)
+  for (int i = lo; i < hi; i++) {
+    double acc[6] = {0, 0, 0, 0, 0, 0};
+    for (int k = 0; k < nd; k++) {
+      int mu = (nd == 8) ? k / 2 : k;
+      int h = (nd == 8) ? (k & 1) : 0;
+      int jf = l->fwd[mu][h][i], jb = l->bwd[mu][h][i];
+      mv_acc(acc, g + k * fs + (size_t)i * 18, x + (size_t)jf * 6, 1.0);
+      mv_adj_acc(acc, g + k * fs + (size_t)jb * 18, x + (size_t)jb * 6, -1.0);
+    }
+    for (int c = 0; c < 6; c++) {
+      double ini = 0;
+      if (a != 0.0) ini += a * r[(size_t)i * 6 + c];
+      if (b != 0.0) ini += b * bx[(size_t)i * 6 + c];
+      r[(size_t)i * 6 + c] = ini + sgn * acc[c];
+    }
+  }
+}
+
+void orc_stagD2(void* lat, int nd, const double* g, double* r, const double* x, double a, double b, int parity) {
+  stag_sweep((Lat*)lat, nd, g, r, x, a, x, b, parity, 1.0);
+}
+// stagD, stagD.nim:405-409
+void orc_stagD(void* lat, int nd, const double* g, double* r, const double* x, double m, double sc, double a, int parity) {
+  Lat* l = (Lat*)lat;
+  orc_stagD2(lat, nd, g, r, x, a / (0.5 * sc), m / (0.5 * sc), parity);
+  int lo = parity ? l->half : 0, hi = parity ? l->vol : l->half;
+#pragma omp parallel for
+  for (int i = lo * 6; i < hi * 6; i++) r[i] = (0.5 * sc) * r[i];
+}
+// D / Ddag, stagD.nim:566-571
+void orc_D(void* lat, int nd, const double* g, double* r, const double* x, double m) {
+  orc_stagD(lat, nd, g, r, x, m, 1.0, 0.0, 0); orc_stagD(lat, nd, g, r, x, m, 1.0, 0.0, 1);
+}
+void orc_Ddag(void* lat, int nd, const double* g, double* r, const double* x, double m) {
+  orc_stagD(lat, nd, g, r, x, m, -1.0, 0.0, 0); orc_stagD(lat, nd, g, r, x, m, -1.0, 0.0, 1);
+}
+// stagD2xx, stagD.nim:433-469: r[px] = 4 m2 x - (2D)_{px,py} (2D)_{py,px} x ; t = scratch full field
+void orc_stagD2xx(void* lat, int nd, const double* g, double* r, const double* x, double m2, int parity, double* t) {
+  Lat* l = (Lat*)lat;
+  stag_sweep(l, nd, g, t, x, 0.0, x, 0.0, 1 - parity, 1.0);       // stagDP, rir := 0
+  stag_sweep(l, nd, g, r, t, 0.0, x, 4.0 * m2, parity, -1.0);     // stagDM, rir := (4 m2) x
+}
+// eoReconstruct, stagD.nim:582-586: r.odd = (b.odd - D_oe r.even)/m
+void orc_eoReconstruct(void* lat, int nd, const double* g, double* r, const double* b, double m) {
+  Lat* l = (Lat*)lat;
+  orc_stagD(lat, nd, g, r, r, 0.0, -1.0 / m, 0.0, 1);
+#pragma omp parallel for
+  for (int i = l->half * 6; i < l->vol * 6; i++) r[i] += b[i] / m;
+}
+
+// ---------------------------------------------------------------------------
+// Field BLAS-1 on a subset (field/fieldET.nim:547-734)
+// subset: 0 even, 1 odd, 2 all
+// ---------------------------------------------------------------------------
+static inline void sub_range(Lat* l, int sub, size_t& lo, size_t& hi) {
+  lo = (sub == 1) ? (size_t)l->half * 6 : 0;
+  hi = (sub == 0) ? (size_t)l->half * 6 : (size_t)l->vol * 6;
+}
+double orc_norm2(void* lat, const double* x, int sub) {
+  size_t lo, hi; sub_range((Lat*)lat, sub, lo, hi);
+  double s = 0;
+#pragma omp parallel for reduction(+ : s)
+  for (size_t i = lo; i < hi; i++) s += x[i] * x[i];
+  return s;
+}
+double orc_redot(void* lat, const double* x, const double* y, int sub) {
+  size_t lo, hi; sub_range((Lat*)lat, sub, lo, hi);
+  double s = 0;
+#pragma omp parallel for reduction(+ : s)
+  for (size_t i = lo; i < hi; i++) s += x[i] * y[i];
+  return s;
+}
+
+// ---------------------------------------------------------------------------
+// CG  (src/solvers/cg.nim:55-272, cpNone), operator A = stagD2xx(m2) on `parity`
+// x in/out (initial guess), b rhs.  Returns iterations; *r2out = final recursive r2.
+// ---------------------------------------------------------------------------
+int orc_cg_xx(void* lat, int nd, const double* g, double* x, const double* b, double m2, int parity,
+              double r2req, int maxits, double* r2out, double* b2out) {
+  Lat* l = (Lat*)lat;
+  size_t n = (size_t)l->vol * 6, lo, hi; sub_range(l, parity, lo, hi);
+  std::vector<double> r(n, 0.0), Ap(n, 0.0), p(n, 0.0), t(n, 0.0);
+  double b2 = orc_norm2(lat, b, parity), r2 = 0.0;
+  if (b2 == 0.0) {
+    for (size_t i = lo; i < hi; i++) x[i] = 0;
+    if (r2out) *r2out = 0; if (b2out) *b2out = 0;
+    return 0;
+  }
+  orc_stagD2xx(lat, nd, g, Ap.data(), x, m2, parity, t.data());          // cg.nim:146
+#pragma omp parallel for
+  for (size_t i = lo; i < hi; i++) { r[i] = b[i] - Ap[i]; p[i] = 0; }   // :148-150
+  r2 = orc_norm2(lat, r.data(), parity);
+  double r2stop = r2req * b2;                                            // :155
+  int itn = 0; double rzo = 1.0, rz;
+  while (itn < maxits && r2 > r2stop) {                                  // :174
+    rz = r2;                                                             // getRz, cpNone
+    double beta = rz / rzo;                                              // :186
+    rzo = rz;
+    if (itn == 0) {
+#pragma omp parallel for
+      for (size_t i = lo; i < hi; i++) p[i] = r[i];                      // :190
+    } else {
+#pragma omp parallel for
+      for (size_t i = lo; i < hi; i++) p[i] = r[i] + beta * p[i];        // :192
+    }
+    itn++;
+    orc_stagD2xx(lat, nd, g, Ap.data(), p.data(), m2, parity, t.data()); // :200
+    double pAp = orc_redot(lat, p.data(), Ap.data(), parity);            // :206
+    double alpha = rz / pAp;                                             // :208
+#pragma omp parallel for
+    for (size_t i = lo; i < hi; i++) { x[i] += alpha * p[i]; r[i] -= alpha * Ap[i]; }  // :209-211
+    r2 = orc_norm2(lat, r.data(), parity);                               // :213
+  }
+  if (r2out) *r2out = r2; if (b2out) *b2out = b2;
+  return itn;
+}
+
+// solveXX with sbQex backend, stagSolve.nim:57-99: r := 0 then CG on A x = b
+int orc_solveXX(void* lat, int nd, const double* g, double* r, const double* x, double m, int parity,
+                double r2req, int maxits, double* r2out) {
+  Lat* l = (Lat*)lat;
+  memset(r, 0, sizeof(double) * (size_t)l->vol * 6);
+  return orc_cg_xx(lat, nd, g, r, x, m * m, parity, r2req, maxits, r2out, nullptr);
+}
+
+struct OrcSolveStats { int iterations; int calls; double r2; double b2; };
+
+// solveReconR, stagSolve.nim:141-176
+static void solveReconR(Lat* l, int nd, const double* g, double* x, const double* b, double m,
+                        double& r2req, int maxits, int& its, double b2e, double b2o) {
+  size_t n = (size_t)l->vol * 6;
+  double b2 = b2e + b2o, r2stop = r2req * b2, r2stop2 = 0.5 * r2stop;
+  double r2stope = (b2o <= r2stop2) ? r2stop - b2o : r2stop2;
+  if (b2e > r2stope) {
+    std::vector<double> y(n, 0.0);
+    r2req = r2stope / b2e;
+    its += orc_solveXX(l, nd, g, y.data(), b, m, 0, r2req, maxits, nullptr);
+    for (size_t i = 0; i < (size_t)l->half * 6; i++) y[i] *= 4;
+    orc_Ddag(l, nd, g, x, y.data(), m);
+    return;
+  }
+  double r2stopo = (b2e <= r2stop2) ? r2stop - b2e : r2stop2;
+  if (b2o > r2stopo) {
+    std::vector<double> y(n, 0.0);
+    r2req = r2stopo / b2o;
+    its += orc_solveXX(l, nd, g, y.data(), b, m, 1, r2req, maxits, nullptr);
+    for (size_t i = (size_t)l->half * 6; i < n; i++) y[i] *= 4;
+    orc_Ddag(l, nd, g, x, y.data(), m);
+    return;
+  }
+}
+// solveReconL, stagSolve.nim:179-208
+static void solveReconL(Lat* l, int nd, const double* g, double* x, const double* b, double m,
+                        double& r2req, int maxits, int& its, double b2e, double b2o) {
+  size_t n = (size_t)l->vol * 6;
+  std::vector<double> d(n, 0.0);
+  orc_Ddag(l, nd, g, d.data(), b, m);
+  memset(x, 0, sizeof(double) * n);
+  double d2e = orc_norm2(l, d.data(), 0);
+  r2req = 0.99 * r2req * (b2e + b2o) * m * m / d2e;
+  its += orc_solveXX(l, nd, g, x, d.data(), m, 0, r2req, maxits, nullptr);
+  for (size_t i = 0; i < (size_t)l->half * 6; i++) x[i] *= 4;
+  orc_eoReconstruct(l, nd, g, x, b, m);
+}
+// solveInner, stagSolve.nim:211-222
+static void solveInner(Lat* l, int nd, const double* g, double* x, const double* b, double m,
+                       double& r2req, int maxits, int& its, double b2e, double b2o) {
+  double b2 = b2e + b2o, r2stop = r2req * b2, r2stop2 = 0.5 * r2stop;
+  double r2stope = (b2o <= r2stop2) ? r2stop - b2o : r2stop2;
+  double r2stopo = (b2e <= r2stop2) ? r2stop - b2e : r2stop2;
+  if (b2e <= r2stope || b2o <= r2stopo || m == 0.0) solveReconR(l, nd, g, x, b, m, r2req, maxits, its, b2e, b2o);
+  else solveReconL(l, nd, g, x, b, m, r2req, maxits, its, b2e, b2o);
+}
+// solve, stagSolve.nim:224-294.  Full-lattice D x = b.
+void orc_solve(void* lat, int nd, const double* g, double* x, const double* b, double m,
+               double r2req0, int maxits0, int usePrevSoln, OrcSolveStats* st) {
+  Lat* l = (Lat*)lat;
+  size_t n = (size_t)l->vol * 6;
+  double b2 = orc_norm2(lat, b, 2);
+  double r2stop = r2req0 * b2;
+  std::vector<double> r(n), y(n, 0.0);
+  if (usePrevSoln) {
+    orc_D(lat, nd, g, r.data(), x, m);
+    for (size_t i = 0; i < n; i++) r[i] = b[i] - r[i];
+  } else {
+    memset(x, 0, sizeof(double) * n);
+    memcpy(r.data(), b, sizeof(double) * n);
+  }
+  double r2e = orc_norm2(lat, r.data(), 0), r2o = orc_norm2(lat, r.data(), 1);
+  double r2 = r2e + r2o;
+  int its = 0, calls = 0;
+  while (r2 > r2stop) {
+    int maxits = maxits0 - its;
+    if (maxits <= 0) break;
+    double r2req = r2stop / r2;
+    solveInner(l, nd, g, y.data(), r.data(), m, r2req, maxits, its, r2e, r2o);
+    calls++;
+    for (size_t i = 0; i < n; i++) x[i] += y[i];
+    orc_D(lat, nd, g, r.data(), x, m);
+    for (size_t i = 0; i < n; i++) r[i] = b[i] - r[i];
+    r2e = orc_norm2(lat, r.data(), 0); r2o = orc_norm2(lat, r.data(), 1);
+    r2 = r2e + r2o;
+  }
+  if (st) { st->iterations = its; st->calls = calls; st->r2 = (b2 > 0 ? r2 / b2 : 0.0); st->b2 = b2; }
+}
+
+int orc_num_threads() { return omp_get_max_threads(); }
+void orc_set_num_threads(int n) { omp_set_num_threads(n); }
+
+}  // extern "C"
