@@ -1,0 +1,354 @@
+#!/usr/bin/env python
+"""Benchmark of the staggered Dslash + CG hot path (BASELINE.json metric), one process per GPU.
+
+  python bench.py [--gpus N --steps K --warmup W] [--impl reference]
+
+Workload (BASELINE.json configs[1]): 32^4 naive staggered, random SU(3) links with antiperiodic-T
+BC + staggered phases, m = 0.1, even-even CG to r2req = 1e-8, fp64; weak scaling keeps 32^4 per GPU
+(32^4, 32^3x64, 32^2x64^2, 32x64^3 for 1/2/4/8 GPUs).
+
+A "step" is one solveEE call (stagSolve.nim:57-138) = one CG solve on a device-resident source.
+value  = QEX's solver Gflop/s, (g.len*4*72+60)*nEven*iterations / seconds (stagSolve.nim:92), whole job.
+e2e    = the same through qexb200_solveXX with HOST (pinned) buffers: H2D of the source and D2H of
+         the solution inside the timed region.
+roofline = the dominant kernel (one parity sweep of the Dslash) timed live with CUDA events on the
+         library's stream over back-to-back launches, against the measured HBM peak.
+The reference arm (--impl reference) times the CPU oracle (the reference itself cannot be built in
+this image: no Nim/MPI/QMP) on all host cores, on a bounded sample of the same solve.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+MASS = 0.1
+R2REQ = 1e-8
+BYTES_PER_SITE = {4: 1248, 8: 2400}     # compulsory bytes per output site of one parity sweep
+FLOPS_PER_SITE = {4: 570, 8: 1146}      # algorithmic flops per output site of one sweep
+WEAK = {1: ((32, 32, 32, 32), (1, 1, 1, 1)), 2: ((32, 32, 32, 64), (1, 1, 1, 2)),
+        4: ((32, 32, 64, 64), (1, 1, 2, 2)), 8: ((32, 64, 64, 64), (1, 2, 2, 2))}
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, dev):
+        self.dev, self.rows, self.stop, self.t = dev, [], False, None
+
+    def _run(self):
+        while not self.stop:
+            try:
+                o = subprocess.run(["nvidia-smi", "-i", str(self.dev), "--query-gpu=" + self.Q,
+                                    "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                self.rows.append([t.strip() for t in o.strip().split(",")])
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def __enter__(self):
+        self.t = threading.Thread(target=self._run, daemon=True)
+        self.t.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop = True
+        self.t.join(timeout=6)
+
+    def summary(self):
+        sm, mx, reasons = [], 0.0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx = max(mx, float(r[1]))
+                for n, v in zip(names, r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def dist_env():
+    return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+
+
+def cpu_reference_leg(lat_shape, nlinks, maxits, threads=None):
+    """Times the CPU oracle's CG (oracle/qex_oracle.cpp orc_cg_xx) on a bounded sample: `maxits`
+    iterations of the same even-even solve.  Returns Gflop/s in QEX's flop model."""
+    import oracle
+    from qex_b200.synth import random_su3_links, gaussian_vector
+    oracle.build()
+    if threads:
+        oracle.set_num_threads(threads)
+    lat = oracle.Lattice(lat_shape)
+    g = np.ascontiguousarray(np.stack(random_su3_links(lat.vol, 4, seed=1)))
+    lat.setBC(g)
+    lat.stagPhase(g)
+    if nlinks == 8:
+        g3 = np.stack(random_su3_links(lat.vol, 4, seed=2, scale=[0.1] * 4))
+        gg = np.zeros((8,) + g.shape[1:])
+        gg[0::2], gg[1::2] = g, g3
+        g = gg
+    b = gaussian_vector(lat.vol, 0)
+    x = lat.vector()
+    lat.cg_xx(g, x, b, MASS * MASS, 0, 0.0, 2)      # warm the caches / thread pool
+    x[:] = 0
+    t0 = time.perf_counter()
+    its, r2, b2 = lat.cg_xx(g, x, b, MASS * MASS, 0, 0.0, maxits)
+    dt = time.perf_counter() - t0
+    flops = (nlinks * 4 * 72 + 60) * lat.half * its
+    return {"value": 1e-9 * flops / dt, "unit": "GFLOP/s", "cores": oracle.num_threads(), "kind": "port",
+            "sample": "%d CG iterations of the %s %s even-even solve (oracle C++/OpenMP port, %.1f s)"
+                      % (its, "x".join(map(str, lat_shape)), "naive" if nlinks == 4 else "fat+Naik", dt),
+            "seconds": dt, "iterations": its}
+
+
+def run_reference(args):
+    rank, _, world = dist_env()
+    if rank != 0:
+        return
+    lat_shape = WEAK[1][0]
+    its = max(2, args.ref_iters)
+    t_all = []
+    res = None
+    for _ in range(args.warmup if args.warmup < 2 else 1):
+        cpu_reference_leg(lat_shape, 4, 2)
+    for _ in range(max(1, min(args.steps, 3))):
+        res = cpu_reference_leg(lat_shape, 4, its)
+        t_all.append(res["value"])
+    v = float(np.median(t_all))
+    res["value"] = v
+    line = {"impl": "reference", "metric": "staggered CG solver throughput (Dslash GFLOP/s, QEX flop model)",
+            "value": v, "unit": "GFLOP/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * res["seconds"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "32^4 naive staggered even-even CG, m=0.1, fp64 (BASELINE configs[1]); "
+                                   "CPU sample = %d iterations" % res["iterations"]},
+            "cpu_baseline": res,
+            "e2e": {"value": v, "unit": "GFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import qex_b200 as qb
+    from qex_b200.synth import random_su3_links, gaussian_vector
+
+    rank, local_rank, world = dist_env()
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("launch with torch.distributed.run --nproc-per-node %d" % args.gpus)
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU arm")
+    torch.cuda.set_device(local_rank)
+    nccl_id = None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            idt = torch.tensor(list(qb.nccl_unique_id()), dtype=torch.uint8, device="cuda")
+        dist.broadcast(idt, 0)
+        nccl_id = bytes(idt.cpu().tolist())
+    lat_shape, rankgeom = WEAK[world]
+    qb.init(lat_shape, rankgeom, rank, local_rank, nccl_id)
+    nsites, neven = qb.local_sites()
+    peak, peak_src = measured_peak()
+
+    def barrier():
+        qb.sync()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def maxreduce(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    out = {}
+    results = {}
+    for nlinks in ((4, 8) if not args.naive_only else (4,)):
+        links = random_su3_links(nsites, 4, seed=1 + 17 * rank)
+        if nlinks == 4:
+            s = qb.Staggered(links)
+            s.rephase()                      # setBC + stagPhase on the device copy
+        else:
+            # synthetic 3-hop operator of the reference's own bench (benchStagProp.nim:84-92):
+            # fat = phased SU(3), long = 0.1 * SU(3)
+            long_links = random_su3_links(nsites, 4, seed=2 + 17 * rank, scale=[0.1] * 4)
+            s = qb.newStag3(phase_on_host(links, lat_shape, rankgeom, rank), long_links)
+            del long_links
+        del links
+        # source in pinned host memory (e2e leg copies from it every step)
+        hb = torch.from_numpy(gaussian_vector(nsites, seed=rank)).contiguous().pin_memory()
+        hx = torch.zeros_like(hb).pin_memory()
+        b_np, x_np = hb.numpy(), hx.numpy()
+        fb, fx = qb.DeviceField(b_np), qb.DeviceField()
+
+        # ---- value: K solves, source resident in HBM --------------------------------
+        def one_solve():
+            sp = qb.SolverParams(r2req=R2REQ, maxits=20000)
+            s.dev_solveXX(fx, fb, MASS, sp, parEven=True)
+            return sp
+        for _ in range(args.warmup):
+            sp = one_solve()
+        barrier()
+        qb.launch_count(reset=True)
+        with ClockSampler(local_rank) as cs:
+            qb.timer_start()
+            for _ in range(args.steps):
+                sp = one_solve()
+            ms = qb.timer_stop()
+        barrier()
+        launches = qb.launch_count()
+        ms = maxreduce(ms)
+        iters = sp.iterations
+        neven_global = neven * world
+        flops_step = (nlinks * 4 * 72 + 60) * neven_global * iters
+        gflops = 1e-9 * flops_step * args.steps / (1e-3 * ms)
+
+        # ---- e2e: same solve through the host-buffer C ABI -------------------------
+        for _ in range(max(1, args.warmup // 2)):
+            spe = qb.SolverParams(r2req=R2REQ, maxits=20000)
+            s.solveXX(x_np, b_np, MASS, spe, parEven=True)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            spe = qb.SolverParams(r2req=R2REQ, maxits=20000)
+            s.solveXX(x_np, b_np, MASS, spe, parEven=True)
+        barrier()
+        e2e_s = maxreduce(time.perf_counter() - t0)
+        e2e_gflops = 1e-9 * (nlinks * 4 * 72 + 60) * neven_global * spe.iterations * args.steps / e2e_s
+
+        # ---- roofline of the dominant kernel: one parity sweep ---------------------
+        nrep = args.sweeps
+        for _ in range(10):
+            s.dev_stagD2(0, fx, fb, 0.0, 0.0)
+            s.dev_stagD2(1, fx, fb, 0.0, 0.0)
+        barrier()
+        qb.timer_start()
+        for _ in range(nrep // 2):
+            s.dev_stagD2(0, fx, fb, 0.0, 0.0)
+            s.dev_stagD2(1, fx, fb, 0.0, 0.0)
+        sw_ms = maxreduce(qb.timer_stop()) / (2 * (nrep // 2))
+        barrier()
+        achieved = neven * BYTES_PER_SITE[nlinks] / (1e-3 * sw_ms) * 1e-9
+        results[nlinks] = {
+            "gflops": gflops, "ms_per_step": ms / args.steps, "iterations": iters, "r2": sp.r2,
+            "launches": launches, "clocks": cs.summary(),
+            "e2e_gflops": e2e_gflops, "e2e_ms_per_step": 1e3 * e2e_s / args.steps,
+            "sweep_ms": sw_ms, "sweep_gbs": achieved, "sweep_frac": achieved / peak,
+            "sweep_gflops": 1e-9 * neven * FLOPS_PER_SITE[nlinks] / (1e-3 * sw_ms),
+            "cg_iter_ms": ms / args.steps / max(1, iters),
+        }
+        fb.free()
+        fx.free()
+        s.free()
+
+    r = results[4]
+    line = {
+        "metric": "staggered CG solver throughput (Dslash GFLOP/s, QEX flop model)",
+        "value": r["gflops"], "unit": "GFLOP/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "%s naive staggered even-even CG to r2req=1e-8, m=0.1, fp64, random SU(3) "
+                               "(BASELINE configs[1]; 32^4 per GPU)" % "x".join(map(str, lat_shape)),
+                   "rankgeom": list(rankgeom), "cg_iterations": r["iterations"],
+                   "l2": "links (604 MB per sweep set) exceed the 126 MB L2; CG vectors (25 MB each) are L2-resident by design",
+                   "time_to_solution_ms": r["ms_per_step"]},
+        "e2e": {"value": r["e2e_gflops"], "unit": "GFLOP/s", "h2d_bytes_per_step": int(nsites * 48),
+                "d2h_bytes_per_step": int(nsites * 48), "ms_per_step": r["e2e_ms_per_step"]},
+        "gpu_launches": r["launches"],
+        "clocks": r["clocks"],
+        "roofline": {"bound": "hbm", "kernel": "k_sweep<1,false> (naive parity sweep)", "achieved": r["sweep_gbs"],
+                     "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": r["sweep_frac"], "traffic": None,
+                     "bytes_per_site": BYTES_PER_SITE[4], "ms_per_launch": r["sweep_ms"],
+                     "gflops": r["sweep_gflops"]},
+    }
+    if 8 in results:
+        h = results[8]
+        line["variants"] = {"hisq_fat_naik": {
+            "workload": "same lattice, fat + 0.1*Naik links (benchStagProp.nim:84-92)",
+            "cg_gflops": h["gflops"], "time_to_solution_ms": h["ms_per_step"], "cg_iterations": h["iterations"],
+            "e2e_gflops": h["e2e_gflops"],
+            "roofline": {"bound": "hbm", "kernel": "k_sweep<2,false>", "achieved": h["sweep_gbs"], "peak": peak,
+                         "unit": "GB/s", "frac": h["sweep_frac"], "bytes_per_site": BYTES_PER_SITE[8],
+                         "ms_per_launch": h["sweep_ms"], "gflops": h["sweep_gflops"]}}}
+    if world == 1 and not args.no_cpu:
+        line["cpu_baseline"] = cpu_reference_leg(lat_shape, 4, args.ref_iters)
+    else:
+        line["cpu_baseline"] = None
+    qb.finalize()
+    if world > 1:
+        dist.destroy_process_group()
+    if rank == 0:
+        print(json.dumps(line))
+
+
+def phase_on_host(links, lat_shape, rankgeom, rank):
+    """setBC + stagPhase (stagD.nim:72-80,509-522) with numpy on V=1 host links of this rank."""
+    G, lat = rankgeom, lat_shape
+    X = [lat[d] // G[d] for d in range(4)]
+    rc, r = [0] * 4, rank
+    for d in (3, 2, 1, 0):
+        rc[d] = r % G[d]
+        r //= G[d]
+    vol = int(np.prod(X))
+    lex = np.arange(vol)
+    x0 = lex % X[0]
+    x1 = (lex // X[0]) % X[1]
+    x2 = (lex // (X[0] * X[1])) % X[2]
+    x3 = lex // (X[0] * X[1] * X[2])
+    par = (x0 + x1 + x2 + x3) & 1
+    idx = np.where(par == 1, (lex + vol) // 2, lex // 2)
+    gx = [x0 + rc[0] * X[0], x1 + rc[1] * X[1], x2 + rc[2] * X[2], x3 + rc[3] * X[3]]
+    flips = [gx[3] & 1, (gx[0] + gx[3]) & 1, (gx[0] + gx[1] + gx[3]) & 1, (gx[3] == lat[3] - 1).astype(int)]
+    out = []
+    for mu in range(4):
+        sgn = np.ones(vol)
+        sgn[idx] = 1.0 - 2.0 * flips[mu]
+        out.append(np.ascontiguousarray(links[mu] * sgn[:, None, None, None]))
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--sweeps", type=int, default=200, help="back-to-back parity sweeps for the roofline leg")
+    ap.add_argument("--ref-iters", type=int, default=40, help="CG iterations of the bounded CPU sample")
+    ap.add_argument("--naive-only", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

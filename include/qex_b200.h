@@ -1,0 +1,158 @@
+/* qex_b200.h -- C ABI of the B200-native staggered Dslash + CG backend for QEX.
+ *
+ * This is the drop-in boundary: exactly what a QEX `importc` wrapper binds, in
+ * the same place and shape as QEX's existing QUDA backend.  Citations are
+ * file:line in the reference tree (ctpeterson/qex).
+ *
+ *   plug point        SolverParams.backend / `case sp.backend` in solveXX
+ *                     (src/solvers/solverBase.nim:6-14, src/physics/stagSolve.nim:57-132)
+ *   ABI precedent     qudaInit/qudaInvert/qudaFinalize
+ *                     (src/quda/quda_milc_interface.nim:75-146,289-295,
+ *                      src/quda/qudaWrapperImpl.nim:71-261)
+ *
+ * Conventions
+ *   - every entry point returns 0 on success, non-zero on error; the message is
+ *     available from qexb200_last_error() (QEX glue turns it into qexError).
+ *   - one host thread per rank calls the library, from outside `threads:`
+ *     (like qudaSolveXX, src/quda/qudaWrapperImpl.nim:165).
+ *   - one rank <-> one GPU.  Ranks are numbered as QEX numbers them:
+ *     lexicographic in rankGeom with dimension 0 slowest (src/layout/qlayout.nim:94-113).
+ *   - host field pointers are NATIVE QEX memory (`Field.s.data`,
+ *     src/field/fieldET.nim:18-22,209): outer site e, then colour (row, col),
+ *     then re/im, then the V SIMD lanes:
+ *        colour vector  double[nSitesOuter][3][2][V]
+ *        colour matrix  double[nSitesOuter][3][3][2][V]
+ *     with QEX's site order (even outer sites first, src/layout/qlayout.nim:110-131).
+ *     V and the lane geometry are given once by qexb200_set_host_layout().
+ *   - parity / subset: 0 = even, 1 = odd, 2 = all.
+ *   - the library never keeps a host pointer past the call.
+ *   - there is no CPU fallback: without a CUDA device every compute entry point
+ *     fails with an error.
+ */
+#ifndef QEX_B200_H
+#define QEX_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define QEXB200_EVEN 0
+#define QEXB200_ODD 1
+#define QEXB200_ALL 2
+
+typedef int qexb200_gauge_t; /* handle of a device-resident link set */
+typedef int qexb200_field_t; /* handle of a device-resident colour-vector field */
+
+/* SolverParams, src/solvers/solverBase.nim:10-28 (inputs first, outputs after). */
+typedef struct {
+  double r2req;      /* stop when r2 <= r2req * |b|^2 (squared relative residual) */
+  int maxits;
+  int use_prev_soln; /* usePrevSoln: x on entry is the initial guess (qexb200_solve only) */
+  int verbosity;
+  /* outputs, accumulated like addStats (solverBase.nim:75-83) after being reset */
+  int calls;
+  int iterations;
+  int iterations_max;
+  double seconds;
+  double flops;      /* QEX flop model (g.len*4*72+60)*nEven*iterations, stagSolve.nim:92 */
+  double r2;         /* solveXX: final recursive r2/b2; solve: true |b-Dx|^2/|b|^2 */
+} qexb200_solver_params;
+
+/* ---- lifetime ---------------------------------------------------------- */
+
+/* Replaces qudaInit + initCommsGridQuda (qudaWrapperImpl.nim:71-127).
+ * latsize = physGeom, rankgeom = rankGeom (product = number of ranks).
+ * nccl_unique_id: the 128-byte ncclUniqueId created on rank 0 with
+ * qexb200_nccl_unique_id() and broadcast by the caller (Comm.broadcast,
+ * src/comms/comms.nim:13); NULL when there is a single rank. */
+int qexb200_init(const int latsize[4], const int rankgeom[4], int myrank, int device,
+                 const void* nccl_unique_id);
+int qexb200_nccl_unique_id(void* out128);
+/* Replaces qudaFinalize (quda_milc_interface.nim:146). */
+int qexb200_finalize(void);
+const char* qexb200_last_error(void);
+/* 1 if a CUDA device was found and the context is live. */
+int qexb200_is_initialized(void);
+
+/* Lane geometry of the caller's fields = Layout.innerGeom (src/layout/layoutX.nim:98-125).
+ * {1,1,1,1} (the default) is a V=1 layout. */
+int qexb200_set_host_layout(const int innergeom[4]);
+/* Local (per-rank) number of sites, and of even sites. */
+int qexb200_local_sites(int* nsites, int* neven);
+
+/* ---- gauge links: Staggered.g (src/physics/stagD.nim:19-22,522-564) ------ */
+
+/* nlinks = 4: naive one-hop, links[mu].  nlinks = 8: fat + Naik, links[2mu] one-hop,
+ * links[2mu+1] three-hop, the order newStag3 builds (stagD.nim:552-564).
+ * The caller has already applied setBC/stagPhase (stagD.nim:72-80,509-520) or uses
+ * qexb200_gauge_rephase. */
+int qexb200_gauge_create(int nlinks, qexb200_gauge_t* g);
+int qexb200_gauge_load(qexb200_gauge_t g, const double* const* links);
+int qexb200_gauge_destroy(qexb200_gauge_t g);
+/* Staggered.rephase on the device copy: setBC then stagPhase with phases {8,9,11,0}
+ * (stagD.nim:72-80,509-522; gauge/gaugeUtils.nim:124-131).  One-hop links only. */
+int qexb200_gauge_rephase(qexb200_gauge_t g);
+
+/* ---- operator on HOST fields (each call: H2D, kernels, D2H) --------------- */
+
+/* stagD2 (stagD.nim:348-395): r[p] = a*r + b*x + sum_k [U_k x(+h_k) - U_k^+ x(-h_k)] */
+int qexb200_stagD2(qexb200_gauge_t g, int parity, double* r, const double* x, double a, double b);
+/* stagD (stagD.nim:405-409): r[p] = a*r + m*x + sc*D*x */
+int qexb200_stagD(qexb200_gauge_t g, int parity, double* r, const double* x, double m, double sc,
+                  double a);
+/* D / Ddag (stagD.nim:566-571), both parities */
+int qexb200_D(qexb200_gauge_t g, double* r, const double* x, double m);
+int qexb200_Ddag(qexb200_gauge_t g, double* r, const double* x, double m);
+/* stagD2ee / stagD2oo (stagD.nim:433-469): r[p] = 4 m2 x - (2D)(2D) x */
+int qexb200_stagD2xx(qexb200_gauge_t g, int parity, double* r, const double* x, double m2);
+/* eoReconstruct (stagD.nim:582-586): r.odd = (b.odd - D_oe r.even)/m */
+int qexb200_eoReconstruct(qexb200_gauge_t g, double* r, const double* b, double m);
+
+/* ---- solvers on HOST fields ---------------------------------------------- */
+
+/* solveXX / solveEE / solveOO with the device backend: same contract as qudaSolveEE/OO
+ * (qudaWrapperImpl.nim:165-267, stagSolve.nim:57-138): r := 0, CG on
+ * stagD2ee/oo(m*m) r = x restricted to `parity`. */
+int qexb200_solveXX(qexb200_gauge_t g, int parity, double* r, const double* x, double m,
+                    qexb200_solver_params* sp);
+/* solve (stagSolve.nim:224-294): full-lattice D x = b with even-odd preconditioning,
+ * reconstruction and the true-residual outer loop. */
+int qexb200_solve(qexb200_gauge_t g, double* x, const double* b, double m,
+                  qexb200_solver_params* sp);
+
+/* ---- device-resident fields (callers that keep vectors on the GPU) ------- */
+
+int qexb200_field_create(qexb200_field_t* f);
+int qexb200_field_destroy(qexb200_field_t f);
+int qexb200_field_upload(qexb200_field_t f, const double* host);
+int qexb200_field_download(qexb200_field_t f, double* host);
+int qexb200_field_zero(qexb200_field_t f);
+/* norm2 / redot on a subset (src/field/fieldET.nim:605-625,704-724), summed over ranks */
+int qexb200_field_norm2(qexb200_field_t f, int subset, double* out);
+int qexb200_field_redot(qexb200_field_t f, qexb200_field_t g, int subset, double* out);
+
+int qexb200_dev_stagD2(qexb200_gauge_t g, int parity, qexb200_field_t r, qexb200_field_t x,
+                       double a, double b);
+int qexb200_dev_stagD(qexb200_gauge_t g, int parity, qexb200_field_t r, qexb200_field_t x,
+                      double m, double sc, double a);
+int qexb200_dev_D(qexb200_gauge_t g, qexb200_field_t r, qexb200_field_t x, double m);
+int qexb200_dev_Ddag(qexb200_gauge_t g, qexb200_field_t r, qexb200_field_t x, double m);
+int qexb200_dev_stagD2xx(qexb200_gauge_t g, int parity, qexb200_field_t r, qexb200_field_t x,
+                         double m2);
+int qexb200_dev_solveXX(qexb200_gauge_t g, int parity, qexb200_field_t r, qexb200_field_t x,
+                        double m, qexb200_solver_params* sp);
+int qexb200_dev_solve(qexb200_gauge_t g, qexb200_field_t x, qexb200_field_t b, double m,
+                      qexb200_solver_params* sp);
+
+/* ---- measurement helpers (CUDA events on the library's compute stream) ---- */
+
+int qexb200_sync(void);
+int qexb200_timer_start(void);
+int qexb200_timer_stop(float* milliseconds); /* synchronises */
+/* number of kernel launches issued by the library since the last call with reset != 0 */
+long long qexb200_launch_count(int reset);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* QEX_B200_H */

@@ -85,6 +85,7 @@ def lib():
         L.orc_layout_setup.argtypes = [C.POINTER(OrcLayout), ip, ip, ip]
         L.orc_layout_index.argtypes = [C.POINTER(OrcLayout), ip, ip, ip]
         L.orc_layout_coord.argtypes = [C.POINTER(OrcLayout), C.c_int, C.c_int, ip]
+        L.orc_layout_table.argtypes = [C.POINTER(OrcLayout), ip, ip]
         L.orc_set_gauss_variant.argtypes = [C.c_int]
         L.orc_set_num_threads.argtypes = [C.c_int]
     return _lib
@@ -235,6 +236,51 @@ class QexLayout:
         r, i = C.c_int(), C.c_int()
         lib().orc_layout_index(C.byref(self.s), _i4(coords), C.byref(r), C.byref(i))
         return r.value, i.value
+
+    def table(self):
+        """(rank[vol], index[vol]) for every global site in the oracle's V=1 order."""
+        vol = int(np.prod(self.s.phys[:]))
+        r = np.zeros(vol, dtype=np.int32)
+        i = np.zeros(vol, dtype=np.int32)
+        ip = C.POINTER(C.c_int)
+        lib().orc_layout_table(C.byref(self.s), r.ctypes.data_as(ip), i.ctypes.data_as(ip))
+        return r, i
+
+    @property
+    def V(self):
+        return self.s.nSitesInner
+
+    @property
+    def nSites(self):
+        return self.s.nSites
+
+    def scatter(self, f):
+        """Global oracle field f[vol, ...] -> list over ranks of native QEX arrays [nOuter, ..., V]."""
+        r, i = self.table()
+        V, ns = self.V, self.nSites
+        nr = int(np.prod(self.s.rankg[:]))
+        inner = f.shape[1:]
+        out = []
+        for rk in range(nr):
+            sel = np.nonzero(r == rk)[0]
+            loc = np.zeros((ns,) + inner, dtype=f.dtype)
+            loc[i[sel]] = f[sel]
+            loc = loc.reshape((ns // V, V) + inner)
+            out.append(np.ascontiguousarray(np.moveaxis(loc, 1, -1)))
+        return out
+
+    def gather(self, parts):
+        """Inverse of scatter."""
+        r, i = self.table()
+        V, ns = self.V, self.nSites
+        inner = parts[0].shape[1:-1]
+        vol = r.shape[0]
+        f = np.zeros((vol,) + inner, dtype=parts[0].dtype)
+        for rk, loc in enumerate(parts):
+            flat = np.moveaxis(loc, -1, 1).reshape((ns,) + inner)
+            sel = np.nonzero(r == rk)[0]
+            f[sel] = flat[i[sel]]
+        return f
 
     def coord(self, rank, index):
         c = (C.c_int * 4)()

@@ -144,6 +144,23 @@ void orc_layout_coord(const OrcLayout* l, int rank, int index, int* coords) {
   for (int i = 0; i < 4; i++) coords[i] += cr[i];
 }
 
+// For every site of the global lattice, in the oracle's own (V=1, single rank)
+// order: owning rank and QEX single-site index i = outer*V + lane in layout `l`.
+void orc_layout_table(const OrcLayout* l, int* rank_out, int* index_out) {
+  const int* L = l->phys;
+  int vol = L[0] * L[1] * L[2] * L[3];
+  int x[4];
+  for (x[3] = 0; x[3] < L[3]; x[3]++)
+  for (x[2] = 0; x[2] < L[2]; x[2]++)
+  for (x[1] = 0; x[1] < L[1]; x[1]++)
+  for (x[0] = 0; x[0] < L[0]; x[0]++) {
+    int lex = ((x[3] * L[2] + x[2]) * L[1] + x[1]) * L[0] + x[0];
+    int p = (x[0] + x[1] + x[2] + x[3]) & 1;
+    int i = p ? (lex + vol) / 2 : lex / 2;
+    orc_layout_index(l, x, &rank_out[i], &index_out[i]);
+  }
+}
+
 // ---------------------------------------------------------------------------
 // The oracle's working lattice: single rank, V=1.
 // ---------------------------------------------------------------------------

@@ -1,0 +1,347 @@
+"""ctypes binding of include/qex_b200.h plus the QEX-shaped convenience layer.
+
+Host fields are numpy float64 arrays holding NATIVE QEX memory:
+colour vector ``[nSitesOuter, 3, 2, V]``, colour matrix ``[nSitesOuter, 3, 3, 2, V]``
+(for V=1 that is simply ``[nSites, 3, 2]`` / ``[nSites, 3, 3, 2]``).
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+EVEN, ODD, ALL = 0, 1, 2
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIBPATH = os.path.join(_HERE, "libqex_b200.so")
+_lib = None
+
+
+class QexB200Error(RuntimeError):
+    pass
+
+
+class _CSolverParams(C.Structure):
+    _fields_ = [("r2req", C.c_double), ("maxits", C.c_int), ("use_prev_soln", C.c_int),
+                ("verbosity", C.c_int), ("calls", C.c_int), ("iterations", C.c_int),
+                ("iterations_max", C.c_int), ("seconds", C.c_double), ("flops", C.c_double),
+                ("r2", C.c_double)]
+
+
+def lib_path():
+    return _LIBPATH
+
+
+def lib():
+    """Loads libqex_b200.so; fails loudly if it has not been built (no fallback)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_LIBPATH):
+            raise QexB200Error("%s not found: build it with `python -m qex_b200.build` "
+                               "(or __graft_entry__.build()); there is no CPU fallback" % _LIBPATH)
+        L = C.CDLL(_LIBPATH)
+        dp, ip = C.POINTER(C.c_double), C.POINTER(C.c_int)
+        spp = C.POINTER(_CSolverParams)
+        L.qexb200_last_error.restype = C.c_char_p
+        L.qexb200_init.argtypes = [ip, ip, C.c_int, C.c_int, C.c_void_p]
+        L.qexb200_nccl_unique_id.argtypes = [C.c_void_p]
+        L.qexb200_set_host_layout.argtypes = [ip]
+        L.qexb200_local_sites.argtypes = [ip, ip]
+        L.qexb200_gauge_create.argtypes = [C.c_int, ip]
+        L.qexb200_gauge_load.argtypes = [C.c_int, C.POINTER(dp)]
+        L.qexb200_gauge_destroy.argtypes = [C.c_int]
+        L.qexb200_gauge_rephase.argtypes = [C.c_int]
+        L.qexb200_stagD2.argtypes = [C.c_int, C.c_int, dp, dp, C.c_double, C.c_double]
+        L.qexb200_stagD.argtypes = [C.c_int, C.c_int, dp, dp, C.c_double, C.c_double, C.c_double]
+        L.qexb200_D.argtypes = [C.c_int, dp, dp, C.c_double]
+        L.qexb200_Ddag.argtypes = [C.c_int, dp, dp, C.c_double]
+        L.qexb200_stagD2xx.argtypes = [C.c_int, C.c_int, dp, dp, C.c_double]
+        L.qexb200_eoReconstruct.argtypes = [C.c_int, dp, dp, C.c_double]
+        L.qexb200_solveXX.argtypes = [C.c_int, C.c_int, dp, dp, C.c_double, spp]
+        L.qexb200_solve.argtypes = [C.c_int, dp, dp, C.c_double, spp]
+        L.qexb200_field_create.argtypes = [ip]
+        L.qexb200_field_destroy.argtypes = [C.c_int]
+        L.qexb200_field_upload.argtypes = [C.c_int, dp]
+        L.qexb200_field_download.argtypes = [C.c_int, dp]
+        L.qexb200_field_zero.argtypes = [C.c_int]
+        L.qexb200_field_norm2.argtypes = [C.c_int, C.c_int, dp]
+        L.qexb200_field_redot.argtypes = [C.c_int, C.c_int, C.c_int, dp]
+        L.qexb200_dev_stagD2.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double]
+        L.qexb200_dev_stagD.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double]
+        L.qexb200_dev_D.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double]
+        L.qexb200_dev_Ddag.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double]
+        L.qexb200_dev_stagD2xx.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_double]
+        L.qexb200_dev_solveXX.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, spp]
+        L.qexb200_dev_solve.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, spp]
+        L.qexb200_timer_stop.argtypes = [C.POINTER(C.c_float)]
+        L.qexb200_launch_count.restype = C.c_longlong
+        L.qexb200_launch_count.argtypes = [C.c_int]
+        _lib = L
+    return _lib
+
+
+def _ck(rc):
+    if rc != 0:
+        raise QexB200Error(lib().qexb200_last_error().decode())
+
+
+def _dp(a):
+    if not (isinstance(a, np.ndarray) and a.dtype == np.float64 and a.flags["C_CONTIGUOUS"]):
+        raise QexB200Error("host fields must be C-contiguous float64 numpy arrays")
+    return a.ctypes.data_as(C.POINTER(C.c_double))
+
+
+def _i4(v):
+    return (C.c_int * 4)(*[int(t) for t in v])
+
+
+# ---- lifetime ----------------------------------------------------------------
+def nccl_unique_id():
+    try:
+        import torch  # noqa: F401  (see init)
+    except ImportError:
+        pass
+    buf = C.create_string_buffer(128)
+    _ck(lib().qexb200_nccl_unique_id(buf))
+    return buf.raw
+
+
+def init(latsize, rankgeom=(1, 1, 1, 1), myrank=0, device=0, nccl_id=None):
+    """qexInit + qudaInit analogue (src/quda/qudaWrapperImpl.nim:71-127)."""
+    if nccl_id is not None:
+        # the process must hold ONE libnccl.so.2; when torch is the launcher its copy has to be
+        # loaded before ours is bound (csrc/capi.cu nccl_load)
+        try:
+            import torch  # noqa: F401
+        except ImportError:
+            pass
+    idbuf = C.create_string_buffer(nccl_id, 128) if nccl_id is not None else None
+    _ck(lib().qexb200_init(_i4(latsize), _i4(rankgeom), int(myrank), int(device), idbuf))
+
+
+def finalize():
+    if _lib is not None:
+        _ck(_lib.qexb200_finalize())
+
+
+def is_initialized():
+    return _lib is not None and bool(_lib.qexb200_is_initialized())
+
+
+def set_host_layout(innergeom):
+    _ck(lib().qexb200_set_host_layout(_i4(innergeom)))
+
+
+def local_sites():
+    n, e = C.c_int(), C.c_int()
+    _ck(lib().qexb200_local_sites(C.byref(n), C.byref(e)))
+    return n.value, e.value
+
+
+def sync():
+    _ck(lib().qexb200_sync())
+
+
+def timer_start():
+    _ck(lib().qexb200_timer_start())
+
+
+def timer_stop():
+    ms = C.c_float()
+    _ck(lib().qexb200_timer_stop(C.byref(ms)))
+    return ms.value
+
+
+def launch_count(reset=False):
+    return int(lib().qexb200_launch_count(int(reset)))
+
+
+# ---- SolverParams (src/solvers/solverBase.nim:10-58) ----------------------------
+class SolverParams:
+    def __init__(self, r2req=1e-6, maxits=50000, usePrevSoln=False, verbosity=1):
+        self.r2req = r2req
+        self.maxits = maxits
+        self.usePrevSoln = usePrevSoln
+        self.verbosity = verbosity
+        self.resetStats()
+
+    def resetStats(self):
+        self.calls = 0
+        self.iterations = 0
+        self.iterationsMax = 0
+        self.seconds = 0.0
+        self.flops = 0.0
+        self.r2 = 0.0
+
+    def _c(self):
+        c = _CSolverParams()
+        c.r2req, c.maxits, c.use_prev_soln, c.verbosity = self.r2req, int(self.maxits), int(self.usePrevSoln), self.verbosity
+        return c
+
+    def _addStats(self, c):  # addStats, solverBase.nim:75-83
+        self.calls += c.calls
+        self.iterations += c.iterations
+        self.iterationsMax = max(self.iterationsMax, c.iterations_max)
+        self.seconds += c.seconds
+        self.flops += c.flops
+        self.r2 = c.r2
+
+    def getStats(self):  # getStats typ 3, solverBase.nim:84-112
+        s = max(1e-12, self.seconds)
+        return "%d  %.4gs  %.4gGf/s  %.4g" % (self.iterations // max(1, self.calls), s / max(1, self.calls),
+                                            1e-9 * self.flops / s, self.r2)
+
+
+# ---- device-resident field -------------------------------------------------------
+class DeviceField:
+    def __init__(self, host=None):
+        h = C.c_int()
+        _ck(lib().qexb200_field_create(C.byref(h)))
+        self.h = h.value
+        if host is not None:
+            self.upload(host)
+
+    def upload(self, host):
+        _ck(lib().qexb200_field_upload(self.h, _dp(host)))
+
+    def download(self, out):
+        _ck(lib().qexb200_field_download(self.h, _dp(out)))
+        return out
+
+    def zero(self):
+        _ck(lib().qexb200_field_zero(self.h))
+
+    def norm2(self, subset=ALL):
+        o = C.c_double()
+        _ck(lib().qexb200_field_norm2(self.h, subset, C.byref(o)))
+        return o.value
+
+    def redot(self, other, subset=ALL):
+        o = C.c_double()
+        _ck(lib().qexb200_field_redot(self.h, other.h, subset, C.byref(o)))
+        return o.value
+
+    def free(self):
+        if self.h is not None and is_initialized():
+            lib().qexb200_field_destroy(self.h)
+        self.h = None
+
+
+# ---- Staggered (src/physics/stagD.nim:15-22,522-586; stagSolve.nim) ---------------
+class Staggered:
+    """Staggered[G,T]: holds the link set (device resident) and offers D/Ddag/solve."""
+
+    def __init__(self, links):
+        self.nlinks = len(links)
+        h = C.c_int()
+        _ck(lib().qexb200_gauge_create(self.nlinks, C.byref(h)))
+        self.h = h.value
+        self.load(links)
+
+    def load(self, links):
+        arr = (C.POINTER(C.c_double) * self.nlinks)(*[_dp(l) for l in links])
+        _ck(lib().qexb200_gauge_load(self.h, arr))
+
+    def rephase(self):
+        _ck(lib().qexb200_gauge_rephase(self.h))
+
+    def free(self):
+        if self.h is not None and is_initialized():
+            lib().qexb200_gauge_destroy(self.h)
+        self.h = None
+
+    # host-field operators
+    def D(self, r, x, m):
+        _ck(lib().qexb200_D(self.h, _dp(r), _dp(x), m))
+
+    def Ddag(self, r, x, m):
+        _ck(lib().qexb200_Ddag(self.h, _dp(r), _dp(x), m))
+
+    def eoReconstruct(self, r, b, m):
+        _ck(lib().qexb200_eoReconstruct(self.h, _dp(r), _dp(b), m))
+
+    def solveXX(self, r, x, m, sp, parEven=True):
+        c = sp._c()
+        _ck(lib().qexb200_solveXX(self.h, EVEN if parEven else ODD, _dp(r), _dp(x), m, C.byref(c)))
+        sp._addStats(c)
+
+    def solveEE(self, r, x, m, sp):
+        self.solveXX(r, x, m, sp, True)
+
+    def solveOO(self, r, x, m, sp):
+        self.solveXX(r, x, m, sp, False)
+
+    def solve(self, x, b, m, sp):
+        """solve(s, x, b, m, sp0) (stagSolve.nim:224-294); `sp` may be a SolverParams or an r2req float
+        like the convenience overload at stagSolve.nim:462-472."""
+        if not isinstance(sp, SolverParams):
+            sp = SolverParams(r2req=float(sp))
+        c = sp._c()
+        _ck(lib().qexb200_solve(self.h, _dp(x), _dp(b), m, C.byref(c)))
+        sp._addStats(c)
+        return sp
+
+    # device-field operators
+    def dev_D(self, r, x, m):
+        _ck(lib().qexb200_dev_D(self.h, r.h, x.h, m))
+
+    def dev_Ddag(self, r, x, m):
+        _ck(lib().qexb200_dev_Ddag(self.h, r.h, x.h, m))
+
+    def dev_stagD2(self, parity, r, x, a, b):
+        _ck(lib().qexb200_dev_stagD2(self.h, parity, r.h, x.h, a, b))
+
+    def dev_stagD(self, parity, r, x, m, sc=1.0, a=0.0):
+        _ck(lib().qexb200_dev_stagD(self.h, parity, r.h, x.h, m, sc, a))
+
+    def dev_stagD2xx(self, parity, r, x, m2):
+        _ck(lib().qexb200_dev_stagD2xx(self.h, parity, r.h, x.h, m2))
+
+    def dev_solveXX(self, r, x, m, sp, parEven=True):
+        c = sp._c()
+        _ck(lib().qexb200_dev_solveXX(self.h, EVEN if parEven else ODD, r.h, x.h, m, C.byref(c)))
+        sp._addStats(c)
+
+    def dev_solve(self, x, b, m, sp):
+        c = sp._c()
+        _ck(lib().qexb200_dev_solve(self.h, x.h, b.h, m, C.byref(c)))
+        sp._addStats(c)
+
+
+def newStag(g):
+    """newStag(g) (stagD.nim:533-542): naive one-hop operator from 4 link fields."""
+    if len(g) != 4:
+        raise QexB200Error("newStag needs 4 link fields")
+    return Staggered(list(g))
+
+
+def newStag3(g, g3=None):
+    """newStag3(g, g3) (stagD.nim:552-564): links interleaved as [fat0, long0, fat1, long1, ...];
+    newStag3(g) with 8 fields takes them already interleaved (stagD.nim:543-551)."""
+    if g3 is None:
+        if len(g) != 8:
+            raise QexB200Error("newStag3(g) needs 8 interleaved link fields")
+        return Staggered(list(g))
+    gg = []
+    for a, b in zip(g, g3):
+        gg += [a, b]
+    return Staggered(gg)
+
+
+def stagD2(s, parity, r, x, a, b):
+    """stagD2(sd, r, g, x, a, b) (stagD.nim:348-395) on the subset `parity`."""
+    _ck(lib().qexb200_stagD2(s.h, parity, _dp(r), _dp(x), a, b))
+
+
+def stagD(s, parity, r, x, m, sc=1.0, a=0.0):
+    """stagD(sd, r, g, x, m, sc, a) (stagD.nim:405-409)."""
+    _ck(lib().qexb200_stagD(s.h, parity, _dp(r), _dp(x), m, sc, a))
+
+
+def stagD2ee(s, r, x, m2):
+    """stagD2ee (stagD.nim:463-465)."""
+    _ck(lib().qexb200_stagD2xx(s.h, EVEN, _dp(r), _dp(x), m2))
+
+
+def stagD2oo(s, r, x, m2):
+    """stagD2oo (stagD.nim:467-469)."""
+    _ck(lib().qexb200_stagD2xx(s.h, ODD, _dp(r), _dp(x), m2))

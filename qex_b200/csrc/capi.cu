@@ -1,0 +1,573 @@
+// extern "C" entry points of libqex_b200.so (include/qex_b200.h) and the host-side
+// logic that sits above the kernels: stagD/D/Ddag/eoReconstruct composition
+// (src/physics/stagD.nim:405-409,566-586) and the solve drivers
+// (src/physics/stagSolve.nim:57-294).
+#include "../../include/qex_b200.h"
+#include "common.cuh"
+#include <chrono>
+#include <cstdarg>
+#include <cstring>
+#include <map>
+#include <dlfcn.h>
+
+namespace qb {
+
+static Context g_ctx;
+static std::string g_err;
+Context& ctx() { return g_ctx; }
+
+int fail(const char* fmt, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return 1;
+}
+void clear_error() { g_err.clear(); }
+
+static NcclApi g_nccl = {};
+NcclApi& nccl() { return g_nccl; }
+int nccl_load() {
+  if (g_nccl.loaded) return 0;
+  void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);   // prefer the copy already in the process
+  if (!h) h = dlopen("libnccl.so.2", RTLD_NOW);
+  if (!h) h = dlopen("libnccl.so", RTLD_NOW);
+  if (!h) return fail("cannot load libnccl.so.2: %s", dlerror());
+#define QB_SYM(field, name)                                                    \
+  *(void**)(&g_nccl.field) = dlsym(h, name);                                   \
+  if (!g_nccl.field) return fail("libnccl: missing symbol %s", name);
+  QB_SYM(GetUniqueId, "ncclGetUniqueId");
+  QB_SYM(CommInitRank, "ncclCommInitRank");
+  QB_SYM(CommDestroy, "ncclCommDestroy");
+  QB_SYM(GroupStart, "ncclGroupStart");
+  QB_SYM(GroupEnd, "ncclGroupEnd");
+  QB_SYM(Send, "ncclSend");
+  QB_SYM(Recv, "ncclRecv");
+  QB_SYM(AllReduce, "ncclAllReduce");
+  QB_SYM(GetErrorString, "ncclGetErrorString");
+#undef QB_SYM
+  g_nccl.loaded = true;
+  return 0;
+}
+
+static std::map<int, Gauge> g_gauges;
+static std::map<int, Field> g_fields;
+static int g_next_handle = 1;
+
+static int need_ctx() {
+  if (!g_ctx.live) return fail("qexb200 is not initialised (call qexb200_init; a CUDA device is required, there is no CPU fallback)");
+  return 0;
+}
+static int get_gauge(int h, Gauge** g) {
+  auto it = g_gauges.find(h);
+  if (it == g_gauges.end()) return fail("invalid gauge handle %d", h);
+  *g = &it->second;
+  return 0;
+}
+static int get_field(int h, Field** f) {
+  auto it = g_fields.find(h);
+  if (it == g_fields.end()) return fail("invalid field handle %d", h);
+  *f = &it->second;
+  return 0;
+}
+static int new_field(Field* f) {
+  QB_CUDA(cudaMalloc(&f->d, sizeof(double2) * 6 * (size_t)g_ctx.g.Vh));
+  return 0;
+}
+static size_t nhalf() { return (size_t)3 * g_ctx.g.Vh; }
+
+// ---- operator composition ----------------------------------------------------
+// stagD2, stagD.nim:348-395
+static int op_stagD2(const Gauge& g, int parity, Field& r, const Field& x, double a, double b) {
+  return sweep(g, parity, hf(r, parity), hf(x, 1 - parity), hf(x, parity), a, b, 1.0, 1.0, nullptr);
+}
+// stagD, stagD.nim:405-409: stagD2(a/(0.5 sc), m/(0.5 sc)) then r *= 0.5 sc -- the
+// rescaling sweep of the reference is folded into the kernel epilogue (`post`).
+static int op_stagD(const Gauge& g, int parity, Field& r, const Field& x, double m, double sc, double a) {
+  const double hs = 0.5 * sc;
+  return sweep(g, parity, hf(r, parity), hf(x, 1 - parity), hf(x, parity), a / hs, m / hs, 1.0, hs, nullptr);
+}
+static int op_D(const Gauge& g, Field& r, const Field& x, double m) {
+  QB_CHECK(op_stagD(g, 0, r, x, m, 1.0, 0.0));
+  return op_stagD(g, 1, r, x, m, 1.0, 0.0);
+}
+static int op_Ddag(const Gauge& g, Field& r, const Field& x, double m) {
+  QB_CHECK(op_stagD(g, 0, r, x, m, -1.0, 0.0));
+  return op_stagD(g, 1, r, x, m, -1.0, 0.0);
+}
+// eoReconstruct, stagD.nim:582-586: r.odd = (b.odd - D_oe r.even)/m
+static int op_eoReconstruct(const Gauge& g, Field& r, const Field& b, double m) {
+  QB_CHECK(op_stagD(g, 1, r, r, 0.0, -1.0 / m, 0.0));
+  return blas_axpy(hf(r, 1), 1.0 / m, hf(b, 1), nhalf());
+}
+
+// norm2 of a subset, summed over ranks, on the host
+static int norm2_host(const Field& f, int subset, double* out) {
+  double* S = g_ctx.d_scal + 32;
+  const double2* p = (subset == QEXB200_ODD) ? hf(f, 1) : f.d;
+  const size_t n = (subset == QEXB200_ALL) ? 2 * nhalf() : nhalf();
+  QB_CHECK(blas_norm2(p, n, S));
+  QB_CHECK(allreduce_scalars(S, 1));
+  return fetch_scalars(S, out, 1);
+}
+
+static double now_s() {
+  return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+// solveXX with the device backend, stagSolve.nim:57-132
+static int op_solveXX(const Gauge& g, int parity, Field& r, const Field& x, double m, qexb200_solver_params* sp) {
+  const double t0 = now_s();
+  QB_CHECK(blas_zero(r.d, 2 * nhalf()));                      // threads: r := 0   (stagSolve.nim:63-64)
+  CgResult res;
+  QB_CHECK(cg_xx(g, parity, hf(r, parity), hf(x, parity), m * m, sp->r2req, sp->maxits, true, &res));
+  sp->calls = 1;
+  sp->iterations = res.iterations;
+  sp->iterations_max = res.iterations;
+  sp->seconds = now_s() - t0;
+  long long neven = (long long)g_ctx.g.Vh * g_ctx.g.nranks;
+  sp->flops = (double)(g.nlinks * 4 * 72 + 60) * (double)neven * res.iterations;  // stagSolve.nim:92
+  sp->r2 = res.b2 > 0 ? res.r2 / res.b2 : 0.0;
+  return 0;
+}
+
+struct SolveWork { Field r, y, d; bool ok = false; int Vh = 0; };
+static SolveWork g_sw;
+static int solve_work() {
+  if (g_sw.ok && g_sw.Vh == g_ctx.g.Vh) return 0;
+  QB_CHECK(new_field(&g_sw.r)); QB_CHECK(new_field(&g_sw.y)); QB_CHECK(new_field(&g_sw.d));
+  g_sw.ok = true; g_sw.Vh = g_ctx.g.Vh;
+  return 0;
+}
+
+// solveReconR, stagSolve.nim:141-176 (right-preconditioned; used when one parity of b is
+// negligible or m == 0)
+static int solveReconR(const Gauge& g, Field& x, const Field& b, double m, qexb200_solver_params* sp,
+                       double b2e, double b2o, int* its) {
+  const double b2 = b2e + b2o, r2stop = sp->r2req * b2, r2stop2 = 0.5 * r2stop;
+  const double r2stope = (b2o <= r2stop2) ? r2stop - b2o : r2stop2;
+  Field& y = g_sw.d;  // scratch (d is unused on this branch)
+  if (b2e > r2stope) {
+    qexb200_solver_params s2 = *sp;
+    s2.r2req = r2stope / b2e;
+    QB_CHECK(op_solveXX(g, 0, y, b, m, &s2));
+    *its += s2.iterations;
+    QB_CHECK(blas_scale(hf(y, 0), 4.0, nhalf()));
+    return op_Ddag(g, x, y, m);
+  }
+  const double r2stopo = (b2e <= r2stop2) ? r2stop - b2e : r2stop2;
+  if (b2o > r2stopo) {
+    qexb200_solver_params s2 = *sp;
+    s2.r2req = r2stopo / b2o;
+    QB_CHECK(op_solveXX(g, 1, y, b, m, &s2));
+    *its += s2.iterations;
+    QB_CHECK(blas_scale(hf(y, 1), 4.0, nhalf()));
+    return op_Ddag(g, x, y, m);
+  }
+  return 0;
+}
+// solveReconL, stagSolve.nim:179-208 (left-preconditioned with odd reconstruction)
+static int solveReconL(const Gauge& g, Field& x, const Field& b, double m, qexb200_solver_params* sp,
+                       double b2e, double b2o, int* its) {
+  Field& d = g_sw.d;
+  QB_CHECK(op_Ddag(g, d, b, m));
+  double d2e;
+  QB_CHECK(norm2_host(d, QEXB200_EVEN, &d2e));
+  qexb200_solver_params s2 = *sp;
+  s2.r2req = 0.99 * sp->r2req * (b2e + b2o) * m * m / d2e;
+  QB_CHECK(op_solveXX(g, 0, x, d, m, &s2));   // also zeroes x
+  *its += s2.iterations;
+  QB_CHECK(blas_scale(hf(x, 0), 4.0, nhalf()));
+  return op_eoReconstruct(g, x, b, m);
+}
+// solveInner, stagSolve.nim:211-222
+static int solveInner(const Gauge& g, Field& x, const Field& b, double m, qexb200_solver_params* sp,
+                      double b2e, double b2o, int* its) {
+  const double b2 = b2e + b2o, r2stop = sp->r2req * b2, r2stop2 = 0.5 * r2stop;
+  const double r2stope = (b2o <= r2stop2) ? r2stop - b2o : r2stop2;
+  const double r2stopo = (b2e <= r2stop2) ? r2stop - b2e : r2stop2;
+  if (b2e <= r2stope || b2o <= r2stopo || m == 0.0) return solveReconR(g, x, b, m, sp, b2e, b2o, its);
+  return solveReconL(g, x, b, m, sp, b2e, b2o, its);
+}
+// solve, stagSolve.nim:224-294
+static int op_solve(const Gauge& g, Field& x, const Field& b, double m, qexb200_solver_params* sp0) {
+  const double t0 = now_s();
+  QB_CHECK(solve_work());
+  Field &r = g_sw.r, &y = g_sw.y;
+  const size_t nfull = 2 * nhalf();
+  double b2, r2e, r2o;
+  QB_CHECK(norm2_host(b, QEXB200_ALL, &b2));
+  const double r2stop = sp0->r2req * b2;
+  if (sp0->use_prev_soln) {
+    QB_CHECK(op_D(g, r, x, m));
+    QB_CHECK(blas_xmy(r.d, b.d, r.d, nfull));
+  } else {
+    QB_CHECK(blas_zero(x.d, nfull));
+    QB_CHECK(blas_copy(r.d, b.d, nfull));
+  }
+  QB_CHECK(norm2_host(r, QEXB200_EVEN, &r2e));
+  QB_CHECK(norm2_host(r, QEXB200_ODD, &r2o));
+  double r2 = r2e + r2o;
+  int its = 0, itsmax = 0, calls = 0;
+  QB_CHECK(blas_zero(y.d, nfull));
+  while (r2 > r2stop) {
+    qexb200_solver_params sp = *sp0;
+    sp.maxits = sp0->maxits - its;
+    if (sp.maxits <= 0) break;
+    sp.r2req = r2stop / r2;
+    const int before = its;
+    QB_CHECK(solveInner(g, y, r, m, &sp, r2e, r2o, &its));
+    if (its - before > itsmax) itsmax = its - before;
+    calls++;
+    QB_CHECK(blas_axpy(x.d, 1.0, y.d, nfull));
+    QB_CHECK(op_D(g, r, x, m));
+    QB_CHECK(blas_xmy(r.d, b.d, r.d, nfull));
+    QB_CHECK(norm2_host(r, QEXB200_EVEN, &r2e));
+    QB_CHECK(norm2_host(r, QEXB200_ODD, &r2o));
+    r2 = r2e + r2o;
+  }
+  sp0->calls = 1;
+  sp0->iterations = its;
+  sp0->iterations_max = itsmax;
+  sp0->seconds = now_s() - t0;
+  const double neven = (double)g_ctx.g.Vh * g_ctx.g.nranks;
+  sp0->flops = (double)(g.nlinks * 4 * 72 + 60) * neven * its + (double)(g.nlinks * 4 * 72 + 24) * neven;  // stagSolve.nim:92,285
+  sp0->r2 = b2 > 0 ? r2 / b2 : 0.0;
+  return 0;
+}
+
+}  // namespace qb
+
+using namespace qb;
+
+extern "C" {
+
+const char* qexb200_last_error(void) { return g_err.c_str(); }
+int qexb200_is_initialized(void) { return g_ctx.live ? 1 : 0; }
+
+int qexb200_nccl_unique_id(void* out128) {
+  QB_CHECK(nccl_load());
+  ncclUniqueId id;
+  QB_NCCL(nccl().GetUniqueId(&id));
+  static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId size");
+  memcpy(out128, &id, 128);
+  return 0;
+}
+
+int qexb200_init(const int latsize[4], const int rankgeom[4], int myrank, int device, const void* nccl_unique_id) {
+  clear_error();
+  if (g_ctx.live) return fail("qexb200_init: already initialised (call qexb200_finalize first)");
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return fail("qexb200_init: no CUDA device (%s); this backend has no CPU fallback", cudaGetErrorString(e));
+  if (device < 0 || device >= ndev) return fail("qexb200_init: device %d out of range (%d devices)", device, ndev);
+  Geom& g = g_ctx.g;
+  g.nranks = 1; g.V = 1; g.comm_mask = 0;
+  for (int d = 0; d < 4; d++) {
+    if (rankgeom[d] < 1 || latsize[d] % rankgeom[d] != 0) return fail("qexb200_init: rankgeom[%d]=%d does not divide latsize %d", d, rankgeom[d], latsize[d]);
+    g.lat[d] = latsize[d]; g.G[d] = rankgeom[d]; g.X[d] = latsize[d] / rankgeom[d];
+    if (g.X[d] & 1) return fail("qexb200_init: local extent %d in direction %d must be even", g.X[d], d);
+    g.nranks *= rankgeom[d]; g.V *= g.X[d];
+    if (rankgeom[d] > 1) g.comm_mask |= 1 << d;
+  }
+  if (myrank < 0 || myrank >= g.nranks) return fail("qexb200_init: rank %d outside rank grid of %d", myrank, g.nranks);
+  g.rank = myrank; g.Vh = g.V / 2;
+  { int r = myrank; for (int d = 3; d >= 0; d--) { g.rc[d] = r % g.G[d]; r /= g.G[d]; } }  // dimension 0 slowest
+  QB_CUDA(cudaSetDevice(device));
+  g_ctx.device = device;
+  QB_CUDA(cudaStreamCreateWithFlags(&g_ctx.stream, cudaStreamNonBlocking));
+  QB_CUDA(cudaStreamCreateWithFlags(&g_ctx.comm_stream, cudaStreamNonBlocking));
+  QB_CUDA(cudaEventCreateWithFlags(&g_ctx.ev_pack, cudaEventDisableTiming));
+  QB_CUDA(cudaEventCreateWithFlags(&g_ctx.ev_comm, cudaEventDisableTiming));
+  QB_CUDA(cudaEventCreate(&g_ctx.ev_t0));
+  QB_CUDA(cudaEventCreate(&g_ctx.ev_t1));
+  const size_t npart = (size_t)g.Vh / 128 + 148 * 8 + 64;
+  QB_CUDA(cudaMalloc(&g_ctx.d_partials, sizeof(double) * npart));
+  QB_CUDA(cudaMalloc(&g_ctx.d_ticket, sizeof(unsigned int) * 4));
+  QB_CUDA(cudaMemset(g_ctx.d_ticket, 0, sizeof(unsigned int) * 4));
+  QB_CUDA(cudaMalloc(&g_ctx.d_scal, sizeof(double) * 64));
+  QB_CUDA(cudaMemset(g_ctx.d_scal, 0, sizeof(double) * 64));
+  QB_CUDA(cudaHostAlloc((void**)&g_ctx.h_scal, sizeof(double) * 64, cudaHostAllocDefault));
+  if (g.nranks > 1) {
+    if (!nccl_unique_id) return fail("qexb200_init: %d ranks need an ncclUniqueId", g.nranks);
+    QB_CHECK(nccl_load());
+    ncclUniqueId id;
+    memcpy(&id, nccl_unique_id, 128);
+    QB_NCCL(nccl().CommInitRank(&g_ctx.nccl, g.nranks, id, myrank));
+  }
+  g_ctx.inner[0] = g_ctx.inner[1] = g_ctx.inner[2] = g_ctx.inner[3] = 1;
+  g_ctx.launches = 0;
+  g_ctx.live = true;
+  return 0;
+}
+
+int qexb200_finalize(void) {
+  if (!g_ctx.live) return 0;
+  cudaStreamSynchronize(g_ctx.stream);
+  cudaStreamSynchronize(g_ctx.comm_stream);
+  for (auto& kv : g_gauges) cudaFree(kv.second.d);
+  for (auto& kv : g_fields) cudaFree(kv.second.d);
+  g_gauges.clear(); g_fields.clear();
+  if (g_sw.ok) { cudaFree(g_sw.r.d); cudaFree(g_sw.y.d); cudaFree(g_sw.d.d); g_sw = SolveWork(); }
+  cg_free();
+  halo_free();
+  if (g_ctx.nccl) { nccl().CommDestroy(g_ctx.nccl); g_ctx.nccl = nullptr; }
+  if (g_ctx.d_perm) cudaFree(g_ctx.d_perm);
+  if (g_ctx.d_stage) cudaFree(g_ctx.d_stage);
+  cudaFree(g_ctx.d_partials); cudaFree(g_ctx.d_ticket); cudaFree(g_ctx.d_scal);
+  cudaFreeHost(g_ctx.h_scal);
+  cudaEventDestroy(g_ctx.ev_pack); cudaEventDestroy(g_ctx.ev_comm);
+  cudaEventDestroy(g_ctx.ev_t0); cudaEventDestroy(g_ctx.ev_t1);
+  cudaStreamDestroy(g_ctx.stream); cudaStreamDestroy(g_ctx.comm_stream);
+  g_ctx = Context();
+  return 0;
+}
+
+int qexb200_set_host_layout(const int innergeom[4]) {
+  QB_CHECK(need_ctx());
+  for (int d = 0; d < 4; d++) {
+    if (innergeom[d] < 1 || g_ctx.g.X[d] % innergeom[d]) return fail("set_host_layout: innergeom[%d]=%d does not divide local extent %d", d, innergeom[d], g_ctx.g.X[d]);
+  }
+  for (int d = 0; d < 4; d++) g_ctx.inner[d] = innergeom[d];
+  g_ctx.permV = 0;  // rebuild lazily
+  return ensure_perm();
+}
+
+int qexb200_local_sites(int* nsites, int* neven) {
+  QB_CHECK(need_ctx());
+  if (nsites) *nsites = g_ctx.g.V;
+  if (neven) *neven = g_ctx.g.Vh;
+  return 0;
+}
+
+// ---- gauge -------------------------------------------------------------------
+int qexb200_gauge_create(int nlinks, qexb200_gauge_t* out) {
+  QB_CHECK(need_ctx());
+  if (nlinks != 4 && nlinks != 8) return fail("gauge_create: nlinks must be 4 (naive) or 8 (fat+Naik), got %d", nlinks);
+  Gauge g;
+  g.nlinks = nlinks;
+  QB_CUDA(cudaMalloc(&g.d, sizeof(double2) * (size_t)nlinks * 18 * g_ctx.g.Vh));
+  const int h = g_next_handle++;
+  g_gauges[h] = g;
+  *out = h;
+  return 0;
+}
+int qexb200_gauge_load(qexb200_gauge_t h, const double* const* links) {
+  QB_CHECK(need_ctx());
+  Gauge* g; QB_CHECK(get_gauge(h, &g));
+  return upload_links(*g, links);
+}
+int qexb200_gauge_destroy(qexb200_gauge_t h) {
+  QB_CHECK(need_ctx());
+  Gauge* g; QB_CHECK(get_gauge(h, &g));
+  cudaStreamSynchronize(g_ctx.stream);
+  cudaFree(g->d);
+  g_gauges.erase(h);
+  return 0;
+}
+int qexb200_gauge_rephase(qexb200_gauge_t h) {
+  QB_CHECK(need_ctx());
+  Gauge* g; QB_CHECK(get_gauge(h, &g));
+  return rephase(*g);
+}
+
+// ---- device fields -----------------------------------------------------------
+int qexb200_field_create(qexb200_field_t* out) {
+  QB_CHECK(need_ctx());
+  Field f;
+  QB_CHECK(new_field(&f));
+  QB_CUDA(cudaMemsetAsync(f.d, 0, sizeof(double2) * 6 * (size_t)g_ctx.g.Vh, g_ctx.stream));
+  const int h = g_next_handle++;
+  g_fields[h] = f;
+  *out = h;
+  return 0;
+}
+int qexb200_field_destroy(qexb200_field_t h) {
+  QB_CHECK(need_ctx());
+  Field* f; QB_CHECK(get_field(h, &f));
+  cudaStreamSynchronize(g_ctx.stream);
+  cudaFree(f->d);
+  g_fields.erase(h);
+  return 0;
+}
+int qexb200_field_upload(qexb200_field_t h, const double* host) {
+  QB_CHECK(need_ctx());
+  Field* f; QB_CHECK(get_field(h, &f));
+  QB_CHECK(upload_vector(*f, host));
+  QB_CUDA(cudaStreamSynchronize(g_ctx.stream));
+  return 0;
+}
+int qexb200_field_download(qexb200_field_t h, double* host) {
+  QB_CHECK(need_ctx());
+  Field* f; QB_CHECK(get_field(h, &f));
+  return download_vector(*f, host);
+}
+int qexb200_field_zero(qexb200_field_t h) {
+  QB_CHECK(need_ctx());
+  Field* f; QB_CHECK(get_field(h, &f));
+  return blas_zero(f->d, 2 * nhalf());
+}
+int qexb200_field_norm2(qexb200_field_t h, int subset, double* out) {
+  QB_CHECK(need_ctx());
+  Field* f; QB_CHECK(get_field(h, &f));
+  return norm2_host(*f, subset, out);
+}
+int qexb200_field_redot(qexb200_field_t hf, qexb200_field_t hg, int subset, double* out) {
+  QB_CHECK(need_ctx());
+  Field *f, *g2; QB_CHECK(get_field(hf, &f)); QB_CHECK(get_field(hg, &g2));
+  double* S = g_ctx.d_scal + 32;
+  const size_t off = (subset == QEXB200_ODD) ? nhalf() : 0;
+  const size_t n = (subset == QEXB200_ALL) ? 2 * nhalf() : nhalf();
+  QB_CHECK(blas_redot(f->d + off, g2->d + off, n, S));
+  QB_CHECK(allreduce_scalars(S, 1));
+  return fetch_scalars(S, out, 1);
+}
+
+#define GET_G_F2(hg, h1, h2)                       \
+  QB_CHECK(need_ctx());                            \
+  Gauge* g; QB_CHECK(get_gauge(hg, &g));           \
+  Field *f1, *f2; QB_CHECK(get_field(h1, &f1)); QB_CHECK(get_field(h2, &f2));
+
+int qexb200_dev_stagD2(qexb200_gauge_t hg, int parity, qexb200_field_t r, qexb200_field_t x, double a, double b) {
+  GET_G_F2(hg, r, x);
+  if (parity != 0 && parity != 1) return fail("stagD2: parity must be 0 or 1");
+  return op_stagD2(*g, parity, *f1, *f2, a, b);
+}
+int qexb200_dev_stagD(qexb200_gauge_t hg, int parity, qexb200_field_t r, qexb200_field_t x, double m, double sc, double a) {
+  GET_G_F2(hg, r, x);
+  if (parity != 0 && parity != 1) return fail("stagD: parity must be 0 or 1");
+  return op_stagD(*g, parity, *f1, *f2, m, sc, a);
+}
+int qexb200_dev_D(qexb200_gauge_t hg, qexb200_field_t r, qexb200_field_t x, double m) {
+  GET_G_F2(hg, r, x);
+  return op_D(*g, *f1, *f2, m);
+}
+int qexb200_dev_Ddag(qexb200_gauge_t hg, qexb200_field_t r, qexb200_field_t x, double m) {
+  GET_G_F2(hg, r, x);
+  return op_Ddag(*g, *f1, *f2, m);
+}
+int qexb200_dev_stagD2xx(qexb200_gauge_t hg, int parity, qexb200_field_t r, qexb200_field_t x, double m2) {
+  GET_G_F2(hg, r, x);
+  if (parity != 0 && parity != 1) return fail("stagD2xx: parity must be 0 or 1");
+  return apply_xx_public(*g, parity, hf(*f1, parity), hf(*f2, parity), m2);
+}
+int qexb200_dev_solveXX(qexb200_gauge_t hg, int parity, qexb200_field_t r, qexb200_field_t x, double m, qexb200_solver_params* sp) {
+  GET_G_F2(hg, r, x);
+  if (parity != 0 && parity != 1) return fail("solveXX: parity must be 0 or 1");
+  return op_solveXX(*g, parity, *f1, *f2, m, sp);
+}
+int qexb200_dev_solve(qexb200_gauge_t hg, qexb200_field_t x, qexb200_field_t b, double m, qexb200_solver_params* sp) {
+  GET_G_F2(hg, x, b);
+  return op_solve(*g, *f1, *f2, m, sp);
+}
+
+// ---- host-buffer entry points: H2D, device op, D2H ---------------------------
+struct HostTmp { Field a, b; bool ok = false; int Vh = 0; };
+static HostTmp g_ht;
+static int host_tmp() {
+  if (g_ht.ok && g_ht.Vh == g_ctx.g.Vh) return 0;
+  QB_CHECK(new_field(&g_ht.a)); QB_CHECK(new_field(&g_ht.b));
+  g_ht.ok = true; g_ht.Vh = g_ctx.g.Vh;
+  return 0;
+}
+#define HOST_PROLOGUE(hg)                    \
+  QB_CHECK(need_ctx());                      \
+  Gauge* g; QB_CHECK(get_gauge(hg, &g));     \
+  QB_CHECK(host_tmp());                      \
+  Field &R = g_ht.a, &X = g_ht.b;
+
+int qexb200_stagD2(qexb200_gauge_t hg, int parity, double* r, const double* x, double a, double b) {
+  HOST_PROLOGUE(hg);
+  if (parity != 0 && parity != 1) return fail("stagD2: parity must be 0 or 1");
+  if (x == r) { QB_CHECK(upload_vector(R, r)); QB_CHECK(op_stagD2(*g, parity, R, R, a, b)); return download_vector(R, r); }
+  QB_CHECK(upload_vector(R, r));
+  QB_CHECK(upload_vector(X, x));
+  QB_CHECK(op_stagD2(*g, parity, R, X, a, b));
+  return download_vector(R, r);
+}
+int qexb200_stagD(qexb200_gauge_t hg, int parity, double* r, const double* x, double m, double sc, double a) {
+  HOST_PROLOGUE(hg);
+  if (parity != 0 && parity != 1) return fail("stagD: parity must be 0 or 1");
+  if (x == r) { QB_CHECK(upload_vector(R, r)); QB_CHECK(op_stagD(*g, parity, R, R, m, sc, a)); return download_vector(R, r); }
+  QB_CHECK(upload_vector(R, r));
+  QB_CHECK(upload_vector(X, x));
+  QB_CHECK(op_stagD(*g, parity, R, X, m, sc, a));
+  return download_vector(R, r);
+}
+int qexb200_D(qexb200_gauge_t hg, double* r, const double* x, double m) {
+  HOST_PROLOGUE(hg);
+  QB_CHECK(upload_vector(X, x));
+  QB_CHECK(op_D(*g, R, X, m));
+  return download_vector(R, r);
+}
+int qexb200_Ddag(qexb200_gauge_t hg, double* r, const double* x, double m) {
+  HOST_PROLOGUE(hg);
+  QB_CHECK(upload_vector(X, x));
+  QB_CHECK(op_Ddag(*g, R, X, m));
+  return download_vector(R, r);
+}
+int qexb200_stagD2xx(qexb200_gauge_t hg, int parity, double* r, const double* x, double m2) {
+  HOST_PROLOGUE(hg);
+  if (parity != 0 && parity != 1) return fail("stagD2xx: parity must be 0 or 1");
+  QB_CHECK(upload_vector(R, r));   // the other parity of r is preserved
+  QB_CHECK(upload_vector(X, x));
+  QB_CHECK(apply_xx_public(*g, parity, hf(R, parity), hf(X, parity), m2));
+  return download_vector(R, r);
+}
+int qexb200_eoReconstruct(qexb200_gauge_t hg, double* r, const double* b, double m) {
+  HOST_PROLOGUE(hg);
+  QB_CHECK(upload_vector(R, r));
+  QB_CHECK(upload_vector(X, b));
+  QB_CHECK(op_eoReconstruct(*g, R, X, m));
+  return download_vector(R, r);
+}
+int qexb200_solveXX(qexb200_gauge_t hg, int parity, double* r, const double* x, double m, qexb200_solver_params* sp) {
+  HOST_PROLOGUE(hg);
+  if (parity != 0 && parity != 1) return fail("solveXX: parity must be 0 or 1");
+  const double t0 = now_s();
+  QB_CHECK(upload_vector(X, x));
+  QB_CHECK(op_solveXX(*g, parity, R, X, m, sp));
+  QB_CHECK(download_vector(R, r));
+  sp->seconds = now_s() - t0;
+  return 0;
+}
+int qexb200_solve(qexb200_gauge_t hg, double* x, const double* b, double m, qexb200_solver_params* sp) {
+  HOST_PROLOGUE(hg);
+  const double t0 = now_s();
+  if (sp->use_prev_soln) QB_CHECK(upload_vector(R, x));
+  QB_CHECK(upload_vector(X, b));
+  QB_CHECK(op_solve(*g, R, X, m, sp));
+  QB_CHECK(download_vector(R, x));
+  sp->seconds = now_s() - t0;
+  return 0;
+}
+
+// ---- measurement -------------------------------------------------------------
+int qexb200_sync(void) {
+  QB_CHECK(need_ctx());
+  QB_CUDA(cudaStreamSynchronize(g_ctx.stream));
+  QB_CUDA(cudaStreamSynchronize(g_ctx.comm_stream));
+  return 0;
+}
+int qexb200_timer_start(void) {
+  QB_CHECK(need_ctx());
+  QB_CUDA(cudaEventRecord(g_ctx.ev_t0, g_ctx.stream));
+  return 0;
+}
+int qexb200_timer_stop(float* ms) {
+  QB_CHECK(need_ctx());
+  QB_CUDA(cudaEventRecord(g_ctx.ev_t1, g_ctx.stream));
+  QB_CUDA(cudaEventSynchronize(g_ctx.ev_t1));
+  QB_CUDA(cudaEventElapsedTime(ms, g_ctx.ev_t0, g_ctx.ev_t1));
+  return 0;
+}
+long long qexb200_launch_count(int reset) {
+  const long long n = g_ctx.launches;
+  if (reset) g_ctx.launches = 0;
+  return n;
+}
+
+}  // extern "C"

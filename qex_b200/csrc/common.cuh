@@ -1,0 +1,179 @@
+// Internal declarations shared by the translation units of libqex_b200.so.
+// Device data layout:
+//   colour-vector field  double2 v[2 parity][3 colour][Vh]          (site fastest)
+//   link set             double2 u[nlinks][2 parity][9 (row,col)][Vh]
+// with Vh = local sites / 2 and the checkerboard index idx = lex(x)/2,
+// lex = ((x3*X2+x2)*X1+x1)*X0+x0 over LOCAL coordinates.
+#pragma once
+#include <cuda_runtime.h>
+#include <nccl.h>
+#include <cstdint>
+#include <cstdio>
+#include <string>
+#include <vector>
+
+namespace qb {
+
+struct Geom {
+  int X[4];      // local extents (all even)
+  int G[4];      // rank grid
+  int rc[4];     // my rank coordinates
+  int lat[4];    // global extents
+  int V, Vh;
+  int comm_mask; // bit mu set: direction mu is split over ranks
+  int nranks, rank;
+};
+
+// Arguments of one parity sweep (kernel parameter block, passed by value).
+struct SweepArgs {
+  const double2* u;   // link set base
+  const double2* x;   // input half field (parity 1-p): x[c*Vh + idx]
+  double2* r;         // output half field (parity p)
+  const double2* bx;  // half field (parity p) scaled by b, may alias r's parity of the source
+  double a, b, sgn, post;   // r = post*(a*r + b*bx + sgn*sum)
+  int X[4];
+  int Vh;
+  int parity;         // output parity p
+  int comm_mask;
+  // reduction epilogue (DOT): sum over sites of Re<bx, r_new>
+  double* partials;
+  unsigned int* ticket;
+  double* result;
+};
+
+// Halo geometry of one split direction.
+struct HaloDir {
+  int mu;
+  int faceh;      // sites of one parity in one face layer
+  int depth;      // 1 (naive) or 3 (Naik)
+  // element (double2) offsets inside the per-sweep send/recv buffers
+  size_t off_f, off_b;     // psi layers / product layers
+  size_t n_f, n_b;         // number of double2 in each
+  int rank_plus, rank_minus;
+};
+
+struct Context {
+  bool live = false;
+  int device = 0;
+  Geom g;
+  cudaStream_t stream = nullptr, comm_stream = nullptr;
+  cudaEvent_t ev_pack = nullptr, ev_comm = nullptr, ev_t0 = nullptr, ev_t1 = nullptr;
+  ncclComm_t nccl = nullptr;
+  int inner[4] = {1, 1, 1, 1};
+  int* d_perm = nullptr;       // device site (parity*Vh+idx) -> host single-site index
+  int permV = 0;               // lanes of the host layout the table was built for
+  double* d_stage = nullptr;   // raw host-layout staging on the device
+  size_t stage_bytes = 0;
+  double* h_pinned = nullptr;  // pinned staging
+  size_t pinned_bytes = 0;
+  // reductions
+  double* d_partials = nullptr;
+  unsigned int* d_ticket = nullptr;
+  double* d_scal = nullptr;    // device scalars
+  double* h_scal = nullptr;    // pinned mirror
+  // halo
+  std::vector<HaloDir> halo;
+  double2 *sendbuf = nullptr, *recvbuf = nullptr;
+  size_t halo_elems = 0;
+  long long launches = 0;
+};
+
+// NCCL is bound at run time (dlopen of libnccl.so.2) the first time a multi-rank
+// context is created: a process that also hosts another NCCL user (e.g. torch) must
+// share ITS copy of the library, and single-rank users need no NCCL at all.
+struct NcclApi {
+  ncclResult_t (*GetUniqueId)(ncclUniqueId*);
+  ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int);
+  ncclResult_t (*CommDestroy)(ncclComm_t);
+  ncclResult_t (*GroupStart)();
+  ncclResult_t (*GroupEnd)();
+  ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
+  ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
+  ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t);
+  const char* (*GetErrorString)(ncclResult_t);
+  bool loaded;
+};
+NcclApi& nccl();
+int nccl_load();
+
+Context& ctx();
+int fail(const char* fmt, ...);
+void clear_error();
+
+#define QB_CUDA(call)                                                                      \
+  do {                                                                                     \
+    cudaError_t e_ = (call);                                                               \
+    if (e_ != cudaSuccess) return qb::fail("%s:%d: %s: %s", __FILE__, __LINE__, #call,      \
+                                           cudaGetErrorString(e_));                        \
+  } while (0)
+#define QB_NCCL(call)                                                                      \
+  do {                                                                                     \
+    ncclResult_t e_ = (call);                                                              \
+    if (e_ != ncclSuccess) return qb::fail("%s:%d: %s: %s", __FILE__, __LINE__, #call,      \
+                                           qb::nccl().GetErrorString(e_));                 \
+  } while (0)
+#define QB_CHECK(call)            \
+  do {                            \
+    int rc_ = (call);             \
+    if (rc_ != 0) return rc_;     \
+  } while (0)
+
+// ---- fields -----------------------------------------------------------------
+struct Field {
+  double2* d = nullptr;  // [2][3][Vh]
+};
+struct Gauge {
+  int nlinks = 0;        // 4 or 8
+  double2* d = nullptr;  // [nlinks][2][9][Vh]
+  bool loaded = false;
+};
+inline double2* hf(const Field& f, int parity) { return f.d + (size_t)parity * 3 * ctx().g.Vh; }
+
+// ---- dslash.cu --------------------------------------------------------------
+// r[p] = post*(a*r + b*bx + sgn*sum_k[U x(+h) - U^+ x(-h)]); dot != nullptr also returns
+// sum Re<bx, r_new> over ranks' local sites into *dot (device pointer, not yet all-reduced).
+int sweep(const Gauge& g, int parity, double2* r, const double2* x, const double2* bx, double a,
+          double b, double sgn, double post, double* dot_out);
+
+// ---- blas.cu ----------------------------------------------------------------
+// All vectors are half fields (3*Vh double2) unless n is given.
+int blas_zero(double2* x, size_t n2);
+int blas_copy(double2* y, const double2* x, size_t n2);
+int blas_scale(double2* x, double s, size_t n2);
+int blas_axpy(double2* y, double a, const double2* x, size_t n2);      // y += a x
+int blas_xpay(double2* y, const double2* x, double a, size_t n2);      // y = x + a y
+int blas_xmy(double2* z, const double2* x, const double2* y, size_t n2);  // z = x - y
+int blas_axpby(double2* y, double a, const double2* x, double b, size_t n2);  // y = a x + b y
+// local (this rank) reductions into device scalar slot; all-reduced by reduce_finish
+int blas_norm2(const double2* x, size_t n2, double* d_out);
+int blas_redot(const double2* x, const double2* y, size_t n2, double* d_out);
+// sum over ranks (NCCL) when nranks > 1, in place on device scalars
+int allreduce_scalars(double* d_ptr, int n);
+// copy n device scalars to host (synchronising)
+int fetch_scalars(const double* d_ptr, double* h_out, int n);
+
+// ---- solver.cu --------------------------------------------------------------
+struct CgResult { int iterations; double r2, b2; };
+int cg_xx(const Gauge& g, int parity, double2* x, const double2* b, double m2, double r2req,
+          int maxits, bool x_is_zero, CgResult* res);
+int apply_xx_public(const Gauge& g, int parity, double2* out, const double2* x, double m2);
+int cg_free();
+
+// ---- layout.cu --------------------------------------------------------------
+int ensure_perm();
+int upload_vector(Field& f, const double* host);
+int download_vector(const Field& f, double* host);
+int upload_links(Gauge& g, const double* const* links);
+int rephase(Gauge& g);
+
+// ---- comm.cu ----------------------------------------------------------------
+int halo_setup();
+int halo_free();
+// Start the exchange for a sweep that outputs `parity`: pack, then send/recv on comm_stream.
+int halo_start(const Gauge& g, int parity, const double2* x);
+// Make the compute stream wait for the exchange.
+int halo_wait();
+
+inline void count_launch(int n = 1) { ctx().launches += n; }
+
+}  // namespace qb

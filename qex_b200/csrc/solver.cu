@@ -1,0 +1,214 @@
+// Conjugate gradient on the even-even / odd-odd normal operator, device resident.
+//
+// WHAT: CgState.solve with cpNone (src/solvers/cg.nim:55-272) applied to
+// A = stagD2ee/oo(m2) (src/physics/stagD.nim:433-469), as driven by solveXX
+// (src/physics/stagSolve.nim:57-99).
+// HOW (B200): every scalar of the recurrence (rz, rzold, pAp, alpha, beta, the
+// iteration counter and the stop flag) lives in device memory; kernels read them,
+// so the host never synchronises inside the loop.  Reductions are fused into the
+// kernels that already stream the vectors (pAp into the second Dslash sweep, |r|^2
+// into the x/r update) and are deterministic (fixed two-level order).  The host
+// runs ahead by a few iterations and watches a status word the step kernel writes
+// to mapped pinned memory; once the stop flag is set the update kernels are
+// no-ops, so the iteration count and x are exactly those of the textbook loop.
+#include "stencil.cuh"
+#include <chrono>
+
+namespace qb {
+
+// device scalar slots
+enum { S_R2 = 0, S_R2OLD, S_PAP, S_R2NEW, S_R2STOP, S_ITN, S_MAXITS, S_DONE, S_B2, S_R2REQ, S_SEQ, S_TMP0, S_TMP1, S_TMP2, S_TMP3, S_N };
+
+// Status ring in mapped pinned memory: execution j of k_cg_step fills slot j % RING and
+// publishes it by writing seq = j last.  The host reads the slot of a FIXED iteration
+// (launched - LAG), so every rank takes the same decision at the same point and the
+// number of NCCL calls stays identical across ranks.
+constexpr int RING = 8;
+struct CgStatus {
+  volatile long long seq;
+  volatile long long itn;
+  volatile long long done;
+  volatile double r2;
+};
+
+static CgStatus* h_status = nullptr;
+static CgStatus* d_status = nullptr;  // device alias of h_status
+static double2 *w_r = nullptr, *w_p = nullptr, *w_Ap = nullptr, *w_t = nullptr;  // CG work vectors
+static int w_Vh = 0;
+
+constexpr int CB = 256;
+
+// p = r + beta p   (cg.nim:186-193; itn==0: p := r)
+__global__ void __launch_bounds__(CB) k_cg_p(double2* __restrict__ p, const double2* __restrict__ r,
+                                              const double* __restrict__ S, size_t n) {
+  if (S[S_DONE] != 0.0) return;
+  const bool first = (S[S_ITN] == 0.0);
+  const double beta = first ? 0.0 : S[S_R2] / S[S_R2OLD];
+  for (size_t i = (size_t)blockIdx.x * CB + threadIdx.x; i < n; i += (size_t)gridDim.x * CB) {
+    const double2 rv = r[i];
+    double2 o = rv;
+    if (!first) { const double2 pv = p[i]; o.x = fma(beta, pv.x, rv.x); o.y = fma(beta, pv.y, rv.y); }
+    p[i] = o;
+  }
+}
+
+// x += alpha p ; r -= alpha Ap ; r2new = |r|^2   (cg.nim:208-213)
+__global__ void __launch_bounds__(CB) k_cg_xr(double2* __restrict__ x, double2* __restrict__ r,
+                                               const double2* __restrict__ p, const double2* __restrict__ Ap,
+                                               double* S, size_t n, double* partials, unsigned int* ticket) {
+  if (S[S_DONE] != 0.0) return;
+  const double alpha = S[S_R2] / S[S_PAP];
+  double s = 0.0;
+  for (size_t i = (size_t)blockIdx.x * CB + threadIdx.x; i < n; i += (size_t)gridDim.x * CB) {
+    const double2 pv = p[i], av = Ap[i];
+    double2 xv = x[i], rv = r[i];
+    xv.x = fma(alpha, pv.x, xv.x); xv.y = fma(alpha, pv.y, xv.y);
+    rv.x = fma(-alpha, av.x, rv.x); rv.y = fma(-alpha, av.y, rv.y);
+    x[i] = xv; r[i] = rv;
+    s = fma(rv.x, rv.x, s); s = fma(rv.y, rv.y, s);
+  }
+  grid_reduce<CB>(s, partials, ticket, S + S_R2NEW);
+}
+
+// loop control of cg.nim:174 on the device
+__global__ void k_cg_step(double* S, CgStatus* st) {
+  if (S[S_DONE] == 0.0) {
+    S[S_R2OLD] = S[S_R2];
+    S[S_R2] = S[S_R2NEW];
+    S[S_ITN] += 1.0;
+    if (!(S[S_R2] > S[S_R2STOP]) || S[S_ITN] >= S[S_MAXITS]) S[S_DONE] = 1.0;
+  }
+  const long long seq = (long long)(S[S_SEQ] += 1.0);
+  CgStatus* slot = st + (seq % RING);
+  slot->itn = (long long)S[S_ITN];
+  slot->done = (long long)S[S_DONE];
+  slot->r2 = S[S_R2];
+  __threadfence_system();
+  slot->seq = seq;
+}
+
+// after the initial residual: r2stop = r2req*b2 (cg.nim:155), loop entry test (:163)
+__global__ void k_cg_init(double* S, CgStatus* st, double r2req, double maxits) {
+  S[S_R2] = S[S_R2NEW];
+  S[S_R2OLD] = 1.0;
+  S[S_R2STOP] = r2req * S[S_B2];
+  S[S_ITN] = 0.0;
+  S[S_MAXITS] = maxits;
+  S[S_DONE] = (!(S[S_R2] > S[S_R2STOP]) || maxits <= 0.0) ? 1.0 : 0.0;
+  S[S_SEQ] = 0.0;
+  st->itn = 0; st->done = (long long)S[S_DONE]; st->r2 = S[S_R2];
+  __threadfence_system();
+  st->seq = 0;
+}
+
+static int cg_workspace() {
+  Context& c = ctx();
+  if (w_Vh == c.g.Vh && w_r) return 0;
+  if (w_r) { cudaFree(w_r); cudaFree(w_p); cudaFree(w_Ap); cudaFree(w_t); w_r = nullptr; }
+  const size_t bytes = sizeof(double2) * 3 * (size_t)c.g.Vh;
+  QB_CUDA(cudaMalloc(&w_r, bytes));
+  QB_CUDA(cudaMalloc(&w_p, bytes));
+  QB_CUDA(cudaMalloc(&w_Ap, bytes));
+  QB_CUDA(cudaMalloc(&w_t, bytes));
+  w_Vh = c.g.Vh;
+  if (!h_status) {
+    QB_CUDA(cudaHostAlloc((void**)&h_status, sizeof(CgStatus) * RING, cudaHostAllocMapped));
+    QB_CUDA(cudaHostGetDevicePointer((void**)&d_status, (void*)h_status, 0));
+  }
+  return 0;
+}
+
+int cg_free() {
+  if (w_r) { cudaFree(w_r); cudaFree(w_p); cudaFree(w_Ap); cudaFree(w_t); w_r = w_p = w_Ap = w_t = nullptr; w_Vh = 0; }
+  if (h_status) { cudaFreeHost((void*)h_status); h_status = nullptr; d_status = nullptr; }
+  return 0;
+}
+
+// A = stagD2xx (stagD.nim:433-469): t[q] = (2D) x ; out[p] = 4 m2 x - (2D) t ; optional <x, out>
+static int apply_xx(const Gauge& g, int parity, double2* out, const double2* x, double m2, double* dot) {
+  QB_CHECK(sweep(g, 1 - parity, w_t, x, nullptr, 0.0, 0.0, 1.0, 1.0, nullptr));
+  QB_CHECK(sweep(g, parity, out, w_t, x, 0.0, 4.0 * m2, -1.0, 1.0, dot));
+  return 0;
+}
+
+int apply_xx_public(const Gauge& g, int parity, double2* out, const double2* x, double m2) {
+  QB_CHECK(cg_workspace());
+  return apply_xx(g, parity, out, x, m2, nullptr);
+}
+
+static inline int cg_grid(size_t n) {
+  size_t gsz = (n + CB - 1) / CB;
+  const size_t cap = 148 * 8;
+  return (int)(gsz < cap ? (gsz ? gsz : 1) : cap);
+}
+
+int cg_xx(const Gauge& g, int parity, double2* x, const double2* b, double m2, double r2req,
+          int maxits, bool x_is_zero, CgResult* res) {
+  Context& c = ctx();
+  QB_CHECK(cg_workspace());
+  const size_t n = (size_t)3 * c.g.Vh;
+  double* S = c.d_scal;
+  const int grid = cg_grid(n);
+
+  QB_CUDA(cudaStreamSynchronize(c.stream));
+  for (int i = 0; i < RING; i++) h_status[i].seq = -1;
+
+  // first call of CgState.solve, cg.nim:132-153
+  QB_CHECK(blas_norm2(b, n, S + S_B2));
+  if (x_is_zero) {
+    QB_CHECK(blas_copy(w_r, b, n));
+  } else {
+    QB_CHECK(apply_xx(g, parity, w_Ap, x, m2, nullptr));
+    QB_CHECK(blas_xmy(w_r, b, w_Ap, n));
+  }
+  QB_CHECK(blas_norm2(w_r, n, S + S_R2NEW));
+  QB_CHECK(allreduce_scalars(S + S_B2, 1));
+  QB_CHECK(allreduce_scalars(S + S_R2NEW, 1));
+  k_cg_init<<<1, 1, 0, c.stream>>>(S, d_status, r2req, (double)maxits);
+  count_launch();
+  double hs[2];
+  QB_CHECK(fetch_scalars(S + S_B2, hs, 1));
+  const double b2 = hs[0];
+  if (b2 == 0.0) {  // cg.nim:139-144
+    QB_CHECK(blas_zero(x, n));
+    res->iterations = 0; res->r2 = 0.0; res->b2 = 0.0;
+    return 0;
+  }
+
+  const int LAG = 3;  // iterations the host may run ahead of the device
+  int launched = 0;
+  bool done = h_status[0].done != 0;  // slot 0 = state after k_cg_init (fetch_scalars synchronised)
+  while (!done && launched < maxits) {
+    k_cg_p<<<grid, CB, 0, c.stream>>>(w_p, w_r, S, n);
+    count_launch();
+    QB_CHECK(apply_xx(g, parity, w_Ap, w_p, m2, S + S_PAP));
+    QB_CHECK(allreduce_scalars(S + S_PAP, 1));
+    k_cg_xr<<<grid, CB, 0, c.stream>>>(x, w_r, w_p, w_Ap, S, n, c.d_partials, c.d_ticket);
+    count_launch();
+    QB_CHECK(allreduce_scalars(S + S_R2NEW, 1));
+    k_cg_step<<<1, 1, 0, c.stream>>>(S, d_status);
+    count_launch();
+    launched++;
+    if (launched > LAG) {
+      const long long want = launched - LAG;
+      const CgStatus* slot = h_status + (want % RING);
+      long long spins = 0;
+      while (slot->seq != want) {
+        if ((++spins & 0xffff) == 0) {  // surface device faults instead of spinning forever
+          cudaError_t e = cudaStreamQuery(c.stream);
+          if (e != cudaSuccess && e != cudaErrorNotReady) return fail("cg_xx: %s", cudaGetErrorString(e));
+        }
+      }
+      done = slot->done != 0;
+    }
+  }
+  QB_CUDA(cudaGetLastError());
+  double fin[S_N];
+  QB_CHECK(fetch_scalars(S, fin, S_N));
+  res->iterations = (int)fin[S_ITN];
+  res->r2 = fin[S_R2];
+  res->b2 = b2;
+  return 0;
+}
+
+}  // namespace qb

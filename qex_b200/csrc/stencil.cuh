@@ -1,0 +1,145 @@
+// Device helpers of the staggered stencil: site <-> coordinate maps on the
+// checkerboarded local lattice, SU(3)-shaped complex mat-vec, streaming loads.
+#pragma once
+#include "common.cuh"
+
+namespace qb {
+
+struct Site {
+  int x[4];
+  int lex;
+};
+
+// idx in [0,Vh) of parity `par` -> local coordinates and lexicographic index
+__device__ __forceinline__ Site site_from_idx(int idx, int par, const int* X) {
+  Site s;
+  int t = idx;
+  const int xh = X[0] >> 1;
+  int x0h = t % xh; t /= xh;
+  s.x[1] = t % X[1]; t /= X[1];
+  s.x[2] = t % X[2];
+  s.x[3] = t / X[2];
+  s.x[0] = 2 * x0h + ((par + s.x[1] + s.x[2] + s.x[3]) & 1);
+  s.lex = 2 * idx + (s.x[0] & 1);
+  return s;
+}
+
+__device__ __forceinline__ int stride_of(int mu, const int* X) {
+  return mu == 0 ? 1 : (mu == 1 ? X[0] : (mu == 2 ? X[0] * X[1] : X[0] * X[1] * X[2]));
+}
+
+// face index (other three coordinates, lower dimension fastest) >> 1
+__device__ __forceinline__ int face_lex(const int* x, int mu, const int* X) {
+  int l = 0;
+#pragma unroll
+  for (int d = 3; d >= 0; d--)
+    if (d != mu) l = l * X[d] + x[d];
+  return l;
+}
+
+// (layer coordinate xmu, face half index, parity) -> full coordinates
+__device__ __forceinline__ Site site_from_face(int fidx, int mu, int xmu, int par, const int* X) {
+  Site s;
+  int d0 = (mu == 0) ? 1 : 0;
+  int d1 = (mu <= 1) ? 2 : 1;
+  int d2 = (mu <= 2) ? 3 : 2;
+  int t = fidx;
+  const int eh = X[d0] >> 1;
+  int c0h = t % eh; t /= eh;
+  int c1 = t % X[d1];
+  int c2 = t / X[d1];
+  int c0 = 2 * c0h + ((par + xmu + c1 + c2) & 1);
+  s.x[mu] = xmu; s.x[d0] = c0; s.x[d1] = c1; s.x[d2] = c2;
+  s.lex = ((s.x[3] * X[2] + s.x[2]) * X[1] + s.x[1]) * X[0] + s.x[0];
+  return s;
+}
+
+// links are read exactly once per sweep: stream them past L1/L2 residency
+__device__ __forceinline__ void load_link(double2 (&U)[9], const double2* __restrict__ p, int Vh) {
+#pragma unroll
+  for (int e = 0; e < 9; e++) U[e] = __ldcs(p + (size_t)e * Vh);
+}
+// vectors are re-read by up to 16 neighbours: keep them cached
+__device__ __forceinline__ void load_vec(double2 (&v)[3], const double2* __restrict__ p, int Vh) {
+#pragma unroll
+  for (int c = 0; c < 3; c++) v[c] = __ldg(p + (size_t)c * Vh);
+}
+
+// acc += U v
+__device__ __forceinline__ void mv_add(double2 (&acc)[3], const double2 (&U)[9], const double2 (&v)[3]) {
+#pragma unroll
+  for (int a = 0; a < 3; a++) {
+#pragma unroll
+    for (int b = 0; b < 3; b++) {
+      const double2 u = U[a * 3 + b];
+      acc[a].x = fma(u.x, v[b].x, acc[a].x);
+      acc[a].x = fma(-u.y, v[b].y, acc[a].x);
+      acc[a].y = fma(u.x, v[b].y, acc[a].y);
+      acc[a].y = fma(u.y, v[b].x, acc[a].y);
+    }
+  }
+}
+// acc -= U^+ v
+__device__ __forceinline__ void mv_adj_sub(double2 (&acc)[3], const double2 (&U)[9], const double2 (&v)[3]) {
+#pragma unroll
+  for (int a = 0; a < 3; a++) {
+#pragma unroll
+    for (int b = 0; b < 3; b++) {
+      const double2 u = U[b * 3 + a];  // conj(u) = (u.x, -u.y)
+      acc[a].x = fma(-u.x, v[b].x, acc[a].x);
+      acc[a].x = fma(-u.y, v[b].y, acc[a].x);
+      acc[a].y = fma(-u.x, v[b].y, acc[a].y);
+      acc[a].y = fma(u.y, v[b].x, acc[a].y);
+    }
+  }
+}
+
+__device__ __forceinline__ const double2* link_ptr(const double2* u, int k, int par, int Vh, int idx) {
+  return u + ((size_t)(k * 2 + par) * 9) * Vh + idx;
+}
+
+// Deterministic grid reduction: per-block partial -> last block sums in fixed order.
+template <int BLOCK>
+__device__ __forceinline__ void grid_reduce(double v, double* partials, unsigned int* ticket,
+                                            double* result) {
+  __shared__ double sm[BLOCK / 32];
+  __shared__ bool last;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (lane == 0) sm[w] = v;
+  __syncthreads();
+  if (w == 0) {
+    v = (lane < BLOCK / 32) ? sm[lane] : 0.0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    if (lane == 0) {
+      partials[blockIdx.x] = v;
+      __threadfence();
+      unsigned int t = atomicAdd(ticket, 1u);
+      last = (t == gridDim.x - 1);
+    }
+  }
+  __syncthreads();
+  if (last) {
+    __threadfence();
+    double s = 0.0;
+    for (int i = threadIdx.x; i < (int)gridDim.x; i += BLOCK) s += __ldcg(partials + i);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
+    __syncthreads();
+    if (lane == 0) sm[w] = s;
+    __syncthreads();
+    if (w == 0) {
+      s = (lane < BLOCK / 32) ? sm[lane] : 0.0;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
+      if (lane == 0) {
+        *result = s;
+        *ticket = 0u;
+      }
+    }
+  }
+}
+
+}  // namespace qb

@@ -1,0 +1,280 @@
+"""GPU parity tests proper: the CUDA path, called through the C ABI with native QEX host memory,
+against the CPU oracle on the same seeded inputs.  Bars: Dslash rel-L2 <= 1e-13,
+CG iterations within +-1 and true residual <= requested."""
+import numpy as np
+import pytest
+
+from util import make_inputs, rel_l2
+
+pytestmark = pytest.mark.gpu
+
+DSLASH_TOL = 1e-13
+
+
+@pytest.fixture()
+def ctx_factory(qb):
+    made = []
+
+    def make(L, inner=(1, 1, 1, 1)):
+        if qb.is_initialized():
+            qb.finalize()
+        qb.init(L)
+        qb.set_host_layout(inner)
+        made.append(1)
+        return qb
+    yield make
+    if qb.is_initialized():
+        qb.finalize()
+
+
+CASES = [
+    ((8, 8, 8, 8), 4, (1, 1, 1, 1)),
+    ((8, 8, 8, 8), 4, (1, 2, 2, 2)),      # QEX's default V=8 lane geometry on 8^4
+    ((8, 8, 8, 8), 8, (1, 2, 2, 2)),
+    ((8, 8, 8, 16), 4, (1, 1, 1, 1)),     # BASELINE config shape 8^3 x 16
+    ((4, 6, 8, 10), 8, (1, 1, 1, 1)),     # ragged extents; Naik wraps more than once in x0 (L=4)
+    ((12, 4, 4, 4), 4, (2, 1, 1, 1)),     # odd outer extent: lane checkerboard twist in the host layout
+    ((16, 16, 16, 16), 8, (1, 2, 2, 2)),
+]
+
+
+@pytest.mark.parametrize("L,nlinks,inner", CASES)
+def test_stagD2_parity(orc, ctx_factory, L, nlinks, inner):
+    """stagD2 (stagD.nim:348-395) on both parities, with a, b != 0."""
+    qb = ctx_factory(L, inner)
+    lat, g, (x, r0) = make_inputs(L, nlinks)
+    lo = orc.QexLayout(L, (1, 1, 1, 1), inner)
+    s = qb.Staggered([lo.scatter(g[k])[0] for k in range(nlinks)])
+    for parity in (0, 1):
+        for a, b in ((0.0, 0.0), (0.7, -0.3)):
+            want = r0.copy()
+            lat.stagD2(g, want, x, a, b, parity)
+            got = lo.scatter(r0)[0]
+            qb.stagD2(s, parity, got, lo.scatter(x)[0], a, b)
+            got = lo.gather([got])
+            sl = slice(0, lat.half) if parity == 0 else slice(lat.half, lat.vol)
+            osl = slice(lat.half, lat.vol) if parity == 0 else slice(0, lat.half)
+            assert rel_l2(got[sl], want[sl]) <= DSLASH_TOL
+            assert np.array_equal(got[osl], r0[osl])      # the other parity is untouched
+    s.free()
+
+
+@pytest.mark.parametrize("L,nlinks,inner", CASES[:5])
+def test_D_Ddag_D2ee_parity(orc, ctx_factory, L, nlinks, inner):
+    qb = ctx_factory(L, inner)
+    lat, g, (x, _) = make_inputs(L, nlinks)
+    lo = orc.QexLayout(L, (1, 1, 1, 1), inner)
+    s = qb.Staggered([lo.scatter(g[k])[0] for k in range(nlinks)])
+    xq = lo.scatter(x)[0]
+    m = 0.1
+    for name in ("D", "Ddag"):
+        want = lat.vector()
+        getattr(lat, name)(g, want, x, m)
+        got = np.zeros_like(xq)
+        getattr(s, name)(got, xq, m)
+        assert rel_l2(lo.gather([got]), want) <= DSLASH_TOL
+    for parity, fn in ((0, qb.stagD2ee), (1, qb.stagD2oo)):
+        want = lat.vector()
+        lat.stagD2xx(g, want, x, m * m, parity)
+        got = np.zeros_like(xq)
+        fn(s, got, xq, m * m)
+        sl = slice(0, lat.half) if parity == 0 else slice(lat.half, lat.vol)
+        assert rel_l2(lo.gather([got])[sl], want[sl]) <= DSLASH_TOL
+    # eoReconstruct (stagD.nim:582-586)
+    want = x.copy()
+    b = make_inputs(L, 4, seed=11, nvec=1)[2][0]
+    lat.eoReconstruct(g, want, b, m)
+    got = xq.copy()
+    s.eoReconstruct(got, lo.scatter(b)[0], m)
+    assert rel_l2(lo.gather([got]), want) <= DSLASH_TOL
+    s.free()
+
+
+def test_point_source_and_ramp(orc, ctx_factory):
+    """The reference's own smoke inputs: point source v{0}[0]=1 (testStagProp.nim:37) and the
+    coordinate-ramp source on unit gauge with BC + phases (stagD.nim:703-714)."""
+    L = (8, 8, 8, 8)
+    qb = ctx_factory(L)
+    lat = orc.Lattice(L)
+    g = lat.unit_gauge()
+    lat.setBC(g)
+    lat.stagPhase(g)
+    s = qb.newStag([g[k] for k in range(4)])
+    v = lat.vector()
+    v[0, 0, 0] = 1.0
+    ramp = lat.vector()
+    c = lat.coords.astype(float)
+    ramp[:, 0, 0] = c[0] * 1000 + c[1] * 100 + c[2] * 10 + c[3]
+    for src in (v, ramp):
+        want, got = lat.vector(), lat.vector()
+        lat.D(g, want, src, 0.5)
+        s.D(got, src, 0.5)
+        assert np.isfinite(got).all()
+        assert rel_l2(got, want) <= DSLASH_TOL
+    s.free()
+
+
+def test_device_rephase_matches_oracle(orc, ctx_factory):
+    """Staggered.rephase on the device copy == setBC + stagPhase of the oracle (stagD.nim:72-80)."""
+    L = (4, 6, 8, 10)
+    qb = ctx_factory(L)
+    lat = orc.Lattice(L)
+    rng = lat.new_rng(3)
+    g0 = lat.random_gauge(rng)
+    x = lat.gaussian_vector(rng)
+    g1 = g0.copy()
+    lat.setBC(g1)
+    lat.stagPhase(g1)
+    s = qb.newStag([g0[k] for k in range(4)])
+    s.rephase()
+    want, got = lat.vector(), lat.vector()
+    lat.D(g1, want, x, 0.0)
+    s.D(got, x, 0.0)
+    assert rel_l2(got, want) <= DSLASH_TOL
+    s.free()
+
+
+@pytest.mark.parametrize("L,nlinks,m,r2req", [
+    ((8, 8, 8, 8), 4, 0.1, 1e-8),        # BASELINE config 1
+    ((8, 8, 8, 8), 8, 0.05, 1e-12),
+    ((8, 8, 8, 16), 4, 0.05, 1e-12),
+    ((16, 16, 16, 16), 4, 0.1, 1e-8),
+])
+def test_solveEE_parity(orc, ctx_factory, L, nlinks, m, r2req):
+    """solveEE / solveOO (stagSolve.nim:57-138): iteration count within +-1 of the oracle's CG,
+    same recursive residual, solution close, true residual below the request."""
+    qb = ctx_factory(L)
+    lat, g, (b, _) = make_inputs(L, nlinks)
+    s = qb.Staggered([g[k] for k in range(nlinks)])
+    for par_even in (True, False):
+        parity = 0 if par_even else 1
+        want = lat.vector()
+        it_o, r2_o = lat.solveXX(g, want, b, m, parity, r2req, 10000)
+        got = np.ones_like(b)      # solveXX must zero r itself (stagSolve.nim:63-64)
+        sp = qb.SolverParams(r2req=r2req, maxits=10000)
+        s.solveXX(got, b, m, sp, parEven=par_even)
+        assert abs(sp.iterations - it_o) <= 1, (sp.iterations, it_o)
+        assert sp.r2 <= r2req
+        sl = slice(0, lat.half) if par_even else slice(lat.half, lat.vol)
+        osl = slice(lat.half, lat.vol) if par_even else slice(0, lat.half)
+        assert np.all(got[osl] == 0)
+        assert rel_l2(got[sl], want[sl]) <= 10 * np.sqrt(r2req)
+        # true residual of the normal equations
+        Ax = lat.vector()
+        lat.stagD2xx(g, Ax, got, m * m, parity)
+        tr = lat.norm2((Ax - b)[sl].copy(), 2) / lat.norm2(b[sl].copy(), 2)
+        assert tr <= 1.01 * r2req
+        nev = lat.half
+        assert sp.flops == (nlinks * 4 * 72 + 60) * nev * sp.iterations   # stagSolve.nim:92
+    s.free()
+
+
+@pytest.mark.parametrize("L,nlinks,m,r2req", [
+    ((8, 8, 8, 8), 4, 0.1, 1e-8),
+    ((8, 8, 8, 8), 8, 0.01, 1e-16),
+    ((4, 6, 8, 10), 4, 0.2, 1e-20),
+])
+def test_solve_parity(orc, ctx_factory, L, nlinks, m, r2req):
+    """Staggered.solve (stagSolve.nim:224-294): D x = b on the full lattice."""
+    qb = ctx_factory(L)
+    lat, g, (b, _) = make_inputs(L, nlinks)
+    s = qb.Staggered([g[k] for k in range(nlinks)])
+    want = lat.vector()
+    st = lat.solve(g, want, b, m, r2req, 20000)
+    got = lat.vector()
+    sp = qb.SolverParams(r2req=r2req, maxits=20000)
+    s.solve(got, b, m, sp)
+    assert abs(sp.iterations - st.iterations) <= max(1, st.calls)
+    Dx = lat.vector()
+    lat.D(g, Dx, got, m)
+    tr = lat.norm2(Dx - b) / lat.norm2(b)
+    assert tr <= r2req
+    assert abs(sp.r2 - tr) <= 1e-3 * tr + 1e-30
+    assert rel_l2(got, want) <= 10 * np.sqrt(r2req)
+    s.free()
+
+
+def test_solve_structural_identities(orc, ctx_factory):
+    """solve(D x0) == x0 (stagSolve.nim:556-574); usePrevSoln restart converges in 0 iterations;
+    zero source gives zero (cg.nim:139-144); maxits is honoured."""
+    L = (8, 8, 8, 8)
+    qb = ctx_factory(L)
+    lat, g, (x0, _) = make_inputs(L, 4)
+    s = qb.Staggered([g[k] for k in range(4)])
+    m = 0.1
+    b = lat.vector()
+    lat.D(g, b, x0, m)
+    x = lat.vector()
+    sp = qb.SolverParams(r2req=1e-22, maxits=5000)
+    s.solve(x, b, m, sp)
+    assert rel_l2(x, x0) < 1e-9
+    sp2 = qb.SolverParams(r2req=1e-20, maxits=5000, usePrevSoln=True)
+    s.solve(x, b, m, sp2)
+    assert sp2.iterations == 0
+    z = lat.vector()
+    out = np.ones_like(z)
+    sp3 = qb.SolverParams(r2req=1e-10)
+    s.solveEE(out, z, m, sp3)
+    assert sp3.iterations == 0 and np.all(out == 0)
+    sp4 = qb.SolverParams(r2req=1e-30, maxits=7)
+    s.solveEE(out, b, m, sp4)
+    assert sp4.iterations == 7
+    s.free()
+
+
+def test_device_resident_api(orc, ctx_factory):
+    """Device-field entry points give the same numbers as the host-buffer ones; reductions match."""
+    L = (8, 8, 8, 8)
+    qb = ctx_factory(L)
+    lat, g, (x, y) = make_inputs(L, 8)
+    s = qb.Staggered([g[k] for k in range(8)])
+    fx, fy, fr = qb.DeviceField(x), qb.DeviceField(y), qb.DeviceField()
+    assert abs(fx.norm2() - lat.norm2(x)) <= 1e-12 * lat.norm2(x)
+    assert abs(fx.norm2(qb.ODD) - lat.norm2(x, 1)) <= 1e-12 * lat.norm2(x)
+    assert abs(fx.redot(fy, qb.EVEN) - lat.redot(x, y, 0)) <= 1e-11 * np.sqrt(lat.norm2(x) * lat.norm2(y))
+    s.dev_D(fr, fx, 0.2)
+    want = lat.vector()
+    lat.D(g, want, x, 0.2)
+    assert rel_l2(fr.download(lat.vector()), want) <= DSLASH_TOL
+    s.dev_stagD2xx(0, fr, fx, 0.01)
+    lat.stagD2xx(g, want, x, 0.01, 0)
+    assert rel_l2(fr.download(lat.vector())[:lat.half], want[:lat.half]) <= DSLASH_TOL
+    # CG determinism: two identical solves give bit-identical results
+    sp = qb.SolverParams(r2req=1e-10)
+    s.dev_solveXX(fr, fx, 0.1, sp)
+    a = fr.download(lat.vector()).copy()
+    sp = qb.SolverParams(r2req=1e-10)
+    s.dev_solveXX(fr, fx, 0.1, sp)
+    assert np.array_equal(a, fr.download(lat.vector()))
+    for f in (fx, fy, fr):
+        f.free()
+    s.free()
+
+
+def test_large_lattice_properties(qb, ctx_factory):
+    """BASELINE config 2 size (32^4) without the oracle: anti-Hermiticity, D^+D block identity and a
+    CG round trip, on synthetic SU(3) links generated with numpy."""
+    from qex_b200.synth import random_su3_links, gaussian_vector
+    L = (32, 32, 32, 32)
+    qb = ctx_factory(L)
+    vol = int(np.prod(L))
+    g = random_su3_links(vol, 4, seed=1)
+    s = qb.Staggered(g)
+    s.rephase()
+    x, y = gaussian_vector(vol, 2), gaussian_vector(vol, 3)
+    fx, fy, fa, fb = qb.DeviceField(x), qb.DeviceField(y), qb.DeviceField(), qb.DeviceField()
+    s.dev_D(fa, fx, 0.0)
+    s.dev_D(fb, fy, 0.0)
+    # Re<y, D x> = -Re<D y, x>
+    lhs, rhs = fy.redot(fa), fb.redot(fx)
+    assert abs(lhs + rhs) <= 1e-12 * np.sqrt(fx.norm2() * fy.norm2()) * 8
+    m = 0.1
+    sp = qb.SolverParams(r2req=1e-16, maxits=5000)
+    s.dev_D(fb, fx, m)               # b = D x
+    s.dev_solve(fa, fb, m, sp)       # solve D a = b
+    assert sp.r2 <= 1e-16 and sp.iterations > 10
+    out = fa.download(np.zeros_like(x))
+    assert rel_l2(out, x) < 1e-6
+    for f in (fx, fy, fa, fb):
+        f.free()
+    s.free()

@@ -1,0 +1,39 @@
+"""Shared helpers of the parity tests: seeded inputs from the oracle, layout conversion."""
+import numpy as np
+
+import oracle
+
+SEED = 987654321  # the reference benchmarks' seed (src/physics/stagD.nim:779)
+
+
+def make_inputs(L, nlinks=4, seed=SEED, nvec=2, long_scale=0.1):
+    """Random SU(3) links with antiperiodic-T BC and staggered phases (stagD.nim:72-80), plus
+    gaussian sources, exactly as QEX's own RNG would produce them.  nlinks=8 adds long links =
+    long_scale * SU(3) from the continuing streams (the synthetic 3-hop operator of
+    src/bench/benchStagProp.nim:84-92), interleaved like newStag3 (stagD.nim:552-564)."""
+    lat = oracle.Lattice(L)
+    rng = lat.new_rng(seed)
+    g = lat.random_gauge(rng, 4)
+    lat.setBC(g)
+    lat.stagPhase(g)
+    if nlinks == 8:
+        g3 = lat.random_gauge(rng, 4) * long_scale
+        gg = np.zeros((8,) + g.shape[1:])
+        gg[0::2] = g
+        gg[1::2] = g3
+        g = gg
+    vecs = [lat.gaussian_vector(rng) for _ in range(nvec)]
+    return lat, np.ascontiguousarray(g), vecs
+
+
+def rel_l2(a, b):
+    return float(np.linalg.norm((a - b).ravel()) / max(np.linalg.norm(b.ravel()), 1e-300))
+
+
+def to_qex(lo, f):
+    """oracle global field -> native QEX array of rank 0 of layout lo (single rank)."""
+    return lo.scatter(f)[0]
+
+
+def from_qex(lo, a):
+    return lo.gather([a])
