@@ -49,7 +49,7 @@ typedef struct {
   int maxits;
   int use_prev_soln; /* usePrevSoln: x on entry is the initial guess (qexb200_solve only) */
   int verbosity;
-  /* outputs, accumulated like addStats (solverBase.nim:75-83) after being reset */
+  /* outputs of THIS call (the Nim glue folds them into sp0 with addStats, solverBase.nim:75-83) */
   int calls;
   int iterations;
   int iterations_max;
@@ -143,6 +143,20 @@ int qexb200_dev_solveXX(qexb200_gauge_t g, int parity, qexb200_field_t r, qexb20
                         double m, qexb200_solver_params* sp);
 int qexb200_dev_solve(qexb200_gauge_t g, qexb200_field_t x, qexb200_field_t b, double m,
                       qexb200_solver_params* sp);
+
+/* ---- halo plan (pure host arithmetic, usable without a GPU) ---------------- */
+
+/* One entry per direction split over ranks: what this rank sends each parity sweep.  It is the
+ * counterpart of the per-shift message tables QEX builds in makeShiftMultiSubQ / prepareShiftBufsQ
+ * (src/layout/qshifts.nim:23-94,355-533).  To rank_minus go `depth` face layers of the source
+ * vector (n_f complex numbers at off_f); to rank_plus go the U^+ x products of the last layers
+ * (n_b at off_b), formed at the source like stagD.nim:359-361.  Receives mirror the sends. */
+typedef struct {
+  int mu, depth, faceh, rank_plus, rank_minus;
+  long long off_f, n_f, off_b, n_b; /* in complex doubles */
+} qexb200_halo_dir;
+int qexb200_plan_halo(const int latsize[4], const int rankgeom[4], int myrank, int nlinks,
+                      qexb200_halo_dir out[4], int* ndirs, long long* total_elems);
 
 /* ---- measurement helpers (CUDA events on the library's compute stream) ---- */
 

@@ -27,6 +27,12 @@ class _CSolverParams(C.Structure):
                 ("r2", C.c_double)]
 
 
+class HaloDir(C.Structure):
+    _fields_ = [("mu", C.c_int), ("depth", C.c_int), ("faceh", C.c_int), ("rank_plus", C.c_int),
+                ("rank_minus", C.c_int), ("off_f", C.c_longlong), ("n_f", C.c_longlong),
+                ("off_b", C.c_longlong), ("n_b", C.c_longlong)]
+
+
 def lib_path():
     return _LIBPATH
 
@@ -72,6 +78,7 @@ def lib():
         L.qexb200_dev_stagD2xx.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_double]
         L.qexb200_dev_solveXX.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, spp]
         L.qexb200_dev_solve.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, spp]
+        L.qexb200_plan_halo.argtypes = [ip, ip, C.c_int, C.c_int, C.POINTER(HaloDir), ip, C.POINTER(C.c_longlong)]
         L.qexb200_timer_stop.argtypes = [C.POINTER(C.c_float)]
         L.qexb200_launch_count.restype = C.c_longlong
         L.qexb200_launch_count.argtypes = [C.c_int]
@@ -116,6 +123,14 @@ def init(latsize, rankgeom=(1, 1, 1, 1), myrank=0, device=0, nccl_id=None):
             pass
     idbuf = C.create_string_buffer(nccl_id, 128) if nccl_id is not None else None
     _ck(lib().qexb200_init(_i4(latsize), _i4(rankgeom), int(myrank), int(device), idbuf))
+
+
+def plan_halo(latsize, rankgeom, myrank, nlinks):
+    """Halo plan of one rank (pure host arithmetic, works without a GPU)."""
+    out = (HaloDir * 4)()
+    n, tot = C.c_int(), C.c_longlong()
+    _ck(lib().qexb200_plan_halo(_i4(latsize), _i4(rankgeom), int(myrank), int(nlinks), out, C.byref(n), C.byref(tot)))
+    return [dict((f[0], getattr(out[i], f[0])) for f in HaloDir._fields_) for i in range(n.value)], tot.value
 
 
 def finalize():

@@ -238,6 +238,24 @@ static int op_solve(const Gauge& g, Field& x, const Field& b, double m, qexb200_
   return 0;
 }
 
+// Local geometry of one rank; ranks are lexicographic with dimension 0 slowest (qlayout.nim:94-113).
+int make_geom(const int latsize[4], const int rankgeom[4], int myrank, Geom* gp) {
+  Geom& g = *gp;
+  g.nranks = 1; g.V = 1; g.comm_mask = 0;
+  for (int d = 0; d < 4; d++) {
+    if (rankgeom[d] < 1 || latsize[d] < 1 || latsize[d] % rankgeom[d] != 0) return fail("rankgeom[%d]=%d does not divide latsize %d", d, rankgeom[d], latsize[d]);
+    g.lat[d] = latsize[d]; g.G[d] = rankgeom[d]; g.X[d] = latsize[d] / rankgeom[d];
+    if (g.X[d] & 1) return fail("local extent %d in direction %d must be even", g.X[d], d);
+    g.nranks *= rankgeom[d]; g.V *= g.X[d];
+    if (rankgeom[d] > 1) g.comm_mask |= 1 << d;
+  }
+  if (myrank < 0 || myrank >= g.nranks) return fail("rank %d outside rank grid of %d", myrank, g.nranks);
+  g.rank = myrank; g.Vh = g.V / 2;
+  int r = myrank;
+  for (int d = 3; d >= 0; d--) { g.rc[d] = r % g.G[d]; r /= g.G[d]; }
+  return 0;
+}
+
 }  // namespace qb
 
 using namespace qb;
@@ -265,17 +283,7 @@ int qexb200_init(const int latsize[4], const int rankgeom[4], int myrank, int de
     return fail("qexb200_init: no CUDA device (%s); this backend has no CPU fallback", cudaGetErrorString(e));
   if (device < 0 || device >= ndev) return fail("qexb200_init: device %d out of range (%d devices)", device, ndev);
   Geom& g = g_ctx.g;
-  g.nranks = 1; g.V = 1; g.comm_mask = 0;
-  for (int d = 0; d < 4; d++) {
-    if (rankgeom[d] < 1 || latsize[d] % rankgeom[d] != 0) return fail("qexb200_init: rankgeom[%d]=%d does not divide latsize %d", d, rankgeom[d], latsize[d]);
-    g.lat[d] = latsize[d]; g.G[d] = rankgeom[d]; g.X[d] = latsize[d] / rankgeom[d];
-    if (g.X[d] & 1) return fail("qexb200_init: local extent %d in direction %d must be even", g.X[d], d);
-    g.nranks *= rankgeom[d]; g.V *= g.X[d];
-    if (rankgeom[d] > 1) g.comm_mask |= 1 << d;
-  }
-  if (myrank < 0 || myrank >= g.nranks) return fail("qexb200_init: rank %d outside rank grid of %d", myrank, g.nranks);
-  g.rank = myrank; g.Vh = g.V / 2;
-  { int r = myrank; for (int d = 3; d >= 0; d--) { g.rc[d] = r % g.G[d]; r /= g.G[d]; } }  // dimension 0 slowest
+  QB_CHECK(make_geom(latsize, rankgeom, myrank, &g));
   QB_CUDA(cudaSetDevice(device));
   g_ctx.device = device;
   QB_CUDA(cudaStreamCreateWithFlags(&g_ctx.stream, cudaStreamNonBlocking));
@@ -301,6 +309,26 @@ int qexb200_init(const int latsize[4], const int rankgeom[4], int myrank, int de
   g_ctx.inner[0] = g_ctx.inner[1] = g_ctx.inner[2] = g_ctx.inner[3] = 1;
   g_ctx.launches = 0;
   g_ctx.live = true;
+  return 0;
+}
+
+int qexb200_plan_halo(const int latsize[4], const int rankgeom[4], int myrank, int nlinks,
+                      qexb200_halo_dir out[4], int* ndirs, long long* total_elems) {
+  clear_error();
+  if (nlinks != 4 && nlinks != 8) return fail("plan_halo: nlinks must be 4 or 8");
+  Geom g;
+  QB_CHECK(make_geom(latsize, rankgeom, myrank, &g));
+  std::vector<HaloDir> dirs;
+  size_t total = 0;
+  QB_CHECK(plan_halo(g, nlinks / 4, dirs, &total));
+  for (size_t i = 0; i < dirs.size(); i++) {
+    out[i].mu = dirs[i].mu; out[i].depth = dirs[i].depth; out[i].faceh = dirs[i].faceh;
+    out[i].rank_plus = dirs[i].rank_plus; out[i].rank_minus = dirs[i].rank_minus;
+    out[i].off_f = (long long)dirs[i].off_f; out[i].n_f = (long long)dirs[i].n_f;
+    out[i].off_b = (long long)dirs[i].off_b; out[i].n_b = (long long)dirs[i].n_b;
+  }
+  *ndirs = (int)dirs.size();
+  *total_elems = (long long)total;
   return 0;
 }
 

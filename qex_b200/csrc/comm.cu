@@ -20,11 +20,10 @@ static int rank_of(const Geom& g, const int* rc) {
 
 static int halo_nl = 0;  // links per direction the buffers were laid out for
 
-static int halo_layout(int nl) {
-  Context& c = ctx();
-  if (halo_nl == nl && (c.sendbuf || c.g.comm_mask == 0)) return 0;
-  QB_CHECK(halo_free());
-  const Geom& g = c.g;
+// Pure host arithmetic (no CUDA): which faces this rank exchanges and where they sit in the
+// send/recv buffers.  Exposed as qexb200_plan_halo so the pairing can be tested without a GPU.
+int plan_halo(const Geom& g, int nl, std::vector<HaloDir>& dirs, size_t* total) {
+  dirs.clear();
   size_t off = 0;
   for (int mu = 0; mu < 4; mu++) {
     if (!((g.comm_mask >> mu) & 1)) continue;
@@ -40,8 +39,18 @@ static int halo_layout(int nl) {
     int rc[4] = {g.rc[0], g.rc[1], g.rc[2], g.rc[3]};
     rc[mu] = g.rc[mu] + 1; h.rank_plus = rank_of(g, rc);
     rc[mu] = g.rc[mu] - 1; h.rank_minus = rank_of(g, rc);
-    c.halo.push_back(h);
+    dirs.push_back(h);
   }
+  *total = off;
+  return 0;
+}
+
+static int halo_layout(int nl) {
+  Context& c = ctx();
+  if (halo_nl == nl && (c.sendbuf || c.g.comm_mask == 0)) return 0;
+  QB_CHECK(halo_free());
+  size_t off = 0;
+  QB_CHECK(plan_halo(c.g, nl, c.halo, &off));
   c.halo_elems = off;
   if (off) {
     QB_CUDA(cudaMalloc(&c.sendbuf, sizeof(double2) * off));

@@ -168,6 +168,8 @@ int rephase(Gauge& g);
 
 // ---- comm.cu ----------------------------------------------------------------
 int halo_setup();
+int plan_halo(const Geom& g, int nl, std::vector<HaloDir>& dirs, size_t* total);
+int make_geom(const int latsize[4], const int rankgeom[4], int myrank, Geom* g);
 int halo_free();
 // Start the exchange for a sweep that outputs `parity`: pack, then send/recv on comm_stream.
 int halo_start(const Gauge& g, int parity, const double2* x);

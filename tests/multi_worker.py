@@ -1,0 +1,160 @@
+"""One rank of a multi-rank parity run (launched by torch.distributed.run; see test_gpu_multi.py and
+test_dist_cpu.py).  Every rank builds the same global inputs with the oracle, keeps its own block in
+native QEX layout, runs the product and compares ITS block with the oracle's global result."""
+import argparse
+import json
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(HERE))
+sys.path.insert(0, HERE)
+
+
+def rank_coords(rank, G):
+    rc = [0] * 4
+    for d in (3, 2, 1, 0):
+        rc[d] = rank % G[d]
+        rank //= G[d]
+    return rc
+
+
+def cpu_plan_check(L, G, nlinks, rank, world, dist):
+    """Host logic of the N>1 path on CPU (gloo): the halo plans of all ranks pair up, and an exchange
+    driven by the plan moves exactly the planned byte counts between the planned peers."""
+    import torch
+    import qex_b200 as qb
+    plan, total = qb.plan_halo(L, G, rank, nlinks)
+    allp = [None] * world
+    dist.all_gather_object(allp, (plan, total))
+    rc = rank_coords(rank, G)
+    for h in plan:
+        mu = h["mu"]
+        up = list(rc); up[mu] = (rc[mu] + 1) % G[mu]
+        dn = list(rc); dn[mu] = (rc[mu] - 1) % G[mu]
+        lex = lambda c: ((c[0] * G[1] + c[1]) * G[2] + c[2]) * G[3] + c[3]   # dimension 0 slowest
+        assert h["rank_plus"] == lex(up) and h["rank_minus"] == lex(dn), (h, rc)
+        peer = [q for q in allp[h["rank_plus"]][0] if q["mu"] == mu][0]
+        assert peer["rank_minus"] == rank and peer["n_f"] == h["n_f"] and peer["n_b"] == h["n_b"]
+        X = [L[d] // G[d] for d in range(4)]
+        assert h["faceh"] == int(np.prod(X)) // X[mu] // 2
+        assert h["depth"] == (3 if nlinks == 8 else 1)
+        assert h["n_f"] == 3 * h["depth"] * h["faceh"] and h["n_b"] == 3 * (4 if nlinks == 8 else 1) * h["faceh"]
+    # emulate one sweep's exchange with gloo: same order as csrc/comm.cu halo_start
+    send = torch.arange(2 * total, dtype=torch.float64) + 1e6 * rank
+    recv = torch.zeros(2 * total, dtype=torch.float64)
+    ops = []
+    for h in plan:
+        f0, f1, b0, b1 = 2 * h["off_f"], 2 * (h["off_f"] + h["n_f"]), 2 * h["off_b"], 2 * (h["off_b"] + h["n_b"])
+        ops += [dist.P2POp(dist.isend, send[f0:f1], h["rank_minus"]), dist.P2POp(dist.isend, send[b0:b1], h["rank_plus"]),
+                dist.P2POp(dist.irecv, recv[f0:f1], h["rank_plus"]), dist.P2POp(dist.irecv, recv[b0:b1], h["rank_minus"])]
+    if ops:
+        for w in dist.batch_isend_irecv(ops):
+            w.wait()
+    for h in plan:
+        f0, b0 = 2 * h["off_f"], 2 * h["off_b"]
+        assert recv[f0] == f0 + 1e6 * h["rank_plus"], "psi faces must come from the + neighbour"
+        assert recv[b0] == b0 + 1e6 * h["rank_minus"], "U^+ psi faces must come from the - neighbour"
+    return True
+
+
+def gpu_case(L, G, nlinks, inner, rank, world, local_rank, dist):
+    import torch
+    import oracle
+    import qex_b200 as qb
+    from util import make_inputs, rel_l2
+    torch.cuda.set_device(local_rank)
+    idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+    if rank == 0:
+        idt = torch.tensor(list(qb.nccl_unique_id()), dtype=torch.uint8, device="cuda")
+    dist.broadcast(idt, 0)
+    qb.init(L, G, rank, local_rank, bytes(idt.cpu().tolist()))
+    qb.set_host_layout(inner)
+    lat, g, (x, b) = make_inputs(L, nlinks)
+    lo = oracle.QexLayout(L, G, inner)
+    mine = lambda f: lo.scatter(f)[rank]
+    s = qb.Staggered([mine(g[k]) for k in range(nlinks)])
+    res = {}
+    # Dslash, all flavours
+    for parity in (0, 1):
+        want = b.copy()
+        lat.stagD2(g, want, x, 0.7, -0.3, parity)
+        got = mine(b)
+        qb.stagD2(s, parity, got, mine(x), 0.7, -0.3)
+        res["stagD2_%d" % parity] = rel_l2(got, mine(want))
+    for name in ("D", "Ddag"):
+        want = lat.vector()
+        getattr(lat, name)(g, want, x, 0.1)
+        got = np.zeros_like(mine(x))
+        getattr(s, name)(got, mine(x), 0.1)
+        res[name] = rel_l2(got, mine(want))
+    want = lat.vector()
+    lat.stagD2xx(g, want, x, 0.01, 0)
+    got = np.zeros_like(mine(x))
+    qb.stagD2ee(s, got, mine(x), 0.01)
+    we = want.copy(); we[lat.half:] = 0
+    res["stagD2ee"] = rel_l2(got, mine(we))
+    for k, v in res.items():
+        assert v <= 1e-13, (k, v)
+    # reductions over ranks
+    fx = qb.DeviceField(mine(x))
+    n2 = fx.norm2()
+    assert abs(n2 - lat.norm2(x)) <= 1e-12 * n2
+    fx.free()
+    # CG and the full solve
+    m, r2req = 0.1, 1e-10
+    want = lat.vector()
+    it_o, _ = lat.solveXX(g, want, b, m, 0, r2req, 10000)
+    got = np.zeros_like(mine(b))
+    sp = qb.SolverParams(r2req=r2req, maxits=10000)
+    s.solveEE(got, mine(b), m, sp)
+    assert abs(sp.iterations - it_o) <= 1, (sp.iterations, it_o)
+    assert rel_l2(got, mine(want)) <= 10 * np.sqrt(r2req)
+    res["solveEE_its"] = (sp.iterations, it_o)
+    want = lat.vector()
+    st = lat.solve(g, want, b, m, r2req, 10000)
+    got = np.zeros_like(mine(b))
+    sp = qb.SolverParams(r2req=r2req, maxits=10000)
+    s.solve(got, mine(b), m, sp)
+    assert abs(sp.iterations - st.iterations) <= 1, (sp.iterations, st.iterations)
+    assert sp.r2 <= r2req
+    assert rel_l2(got, mine(want)) <= 10 * np.sqrt(r2req)
+    res["solve_its"] = (sp.iterations, st.iterations)
+    s.free()
+    qb.finalize()
+    return res
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--cpu", action="store_true")
+    ap.add_argument("--lat", default="8,8,8,16")
+    ap.add_argument("--rankgeom", default="1,1,1,2")
+    ap.add_argument("--inner", default="1,1,1,1")
+    ap.add_argument("--nlinks", type=int, default=4)
+    a = ap.parse_args()
+    import torch.distributed as dist
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    local_rank = int(os.environ.get("LOCAL_RANK", 0))
+    L = tuple(int(t) for t in a.lat.split(","))
+    G = tuple(int(t) for t in a.rankgeom.split(","))
+    inner = tuple(int(t) for t in a.inner.split(","))
+    assert int(np.prod(G)) == world
+    if a.cpu:
+        dist.init_process_group("gloo")
+        ok = cpu_plan_check(L, G, a.nlinks, rank, world, dist)
+        out = {"ok": ok}
+    else:
+        import torch
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        out = gpu_case(L, G, a.nlinks, inner, rank, world, local_rank, dist)
+    dist.barrier()
+    if rank == 0:
+        print("MULTI_OK " + json.dumps(out))
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,27 @@
+"""Multi-GPU parity (one process per GPU, NCCL halo exchange): every rank checks its block of the
+Dslash / CG / solve results against the oracle's global result.  Needs >= 2 GPUs on the box."""
+import pytest
+
+from test_dist_cpu import launch
+
+pytestmark = pytest.mark.gpu
+
+
+def ngpus():
+    import torch
+    return torch.cuda.device_count()
+
+
+@pytest.mark.parametrize("nproc,lat,rg,inner,nlinks", [
+    (2, "8,8,8,16", "1,1,1,2", "1,1,1,1", 4),
+    (2, "8,8,8,16", "1,1,1,2", "1,2,2,2", 8),
+    (2, "8,8,12,8", "1,1,2,1", "1,1,1,1", 8),       # local extent 6 in the split direction: 3-hop both ways
+    (4, "8,8,16,16", "1,1,2,2", "1,1,1,1", 8),
+    (4, "16,8,8,8", "4,1,1,1", "1,1,1,1", 4),       # x0 split; neighbours are distinct ranks
+    (8, "8,16,16,16", "1,2,2,2", "1,1,1,1", 8),
+])
+def test_multi_gpu_parity(nproc, lat, rg, inner, nlinks):
+    if ngpus() < nproc:
+        pytest.skip("needs %d GPUs" % nproc)
+    r = launch(nproc, ["--lat", lat, "--rankgeom", rg, "--inner", inner, "--nlinks", str(nlinks)], timeout=600)
+    assert r.returncode == 0 and "MULTI_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
