@@ -165,13 +165,16 @@ def run_ours(args):
     nccl_id = None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-        idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
-        if rank == 0:
-            idt = torch.tensor(list(qb.nccl_unique_id()), dtype=torch.uint8, device="cuda")
-        dist.broadcast(idt, 0)
-        nccl_id = bytes(idt.cpu().tolist())
+        if args.transport == "nccl":
+            idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+            if rank == 0:
+                idt = torch.tensor(list(qb.nccl_unique_id()), dtype=torch.uint8, device="cuda")
+            dist.broadcast(idt, 0)
+            nccl_id = bytes(idt.cpu().tolist())
     lat_shape, rankgeom = WEAK[world]
     qb.init(lat_shape, rankgeom, rank, local_rank, nccl_id)
+    if world > 1 and args.transport == "p2p":
+        qb.p2p_attach_torch(dist)     # halos and scalar sums over NVLink stores (csrc/comm.cu)
     nsites, neven = qb.local_sites()
     peak, peak_src = measured_peak()
 
@@ -276,7 +279,7 @@ def run_ours(args):
         "dtype": "f64", "data": "synthetic",
         "config": {"workload": "%s naive staggered even-even CG to r2req=1e-8, m=0.1, fp64, random SU(3) "
                                "(BASELINE configs[1]; 32^4 per GPU)" % "x".join(map(str, lat_shape)),
-                   "rankgeom": list(rankgeom), "cg_iterations": r["iterations"],
+                   "rankgeom": list(rankgeom), "transport": (args.transport if world > 1 else "none"), "cg_iterations": r["iterations"],
                    "l2": "links (604 MB per sweep set) exceed the 126 MB L2; CG vectors (25 MB each) are L2-resident by design",
                    "time_to_solution_ms": r["ms_per_step"]},
         "e2e": {"value": r["e2e_gflops"], "unit": "GFLOP/s", "h2d_bytes_per_step": int(nsites * 48),
@@ -343,6 +346,8 @@ def main():
     ap.add_argument("--sweeps", type=int, default=200, help="back-to-back parity sweeps for the roofline leg")
     ap.add_argument("--ref-solves", type=int, default=8, help="complete CPU solves in the bounded cpu_baseline sample")
     ap.add_argument("--naive-only", action="store_true")
+    ap.add_argument("--transport", default="p2p", choices=["p2p", "nccl"],
+                    help="multi-GPU halo/sum transport: peer-memory NVLink stores (default) or NCCL send/recv + allreduce")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

@@ -68,6 +68,18 @@ typedef struct {
 int qexb200_init(const int latsize[4], const int rankgeom[4], int myrank, int device,
                  const void* nccl_unique_id);
 int qexb200_nccl_unique_id(void* out128);
+/* Peer-memory transport for the ranks of ONE box (NVLink / NVSwitch): every rank exports a 64-byte
+ * handle of its receive window (cudaIpcMemHandle_t), the caller all-gathers the handles in rank
+ * order (the same Comm the id above travels on, src/comms/comms.nim:13) and every rank attaches.
+ * From then on the face-pack kernel stores halos straight into the neighbours' windows, the
+ * boundary kernel waits on flags the neighbours raise, and the CG's scalar sums are completed
+ * inside the reducing kernels: the startSB / QMP_wait / boundarySB2 sequence of
+ * src/layout/shifts.nim:67-94,254-285 and the two QMP_sum_double per iteration (src/solvers/cg.nim:206,213)
+ * without a host round trip.  Optional: without it the NCCL send/recv path is used; with it,
+ * qexb200_init may be given a NULL nccl_unique_id. */
+int qexb200_p2p_export(void* handle_out64);
+int qexb200_p2p_attach(const void* handles_nranks_x_64);
+int qexb200_p2p_active(void);
 /* Replaces qudaFinalize (quda_milc_interface.nim:146). */
 int qexb200_finalize(void);
 const char* qexb200_last_error(void);

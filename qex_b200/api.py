@@ -50,6 +50,8 @@ def lib():
         L.qexb200_last_error.restype = C.c_char_p
         L.qexb200_init.argtypes = [ip, ip, C.c_int, C.c_int, C.c_void_p]
         L.qexb200_nccl_unique_id.argtypes = [C.c_void_p]
+        L.qexb200_p2p_export.argtypes = [C.c_void_p]
+        L.qexb200_p2p_attach.argtypes = [C.c_void_p]
         L.qexb200_set_host_layout.argtypes = [ip]
         L.qexb200_local_sites.argtypes = [ip, ip]
         L.qexb200_gauge_create.argtypes = [C.c_int, ip]
@@ -123,6 +125,33 @@ def init(latsize, rankgeom=(1, 1, 1, 1), myrank=0, device=0, nccl_id=None):
             pass
     idbuf = C.create_string_buffer(nccl_id, 128) if nccl_id is not None else None
     _ck(lib().qexb200_init(_i4(latsize), _i4(rankgeom), int(myrank), int(device), idbuf))
+
+
+def p2p_export():
+    """64-byte handle of this rank's peer-memory window (to be all-gathered in rank order)."""
+    buf = C.create_string_buffer(64)
+    _ck(lib().qexb200_p2p_export(buf))
+    return buf.raw
+
+
+def p2p_attach(handles):
+    """handles: the concatenated 64-byte handles of all ranks, in rank order."""
+    buf = C.create_string_buffer(bytes(handles), len(handles))
+    _ck(lib().qexb200_p2p_attach(buf))
+
+
+def p2p_active():
+    return _lib is not None and bool(_lib.qexb200_p2p_active())
+
+
+def p2p_attach_torch(dist, device="cuda"):
+    """Convenience for torch.distributed launchers: all-gather the window handles and attach."""
+    import torch
+    mine = torch.tensor(list(p2p_export()), dtype=torch.uint8, device=device)
+    allh = [torch.zeros_like(mine) for _ in range(dist.get_world_size())]
+    dist.all_gather(allh, mine)
+    p2p_attach(b"".join(bytes(t.cpu().tolist()) for t in allh))
+    dist.barrier()
 
 
 def plan_halo(latsize, rankgeom, myrank, nlinks):

@@ -49,34 +49,37 @@ int blas_axpby(double2* y, double a, const double2* x, double b, size_t n) { LAU
 
 template <bool TWO>
 __global__ void __launch_bounds__(BB) k_reduce(const double2* __restrict__ x, const double2* __restrict__ y,
-                                                size_t n, double* partials, unsigned int* ticket, double* out) {
+                                                size_t n, double* partials, unsigned int* ticket, double* out,
+                                                XRank* xr) {
   double s = 0.0;
   for (size_t i = (size_t)blockIdx.x * BB + threadIdx.x; i < n; i += (size_t)gridDim.x * BB) {
     const double2 v = x[i];
     if (TWO) { const double2 w = y[i]; s = fma(v.x, w.x, s); s = fma(v.y, w.y, s); }
     else { s = fma(v.x, v.x, s); s = fma(v.y, v.y, s); }
   }
-  grid_reduce<BB>(s, partials, ticket, out);
+  grid_reduce<BB>(s, partials, ticket, out, xr);
 }
 
 int blas_norm2(const double2* x, size_t n, double* d_out) {
   Context& c = ctx();
-  k_reduce<false><<<blas_grid(n), BB, 0, c.stream>>>(x, nullptr, n, c.d_partials, c.d_ticket, d_out);
+  k_reduce<false><<<blas_grid(n), BB, 0, c.stream>>>(x, nullptr, n, c.d_partials, c.d_ticket, d_out, xrank());
   count_launch();
   QB_CUDA(cudaGetLastError());
   return 0;
 }
 int blas_redot(const double2* x, const double2* y, size_t n, double* d_out) {
   Context& c = ctx();
-  k_reduce<true><<<blas_grid(n), BB, 0, c.stream>>>(x, y, n, c.d_partials, c.d_ticket, d_out);
+  k_reduce<true><<<blas_grid(n), BB, 0, c.stream>>>(x, y, n, c.d_partials, c.d_ticket, d_out, xrank());
   count_launch();
   QB_CUDA(cudaGetLastError());
   return 0;
 }
 
+// Sum over ranks of scalars produced by blas_norm2 / blas_redot / the fused CG kernels.  On the
+// peer-memory path those kernels already summed over the ranks (xrank_sum in their last block).
 int allreduce_scalars(double* d_ptr, int n) {
   Context& c = ctx();
-  if (c.g.nranks > 1) QB_NCCL(nccl().AllReduce(d_ptr, d_ptr, n, ncclDouble, ncclSum, c.nccl, c.stream));
+  if (c.g.nranks > 1 && !c.p2p) QB_NCCL(nccl().AllReduce(d_ptr, d_ptr, n, ncclDouble, ncclSum, c.nccl, c.stream));
   return 0;
 }
 
@@ -85,6 +88,16 @@ int fetch_scalars(const double* d_ptr, double* h_out, int n) {
   QB_CUDA(cudaMemcpyAsync(c.h_scal, d_ptr, sizeof(double) * n, cudaMemcpyDeviceToHost, c.stream));
   QB_CUDA(cudaStreamSynchronize(c.stream));
   for (int i = 0; i < n; i++) h_out[i] = c.h_scal[i];
+  return check_device_error();
+}
+
+int check_device_error() {
+  Context& c = ctx();
+  if (c.h_err && *(volatile int*)c.h_err != 0) {
+    const int e = *(volatile int*)c.h_err;
+    return fail("a device-side wait on a peer rank timed out (%s); the result is invalid",
+                e == 1 ? "halo flag" : "cross-rank sum");
+  }
   return 0;
 }
 

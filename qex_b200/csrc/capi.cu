@@ -299,8 +299,10 @@ int qexb200_init(const int latsize[4], const int rankgeom[4], int myrank, int de
   QB_CUDA(cudaMalloc(&g_ctx.d_scal, sizeof(double) * 64));
   QB_CUDA(cudaMemset(g_ctx.d_scal, 0, sizeof(double) * 64));
   QB_CUDA(cudaHostAlloc((void**)&g_ctx.h_scal, sizeof(double) * 64, cudaHostAllocDefault));
-  if (g.nranks > 1) {
-    if (!nccl_unique_id) return fail("qexb200_init: %d ranks need an ncclUniqueId", g.nranks);
+  QB_CUDA(cudaHostAlloc((void**)&g_ctx.h_err, sizeof(int) * 4, cudaHostAllocMapped));
+  g_ctx.h_err[0] = 0;
+  QB_CUDA(cudaHostGetDevicePointer((void**)&g_ctx.d_err, (void*)g_ctx.h_err, 0));
+  if (g.nranks > 1 && nccl_unique_id) {
     QB_CHECK(nccl_load());
     ncclUniqueId id;
     memcpy(&id, nccl_unique_id, 128);
@@ -332,6 +334,16 @@ int qexb200_plan_halo(const int latsize[4], const int rankgeom[4], int myrank, i
   return 0;
 }
 
+int qexb200_p2p_export(void* out64) {
+  QB_CHECK(need_ctx());
+  return p2p_export(out64);
+}
+int qexb200_p2p_attach(const void* handles) {
+  QB_CHECK(need_ctx());
+  return p2p_attach(handles);
+}
+int qexb200_p2p_active(void) { return g_ctx.live && g_ctx.p2p ? 1 : 0; }
+
 int qexb200_finalize(void) {
   if (!g_ctx.live) return 0;
   cudaStreamSynchronize(g_ctx.stream);
@@ -342,6 +354,8 @@ int qexb200_finalize(void) {
   if (g_sw.ok) { cudaFree(g_sw.r.d); cudaFree(g_sw.y.d); cudaFree(g_sw.d.d); g_sw = SolveWork(); }
   cg_free();
   halo_free();
+  p2p_free();
+  if (g_ctx.h_err) cudaFreeHost(g_ctx.h_err);
   if (g_ctx.nccl) { nccl().CommDestroy(g_ctx.nccl); g_ctx.nccl = nullptr; }
   if (g_ctx.d_perm) cudaFree(g_ctx.d_perm);
   if (g_ctx.d_stage) cudaFree(g_ctx.d_stage);
@@ -578,7 +592,7 @@ int qexb200_sync(void) {
   QB_CHECK(need_ctx());
   QB_CUDA(cudaStreamSynchronize(g_ctx.stream));
   QB_CUDA(cudaStreamSynchronize(g_ctx.comm_stream));
-  return 0;
+  return check_device_error();
 }
 int qexb200_timer_start(void) {
   QB_CHECK(need_ctx());

@@ -7,10 +7,12 @@
 // All messages of a sweep go out in one ncclGroup on a dedicated stream so the
 // interior kernel overlaps the transfer; the exterior kernels wait on an event.
 #include "common.cuh"
+#include <cstdlib>
+#include <cstring>
 
 namespace qb {
 
-int pack_faces(const Gauge& g, int q, const double2* x);  // dslash.cu
+int pack_faces(const Gauge& g, int q, const double2* x, unsigned int seq, cudaStream_t st);  // dslash.cu
 
 static int rank_of(const Geom& g, const int* rc) {
   int r = 0;
@@ -47,15 +49,20 @@ int plan_halo(const Geom& g, int nl, std::vector<HaloDir>& dirs, size_t* total) 
 
 static int halo_layout(int nl) {
   Context& c = ctx();
-  if (halo_nl == nl && (c.sendbuf || c.g.comm_mask == 0)) return 0;
-  QB_CHECK(halo_free());
+  if (halo_nl == nl && (c.sendbuf || c.p2p || c.g.comm_mask == 0)) return 0;
+  if (c.sendbuf) cudaFree(c.sendbuf);
+  if (c.recvbuf) cudaFree(c.recvbuf);
+  c.sendbuf = c.recvbuf = nullptr;
   size_t off = 0;
   QB_CHECK(plan_halo(c.g, nl, c.halo, &off));
   c.halo_elems = off;
-  if (off) {
+  if (off && !c.p2p) {
+    if (!c.nccl) return fail("multi-rank sweep needs either an NCCL communicator (qexb200_init with an id) or an attached peer window (qexb200_p2p_attach)");
+    QB_CUDA(cudaStreamSynchronize(c.comm_stream));
     QB_CUDA(cudaMalloc(&c.sendbuf, sizeof(double2) * off));
     QB_CUDA(cudaMalloc(&c.recvbuf, sizeof(double2) * off));
   }
+  if (c.p2p && off > c.halo_cap) return fail("halo of %zu elements exceeds the peer window (%zu)", off, c.halo_cap);
   halo_nl = nl;
   return 0;
 }
@@ -73,22 +80,110 @@ int halo_free() {
   return 0;
 }
 
+// ---- peer-memory window ---------------------------------------------------------------------
+int p2p_alloc() {
+  Context& c = ctx();
+  if (c.g.nranks < 2 || c.win) return 0;
+  std::vector<HaloDir> dirs;
+  size_t cap = 0;
+  bool naik_ok = true;   // size for the deeper (fat + Naik) halo when the local extents allow it
+  for (int mu = 0; mu < 4; mu++)
+    if (((c.g.comm_mask >> mu) & 1) && c.g.X[mu] < 3) naik_ok = false;
+  QB_CHECK(plan_halo(c.g, naik_ok ? 2 : 1, dirs, &cap));
+  c.halo_cap = cap;
+  c.win_bytes = WIN_HDR + 2 * cap * sizeof(double2);
+  QB_CUDA(cudaMalloc(&c.win, c.win_bytes));
+  QB_CUDA(cudaMemset(c.win, 0, c.win_bytes));
+  QB_CUDA(cudaDeviceSynchronize());
+  return 0;
+}
+
+int p2p_export(void* out64) {
+  Context& c = ctx();
+  if (c.g.nranks < 2) return fail("p2p_export: single-rank context has no peer window");
+  QB_CHECK(p2p_alloc());
+  cudaIpcMemHandle_t h;
+  static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t size");
+  QB_CUDA(cudaIpcGetMemHandle(&h, c.win));
+  memcpy(out64, &h, 64);
+  return 0;
+}
+
+int p2p_attach(const void* handles) {
+  Context& c = ctx();
+  if (c.g.nranks < 2) return 0;
+  if (c.g.nranks > XR_MAXR) return fail("p2p_attach: at most %d ranks (one box)", XR_MAXR);
+  if (c.p2p) return fail("p2p_attach: already attached");
+  QB_CHECK(p2p_alloc());
+  QB_CUDA(cudaStreamSynchronize(c.stream));
+  QB_CUDA(cudaStreamSynchronize(c.comm_stream));
+  const char* hb = static_cast<const char*>(handles);
+  for (int r = 0; r < c.g.nranks; r++) {
+    if (r == c.g.rank) { c.peer_win[r] = c.win; continue; }
+    cudaIpcMemHandle_t h;
+    memcpy(&h, hb + (size_t)64 * r, 64);
+    void* p = nullptr;
+    cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) {
+      for (int q = 0; q < r; q++) if (q != c.g.rank && c.peer_win[q]) { cudaIpcCloseMemHandle(c.peer_win[q]); c.peer_win[q] = nullptr; }
+      return fail("p2p_attach: cannot map the window of rank %d: %s", r, cudaGetErrorString(e));
+    }
+    c.peer_win[r] = static_cast<char*>(p);
+  }
+  XRank xr;
+  memset(&xr, 0, sizeof xr);
+  for (int r = 0; r < c.g.nranks; r++) xr.ll[r] = reinterpret_cast<unsigned long long*>(c.peer_win[r] + WIN_FLAGS);
+  xr.nranks = c.g.nranks; xr.rank = c.g.rank; xr.seq = 0; xr.err = c.d_err;
+  if (const char* ev = getenv("QEXB200_P2P_TIMEOUT_S")) {
+    const double sec = atof(ev);
+    if (sec > 0) c.p2p_timeout_ns = (unsigned long long)(sec * 1e9);
+  }
+  xr.timeout_ns = c.p2p_timeout_ns;
+  if (!c.d_xr) QB_CUDA(cudaMalloc(&c.d_xr, sizeof(XRank)));
+  QB_CUDA(cudaMemcpy(c.d_xr, &xr, sizeof xr, cudaMemcpyHostToDevice));
+  // buffers laid out for the NCCL path are no longer needed
+  QB_CHECK(halo_free());
+  c.halo_seq = 0;
+  c.p2p = true;
+  return 0;
+}
+
+int p2p_free() {
+  Context& c = ctx();
+  for (int r = 0; r < XR_MAXR; r++) {
+    if (c.peer_win[r] && c.peer_win[r] != c.win) cudaIpcCloseMemHandle(c.peer_win[r]);
+    c.peer_win[r] = nullptr;
+  }
+  if (c.win) cudaFree(c.win);
+  if (c.d_xr) cudaFree(c.d_xr);
+  c.win = nullptr; c.d_xr = nullptr; c.p2p = false; c.win_bytes = 0; c.halo_cap = 0;
+  return 0;
+}
+
+// The exchange of one parity sweep.  Both paths pack on the comm stream, concurrently with the
+// interior kernel on the compute stream:
+//   peer-memory : k_pack stores straight into the neighbours' windows and raises their flags;
+//                 the exterior kernel spins on its own flags (no host or NCCL involvement);
+//   NCCL        : k_pack fills the local send buffer, one ncclGroup of send/recv follows.
 int halo_start(const Gauge& g, int parity, const double2* x) {
   Context& c = ctx();
   QB_CHECK(halo_layout(g.nlinks / 4));
-  QB_CHECK(pack_faces(g, 1 - parity, x));
-  QB_CUDA(cudaEventRecord(c.ev_pack, c.stream));
+  c.halo_seq++;
+  QB_CUDA(cudaEventRecord(c.ev_pack, c.stream));            // x is ready
   QB_CUDA(cudaStreamWaitEvent(c.comm_stream, c.ev_pack, 0));
-  QB_NCCL(nccl().GroupStart());
-  // order matters when + and - neighbour are the same rank (rank grid of 2): the first
-  // send to a peer pairs with that peer's first receive.
-  for (const HaloDir& h : c.halo) {
-    QB_NCCL(nccl().Send(c.sendbuf + h.off_f, h.n_f * 2, ncclDouble, h.rank_minus, c.nccl, c.comm_stream));
-    QB_NCCL(nccl().Send(c.sendbuf + h.off_b, h.n_b * 2, ncclDouble, h.rank_plus, c.nccl, c.comm_stream));
-    QB_NCCL(nccl().Recv(c.recvbuf + h.off_f, h.n_f * 2, ncclDouble, h.rank_plus, c.nccl, c.comm_stream));
-    QB_NCCL(nccl().Recv(c.recvbuf + h.off_b, h.n_b * 2, ncclDouble, h.rank_minus, c.nccl, c.comm_stream));
+  QB_CHECK(pack_faces(g, 1 - parity, x, c.halo_seq, c.comm_stream));
+  if (!c.p2p) {
+    QB_NCCL(nccl().GroupStart());
+    // order matters when + and - neighbour are the same rank (rank grid of 2): the first
+    // send to a peer pairs with that peer's first receive.
+    for (const HaloDir& h : c.halo) {
+      QB_NCCL(nccl().Send(c.sendbuf + h.off_f, h.n_f * 2, ncclDouble, h.rank_minus, c.nccl, c.comm_stream));
+      QB_NCCL(nccl().Send(c.sendbuf + h.off_b, h.n_b * 2, ncclDouble, h.rank_plus, c.nccl, c.comm_stream));
+      QB_NCCL(nccl().Recv(c.recvbuf + h.off_f, h.n_f * 2, ncclDouble, h.rank_plus, c.nccl, c.comm_stream));
+      QB_NCCL(nccl().Recv(c.recvbuf + h.off_b, h.n_b * 2, ncclDouble, h.rank_minus, c.nccl, c.comm_stream));
+    }
+    QB_NCCL(nccl().GroupEnd());
   }
-  QB_NCCL(nccl().GroupEnd());
   QB_CUDA(cudaEventRecord(c.ev_comm, c.comm_stream));
   return 0;
 }

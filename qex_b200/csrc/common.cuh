@@ -52,6 +52,29 @@ struct HaloDir {
   int rank_plus, rank_minus;
 };
 
+// ---- peer-memory window (NVLink direct stores between the ranks of one box) --------------
+// Every rank owns one cudaMalloc'ed window with the same layout and exports it with
+// cudaIpcGetMemHandle; peers map it (qexb200_p2p_export / qexb200_p2p_attach).
+//   [0, 256)                 halo flags   unsigned f[2 buf][4 dir][2 side], written by the neighbours
+//   [256, 256 + LL bytes)    LL slots of the cross-rank scalar sums: u64 ll[NB][MAXR][2]
+//   [WIN_HDR, ...)           2 receive buffers of halo_cap double2 each
+constexpr int XR_MAXR = 16;      // ranks an in-kernel cross-rank sum supports (one box has 8 GPUs)
+constexpr int XR_NB = 4;         // LL slots in flight
+constexpr size_t WIN_FLAGS = 256;
+constexpr size_t WIN_LL = sizeof(unsigned long long) * XR_NB * XR_MAXR * 2;
+constexpr size_t WIN_HDR = 4096;
+static_assert(WIN_FLAGS + WIN_LL <= WIN_HDR, "window header overflow");
+
+// Cross-rank scalar sum descriptor, in device memory.  ll[j] is rank j's LL array (peer mapping;
+// ll[rank] is the local one).  Protocol: NCCL-LL style 8-byte words {seq:32 | half of the double:32}.
+struct XRank {
+  unsigned long long* ll[XR_MAXR];
+  int nranks, rank;
+  unsigned int seq;        // reductions done so far (device side counter)
+  int* err;                // mapped host word: != 0 after a wait timed out
+  unsigned long long timeout_ns;
+};
+
 struct Context {
   bool live = false;
   int device = 0;
@@ -76,6 +99,16 @@ struct Context {
   double2 *sendbuf = nullptr, *recvbuf = nullptr;
   size_t halo_elems = 0;
   long long launches = 0;
+  // peer-memory path
+  bool p2p = false;                 // window attached on every rank: halos and sums go over NVLink stores
+  char* win = nullptr;              // my window
+  size_t win_bytes = 0, halo_cap = 0;   // halo_cap: double2 per receive buffer
+  char* peer_win[XR_MAXR] = {};     // mapped windows (peer_win[rank] == win)
+  XRank* d_xr = nullptr;            // device copy of the descriptor
+  int* h_err = nullptr;             // mapped pinned error word
+  int* d_err = nullptr;             // its device alias
+  unsigned int halo_seq = 0;        // parity sweeps exchanged so far (identical on all ranks)
+  unsigned long long p2p_timeout_ns = 120ull * 1000000000ull;  // QEXB200_P2P_TIMEOUT_S
 };
 
 // NCCL is bound at run time (dlopen of libnccl.so.2) the first time a multi-rank
@@ -97,6 +130,7 @@ NcclApi& nccl();
 int nccl_load();
 
 Context& ctx();
+inline XRank* xrank() { return ctx().p2p ? ctx().d_xr : nullptr; }
 int fail(const char* fmt, ...);
 void clear_error();
 
@@ -151,6 +185,8 @@ int blas_redot(const double2* x, const double2* y, size_t n2, double* d_out);
 int allreduce_scalars(double* d_ptr, int n);
 // copy n device scalars to host (synchronising)
 int fetch_scalars(const double* d_ptr, double* h_out, int n);
+// non-zero status if a device-side wait on a peer timed out
+int check_device_error();
 
 // ---- solver.cu --------------------------------------------------------------
 struct CgResult { int iterations; double r2, b2; };
@@ -171,6 +207,10 @@ int halo_setup();
 int plan_halo(const Geom& g, int nl, std::vector<HaloDir>& dirs, size_t* total);
 int make_geom(const int latsize[4], const int rankgeom[4], int myrank, Geom* g);
 int halo_free();
+int p2p_alloc();                       // allocate the window (multi-rank contexts)
+int p2p_export(void* out64);
+int p2p_attach(const void* handles);   // nranks * 64 bytes, rank order
+int p2p_free();
 // Start the exchange for a sweep that outputs `parity`: pack, then send/recv on comm_stream.
 int halo_start(const Gauge& g, int parity, const double2* x);
 // Make the compute stream wait for the exchange.

@@ -78,46 +78,98 @@ __global__ void __launch_bounds__(SWEEP_BLOCK) k_sweep(const SweepArgs A) {
   if (DOT) grid_reduce<SWEEP_BLOCK>(dot, A.partials, A.ticket, A.result);
 }
 
-// Exterior kernel of split direction mu: adds the terms whose neighbour lives on
-// another rank (boundarySB2 of stagD.nim:381-393).  ghost_f holds the + neighbour's
-// first `depth` layers of x; ghost_b[j] holds U_k^+ x of the - neighbour's last h_j layers.
+// ---- exterior: one launch for all split directions -----------------------------------------
+// Adds the terms whose neighbour lives on another rank (boundarySB2 of stagD.nim:381-393).
+// ghost_f holds the + neighbour's first `depth` layers of x; ghost_b[j] holds U_k^+ x of the
+// - neighbour's last h_j layers.  The boundary sites are enumerated as DISJOINT regions
+// (region i: interior in split directions m_1..m_{i-1}, boundary in m_i, anything elsewhere),
+// one thread per site, which handles every split direction of its site in a fixed order:
+// no site is touched by two threads, so corners need no atomics and the sum is deterministic.
+struct ExtDir {
+  int mu, depth, faceh, nb;
+  const double2 *ghost_f, *ghost_b0, *ghost_b1;
+  const unsigned int *flag_f, *flag_b;   // p2p: set by the + / - neighbour's pack kernel
+};
+struct ExtRegion {
+  int n[4];      // index counts per direction (n[0] even)
+  int type[4];   // 0: whole extent, 1: boundary layers, 2: interior layers
+  int end;       // prefix end in threads (sites of one parity)
+};
 struct ExtArgs {
   const double2* u;
   double2* r;
-  const double2* ghost_f;
-  const double2* ghost_b[2];
   double scale;  // post*sgn
-  int X[4];
-  int Vh, parity, mu, nb, depth, faceh;
+  int X[4], dep[4], nbv[4];
+  int Vh, parity, ndir, nreg;
+  ExtDir d[4];
+  ExtRegion reg[4];
+  unsigned int seq;
+  int wait;      // p2p: spin on the neighbours' flags before touching the ghosts
+  int* err;
+  unsigned long long timeout_ns;
 };
 
 template <int NL>
 __global__ void __launch_bounds__(SWEEP_BLOCK) k_exterior(const ExtArgs A) {
-  const int t = blockIdx.x * SWEEP_BLOCK + threadIdx.x;
-  if (t >= A.nb * A.faceh) return;
-  const int b = t / A.faceh, fidx = t - b * A.faceh;
-  const int mu = A.mu, Xm = A.X[mu], d = A.depth;
-  const int xmu = (b < d) ? b : Xm - A.nb + b;
-  const Site s = site_from_face(fidx, mu, xmu, A.parity, A.X);
-  const int idx = s.lex >> 1, Vh = A.Vh;
-  double2 acc[3] = {{0, 0}, {0, 0}, {0, 0}};
-#pragma unroll
-  for (int j = 0; j < NL; j++) {
-    const int h = (j == 0) ? 1 : 3;
-    const int k = mu * NL + j;
-    if (xmu + h >= Xm) {
-      const int l = xmu + h - Xm;
-      double2 U[9], v[3];
-      load_link(U, link_ptr(A.u, k, A.parity, Vh, idx), Vh);
-#pragma unroll
-      for (int c = 0; c < 3; c++) v[c] = A.ghost_f[(size_t)c * d * A.faceh + (size_t)l * A.faceh + fidx];
-      mv_add(acc, U, v);
+  if (A.wait) {
+    if ((int)threadIdx.x < 2 * A.ndir) {
+      const ExtDir& D = A.d[threadIdx.x >> 1];
+      wait_flag((threadIdx.x & 1) ? D.flag_b : D.flag_f, A.seq, A.err, A.timeout_ns);
     }
-    if (xmu - h < 0) {
+    __syncthreads();
+  }
+  const int t = blockIdx.x * SWEEP_BLOCK + threadIdx.x;
+  if (t >= A.reg[A.nreg - 1].end) return;
+  int ri = 0, base = 0;
 #pragma unroll
-      for (int c = 0; c < 3; c++) {
-        const double2 w = A.ghost_b[j][(size_t)c * h * A.faceh + (size_t)xmu * A.faceh + fidx];
-        acc[c].x -= w.x; acc[c].y -= w.y;
+  for (int i = 0; i < 3; i++)
+    if (i + 1 < A.nreg && t >= A.reg[i].end) { ri = i + 1; base = A.reg[i].end; }
+  const ExtRegion& R = A.reg[ri];
+  int tt = t - base;
+  int id[4];
+  const int n0h = R.n[0] >> 1;
+  const int i0h = tt % n0h; tt /= n0h;
+  id[1] = tt % R.n[1]; tt /= R.n[1];
+  id[2] = tt % R.n[2];
+  id[3] = tt / R.n[2];
+  int par = A.parity;
+#pragma unroll
+  for (int d = 1; d < 4; d++) par += id[d] + (R.type[d] == 2 ? A.dep[d] : 0);
+  par += (R.type[0] == 2 ? A.dep[0] : 0);
+  id[0] = 2 * i0h + (par & 1);
+  int x[4];
+#pragma unroll
+  for (int d = 0; d < 4; d++) {
+    const int i = id[d];
+    x[d] = (R.type[d] == 0) ? i : (R.type[d] == 2) ? A.dep[d] + i : (i < A.dep[d] ? i : A.X[d] - A.nbv[d] + i);
+  }
+  const int lex = ((x[3] * A.X[2] + x[2]) * A.X[1] + x[1]) * A.X[0] + x[0];
+  const int idx = lex >> 1, Vh = A.Vh;
+  double2 acc[3] = {{0, 0}, {0, 0}, {0, 0}};
+  for (int di = 0; di < A.ndir; di++) {
+    const ExtDir& D = A.d[di];
+    const int mu = D.mu, Xm = A.X[mu], xmu = x[mu], d = D.depth;
+    if (xmu + d < Xm && xmu - d >= 0) continue;   // no off-rank hop in this direction
+    const int fidx = face_lex(x, mu, A.X) >> 1;
+#pragma unroll
+    for (int j = 0; j < NL; j++) {
+      const int h = (j == 0) ? 1 : 3;
+      const int k = mu * NL + j;
+      if (xmu + h >= Xm) {
+        const int l = xmu + h - Xm;
+        double2 U[9], v[3];
+        load_link(U, link_ptr(A.u, k, A.parity, Vh, idx), Vh);
+#pragma unroll
+        for (int c = 0; c < 3; c++) v[c] = __ldcg(D.ghost_f + (size_t)c * d * D.faceh + (size_t)l * D.faceh + fidx);
+        mv_add(acc, U, v);
+      }
+      if (xmu - h < 0) {
+        const double2* gb = (j == 0) ? D.ghost_b0 : D.ghost_b1;
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+          const double2 w = __ldcg(gb + (size_t)c * h * D.faceh + (size_t)xmu * D.faceh + fidx);
+          acc[c].x -= w.x; acc[c].y -= w.y;
+        }
       }
     }
   }
@@ -129,87 +181,168 @@ __global__ void __launch_bounds__(SWEEP_BLOCK) k_exterior(const ExtArgs A) {
   }
 }
 
-// Face packing (startSB of stagD.nim:355-361): x of my first `depth` layers for the
-// - neighbour, and U_k^+ x of my last h_j layers for the + neighbour.
+// ---- face packing: one launch for all split directions --------------------------------------
+// startSB of stagD.nim:355-361: x of my first `depth` layers for the - neighbour, and U_k^+ x of
+// my last h_j layers for the + neighbour.  On the peer-memory path the destinations are the
+// neighbours' receive buffers (NVLink stores) and the last block to finish raises the
+// neighbours' flags; on the NCCL path they are the local send buffer.
+struct PackDir {
+  int mu, depth, faceh, end;
+  double2 *out_f, *out_b0, *out_b1;
+  unsigned int *flag_f, *flag_b;   // flag at the - neighbour (its side 0) / + neighbour (its side 1)
+};
 struct PackArgs {
   const double2* u;
   const double2* x;   // half field of parity q (the sweep's input parity)
-  double2* out_f;
-  double2* out_b[2];
   int X[4];
-  int Vh, q, mu, depth, faceh;
+  int Vh, q, ndir;
+  PackDir d[4];
+  unsigned int seq;
+  unsigned int* ticket;   // nullptr: no signalling
 };
 
 template <int NL>
 __global__ void __launch_bounds__(SWEEP_BLOCK) k_pack(const PackArgs A) {
   const int t = blockIdx.x * SWEEP_BLOCK + threadIdx.x;
-  const int nf = A.depth * A.faceh;        // forward-psi items
-  const int ntot = nf + ((NL == 2) ? 4 : 1) * A.faceh;
-  if (t >= ntot) return;
-  const int mu = A.mu, Xm = A.X[mu], Vh = A.Vh;
-  if (t < nf) {
-    const int l = t / A.faceh, fidx = t - l * A.faceh;
-    const Site s = site_from_face(fidx, mu, l, A.q, A.X);
-    const int idx = s.lex >> 1;
+  if (t < A.d[A.ndir - 1].end) {
+    int di = 0, base = 0;
 #pragma unroll
-    for (int c = 0; c < 3; c++) A.out_f[(size_t)c * nf + t] = A.x[(size_t)c * Vh + idx];
-  } else {
-    int tb = t - nf;
-    int j = 0, h = 1;
-    if (NL == 2 && tb >= A.faceh) { j = 1; h = 3; tb -= A.faceh; }
-    const int jl = tb / A.faceh, fidx = tb - jl * A.faceh;
-    const Site s = site_from_face(fidx, mu, Xm - h + jl, A.q, A.X);
-    const int idx = s.lex >> 1;
-    double2 U[9], v[3], acc[3] = {{0, 0}, {0, 0}, {0, 0}};
-    load_link(U, link_ptr(A.u, mu * NL + j, A.q, Vh, idx), Vh);
-    load_vec(v, A.x + idx, Vh);
-    mv_adj_sub(acc, U, v);
+    for (int i = 0; i < 3; i++)
+      if (i + 1 < A.ndir && t >= A.d[i].end) { di = i + 1; base = A.d[i].end; }
+    const PackDir& P = A.d[di];
+    const int tt = t - base;
+    const int nf = P.depth * P.faceh;        // forward-psi items
+    const int mu = P.mu, Xm = A.X[mu], Vh = A.Vh;
+    if (tt < nf) {
+      const int l = tt / P.faceh, fidx = tt - l * P.faceh;
+      const Site s = site_from_face(fidx, mu, l, A.q, A.X);
+      const int idx = s.lex >> 1;
 #pragma unroll
-    for (int c = 0; c < 3; c++)
-      A.out_b[j][(size_t)c * h * A.faceh + tb] = make_double2(-acc[c].x, -acc[c].y);
+      for (int c = 0; c < 3; c++) P.out_f[(size_t)c * nf + tt] = A.x[(size_t)c * Vh + idx];
+    } else {
+      int tb = tt - nf;
+      int j = 0, h = 1;
+      if (NL == 2 && tb >= P.faceh) { j = 1; h = 3; tb -= P.faceh; }
+      const int jl = tb / P.faceh, fidx = tb - jl * P.faceh;
+      const Site s = site_from_face(fidx, mu, Xm - h + jl, A.q, A.X);
+      const int idx = s.lex >> 1;
+      double2 U[9], v[3], acc[3] = {{0, 0}, {0, 0}, {0, 0}};
+      load_link(U, link_ptr(A.u, mu * NL + j, A.q, Vh, idx), Vh);
+      load_vec(v, A.x + idx, Vh);
+      mv_adj_sub(acc, U, v);
+      double2* ob = (j == 0) ? P.out_b0 : P.out_b1;
+#pragma unroll
+      for (int c = 0; c < 3; c++)
+        ob[(size_t)c * h * P.faceh + tb] = make_double2(-acc[c].x, -acc[c].y);
+    }
+  }
+  if (A.ticket) {
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const unsigned int tk = atomicAdd(A.ticket, 1u);
+      if (tk == gridDim.x - 1) {
+        *A.ticket = 0u;
+        __threadfence_system();
+        for (int i = 0; i < A.ndir; i++) {
+          st_release_sys(A.d[i].flag_f, A.seq);
+          st_release_sys(A.d[i].flag_b, A.seq);
+        }
+      }
+    }
   }
 }
 
-int pack_faces(const Gauge& g, int q, const double2* x) {
+static inline unsigned int* win_flag(char* win, int buf, int mu, int side) {
+  return reinterpret_cast<unsigned int*>(win) + ((buf * 4 + mu) * 2 + side);
+}
+static inline double2* win_recv(char* win, int buf, size_t cap) {
+  return reinterpret_cast<double2*>(win + WIN_HDR) + (size_t)buf * cap;
+}
+
+// Launched on `st` (the comm stream).  seq is the sweep's exchange number.
+int pack_faces(const Gauge& g, int q, const double2* x, unsigned int seq, cudaStream_t st) {
   Context& c = ctx();
-  for (const HaloDir& hd : c.halo) {
-    PackArgs P;
-    P.u = g.d; P.x = x;
-    P.out_f = c.sendbuf + hd.off_f;
-    P.out_b[0] = c.sendbuf + hd.off_b;
-    P.out_b[1] = c.sendbuf + hd.off_b + (size_t)3 * hd.faceh;
-    for (int i = 0; i < 4; i++) P.X[i] = c.g.X[i];
-    P.Vh = c.g.Vh; P.q = q; P.mu = hd.mu; P.depth = hd.depth; P.faceh = hd.faceh;
-    const int nl = g.nlinks / 4;
-    const int ntot = (hd.depth + (nl == 2 ? 4 : 1)) * hd.faceh;
-    const int grid = (ntot + SWEEP_BLOCK - 1) / SWEEP_BLOCK;
-    if (nl == 2) k_pack<2><<<grid, SWEEP_BLOCK, 0, c.stream>>>(P);
-    else k_pack<1><<<grid, SWEEP_BLOCK, 0, c.stream>>>(P);
-    count_launch();
+  PackArgs P;
+  P.u = g.d; P.x = x;
+  for (int i = 0; i < 4; i++) P.X[i] = c.g.X[i];
+  P.Vh = c.g.Vh; P.q = q; P.ndir = (int)c.halo.size();
+  P.seq = seq; P.ticket = c.p2p ? c.d_ticket + 1 : nullptr;
+  const int nl = g.nlinks / 4;
+  const int buf = seq & 1;
+  int end = 0;
+  for (int i = 0; i < P.ndir; i++) {
+    const HaloDir& hd = c.halo[i];
+    PackDir& D = P.d[i];
+    D.mu = hd.mu; D.depth = hd.depth; D.faceh = hd.faceh;
+    end += (hd.depth + (nl == 2 ? 4 : 1)) * hd.faceh;
+    D.end = end;
+    if (c.p2p) {
+      double2* rm = win_recv(c.peer_win[hd.rank_minus], buf, c.halo_cap);
+      double2* rp = win_recv(c.peer_win[hd.rank_plus], buf, c.halo_cap);
+      D.out_f = rm + hd.off_f;
+      D.out_b0 = rp + hd.off_b;
+      D.out_b1 = rp + hd.off_b + (size_t)3 * hd.faceh;
+      D.flag_f = win_flag(c.peer_win[hd.rank_minus], buf, hd.mu, 0);
+      D.flag_b = win_flag(c.peer_win[hd.rank_plus], buf, hd.mu, 1);
+    } else {
+      D.out_f = c.sendbuf + hd.off_f;
+      D.out_b0 = c.sendbuf + hd.off_b;
+      D.out_b1 = c.sendbuf + hd.off_b + (size_t)3 * hd.faceh;
+      D.flag_f = D.flag_b = nullptr;
+    }
   }
+  const int grid = (end + SWEEP_BLOCK - 1) / SWEEP_BLOCK;
+  if (nl == 2) k_pack<2><<<grid, SWEEP_BLOCK, 0, st>>>(P);
+  else k_pack<1><<<grid, SWEEP_BLOCK, 0, st>>>(P);
+  count_launch();
   QB_CUDA(cudaGetLastError());
   return 0;
 }
 
 static int exterior(const Gauge& g, int parity, double2* r, double scale) {
   Context& c = ctx();
-  for (const HaloDir& hd : c.halo) {
-    ExtArgs E;
-    E.u = g.d; E.r = r;
-    E.ghost_f = c.recvbuf + hd.off_f;
-    E.ghost_b[0] = c.recvbuf + hd.off_b;
-    E.ghost_b[1] = c.recvbuf + hd.off_b + (size_t)3 * hd.faceh;
-    E.scale = scale;
-    for (int i = 0; i < 4; i++) E.X[i] = c.g.X[i];
-    E.Vh = c.g.Vh; E.parity = parity; E.mu = hd.mu; E.depth = hd.depth; E.faceh = hd.faceh;
+  ExtArgs E;
+  E.u = g.d; E.r = r; E.scale = scale;
+  for (int i = 0; i < 4; i++) { E.X[i] = c.g.X[i]; E.dep[i] = 0; E.nbv[i] = 0; }
+  E.Vh = c.g.Vh; E.parity = parity; E.ndir = (int)c.halo.size();
+  E.seq = c.halo_seq; E.wait = c.p2p ? 1 : 0; E.err = c.d_err;
+  E.timeout_ns = c.p2p_timeout_ns;
+  const int buf = c.halo_seq & 1;
+  const double2* rb = c.p2p ? win_recv(c.win, buf, c.halo_cap) : c.recvbuf;
+  for (int i = 0; i < E.ndir; i++) {
+    const HaloDir& hd = c.halo[i];
+    ExtDir& D = E.d[i];
     const int Xm = c.g.X[hd.mu];
-    E.nb = (2 * hd.depth < Xm) ? 2 * hd.depth : Xm;
-    const int n = E.nb * hd.faceh;
-    const int grid = (n + SWEEP_BLOCK - 1) / SWEEP_BLOCK;
-    if (g.nlinks == 8) k_exterior<2><<<grid, SWEEP_BLOCK, 0, c.stream>>>(E);
-    else k_exterior<1><<<grid, SWEEP_BLOCK, 0, c.stream>>>(E);
-    count_launch();
+    D.mu = hd.mu; D.depth = hd.depth; D.faceh = hd.faceh;
+    D.nb = (2 * hd.depth < Xm) ? 2 * hd.depth : Xm;
+    D.ghost_f = rb + hd.off_f;
+    D.ghost_b0 = rb + hd.off_b;
+    D.ghost_b1 = rb + hd.off_b + (size_t)3 * hd.faceh;
+    D.flag_f = c.p2p ? win_flag(c.win, buf, hd.mu, 0) : nullptr;
+    D.flag_b = c.p2p ? win_flag(c.win, buf, hd.mu, 1) : nullptr;
+    E.dep[hd.mu] = hd.depth; E.nbv[hd.mu] = D.nb;
   }
+  int end = 0, nreg = 0;
+  for (int i = 0; i < E.ndir; i++) {
+    ExtRegion R;
+    long long cnt = 1;
+    for (int d = 0; d < 4; d++) { R.type[d] = 0; R.n[d] = c.g.X[d]; }
+    for (int j = 0; j < i; j++) { const int m = c.halo[j].mu; R.type[m] = 2; R.n[m] = c.g.X[m] - E.nbv[m]; }
+    const int mi = c.halo[i].mu;
+    R.type[mi] = 1; R.n[mi] = E.nbv[mi];
+    for (int d = 0; d < 4; d++) cnt *= R.n[d];
+    if (cnt == 0) continue;
+    end += (int)(cnt / 2);
+    R.end = end;
+    E.reg[nreg++] = R;
+  }
+  E.nreg = nreg;
+  if (nreg == 0) return 0;
+  const int grid = (end + SWEEP_BLOCK - 1) / SWEEP_BLOCK;
+  if (g.nlinks == 8) k_exterior<2><<<grid, SWEEP_BLOCK, 0, c.stream>>>(E);
+  else k_exterior<1><<<grid, SWEEP_BLOCK, 0, c.stream>>>(E);
+  count_launch();
   QB_CUDA(cudaGetLastError());
   return 0;
 }

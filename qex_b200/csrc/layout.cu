@@ -160,7 +160,7 @@ int download_vector(const Field& f, double* host) {
   QB_CUDA(cudaGetLastError());
   QB_CUDA(cudaMemcpyAsync(host, c.d_stage, bytes, cudaMemcpyDeviceToHost, c.stream));
   QB_CUDA(cudaStreamSynchronize(c.stream));
-  return 0;
+  return check_device_error();
 }
 
 int upload_links(Gauge& g, const double* const* links) {

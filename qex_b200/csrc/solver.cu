@@ -55,7 +55,8 @@ __global__ void __launch_bounds__(CB) k_cg_p(double2* __restrict__ p, const doub
 // x += alpha p ; r -= alpha Ap ; r2new = |r|^2   (cg.nim:208-213)
 __global__ void __launch_bounds__(CB) k_cg_xr(double2* __restrict__ x, double2* __restrict__ r,
                                                const double2* __restrict__ p, const double2* __restrict__ Ap,
-                                               double* S, size_t n, double* partials, unsigned int* ticket) {
+                                               double* S, size_t n, double* partials, unsigned int* ticket,
+                                               XRank* xr) {
   if (S[S_DONE] != 0.0) return;
   const double alpha = S[S_R2] / S[S_PAP];
   double s = 0.0;
@@ -67,7 +68,7 @@ __global__ void __launch_bounds__(CB) k_cg_xr(double2* __restrict__ x, double2* 
     x[i] = xv; r[i] = rv;
     s = fma(rv.x, rv.x, s); s = fma(rv.y, rv.y, s);
   }
-  grid_reduce<CB>(s, partials, ticket, S + S_R2NEW);
+  grid_reduce<CB>(s, partials, ticket, S + S_R2NEW, xr);
 }
 
 // loop control of cg.nim:174 on the device
@@ -183,7 +184,7 @@ int cg_xx(const Gauge& g, int parity, double2* x, const double2* b, double m2, d
     count_launch();
     QB_CHECK(apply_xx(g, parity, w_Ap, w_p, m2, S + S_PAP));
     QB_CHECK(allreduce_scalars(S + S_PAP, 1));
-    k_cg_xr<<<grid, CB, 0, c.stream>>>(x, w_r, w_p, w_Ap, S, n, c.d_partials, c.d_ticket);
+    k_cg_xr<<<grid, CB, 0, c.stream>>>(x, w_r, w_p, w_Ap, S, n, c.d_partials, c.d_ticket, xrank());
     count_launch();
     QB_CHECK(allreduce_scalars(S + S_R2NEW, 1));
     k_cg_step<<<1, 1, 0, c.stream>>>(S, d_status);
@@ -197,6 +198,7 @@ int cg_xx(const Gauge& g, int parity, double2* x, const double2* b, double m2, d
         if ((++spins & 0xffff) == 0) {  // surface device faults instead of spinning forever
           cudaError_t e = cudaStreamQuery(c.stream);
           if (e != cudaSuccess && e != cudaErrorNotReady) return fail("cg_xx: %s", cudaGetErrorString(e));
+          QB_CHECK(check_device_error());
         }
       }
       done = slot->done != 0;

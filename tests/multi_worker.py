@@ -60,17 +60,21 @@ def cpu_plan_check(L, G, nlinks, rank, world, dist):
     return True
 
 
-def gpu_case(L, G, nlinks, inner, rank, world, local_rank, dist):
+def gpu_case(L, G, nlinks, inner, rank, world, local_rank, dist, transport="nccl"):
     import torch
     import oracle
     import qex_b200 as qb
     from util import make_inputs, rel_l2
     torch.cuda.set_device(local_rank)
     idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
-    if rank == 0:
-        idt = torch.tensor(list(qb.nccl_unique_id()), dtype=torch.uint8, device="cuda")
-    dist.broadcast(idt, 0)
-    qb.init(L, G, rank, local_rank, bytes(idt.cpu().tolist()))
+    if transport == "nccl":
+        if rank == 0:
+            idt = torch.tensor(list(qb.nccl_unique_id()), dtype=torch.uint8, device="cuda")
+        dist.broadcast(idt, 0)
+    qb.init(L, G, rank, local_rank, bytes(idt.cpu().tolist()) if transport == "nccl" else None)
+    if transport == "p2p":
+        qb.p2p_attach_torch(dist)
+        assert qb.p2p_active()
     qb.set_host_layout(inner)
     lat, g, (x, b) = make_inputs(L, nlinks)
     lo = oracle.QexLayout(L, G, inner)
@@ -134,6 +138,7 @@ def main():
     ap.add_argument("--rankgeom", default="1,1,1,2")
     ap.add_argument("--inner", default="1,1,1,1")
     ap.add_argument("--nlinks", type=int, default=4)
+    ap.add_argument("--transport", default="nccl", choices=["nccl", "p2p"])
     a = ap.parse_args()
     import torch.distributed as dist
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
@@ -149,7 +154,7 @@ def main():
     else:
         import torch
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-        out = gpu_case(L, G, a.nlinks, inner, rank, world, local_rank, dist)
+        out = gpu_case(L, G, a.nlinks, inner, rank, world, local_rank, dist, a.transport)
     dist.barrier()
     if rank == 0:
         print("MULTI_OK " + json.dumps(out))

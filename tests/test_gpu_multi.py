@@ -16,12 +16,17 @@ def ngpus():
     (2, "8,8,8,16", "1,1,1,2", "1,1,1,1", 4),
     (2, "8,8,8,16", "1,1,1,2", "1,2,2,2", 8),
     (2, "8,8,12,8", "1,1,2,1", "1,1,1,1", 8),       # local extent 6 in the split direction: 3-hop both ways
+    (2, "8,8,8,8", "1,1,1,2", "1,1,1,1", 8),        # local extent 4 < 2*depth: a site hops off-rank both ways
     (4, "8,8,16,16", "1,1,2,2", "1,1,1,1", 8),
     (4, "16,8,8,8", "4,1,1,1", "1,1,1,1", 4),       # x0 split; neighbours are distinct ranks
     (8, "8,16,16,16", "1,2,2,2", "1,1,1,1", 8),
 ])
-def test_multi_gpu_parity(nproc, lat, rg, inner, nlinks):
+@pytest.mark.parametrize("transport", ["p2p", "nccl"])
+def test_multi_gpu_parity(nproc, lat, rg, inner, nlinks, transport):
+    """transport p2p: NVLink stores into the neighbours' windows + in-kernel cross-rank sums;
+    nccl: ncclSend/ncclRecv + ncclAllReduce."""
     if ngpus() < nproc:
         pytest.skip("needs %d GPUs" % nproc)
-    r = launch(nproc, ["--lat", lat, "--rankgeom", rg, "--inner", inner, "--nlinks", str(nlinks)], timeout=600)
+    r = launch(nproc, ["--lat", lat, "--rankgeom", rg, "--inner", inner, "--nlinks", str(nlinks),
+                       "--transport", transport], timeout=600)
     assert r.returncode == 0 and "MULTI_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
