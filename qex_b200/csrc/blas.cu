@@ -95,8 +95,8 @@ int check_device_error() {
   Context& c = ctx();
   if (c.h_err && *(volatile int*)c.h_err != 0) {
     const int e = *(volatile int*)c.h_err;
-    return fail("a device-side wait on a peer rank timed out (%s); the result is invalid",
-                e == 1 ? "halo flag" : "cross-rank sum");
+    return fail("a device-side wait on a peer rank timed out (%s; awaited seq %d, found %d, waiter %d of exchange %u); the result is invalid",
+                e == 1 ? "halo flag" : "cross-rank sum", c.h_err[1], c.h_err[2], c.h_err[3], c.halo_seq);
   }
   return 0;
 }

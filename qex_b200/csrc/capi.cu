@@ -292,7 +292,9 @@ int qexb200_init(const int latsize[4], const int rankgeom[4], int myrank, int de
   QB_CUDA(cudaEventCreateWithFlags(&g_ctx.ev_comm, cudaEventDisableTiming));
   QB_CUDA(cudaEventCreate(&g_ctx.ev_t0));
   QB_CUDA(cudaEventCreate(&g_ctx.ev_t1));
-  const size_t npart = (size_t)g.Vh / 128 + 148 * 8 + 64;
+  // one slot per block of the largest reducing grid (the fused multi-rank sweep: pack + all sites + boundary)
+  const size_t npart = 3 * ((size_t)g.Vh / 128) + 148 * 8 + 4096;
+  g_ctx.npart = npart;
   QB_CUDA(cudaMalloc(&g_ctx.d_partials, sizeof(double) * npart));
   QB_CUDA(cudaMalloc(&g_ctx.d_ticket, sizeof(unsigned int) * 4));
   QB_CUDA(cudaMemset(g_ctx.d_ticket, 0, sizeof(unsigned int) * 4));

@@ -165,10 +165,16 @@ int p2p_free() {
 //   peer-memory : k_pack stores straight into the neighbours' windows and raises their flags;
 //                 the exterior kernel spins on its own flags (no host or NCCL involvement);
 //   NCCL        : k_pack fills the local send buffer, one ncclGroup of send/recv follows.
+// Lay out the halo for this link set and open exchange number halo_seq.
+int halo_begin(const Gauge& g) {
+  QB_CHECK(halo_layout(g.nlinks / 4));
+  ctx().halo_seq++;
+  return 0;
+}
+
 int halo_start(const Gauge& g, int parity, const double2* x) {
   Context& c = ctx();
-  QB_CHECK(halo_layout(g.nlinks / 4));
-  c.halo_seq++;
+  QB_CHECK(halo_begin(g));
   QB_CUDA(cudaEventRecord(c.ev_pack, c.stream));            // x is ready
   QB_CUDA(cudaStreamWaitEvent(c.comm_stream, c.ev_pack, 0));
   QB_CHECK(pack_faces(g, 1 - parity, x, c.halo_seq, c.comm_stream));

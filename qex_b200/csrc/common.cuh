@@ -91,6 +91,7 @@ struct Context {
   size_t pinned_bytes = 0;
   // reductions
   double* d_partials = nullptr;
+  size_t npart = 0;            // slots in d_partials
   unsigned int* d_ticket = nullptr;
   double* d_scal = nullptr;    // device scalars
   double* h_scal = nullptr;    // pinned mirror
@@ -211,6 +212,7 @@ int p2p_alloc();                       // allocate the window (multi-rank contex
 int p2p_export(void* out64);
 int p2p_attach(const void* handles);   // nranks * 64 bytes, rank order
 int p2p_free();
+int halo_begin(const Gauge& g);
 // Start the exchange for a sweep that outputs `parity`: pack, then send/recv on comm_stream.
 int halo_start(const Gauge& g, int parity, const double2* x);
 // Make the compute stream wait for the exchange.

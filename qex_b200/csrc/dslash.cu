@@ -16,6 +16,28 @@ namespace qb {
 
 constexpr int SWEEP_BLOCK = 128;
 
+// r = post*(a*r + b*bx + sgn*acc) for one site; returns Re<bx, r_new> when DOT
+template <bool DOT>
+__device__ __forceinline__ double site_epilogue(const SweepArgs& A, int idx, const double2 (&acc)[3]) {
+  const int Vh = A.Vh;
+  double dot = 0.0;
+#pragma unroll
+  for (int c = 0; c < 3; c++) {
+    double2 o = {A.sgn * acc[c].x, A.sgn * acc[c].y};
+    double2 bxv = {0, 0};
+    if (A.b != 0.0 || DOT) bxv = A.bx[(size_t)c * Vh + idx];
+    if (A.b != 0.0) { o.x = fma(A.b, bxv.x, o.x); o.y = fma(A.b, bxv.y, o.y); }
+    if (A.a != 0.0) {
+      const double2 ro = A.r[(size_t)c * Vh + idx];
+      o.x = fma(A.a, ro.x, o.x); o.y = fma(A.a, ro.y, o.y);
+    }
+    o.x *= A.post; o.y *= A.post;
+    A.r[(size_t)c * Vh + idx] = o;
+    if (DOT) dot += bxv.x * o.x + bxv.y * o.y;
+  }
+  return dot;
+}
+
 template <int NL, bool DOT>
 __global__ void __launch_bounds__(SWEEP_BLOCK) k_sweep(const SweepArgs A) {
   const int idx = blockIdx.x * SWEEP_BLOCK + threadIdx.x;
@@ -60,19 +82,15 @@ __global__ void __launch_bounds__(SWEEP_BLOCK) k_sweep(const SweepArgs A) {
         }
       }
     }
+    dot = site_epilogue<DOT>(A, idx, acc);
+    if (DOT && A.comm_mask) {
+      // multi-rank: sites with an off-rank hop are finished (and counted) by k_exterior
+      constexpr int dep = (NL == 2) ? 3 : 1;
+      bool bnd = false;
 #pragma unroll
-    for (int c = 0; c < 3; c++) {
-      double2 o = {A.sgn * acc[c].x, A.sgn * acc[c].y};
-      double2 bxv = {0, 0};
-      if (A.b != 0.0 || DOT) bxv = A.bx[(size_t)c * Vh + idx];
-      if (A.b != 0.0) { o.x = fma(A.b, bxv.x, o.x); o.y = fma(A.b, bxv.y, o.y); }
-      if (A.a != 0.0) {
-        const double2 ro = A.r[(size_t)c * Vh + idx];
-        o.x = fma(A.a, ro.x, o.x); o.y = fma(A.a, ro.y, o.y);
-      }
-      o.x *= A.post; o.y *= A.post;
-      A.r[(size_t)c * Vh + idx] = o;
-      if (DOT) dot += bxv.x * o.x + bxv.y * o.y;
+      for (int mu = 0; mu < 4; mu++)
+        if ((A.comm_mask >> mu) & 1) bnd = bnd || s.x[mu] < dep || s.x[mu] >= A.X[mu] - dep;
+      if (bnd) dot = 0.0;
     }
   }
   if (DOT) grid_reduce<SWEEP_BLOCK>(dot, A.partials, A.ticket, A.result);
@@ -107,19 +125,17 @@ struct ExtArgs {
   int wait;      // p2p: spin on the neighbours' flags before touching the ghosts
   int* err;
   unsigned long long timeout_ns;
+  // DOT epilogue: *result = sum over ranks of (*interior + sum over my sites Re<bx, r_new>)
+  const double2* bx;
+  double* partials;
+  unsigned int* ticket;
+  double* result;
+  const double* interior;
+  XRank* xr;
 };
 
-template <int NL>
-__global__ void __launch_bounds__(SWEEP_BLOCK) k_exterior(const ExtArgs A) {
-  if (A.wait) {
-    if ((int)threadIdx.x < 2 * A.ndir) {
-      const ExtDir& D = A.d[threadIdx.x >> 1];
-      wait_flag((threadIdx.x & 1) ? D.flag_b : D.flag_f, A.seq, A.err, A.timeout_ns);
-    }
-    __syncthreads();
-  }
-  const int t = blockIdx.x * SWEEP_BLOCK + threadIdx.x;
-  if (t >= A.reg[A.nreg - 1].end) return;
+// thread t of the boundary enumeration -> local coordinates of its site (parity A.parity)
+__device__ __forceinline__ void region_site(const ExtArgs& A, int t, int (&x)[4]) {
   int ri = 0, base = 0;
 #pragma unroll
   for (int i = 0; i < 3; i++)
@@ -137,12 +153,27 @@ __global__ void __launch_bounds__(SWEEP_BLOCK) k_exterior(const ExtArgs A) {
   for (int d = 1; d < 4; d++) par += id[d] + (R.type[d] == 2 ? A.dep[d] : 0);
   par += (R.type[0] == 2 ? A.dep[0] : 0);
   id[0] = 2 * i0h + (par & 1);
-  int x[4];
 #pragma unroll
   for (int d = 0; d < 4; d++) {
     const int i = id[d];
     x[d] = (R.type[d] == 0) ? i : (R.type[d] == 2) ? A.dep[d] + i : (i < A.dep[d] ? i : A.X[d] - A.nbv[d] + i);
   }
+}
+
+template <int NL, bool DOT>
+__global__ void __launch_bounds__(SWEEP_BLOCK) k_exterior(const ExtArgs A) {
+  if (A.wait) {
+    if ((int)threadIdx.x < 2 * A.ndir) {
+      const ExtDir& D = A.d[threadIdx.x >> 1];
+      wait_flag((threadIdx.x & 1) ? D.flag_b : D.flag_f, A.seq, A.err, A.timeout_ns);
+    }
+    __syncthreads();
+  }
+  const int t = blockIdx.x * SWEEP_BLOCK + threadIdx.x;
+  double dot = 0.0;
+  if (t < A.reg[A.nreg - 1].end) {
+  int x[4];
+  region_site(A, t, x);
   const int lex = ((x[3] * A.X[2] + x[2]) * A.X[1] + x[1]) * A.X[0] + x[0];
   const int idx = lex >> 1, Vh = A.Vh;
   double2 acc[3] = {{0, 0}, {0, 0}, {0, 0}};
@@ -178,7 +209,10 @@ __global__ void __launch_bounds__(SWEEP_BLOCK) k_exterior(const ExtArgs A) {
     double2 o = A.r[(size_t)c * Vh + idx];
     o.x = fma(A.scale, acc[c].x, o.x); o.y = fma(A.scale, acc[c].y, o.y);
     A.r[(size_t)c * Vh + idx] = o;
+    if (DOT) { const double2 bxv = A.bx[(size_t)c * Vh + idx]; dot += bxv.x * o.x + bxv.y * o.y; }
   }
+  }
+  if (DOT) grid_reduce<SWEEP_BLOCK>(dot, A.partials, A.ticket, A.result, A.xr, A.interior);
 }
 
 // ---- face packing: one launch for all split directions --------------------------------------
@@ -201,56 +235,183 @@ struct PackArgs {
   unsigned int* ticket;   // nullptr: no signalling
 };
 
+// one work item of the packing (t < A.d[ndir-1].end)
 template <int NL>
-__global__ void __launch_bounds__(SWEEP_BLOCK) k_pack(const PackArgs A) {
-  const int t = blockIdx.x * SWEEP_BLOCK + threadIdx.x;
-  if (t < A.d[A.ndir - 1].end) {
-    int di = 0, base = 0;
+__device__ __forceinline__ void pack_item(const PackArgs& A, int t) {
+  int di = 0, base = 0;
 #pragma unroll
-    for (int i = 0; i < 3; i++)
-      if (i + 1 < A.ndir && t >= A.d[i].end) { di = i + 1; base = A.d[i].end; }
-    const PackDir& P = A.d[di];
-    const int tt = t - base;
-    const int nf = P.depth * P.faceh;        // forward-psi items
-    const int mu = P.mu, Xm = A.X[mu], Vh = A.Vh;
-    if (tt < nf) {
-      const int l = tt / P.faceh, fidx = tt - l * P.faceh;
-      const Site s = site_from_face(fidx, mu, l, A.q, A.X);
-      const int idx = s.lex >> 1;
+  for (int i = 0; i < 3; i++)
+    if (i + 1 < A.ndir && t >= A.d[i].end) { di = i + 1; base = A.d[i].end; }
+  const PackDir& P = A.d[di];
+  const int tt = t - base;
+  const int nf = P.depth * P.faceh;        // forward-psi items
+  const int mu = P.mu, Xm = A.X[mu], Vh = A.Vh;
+  if (tt < nf) {
+    const int l = tt / P.faceh, fidx = tt - l * P.faceh;
+    const Site s = site_from_face(fidx, mu, l, A.q, A.X);
+    const int idx = s.lex >> 1;
 #pragma unroll
-      for (int c = 0; c < 3; c++) P.out_f[(size_t)c * nf + tt] = A.x[(size_t)c * Vh + idx];
-    } else {
-      int tb = tt - nf;
-      int j = 0, h = 1;
-      if (NL == 2 && tb >= P.faceh) { j = 1; h = 3; tb -= P.faceh; }
-      const int jl = tb / P.faceh, fidx = tb - jl * P.faceh;
-      const Site s = site_from_face(fidx, mu, Xm - h + jl, A.q, A.X);
-      const int idx = s.lex >> 1;
-      double2 U[9], v[3], acc[3] = {{0, 0}, {0, 0}, {0, 0}};
-      load_link(U, link_ptr(A.u, mu * NL + j, A.q, Vh, idx), Vh);
-      load_vec(v, A.x + idx, Vh);
-      mv_adj_sub(acc, U, v);
-      double2* ob = (j == 0) ? P.out_b0 : P.out_b1;
+    for (int c = 0; c < 3; c++) P.out_f[(size_t)c * nf + tt] = A.x[(size_t)c * Vh + idx];
+  } else {
+    int tb = tt - nf;
+    int j = 0, h = 1;
+    if (NL == 2 && tb >= P.faceh) { j = 1; h = 3; tb -= P.faceh; }
+    const int jl = tb / P.faceh, fidx = tb - jl * P.faceh;
+    const Site s = site_from_face(fidx, mu, Xm - h + jl, A.q, A.X);
+    const int idx = s.lex >> 1;
+    double2 U[9], v[3], acc[3] = {{0, 0}, {0, 0}, {0, 0}};
+    load_link(U, link_ptr(A.u, mu * NL + j, A.q, Vh, idx), Vh);
+    load_vec(v, A.x + idx, Vh);
+    mv_adj_sub(acc, U, v);
+    double2* ob = (j == 0) ? P.out_b0 : P.out_b1;
 #pragma unroll
-      for (int c = 0; c < 3; c++)
-        ob[(size_t)c * h * P.faceh + tb] = make_double2(-acc[c].x, -acc[c].y);
-    }
+    for (int c = 0; c < 3; c++)
+      ob[(size_t)c * h * P.faceh + tb] = make_double2(-acc[c].x, -acc[c].y);
   }
-  if (A.ticket) {
-    __threadfence_system();
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      const unsigned int tk = atomicAdd(A.ticket, 1u);
-      if (tk == gridDim.x - 1) {
-        *A.ticket = 0u;
-        __threadfence_system();
-        for (int i = 0; i < A.ndir; i++) {
-          st_release_sys(A.d[i].flag_f, A.seq);
-          st_release_sys(A.d[i].flag_b, A.seq);
-        }
+}
+
+// Called by every thread of every packing block after its stores: the last block to arrive
+// raises the neighbours' flags (release at system scope, after the data of all blocks).
+__device__ __forceinline__ void pack_signal(const PackArgs& A, unsigned int nblocks) {
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int tk = atomicAdd(A.ticket, 1u);
+    if (tk == nblocks - 1) {
+      *A.ticket = 0u;
+      __threadfence_system();
+      for (int i = 0; i < A.ndir; i++) {
+        st_release_sys(A.d[i].flag_f, A.seq);
+        st_release_sys(A.d[i].flag_b, A.seq);
       }
     }
   }
+}
+
+template <int NL>
+__global__ void __launch_bounds__(SWEEP_BLOCK) k_pack(const PackArgs A) {
+  const int t = blockIdx.x * SWEEP_BLOCK + threadIdx.x;
+  if (t < A.d[A.ndir - 1].end) pack_item<NL>(A, t);
+  if (A.ticket) pack_signal(A, gridDim.x);
+}
+
+// ---- the whole multi-rank sweep as ONE kernel (peer-memory path) -----------------------------
+// Blocks take one of three roles by index, in the order the hardware dispatches them:
+//   [0, npack)          pack the faces straight into the neighbours' windows over NVLink and,
+//                       when the last of them is done, raise the neighbours' flags;
+//   [npack, +nint)      all sites WITHOUT an off-rank hop: the plain stencil (the transfer is in
+//                       flight meanwhile);
+//   [.., +next)         the boundary sites: wait for the neighbours' flags, then the full stencil
+//                       with ghost data substituted for off-rank hops.
+// Pack blocks never wait, boundary blocks wait only on REMOTE pack blocks: no cycle.  The
+// Re<bx, r> reduction (and its sum over ranks) closes the same kernel, so a CG iteration on
+// N GPUs launches exactly the kernels it launches on one.
+struct FusedArgs {
+  SweepArgs A;
+  PackArgs P;
+  ExtArgs E;
+  int npack, nint;
+};
+
+template <int NL, bool DOT>
+__global__ void __launch_bounds__(SWEEP_BLOCK, 8) k_sweep_fused(const FusedArgs F) {
+  const SweepArgs& A = F.A;
+  const int bid = blockIdx.x;
+  double dot = 0.0;
+  if (bid < F.npack) {
+    const int t = bid * SWEEP_BLOCK + threadIdx.x;
+    if (t < F.P.d[F.P.ndir - 1].end) pack_item<NL>(F.P, t);
+    pack_signal(F.P, F.npack);
+  } else {
+    const ExtArgs& E = F.E;
+    const bool tail = bid >= F.npack + F.nint;
+    const int Vh = A.Vh, p = A.parity, q = 1 - A.parity;
+    constexpr int dep = (NL == 2) ? 3 : 1;
+    bool active;
+    Site s;
+    if (!tail) {
+      const int idx0 = (bid - F.npack) * SWEEP_BLOCK + threadIdx.x;
+      active = idx0 < Vh;
+      if (active) {
+        s = site_from_idx(idx0, p, A.X);
+#pragma unroll
+        for (int mu = 0; mu < 4; mu++)
+          if ((A.comm_mask >> mu) & 1) active = active && s.x[mu] >= dep && s.x[mu] < A.X[mu] - dep;
+      }
+    } else {
+      if ((int)threadIdx.x < 2 * E.ndir) {
+        const ExtDir& D = E.d[threadIdx.x >> 1];
+        wait_flag((threadIdx.x & 1) ? D.flag_b : D.flag_f, E.seq, E.err, E.timeout_ns);
+      }
+      __syncthreads();
+      const int t = (bid - F.npack - F.nint) * SWEEP_BLOCK + threadIdx.x;
+      active = t < E.reg[E.nreg - 1].end;
+      if (active) {
+        region_site(E, t, s.x);
+        s.lex = ((s.x[3] * A.X[2] + s.x[2]) * A.X[1] + s.x[1]) * A.X[0] + s.x[0];
+      }
+    }
+    if (active) {
+      const int idx = s.lex >> 1;
+      double2 acc[3] = {{0, 0}, {0, 0}, {0, 0}};
+      int di = 0;   // index into E.d of the current split direction (tail only)
+#pragma unroll
+      for (int mu = 0; mu < 4; mu++) {
+        const int st = stride_of(mu, A.X);
+        const int Xm = A.X[mu];
+        const bool split = (A.comm_mask >> mu) & 1;
+        const bool ghost = tail && split && (s.x[mu] < dep || s.x[mu] >= Xm - dep);
+        int fidx = 0;
+        if (ghost) fidx = face_lex(s.x, mu, A.X) >> 1;
+#pragma unroll
+        for (int j = 0; j < NL; j++) {
+          const int h = (j == 0) ? 1 : 3;
+          const int k = mu * NL + j;
+          {  // forward hop
+            const int y = s.x[mu] + h;
+            int ln = s.lex + h * st;
+            const bool off = y >= Xm;
+            if (off) ln -= Xm * st;
+            double2 U[9], v[3];
+            load_link(U, link_ptr(A.u, k, p, Vh, idx), Vh);
+            if (off && split) {
+              const ExtDir& D = E.d[di];
+#pragma unroll
+              for (int c = 0; c < 3; c++)
+                v[c] = __ldcg(D.ghost_f + (size_t)c * dep * D.faceh + (size_t)(y - Xm) * D.faceh + fidx);
+            } else {
+              load_vec(v, A.x + (ln >> 1), Vh);
+            }
+            mv_add(acc, U, v);
+          }
+          {  // backward hop
+            const int y = s.x[mu] - h;
+            int ln = s.lex - h * st;
+            const bool off = y < 0;
+            if (off) ln += Xm * st;
+            if (off && split) {
+              const ExtDir& D = E.d[di];
+              const double2* gb = (j == 0) ? D.ghost_b0 : D.ghost_b1;
+#pragma unroll
+              for (int c = 0; c < 3; c++) {
+                const double2 w = __ldcg(gb + (size_t)c * h * D.faceh + (size_t)s.x[mu] * D.faceh + fidx);
+                acc[c].x -= w.x; acc[c].y -= w.y;
+              }
+            } else {
+              double2 U[9], v[3];
+              const int ib = ln >> 1;
+              load_link(U, link_ptr(A.u, k, q, Vh, ib), Vh);
+              load_vec(v, A.x + ib, Vh);
+              mv_adj_sub(acc, U, v);
+            }
+          }
+        }
+        if (split) di++;
+      }
+      dot = site_epilogue<DOT>(A, idx, acc);
+    }
+  }
+  if (DOT) grid_reduce<SWEEP_BLOCK>(dot, A.partials, A.ticket, A.result, F.E.xr);
 }
 
 static inline unsigned int* win_flag(char* win, int buf, int mu, int side) {
@@ -261,9 +422,8 @@ static inline double2* win_recv(char* win, int buf, size_t cap) {
 }
 
 // Launched on `st` (the comm stream).  seq is the sweep's exchange number.
-int pack_faces(const Gauge& g, int q, const double2* x, unsigned int seq, cudaStream_t st) {
+static int fill_pack(const Gauge& g, int q, const double2* x, unsigned int seq, PackArgs& P) {
   Context& c = ctx();
-  PackArgs P;
   P.u = g.d; P.x = x;
   for (int i = 0; i < 4; i++) P.X[i] = c.g.X[i];
   P.Vh = c.g.Vh; P.q = q; P.ndir = (int)c.halo.size();
@@ -292,17 +452,27 @@ int pack_faces(const Gauge& g, int q, const double2* x, unsigned int seq, cudaSt
       D.flag_f = D.flag_b = nullptr;
     }
   }
+  return end;   // work items
+}
+
+// NCCL path: launched on `st` (the comm stream).  seq is the sweep's exchange number.
+int pack_faces(const Gauge& g, int q, const double2* x, unsigned int seq, cudaStream_t st) {
+  PackArgs P;
+  const int end = fill_pack(g, q, x, seq, P);
   const int grid = (end + SWEEP_BLOCK - 1) / SWEEP_BLOCK;
-  if (nl == 2) k_pack<2><<<grid, SWEEP_BLOCK, 0, st>>>(P);
+  if (g.nlinks == 8) k_pack<2><<<grid, SWEEP_BLOCK, 0, st>>>(P);
   else k_pack<1><<<grid, SWEEP_BLOCK, 0, st>>>(P);
   count_launch();
   QB_CUDA(cudaGetLastError());
   return 0;
 }
 
-static int exterior(const Gauge& g, int parity, double2* r, double scale) {
+// Boundary enumeration + ghost pointers of the current exchange; returns the number of sites.
+static int fill_ext(const Gauge& g, int parity, double2* r, double scale, const double2* bx,
+                    double* dot_out, const double* dot_interior, ExtArgs& E) {
   Context& c = ctx();
-  ExtArgs E;
+  E.bx = bx; E.partials = c.d_partials; E.ticket = c.d_ticket; E.result = dot_out;
+  E.interior = dot_interior; E.xr = xrank();
   E.u = g.d; E.r = r; E.scale = scale;
   for (int i = 0; i < 4; i++) { E.X[i] = c.g.X[i]; E.dep[i] = 0; E.nbv[i] = 0; }
   E.Vh = c.g.Vh; E.parity = parity; E.ndir = (int)c.halo.size();
@@ -338,10 +508,24 @@ static int exterior(const Gauge& g, int parity, double2* r, double scale) {
     E.reg[nreg++] = R;
   }
   E.nreg = nreg;
-  if (nreg == 0) return 0;
+  return end;
+}
+
+// NCCL path.  dot_out != nullptr: also completes Re<bx, r> (interior part already in *dot_interior).
+static int exterior(const Gauge& g, int parity, double2* r, double scale, const double2* bx,
+                    double* dot_out, const double* dot_interior) {
+  Context& c = ctx();
+  ExtArgs E;
+  const int end = fill_ext(g, parity, r, scale, bx, dot_out, dot_interior, E);
+  if (end == 0) return 0;
   const int grid = (end + SWEEP_BLOCK - 1) / SWEEP_BLOCK;
-  if (g.nlinks == 8) k_exterior<2><<<grid, SWEEP_BLOCK, 0, c.stream>>>(E);
-  else k_exterior<1><<<grid, SWEEP_BLOCK, 0, c.stream>>>(E);
+  if (g.nlinks == 8) {
+    if (dot_out) k_exterior<2, true><<<grid, SWEEP_BLOCK, 0, c.stream>>>(E);
+    else k_exterior<2, false><<<grid, SWEEP_BLOCK, 0, c.stream>>>(E);
+  } else {
+    if (dot_out) k_exterior<1, true><<<grid, SWEEP_BLOCK, 0, c.stream>>>(E);
+    else k_exterior<1, false><<<grid, SWEEP_BLOCK, 0, c.stream>>>(E);
+  }
   count_launch();
   QB_CUDA(cudaGetLastError());
   return 0;
@@ -352,7 +536,6 @@ int sweep(const Gauge& g, int parity, double2* r, const double2* x, const double
   Context& c = ctx();
   if (!g.loaded) return fail("sweep: gauge not loaded");
   const bool multi = c.g.comm_mask != 0;
-  if (multi) QB_CHECK(halo_start(g, parity, x));
 
   SweepArgs A;
   A.u = g.d; A.x = x; A.r = r; A.bx = bx ? bx : r;
@@ -361,7 +544,35 @@ int sweep(const Gauge& g, int parity, double2* r, const double2* x, const double
   A.Vh = c.g.Vh; A.parity = parity; A.comm_mask = c.g.comm_mask;
   A.partials = c.d_partials; A.ticket = c.d_ticket; A.result = dot_out;
   const int grid = (c.g.Vh + SWEEP_BLOCK - 1) / SWEEP_BLOCK;
-  const bool fused_dot = dot_out && !multi;
+  const bool fused_dot = dot_out != nullptr;
+
+  if (multi && c.p2p) {
+    // peer-memory path: pack + interior + boundary (+ dot over ranks) in one launch
+    QB_CHECK(halo_begin(g));
+    FusedArgs F;
+    F.A = A;
+    const int npk = fill_pack(g, 1 - parity, x, c.halo_seq, F.P);
+    const int nbd = fill_ext(g, parity, r, post * sgn, bx, dot_out, nullptr, F.E);
+    F.npack = (npk + SWEEP_BLOCK - 1) / SWEEP_BLOCK;
+    F.nint = grid;
+    const int total = F.npack + F.nint + (nbd + SWEEP_BLOCK - 1) / SWEEP_BLOCK;
+    if ((size_t)total > c.npart) return fail("sweep: %d blocks exceed the %zu reduction slots", total, c.npart);
+    if (g.nlinks == 8) {
+      if (fused_dot) k_sweep_fused<2, true><<<total, SWEEP_BLOCK, 0, c.stream>>>(F);
+      else k_sweep_fused<2, false><<<total, SWEEP_BLOCK, 0, c.stream>>>(F);
+    } else {
+      if (fused_dot) k_sweep_fused<1, true><<<total, SWEEP_BLOCK, 0, c.stream>>>(F);
+      else k_sweep_fused<1, false><<<total, SWEEP_BLOCK, 0, c.stream>>>(F);
+    }
+    count_launch();
+    QB_CUDA(cudaGetLastError());
+    return 0;
+  }
+
+  if (multi) QB_CHECK(halo_start(g, parity, x));
+  // NCCL path: the interior part of the dot goes to a scratch scalar, k_exterior finishes it
+  double* dot_interior = c.d_scal + 48;
+  if (multi) A.result = dot_interior;
   if (g.nlinks == 8) {
     if (fused_dot) k_sweep<2, true><<<grid, SWEEP_BLOCK, 0, c.stream>>>(A);
     else k_sweep<2, false><<<grid, SWEEP_BLOCK, 0, c.stream>>>(A);
@@ -373,8 +584,7 @@ int sweep(const Gauge& g, int parity, double2* r, const double2* x, const double
   QB_CUDA(cudaGetLastError());
   if (multi) {
     QB_CHECK(halo_wait());
-    QB_CHECK(exterior(g, parity, r, post * sgn));
-    if (dot_out) QB_CHECK(blas_redot(bx, r, (size_t)3 * c.g.Vh, dot_out));
+    QB_CHECK(exterior(g, parity, r, post * sgn, bx, dot_out, dot_interior));
   }
   return 0;
 }

@@ -52,11 +52,50 @@ __global__ void __launch_bounds__(CB) k_cg_p(double2* __restrict__ p, const doub
   }
 }
 
-// x += alpha p ; r -= alpha Ap ; r2new = |r|^2   (cg.nim:208-213)
+// publishes the loop state to the host ring (execution j fills slot j % RING, seq written last)
+__device__ __forceinline__ void cg_publish(double* S, CgStatus* st) {
+  const long long seq = (long long)(S[S_SEQ] += 1.0);
+  CgStatus* slot = st + (seq % RING);
+  slot->itn = (long long)S[S_ITN];
+  slot->done = (long long)S[S_DONE];
+  slot->r2 = S[S_R2];
+  __threadfence_system();
+  slot->seq = seq;
+}
+
+// x += alpha p ; r -= alpha Ap ; r2new = |r|^2   (cg.nim:208-213), then -- on the thread that
+// completes the reduction -- the loop control of cg.nim:174 and the status for the host.
 __global__ void __launch_bounds__(CB) k_cg_xr(double2* __restrict__ x, double2* __restrict__ r,
                                                const double2* __restrict__ p, const double2* __restrict__ Ap,
                                                double* S, size_t n, double* partials, unsigned int* ticket,
-                                               XRank* xr) {
+                                               XRank* xr, CgStatus* st) {
+  if (S[S_DONE] != 0.0) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) cg_publish(S, st);
+    return;
+  }
+  const double alpha = S[S_R2] / S[S_PAP];
+  double s = 0.0;
+  for (size_t i = (size_t)blockIdx.x * CB + threadIdx.x; i < n; i += (size_t)gridDim.x * CB) {
+    const double2 pv = p[i], av = Ap[i];
+    double2 xv = x[i], rv = r[i];
+    xv.x = fma(alpha, pv.x, xv.x); xv.y = fma(alpha, pv.y, xv.y);
+    rv.x = fma(-alpha, av.x, rv.x); rv.y = fma(-alpha, av.y, rv.y);
+    x[i] = xv; r[i] = rv;
+    s = fma(rv.x, rv.x, s); s = fma(rv.y, rv.y, s);
+  }
+  if (grid_reduce<CB>(s, partials, ticket, S + S_R2NEW, xr)) {
+    S[S_R2OLD] = S[S_R2];
+    S[S_R2] = S[S_R2NEW];
+    S[S_ITN] += 1.0;
+    if (!(S[S_R2] > S[S_R2STOP]) || S[S_ITN] >= S[S_MAXITS]) S[S_DONE] = 1.0;
+    cg_publish(S, st);
+  }
+}
+
+// NCCL path: update without loop control (ncclAllReduce of r2new follows), then k_cg_step
+__global__ void __launch_bounds__(CB) k_cg_xr_nostep(double2* __restrict__ x, double2* __restrict__ r,
+                                                      const double2* __restrict__ p, const double2* __restrict__ Ap,
+                                                      double* S, size_t n, double* partials, unsigned int* ticket) {
   if (S[S_DONE] != 0.0) return;
   const double alpha = S[S_R2] / S[S_PAP];
   double s = 0.0;
@@ -68,10 +107,8 @@ __global__ void __launch_bounds__(CB) k_cg_xr(double2* __restrict__ x, double2* 
     x[i] = xv; r[i] = rv;
     s = fma(rv.x, rv.x, s); s = fma(rv.y, rv.y, s);
   }
-  grid_reduce<CB>(s, partials, ticket, S + S_R2NEW, xr);
+  grid_reduce<CB>(s, partials, ticket, S + S_R2NEW);
 }
-
-// loop control of cg.nim:174 on the device
 __global__ void k_cg_step(double* S, CgStatus* st) {
   if (S[S_DONE] == 0.0) {
     S[S_R2OLD] = S[S_R2];
@@ -79,13 +116,7 @@ __global__ void k_cg_step(double* S, CgStatus* st) {
     S[S_ITN] += 1.0;
     if (!(S[S_R2] > S[S_R2STOP]) || S[S_ITN] >= S[S_MAXITS]) S[S_DONE] = 1.0;
   }
-  const long long seq = (long long)(S[S_SEQ] += 1.0);
-  CgStatus* slot = st + (seq % RING);
-  slot->itn = (long long)S[S_ITN];
-  slot->done = (long long)S[S_DONE];
-  slot->r2 = S[S_R2];
-  __threadfence_system();
-  slot->seq = seq;
+  cg_publish(S, st);
 }
 
 // after the initial residual: r2stop = r2req*b2 (cg.nim:155), loop entry test (:163)
@@ -184,11 +215,17 @@ int cg_xx(const Gauge& g, int parity, double2* x, const double2* b, double m2, d
     count_launch();
     QB_CHECK(apply_xx(g, parity, w_Ap, w_p, m2, S + S_PAP));
     QB_CHECK(allreduce_scalars(S + S_PAP, 1));
-    k_cg_xr<<<grid, CB, 0, c.stream>>>(x, w_r, w_p, w_Ap, S, n, c.d_partials, c.d_ticket, xrank());
-    count_launch();
-    QB_CHECK(allreduce_scalars(S + S_R2NEW, 1));
-    k_cg_step<<<1, 1, 0, c.stream>>>(S, d_status);
-    count_launch();
+    if (c.g.nranks > 1 && !c.p2p) {
+      // NCCL path: the sum over ranks sits between the update and the loop control
+      k_cg_xr_nostep<<<grid, CB, 0, c.stream>>>(x, w_r, w_p, w_Ap, S, n, c.d_partials, c.d_ticket);
+      count_launch();
+      QB_CHECK(allreduce_scalars(S + S_R2NEW, 1));
+      k_cg_step<<<1, 1, 0, c.stream>>>(S, d_status);
+      count_launch();
+    } else {
+      k_cg_xr<<<grid, CB, 0, c.stream>>>(x, w_r, w_p, w_Ap, S, n, c.d_partials, c.d_ticket, xrank(), d_status);
+      count_launch();
+    }
     launched++;
     if (launched > LAG) {
       const long long want = launched - LAG;

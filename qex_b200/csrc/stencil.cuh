@@ -129,7 +129,13 @@ __device__ __forceinline__ void wait_flag(const unsigned int* flag, unsigned int
   if (ld_acquire_sys(flag) == want) return;
   const unsigned long long t0 = globaltimer_ns();
   while (ld_acquire_sys(flag) != want) {
-    if (globaltimer_ns() - t0 > timeout_ns) { *err = 1; __threadfence_system(); break; }
+    if (globaltimer_ns() - t0 > timeout_ns) {
+      // diagnostics for the host: what was awaited, what was there, who waited
+      err[1] = (int)want; err[2] = (int)ld_acquire_sys(flag); err[3] = (int)((blockIdx.x << 4) | (threadIdx.x & 15));
+      err[0] = 1;
+      __threadfence_system();
+      break;
+    }
   }
 }
 
@@ -170,11 +176,14 @@ __device__ __forceinline__ double xrank_sum(XRank* xr, double v) {
   return s;
 }
 
-// Deterministic grid reduction: per-block partial -> last block sums in fixed order; with
-// xr != nullptr the last block also sums over the ranks (xrank_sum).
+// Deterministic grid reduction: per-block partial -> last block sums in fixed order; *addend
+// (a partial sum left by an earlier kernel) is added next; with xr != nullptr the last block
+// also sums over the ranks (xrank_sum).  Returns true on the one thread that stored *result
+// (it runs after every block has finished its loads, so it may update loop-control scalars).
 template <int BLOCK>
-__device__ __forceinline__ void grid_reduce(double v, double* partials, unsigned int* ticket,
-                                            double* result, XRank* xr = nullptr) {
+__device__ __forceinline__ bool grid_reduce(double v, double* partials, unsigned int* ticket,
+                                            double* result, XRank* xr = nullptr,
+                                            const double* addend = nullptr) {
   __shared__ double sm[BLOCK / 32];
   __shared__ bool last;
 #pragma unroll
@@ -208,13 +217,16 @@ __device__ __forceinline__ void grid_reduce(double v, double* partials, unsigned
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
       s = __shfl_sync(0xffffffffu, s, 0);
+      if (addend) s += *addend;
       if (xr) s = xrank_sum(xr, s);
       if (lane == 0) {
         *result = s;
         *ticket = 0u;
+        return true;
       }
     }
   }
+  return false;
 }
 
 }  // namespace qb
