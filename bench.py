@@ -45,20 +45,52 @@ def measured_peak():
 
 
 class ClockSampler:
+    """SM clock and throttle reasons DURING the timed region: NVML polled every ~5 ms in a thread
+    (nvidia-smi subprocesses are too slow for a 0.1 s region); falls back to nvidia-smi."""
     Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
 
     def __init__(self, dev):
-        self.dev, self.rows, self.stop, self.t = dev, [], False, None
+        self.dev, self.sm, self.mx, self.reasons, self.stop, self.t = dev, [], 0.0, set(), False, None
+        self.nv = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(dev)
+            self.mx = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self.nv = None
+
+    def _sample_nvml(self):
+        nv = self.nv
+        self.sm.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+        r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h) if hasattr(nv, "nvmlDeviceGetCurrentClocksEventReasons") \
+            else nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+        for name, bit in (("hw_slowdown", 0x8), ("sw_power_cap", 0x4), ("sw_thermal_slowdown", 0x20),
+                          ("hw_thermal_slowdown", 0x40)):
+            if r & bit:
+                self.reasons.add(name)
+
+    def _sample_smi(self):
+        o = subprocess.run(["nvidia-smi", "-i", str(self.dev), "--query-gpu=" + self.Q,
+                            "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+        r = [t.strip() for t in o.strip().split(",")]
+        self.sm.append(float(r[0]))
+        self.mx = max(self.mx, float(r[1]))
+        for n, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], r[3:7]):
+            if v.lower().startswith("active"):
+                self.reasons.add(n)
 
     def _run(self):
         while not self.stop:
             try:
-                o = subprocess.run(["nvidia-smi", "-i", str(self.dev), "--query-gpu=" + self.Q,
-                                    "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
-                self.rows.append([t.strip() for t in o.strip().split(",")])
+                if self.nv:
+                    self._sample_nvml()
+                else:
+                    self._sample_smi()
             except Exception:
                 pass
-            time.sleep(0.1)
+            time.sleep(0.005 if self.nv else 0.1)
 
     def __enter__(self):
         self.t = threading.Thread(target=self._run, daemon=True)
@@ -70,19 +102,9 @@ class ClockSampler:
         self.t.join(timeout=6)
 
     def summary(self):
-        sm, mx, reasons = [], 0.0, set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
-            try:
-                sm.append(float(r[0]))
-                mx = max(mx, float(r[1]))
-                for n, v in zip(names, r[3:7]):
-                    if v.lower().startswith("active"):
-                        reasons.add(n)
-            except Exception:
-                pass
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+        return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": self.mx or None,
+                "reasons": sorted(self.reasons), "samples": len(self.sm),
+                "source": "nvml" if self.nv else "nvidia-smi"}
 
 
 def dist_env():
@@ -191,7 +213,6 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    out = {}
     results = {}
     for nlinks in ((4, 8) if not args.naive_only else (4,)):
         links = random_su3_links(nsites, 4, seed=1 + 17 * rank)
@@ -210,68 +231,92 @@ def run_ours(args):
         hx = torch.zeros_like(hb).pin_memory()
         b_np, x_np = hb.numpy(), hx.numpy()
         fb, fx = qb.DeviceField(b_np), qb.DeviceField()
+        # link storage modes: the requested one first (headline), then the 18-real form.  For the
+        # fat+Naik set only the Naik class is compressed (1812): real HISQ fat links are not unitary.
+        modes = [18] if args.recon == 18 else ([12, 18] if nlinks == 4 else [1812, 18])
+        for mode in modes:
+            got_rc, dev = s.recon(mode)
+            nclass = nlinks // 4
+            bytes_site = sum(8 * (96 if got_rc[j] == 12 else 144) for j in range(nclass)) + 96
+            key = (nlinks, mode)
 
-        # ---- value: K solves, source resident in HBM --------------------------------
-        def one_solve():
-            sp = qb.SolverParams(r2req=R2REQ, maxits=20000)
-            s.dev_solveXX(fx, fb, MASS, sp, parEven=True)
-            return sp
-        for _ in range(args.warmup):
-            sp = one_solve()
-        barrier()
-        qb.launch_count(reset=True)
-        with ClockSampler(local_rank) as cs:
-            qb.timer_start()
-            for _ in range(args.steps):
+            # ---- value: K solves, source resident in HBM --------------------------------
+            def one_solve():
+                sp = qb.SolverParams(r2req=R2REQ, maxits=20000)
+                s.dev_solveXX(fx, fb, MASS, sp, parEven=True)
+                return sp
+            for _ in range(args.warmup):
                 sp = one_solve()
-            ms = qb.timer_stop()
-        barrier()
-        launches = qb.launch_count()
-        ms = maxreduce(ms)
-        iters = sp.iterations
-        neven_global = neven * world
-        flops_step = (nlinks * 4 * 72 + 60) * neven_global * iters
-        gflops = 1e-9 * flops_step * args.steps / (1e-3 * ms)
+            barrier()
+            qb.launch_count(reset=True)
+            with ClockSampler(local_rank) as cs:
+                qb.timer_start()
+                for _ in range(args.steps):
+                    sp = one_solve()
+                ms = qb.timer_stop()
+            barrier()
+            launches = qb.launch_count()
+            ms = maxreduce(ms)
+            iters = sp.iterations
+            neven_global = neven * world
+            flops_step = (nlinks * 4 * 72 + 60) * neven_global * iters
+            gflops = 1e-9 * flops_step * args.steps / (1e-3 * ms)
 
-        # ---- e2e: same solve through the host-buffer C ABI -------------------------
-        for _ in range(max(1, args.warmup // 2)):
-            spe = qb.SolverParams(r2req=R2REQ, maxits=20000)
-            s.solveXX(x_np, b_np, MASS, spe, parEven=True)
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(args.steps):
-            spe = qb.SolverParams(r2req=R2REQ, maxits=20000)
-            s.solveXX(x_np, b_np, MASS, spe, parEven=True)
-        barrier()
-        e2e_s = maxreduce(time.perf_counter() - t0)
-        e2e_gflops = 1e-9 * (nlinks * 4 * 72 + 60) * neven_global * spe.iterations * args.steps / e2e_s
+            # ---- e2e: same solve through the host-buffer C ABI -------------------------
+            for _ in range(max(1, args.warmup // 2)):
+                spe = qb.SolverParams(r2req=R2REQ, maxits=20000)
+                s.solveXX(x_np, b_np, MASS, spe, parEven=True)
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(args.steps):
+                spe = qb.SolverParams(r2req=R2REQ, maxits=20000)
+                s.solveXX(x_np, b_np, MASS, spe, parEven=True)
+            barrier()
+            e2e_s = maxreduce(time.perf_counter() - t0)
+            e2e_gflops = 1e-9 * (nlinks * 4 * 72 + 60) * neven_global * spe.iterations * args.steps / e2e_s
 
-        # ---- roofline of the dominant kernel: one parity sweep ---------------------
-        nrep = args.sweeps
-        for _ in range(10):
-            s.dev_stagD2(0, fx, fb, 0.0, 0.0)
-            s.dev_stagD2(1, fx, fb, 0.0, 0.0)
-        barrier()
-        qb.timer_start()
-        for _ in range(nrep // 2):
-            s.dev_stagD2(0, fx, fb, 0.0, 0.0)
-            s.dev_stagD2(1, fx, fb, 0.0, 0.0)
-        sw_ms = maxreduce(qb.timer_stop()) / (2 * (nrep // 2))
-        barrier()
-        achieved = neven * BYTES_PER_SITE[nlinks] / (1e-3 * sw_ms) * 1e-9
-        results[nlinks] = {
-            "gflops": gflops, "ms_per_step": ms / args.steps, "iterations": iters, "r2": sp.r2,
-            "launches": launches, "clocks": cs.summary(),
-            "e2e_gflops": e2e_gflops, "e2e_ms_per_step": 1e3 * e2e_s / args.steps,
-            "sweep_ms": sw_ms, "sweep_gbs": achieved, "sweep_frac": achieved / peak,
-            "sweep_gflops": 1e-9 * neven * FLOPS_PER_SITE[nlinks] / (1e-3 * sw_ms),
-            "cg_iter_ms": ms / args.steps / max(1, iters),
-        }
+            # ---- roofline of the dominant kernel: one parity sweep ---------------------
+            nrep = args.sweeps
+            for _ in range(10):
+                s.dev_stagD2(0, fx, fb, 0.0, 0.0)
+                s.dev_stagD2(1, fx, fb, 0.0, 0.0)
+            barrier()
+            qb.timer_start()
+            for _ in range(nrep // 2):
+                s.dev_stagD2(0, fx, fb, 0.0, 0.0)
+                s.dev_stagD2(1, fx, fb, 0.0, 0.0)
+            sw_ms = maxreduce(qb.timer_stop()) / (2 * (nrep // 2))
+            barrier()
+            achieved = neven * bytes_site / (1e-3 * sw_ms) * 1e-9
+            cg_bytes = 2 * bytes_site + 48 + 432      # 2 sweeps + 4m^2 x read + fused BLAS-1
+            results[key] = {
+                "gflops": gflops, "ms_per_step": ms / args.steps, "iterations": iters, "r2": sp.r2,
+                "launches": launches, "clocks": cs.summary(), "recon": got_rc[:nclass], "recon_dev": dev[:nclass],
+                "e2e_gflops": e2e_gflops, "e2e_ms_per_step": 1e3 * e2e_s / args.steps,
+                "bytes_site": bytes_site, "sweep_ms": sw_ms, "sweep_gbs": achieved, "sweep_frac": achieved / peak,
+                "sweep_gflops": 1e-9 * neven * FLOPS_PER_SITE[nlinks] / (1e-3 * sw_ms),
+                "cg_iter_ms": ms / args.steps / max(1, iters),
+                "cg_iter_gbs": 1e-9 * neven * cg_bytes / (1e-3 * ms / args.steps / max(1, iters)),
+            }
         fb.free()
         fx.free()
         s.free()
 
-    r = results[4]
+    def kernel_name(nlinks, rc):
+        return "k_sweep%s<NL=%d, links %s real>" % ("_fused" if world > 1 and args.transport == "p2p" else "", nlinks // 4,
+                                                     "/".join(str(t) for t in rc))
+
+    def roof(rr, nlinks):
+        tr = ncu_traffic(nlinks, rr["recon"]) if world == 1 else None
+        return {"bound": "hbm", "kernel": kernel_name(nlinks, rr["recon"]) + " (one parity sweep of the Dslash)",
+                "achieved": rr["sweep_gbs"], "peak": peak, "peak_source": peak_src, "unit": "GB/s",
+                "frac": rr["sweep_frac"], "traffic": tr, "bytes_per_site": rr["bytes_site"],
+                "algorithmic_bytes_per_launch": rr["bytes_site"] * neven, "ms_per_launch": rr["sweep_ms"],
+                "gflops": rr["sweep_gflops"], "cg_iteration_gbs": rr["cg_iter_gbs"],
+                "cg_iteration_frac": rr["cg_iter_gbs"] / peak}
+
+    head_mode = 18 if args.recon == 18 else 12
+    r = results[(4, head_mode)]
     line = {
         "metric": "staggered CG solver throughput (Dslash GFLOP/s, QEX flop model)",
         "value": r["gflops"], "unit": "GFLOP/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -279,27 +324,27 @@ def run_ours(args):
         "dtype": "f64", "data": "synthetic",
         "config": {"workload": "%s naive staggered even-even CG to r2req=1e-8, m=0.1, fp64, random SU(3) "
                                "(BASELINE configs[1]; 32^4 per GPU)" % "x".join(map(str, lat_shape)),
-                   "rankgeom": list(rankgeom), "transport": (args.transport if world > 1 else "none"), "cg_iterations": r["iterations"],
-                   "l2": "links (604 MB per sweep set) exceed the 126 MB L2; CG vectors (25 MB each) are L2-resident by design",
+                   "rankgeom": list(rankgeom), "transport": (args.transport if world > 1 else "none"),
+                   "link_storage": "%s-real" % "/".join(str(t) for t in r["recon"]), "cg_iterations": r["iterations"],
+                   "l2": "links (403-604 MB per sweep) exceed the 126 MB L2; CG vectors (25 MB each) are L2-resident by design",
                    "time_to_solution_ms": r["ms_per_step"]},
         "e2e": {"value": r["e2e_gflops"], "unit": "GFLOP/s", "h2d_bytes_per_step": int(nsites * 48),
                 "d2h_bytes_per_step": int(nsites * 48), "ms_per_step": r["e2e_ms_per_step"]},
         "gpu_launches": r["launches"],
         "clocks": r["clocks"],
-        "roofline": {"bound": "hbm", "kernel": "k_sweep<1,false> (naive parity sweep)", "achieved": r["sweep_gbs"],
-                     "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": r["sweep_frac"], "traffic": None,
-                     "bytes_per_site": BYTES_PER_SITE[4], "ms_per_launch": r["sweep_ms"],
-                     "gflops": r["sweep_gflops"]},
+        "roofline": roof(r, 4),
     }
-    if 8 in results:
-        h = results[8]
-        line["variants"] = {"hisq_fat_naik": {
-            "workload": "same lattice, fat + 0.1*Naik links (benchStagProp.nim:84-92)",
-            "cg_gflops": h["gflops"], "time_to_solution_ms": h["ms_per_step"], "cg_iterations": h["iterations"],
-            "e2e_gflops": h["e2e_gflops"],
-            "roofline": {"bound": "hbm", "kernel": "k_sweep<2,false>", "achieved": h["sweep_gbs"], "peak": peak,
-                         "unit": "GB/s", "frac": h["sweep_frac"], "bytes_per_site": BYTES_PER_SITE[8],
-                         "ms_per_launch": h["sweep_ms"], "gflops": h["sweep_gflops"]}}}
+    variants = {}
+    for (nlinks, mode), rr in results.items():
+        if (nlinks, mode) == (4, head_mode):
+            continue
+        name = ("naive" if nlinks == 4 else "hisq_fat_naik") + "_links%s" % "_".join(str(t) for t in rr["recon"])
+        variants[name] = {
+            "workload": "same lattice, " + ("naive one-hop links" if nlinks == 4 else
+                                           "fat + 0.1*Naik links (benchStagProp.nim:84-92)"),
+            "cg_gflops": rr["gflops"], "time_to_solution_ms": rr["ms_per_step"], "cg_iterations": rr["iterations"],
+            "e2e_gflops": rr["e2e_gflops"], "roofline": roof(rr, nlinks)}
+    line["variants"] = variants
     if world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_reference_leg(lat_shape, 4, args.ref_solves)
     else:
@@ -309,6 +354,16 @@ def run_ours(args):
         dist.destroy_process_group()
     if rank == 0:
         print(json.dumps(line))
+
+
+def ncu_traffic(nlinks, recon):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the 32^4 parity sweep, from the
+    committed `ncu --set full` capture (profiles/ncu_traffic.json); None if that variant was not captured."""
+    p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if not os.path.exists(p):
+        return None
+    key = "nl%d_%s" % (nlinks // 4, "_".join(str(t) for t in recon))
+    return json.load(open(p)).get(key)
 
 
 def phase_on_host(links, lat_shape, rankgeom, rank):
@@ -346,6 +401,8 @@ def main():
     ap.add_argument("--sweeps", type=int, default=200, help="back-to-back parity sweeps for the roofline leg")
     ap.add_argument("--ref-solves", type=int, default=8, help="complete CPU solves in the bounded cpu_baseline sample")
     ap.add_argument("--naive-only", action="store_true")
+    ap.add_argument("--recon", type=int, default=12, choices=[12, 18],
+                    help="link storage of the headline run: 12 = rows 0,1 + rebuilt third row where the links allow it")
     ap.add_argument("--transport", default="p2p", choices=["p2p", "nccl"],
                     help="multi-GPU halo/sum transport: peer-memory NVLink stores (default) or NCCL send/recv + allreduce")
     ap.add_argument("--no-cpu", action="store_true")

@@ -101,6 +101,17 @@ int qexb200_local_sites(int* nsites, int* neven);
 int qexb200_gauge_create(int nlinks, qexb200_gauge_t* g);
 int qexb200_gauge_load(qexb200_gauge_t g, const double* const* links);
 int qexb200_gauge_destroy(qexb200_gauge_t g);
+/* Link storage the sweeps read.  want = 18: all 18 reals of every link (default).  want = 12: each
+ * link class (one-hop, three-hop) whose matrices are s*SU(3) with a single |s| -- naive links with
+ * staggered phases and BC (+-SU(3)), Naik links -- is additionally held as rows 0,1 and the third
+ * row is rebuilt in registers (96 instead of 144 bytes per link, the bandwidth lever of this
+ * HBM-bound stencil); classes that do not qualify (fat7-smeared links) stay at 18.  The library
+ * verifies the form on the device (rebuilt matrix within 2e-14 |s|) and reports per class what it
+ * uses in got[2] (12 or 18) and the measured deviation in dev[2].  want = 1812 / 1218 restricts
+ * the request to the three-hop / one-hop class (1812: fat links 18, Naik links 12 -- what a real
+ * HISQ or asqtad link set allows).  The request is sticky: it is
+ * re-applied after every qexb200_gauge_load / qexb200_gauge_rephase. */
+int qexb200_gauge_recon(qexb200_gauge_t g, int want, int got[2], double dev[2]);
 /* Staggered.rephase on the device copy: setBC then stagPhase with phases {8,9,11,0}
  * (stagD.nim:72-80,509-522; gauge/gaugeUtils.nim:124-131).  One-hop links only. */
 int qexb200_gauge_rephase(qexb200_gauge_t g);

@@ -58,6 +58,7 @@ def lib():
         L.qexb200_gauge_load.argtypes = [C.c_int, C.POINTER(dp)]
         L.qexb200_gauge_destroy.argtypes = [C.c_int]
         L.qexb200_gauge_rephase.argtypes = [C.c_int]
+        L.qexb200_gauge_recon.argtypes = [C.c_int, C.c_int, ip, dp]
         L.qexb200_stagD2.argtypes = [C.c_int, C.c_int, dp, dp, C.c_double, C.c_double]
         L.qexb200_stagD.argtypes = [C.c_int, C.c_int, dp, dp, C.c_double, C.c_double, C.c_double]
         L.qexb200_D.argtypes = [C.c_int, dp, dp, C.c_double]
@@ -287,6 +288,13 @@ class Staggered:
 
     def rephase(self):
         _ck(lib().qexb200_gauge_rephase(self.h))
+
+    def recon(self, want=12):
+        """Ask for 12-real (rows 0,1 + rebuilt third row) or 18-real link storage; returns
+        ([recon of one-hop class, recon of three-hop class], [measured deviation per class])."""
+        got, dev = (C.c_int * 2)(), (C.c_double * 2)()
+        _ck(lib().qexb200_gauge_recon(self.h, int(want), got, dev))
+        return [got[0], got[1]], [dev[0], dev[1]]
 
     def free(self):
         if self.h is not None and is_initialized():

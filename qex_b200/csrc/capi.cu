@@ -350,7 +350,7 @@ int qexb200_finalize(void) {
   if (!g_ctx.live) return 0;
   cudaStreamSynchronize(g_ctx.stream);
   cudaStreamSynchronize(g_ctx.comm_stream);
-  for (auto& kv : g_gauges) cudaFree(kv.second.d);
+  for (auto& kv : g_gauges) { cudaFree(kv.second.d); free_compressed(kv.second); }
   for (auto& kv : g_fields) cudaFree(kv.second.d);
   g_gauges.clear(); g_fields.clear();
   if (g_sw.ok) { cudaFree(g_sw.r.d); cudaFree(g_sw.y.d); cudaFree(g_sw.d.d); g_sw = SolveWork(); }
@@ -409,7 +409,18 @@ int qexb200_gauge_destroy(qexb200_gauge_t h) {
   Gauge* g; QB_CHECK(get_gauge(h, &g));
   cudaStreamSynchronize(g_ctx.stream);
   cudaFree(g->d);
+  free_compressed(*g);
   g_gauges.erase(h);
+  return 0;
+}
+int qexb200_gauge_recon(qexb200_gauge_t h, int want, int got[2], double dev[2]) {
+  QB_CHECK(need_ctx());
+  Gauge* g; QB_CHECK(get_gauge(h, &g));
+  if (want != 12 && want != 18 && want != 1812 && want != 1218) return fail("gauge_recon: want must be 12, 18, 1812 or 1218");
+  g->want12 = (want == 12) ? 3 : (want == 1812) ? 2 : (want == 1218) ? 1 : 0;
+  QB_CHECK(compress_links(*g));
+  if (got) { got[0] = g->recon[0]; got[1] = g->recon[1]; }
+  if (dev) { dev[0] = g->dev[0]; dev[1] = g->dev[1]; }
   return 0;
 }
 int qexb200_gauge_rephase(qexb200_gauge_t h) {

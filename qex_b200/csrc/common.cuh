@@ -24,9 +24,21 @@ struct Geom {
   int nranks, rank;
 };
 
+// A link set as the kernels see it.  Every link class j (0: one-hop, 1: three-hop) is held with
+// all 18 reals; a class whose links are s * SU(3) with one |s| for the whole field (naive links
+// with staggered phases, Naik links) can ALSO be held as 12 reals: rows 0 and 1, the third row is
+// rebuilt in registers as (sigma/|s|) conj(row0 x row1).  sigma = sign of det, one bit per link:
+// sgn[par][idx] bit (2 mu + j) for U_{mu,j}(s), bit 8 + (2 mu + j) for U_{mu,j}(s - h_j mu).
+struct Links {
+  const double2* u;          // [nlinks][2][9][Vh]
+  const double2* u12[2];     // per class: [4 mu][2][6][Vh] or nullptr
+  const unsigned short* sgn; // [2][Vh]
+  double inv[2];             // 1/|s| per class
+};
+
 // Arguments of one parity sweep (kernel parameter block, passed by value).
 struct SweepArgs {
-  const double2* u;   // link set base
+  Links L;            // link set
   const double2* x;   // input half field (parity 1-p): x[c*Vh + idx]
   double2* r;         // output half field (parity p)
   const double2* bx;  // half field (parity p) scaled by b, may alias r's parity of the source
@@ -161,6 +173,19 @@ struct Gauge {
   int nlinks = 0;        // 4 or 8
   double2* d = nullptr;  // [nlinks][2][9][Vh]
   bool loaded = false;
+  // 12-real compression (layout.cu compress_links)
+  int want12 = 0;                 // sticky request (bit j: class j), re-applied after every load / rephase
+  int recon[2] = {18, 18};        // what the sweeps read per link class
+  double2* d12[2] = {nullptr, nullptr};
+  unsigned short* sgn = nullptr;
+  double inv[2] = {1.0, 1.0};
+  double dev[2] = {0.0, 0.0};     // measured max |U - rebuilt U| / |s| per class (diagnostic)
+  int rc() const { return (recon[0] == 12 ? 1 : 0) | (recon[1] == 12 ? 2 : 0); }
+  Links links() const {
+    Links L;
+    L.u = d; L.u12[0] = d12[0]; L.u12[1] = d12[1]; L.sgn = sgn; L.inv[0] = inv[0]; L.inv[1] = inv[1];
+    return L;
+  }
 };
 inline double2* hf(const Field& f, int parity) { return f.d + (size_t)parity * 3 * ctx().g.Vh; }
 
@@ -202,6 +227,8 @@ int upload_vector(Field& f, const double* host);
 int download_vector(const Field& f, double* host);
 int upload_links(Gauge& g, const double* const* links);
 int rephase(Gauge& g);
+int compress_links(Gauge& g);      // honours g.want12; sets g.recon
+void free_compressed(Gauge& g);
 
 // ---- comm.cu ----------------------------------------------------------------
 int halo_setup();

@@ -11,10 +11,30 @@
 // coalesced along the site index.  Links are streamed with ld.global.cs, vectors
 // go through the read-only path so the 8/16 neighbour re-reads hit L1/L2.
 #include "stencil.cuh"
+#include <cstdlib>
 
 namespace qb {
 
 constexpr int SWEEP_BLOCK = 128;
+
+// Expands LAUNCH once with the compile-time constants NL (link classes), RC (bit j: class j is
+// read as 12 reals) and DOT that match the link set and the request.
+#define QB_CASE(KEY, NLV, RCV, DOTV, ...) \
+  case KEY: { constexpr int NL = NLV; constexpr int RC = RCV; constexpr bool DOT = DOTV; (void)DOT; __VA_ARGS__; } break;
+#define QB_DISPATCH(g, dot, ...)                                                           \
+  do {                                                                                     \
+    const int nl_ = (g).nlinks / 4;                                                        \
+    const int rc_ = (nl_ == 2) ? (g).rc() : ((g).rc() & 1);                                \
+    switch ((nl_ == 2 ? 8 : 0) | (rc_ << 1) | ((dot) ? 1 : 0)) {                           \
+      QB_CASE(0, 1, 0, false, __VA_ARGS__) QB_CASE(1, 1, 0, true, __VA_ARGS__)                       \
+      QB_CASE(2, 1, 1, false, __VA_ARGS__) QB_CASE(3, 1, 1, true, __VA_ARGS__)                       \
+      QB_CASE(8, 2, 0, false, __VA_ARGS__) QB_CASE(9, 2, 0, true, __VA_ARGS__)                       \
+      QB_CASE(10, 2, 1, false, __VA_ARGS__) QB_CASE(11, 2, 1, true, __VA_ARGS__)                     \
+      QB_CASE(12, 2, 2, false, __VA_ARGS__) QB_CASE(13, 2, 2, true, __VA_ARGS__)                     \
+      QB_CASE(14, 2, 3, false, __VA_ARGS__) QB_CASE(15, 2, 3, true, __VA_ARGS__)                     \
+      default: return fail("sweep: no kernel for this link set");                          \
+    }                                                                                      \
+  } while (0)
 
 // r = post*(a*r + b*bx + sgn*acc) for one site; returns Re<bx, r_new> when DOT
 template <bool DOT>
@@ -38,50 +58,61 @@ __device__ __forceinline__ double site_epilogue(const SweepArgs& A, int idx, con
   return dot;
 }
 
-template <int NL, bool DOT>
-__global__ void __launch_bounds__(SWEEP_BLOCK) k_sweep(const SweepArgs A) {
-  const int idx = blockIdx.x * SWEEP_BLOCK + threadIdx.x;
-  double dot = 0.0;
-  if (idx < A.Vh) {
-    const int Vh = A.Vh, p = A.parity, q = 1 - A.parity;
-    const Site s = site_from_idx(idx, p, A.X);
-    double2 acc[3] = {{0, 0}, {0, 0}, {0, 0}};
+// sum_k [U_k(s) x(s+h_k) - U_k(s-h_k)^+ x(s-h_k)] over the hops that stay on this rank
+template <int NL, int RC>
+__device__ __forceinline__ void stencil_local(const SweepArgs& A, const Site& s, int idx, double2 (&acc)[3]) {
+  const int Vh = A.Vh, p = A.parity, q = 1 - A.parity;
+  const unsigned int sg = RC ? A.L.sgn[(size_t)p * Vh + idx] : 0u;
 #pragma unroll
-    for (int mu = 0; mu < 4; mu++) {
-      const int st = stride_of(mu, A.X);
-      const int Xm = A.X[mu];
-      const bool split = (A.comm_mask >> mu) & 1;
+  for (int mu = 0; mu < 4; mu++) {
+    const int st = stride_of(mu, A.X);
+    const int Xm = A.X[mu];
+    const bool split = (A.comm_mask >> mu) & 1;
 #pragma unroll
-      for (int j = 0; j < NL; j++) {
-        const int h = (j == 0) ? 1 : 3;
-        const int k = mu * NL + j;
-        {  // forward hop: U_k(s) x(s + h mu)
-          int y = s.x[mu] + h;
-          int ln = s.lex + h * st;
-          bool off = y >= Xm;
-          if (off) ln -= Xm * st;
-          if (!(off && split)) {
-            double2 U[9], v[3];
-            load_link(U, link_ptr(A.u, k, p, Vh, idx), Vh);
-            load_vec(v, A.x + (ln >> 1), Vh);
-            mv_add(acc, U, v);
-          }
+    for (int j = 0; j < NL; j++) {
+      const int h = (j == 0) ? 1 : 3;
+      {  // forward hop: U_k(s) x(s + h mu)
+        int y = s.x[mu] + h;
+        int ln = s.lex + h * st;
+        bool off = y >= Xm;
+        if (off) ln -= Xm * st;
+        if (!(off && split)) {
+          double2 U[9], v[3];
+          load_link_k<NL, RC>(U, A.L, mu, j, p, idx, Vh, (sg >> (2 * mu + j)) & 1u);
+          load_vec(v, A.x + (ln >> 1), Vh);
+          mv_add(acc, U, v);
         }
-        {  // backward hop: U_k(s - h mu)^+ x(s - h mu)
-          int y = s.x[mu] - h;
-          int ln = s.lex - h * st;
-          bool off = y < 0;
-          if (off) ln += Xm * st;
-          if (!(off && split)) {
-            double2 U[9], v[3];
-            const int ib = ln >> 1;
-            load_link(U, link_ptr(A.u, k, q, Vh, ib), Vh);
-            load_vec(v, A.x + ib, Vh);
-            mv_adj_sub(acc, U, v);
-          }
+      }
+      {  // backward hop: U_k(s - h mu)^+ x(s - h mu)
+        int y = s.x[mu] - h;
+        int ln = s.lex - h * st;
+        bool off = y < 0;
+        if (off) ln += Xm * st;
+        if (!(off && split)) {
+          double2 U[9], v[3];
+          const int ib = ln >> 1;
+          load_link_k<NL, RC>(U, A.L, mu, j, q, ib, Vh, (sg >> (8 + 2 * mu + j)) & 1u);
+          load_vec(v, A.x + ib, Vh);
+          mv_adj_sub(acc, U, v);
         }
       }
     }
+  }
+}
+
+// Residency: 6 blocks of 128 threads per SM (<= 85 registers) measured fastest on B200 -- the
+// compiler keeps more 16-byte loads in flight per thread than at the default 9 blocks/SM
+// (tools/tune_sweep.py: 32^4 naive 0.0971 ms vs 0.1085 ms, fat+Naik 0.1827 ms vs 0.1909 ms).
+constexpr int SWEEP_MINB = 6;
+
+template <int NL, int RC, bool DOT>
+__global__ void __launch_bounds__(SWEEP_BLOCK, SWEEP_MINB) k_sweep(const SweepArgs A) {
+  const int idx = blockIdx.x * SWEEP_BLOCK + threadIdx.x;
+  double dot = 0.0;
+  if (idx < A.Vh) {
+    const Site s = site_from_idx(idx, A.parity, A.X);
+    double2 acc[3] = {{0, 0}, {0, 0}, {0, 0}};
+    stencil_local<NL, RC>(A, s, idx, acc);
     dot = site_epilogue<DOT>(A, idx, acc);
     if (DOT && A.comm_mask) {
       // multi-rank: sites with an off-rank hop are finished (and counted) by k_exterior
@@ -94,6 +125,18 @@ __global__ void __launch_bounds__(SWEEP_BLOCK) k_sweep(const SweepArgs A) {
     }
   }
   if (DOT) grid_reduce<SWEEP_BLOCK>(dot, A.partials, A.ticket, A.result);
+}
+
+// launch-shape experiments (QEXB200_SWEEP_TUNE): same body, other block size / residency
+template <int NL, int BLOCK, int MINB>
+__global__ void __launch_bounds__(BLOCK, MINB) k_sweep_t(const SweepArgs A) {
+  const int idx = blockIdx.x * BLOCK + threadIdx.x;
+  if (idx < A.Vh) {
+    const Site s = site_from_idx(idx, A.parity, A.X);
+    double2 acc[3] = {{0, 0}, {0, 0}, {0, 0}};
+    stencil_local<NL, 0>(A, s, idx, acc);
+    site_epilogue<false>(A, idx, acc);
+  }
 }
 
 // ---- exterior: one launch for all split directions -----------------------------------------
@@ -114,7 +157,7 @@ struct ExtRegion {
   int end;       // prefix end in threads (sites of one parity)
 };
 struct ExtArgs {
-  const double2* u;
+  Links L;
   double2* r;
   double scale;  // post*sgn
   int X[4], dep[4], nbv[4];
@@ -160,7 +203,7 @@ __device__ __forceinline__ void region_site(const ExtArgs& A, int t, int (&x)[4]
   }
 }
 
-template <int NL, bool DOT>
+template <int NL, int RC, bool DOT>
 __global__ void __launch_bounds__(SWEEP_BLOCK) k_exterior(const ExtArgs A) {
   if (A.wait) {
     if ((int)threadIdx.x < 2 * A.ndir) {
@@ -177,6 +220,7 @@ __global__ void __launch_bounds__(SWEEP_BLOCK) k_exterior(const ExtArgs A) {
   const int lex = ((x[3] * A.X[2] + x[2]) * A.X[1] + x[1]) * A.X[0] + x[0];
   const int idx = lex >> 1, Vh = A.Vh;
   double2 acc[3] = {{0, 0}, {0, 0}, {0, 0}};
+  const unsigned int sg = RC ? A.L.sgn[(size_t)A.parity * Vh + idx] : 0u;
   for (int di = 0; di < A.ndir; di++) {
     const ExtDir& D = A.d[di];
     const int mu = D.mu, Xm = A.X[mu], xmu = x[mu], d = D.depth;
@@ -185,11 +229,10 @@ __global__ void __launch_bounds__(SWEEP_BLOCK) k_exterior(const ExtArgs A) {
 #pragma unroll
     for (int j = 0; j < NL; j++) {
       const int h = (j == 0) ? 1 : 3;
-      const int k = mu * NL + j;
       if (xmu + h >= Xm) {
         const int l = xmu + h - Xm;
         double2 U[9], v[3];
-        load_link(U, link_ptr(A.u, k, A.parity, Vh, idx), Vh);
+        load_link_k<NL, RC>(U, A.L, mu, j, A.parity, idx, Vh, (sg >> (2 * mu + j)) & 1u);
 #pragma unroll
         for (int c = 0; c < 3; c++) v[c] = __ldcg(D.ghost_f + (size_t)c * d * D.faceh + (size_t)l * D.faceh + fidx);
         mv_add(acc, U, v);
@@ -226,7 +269,7 @@ struct PackDir {
   unsigned int *flag_f, *flag_b;   // flag at the - neighbour (its side 0) / + neighbour (its side 1)
 };
 struct PackArgs {
-  const double2* u;
+  Links L;
   const double2* x;   // half field of parity q (the sweep's input parity)
   int X[4];
   int Vh, q, ndir;
@@ -236,7 +279,7 @@ struct PackArgs {
 };
 
 // one work item of the packing (t < A.d[ndir-1].end)
-template <int NL>
+template <int NL, int RC>
 __device__ __forceinline__ void pack_item(const PackArgs& A, int t) {
   int di = 0, base = 0;
 #pragma unroll
@@ -260,7 +303,9 @@ __device__ __forceinline__ void pack_item(const PackArgs& A, int t) {
     const Site s = site_from_face(fidx, mu, Xm - h + jl, A.q, A.X);
     const int idx = s.lex >> 1;
     double2 U[9], v[3], acc[3] = {{0, 0}, {0, 0}, {0, 0}};
-    load_link(U, link_ptr(A.u, mu * NL + j, A.q, Vh, idx), Vh);
+    const unsigned int sg = RC ? A.L.sgn[(size_t)A.q * Vh + idx] : 0u;
+    if (NL == 2 && j == 1) load_link_k<NL, RC>(U, A.L, mu, 1, A.q, idx, Vh, (sg >> (2 * mu + 1)) & 1u);
+    else load_link_k<NL, RC>(U, A.L, mu, 0, A.q, idx, Vh, (sg >> (2 * mu)) & 1u);
     load_vec(v, A.x + idx, Vh);
     mv_adj_sub(acc, U, v);
     double2* ob = (j == 0) ? P.out_b0 : P.out_b1;
@@ -288,10 +333,10 @@ __device__ __forceinline__ void pack_signal(const PackArgs& A, unsigned int nblo
   }
 }
 
-template <int NL>
+template <int NL, int RC>
 __global__ void __launch_bounds__(SWEEP_BLOCK) k_pack(const PackArgs A) {
   const int t = blockIdx.x * SWEEP_BLOCK + threadIdx.x;
-  if (t < A.d[A.ndir - 1].end) pack_item<NL>(A, t);
+  if (t < A.d[A.ndir - 1].end) pack_item<NL, RC>(A, t);
   if (A.ticket) pack_signal(A, gridDim.x);
 }
 
@@ -313,14 +358,14 @@ struct FusedArgs {
   int npack, nint;
 };
 
-template <int NL, bool DOT>
-__global__ void __launch_bounds__(SWEEP_BLOCK, 8) k_sweep_fused(const FusedArgs F) {
+template <int NL, int RC, bool DOT>
+__global__ void __launch_bounds__(SWEEP_BLOCK, SWEEP_MINB) k_sweep_fused(const FusedArgs F) {
   const SweepArgs& A = F.A;
   const int bid = blockIdx.x;
   double dot = 0.0;
   if (bid < F.npack) {
     const int t = bid * SWEEP_BLOCK + threadIdx.x;
-    if (t < F.P.d[F.P.ndir - 1].end) pack_item<NL>(F.P, t);
+    if (t < F.P.d[F.P.ndir - 1].end) pack_item<NL, RC>(F.P, t);
     pack_signal(F.P, F.npack);
   } else {
     const ExtArgs& E = F.E;
@@ -354,6 +399,7 @@ __global__ void __launch_bounds__(SWEEP_BLOCK, 8) k_sweep_fused(const FusedArgs 
     if (active) {
       const int idx = s.lex >> 1;
       double2 acc[3] = {{0, 0}, {0, 0}, {0, 0}};
+      const unsigned int sg = RC ? A.L.sgn[(size_t)p * Vh + idx] : 0u;
       int di = 0;   // index into E.d of the current split direction (tail only)
 #pragma unroll
       for (int mu = 0; mu < 4; mu++) {
@@ -366,14 +412,13 @@ __global__ void __launch_bounds__(SWEEP_BLOCK, 8) k_sweep_fused(const FusedArgs 
 #pragma unroll
         for (int j = 0; j < NL; j++) {
           const int h = (j == 0) ? 1 : 3;
-          const int k = mu * NL + j;
-          {  // forward hop
+              {  // forward hop
             const int y = s.x[mu] + h;
             int ln = s.lex + h * st;
             const bool off = y >= Xm;
             if (off) ln -= Xm * st;
             double2 U[9], v[3];
-            load_link(U, link_ptr(A.u, k, p, Vh, idx), Vh);
+            load_link_k<NL, RC>(U, A.L, mu, j, p, idx, Vh, (sg >> (2 * mu + j)) & 1u);
             if (off && split) {
               const ExtDir& D = E.d[di];
 #pragma unroll
@@ -400,7 +445,7 @@ __global__ void __launch_bounds__(SWEEP_BLOCK, 8) k_sweep_fused(const FusedArgs 
             } else {
               double2 U[9], v[3];
               const int ib = ln >> 1;
-              load_link(U, link_ptr(A.u, k, q, Vh, ib), Vh);
+              load_link_k<NL, RC>(U, A.L, mu, j, q, ib, Vh, (sg >> (8 + 2 * mu + j)) & 1u);
               load_vec(v, A.x + ib, Vh);
               mv_adj_sub(acc, U, v);
             }
@@ -424,7 +469,7 @@ static inline double2* win_recv(char* win, int buf, size_t cap) {
 // Launched on `st` (the comm stream).  seq is the sweep's exchange number.
 static int fill_pack(const Gauge& g, int q, const double2* x, unsigned int seq, PackArgs& P) {
   Context& c = ctx();
-  P.u = g.d; P.x = x;
+  P.L = g.links(); P.x = x;
   for (int i = 0; i < 4; i++) P.X[i] = c.g.X[i];
   P.Vh = c.g.Vh; P.q = q; P.ndir = (int)c.halo.size();
   P.seq = seq; P.ticket = c.p2p ? c.d_ticket + 1 : nullptr;
@@ -460,8 +505,7 @@ int pack_faces(const Gauge& g, int q, const double2* x, unsigned int seq, cudaSt
   PackArgs P;
   const int end = fill_pack(g, q, x, seq, P);
   const int grid = (end + SWEEP_BLOCK - 1) / SWEEP_BLOCK;
-  if (g.nlinks == 8) k_pack<2><<<grid, SWEEP_BLOCK, 0, st>>>(P);
-  else k_pack<1><<<grid, SWEEP_BLOCK, 0, st>>>(P);
+  QB_DISPATCH(g, false, k_pack<NL, RC><<<grid, SWEEP_BLOCK, 0, st>>>(P));
   count_launch();
   QB_CUDA(cudaGetLastError());
   return 0;
@@ -473,7 +517,7 @@ static int fill_ext(const Gauge& g, int parity, double2* r, double scale, const 
   Context& c = ctx();
   E.bx = bx; E.partials = c.d_partials; E.ticket = c.d_ticket; E.result = dot_out;
   E.interior = dot_interior; E.xr = xrank();
-  E.u = g.d; E.r = r; E.scale = scale;
+  E.L = g.links(); E.r = r; E.scale = scale;
   for (int i = 0; i < 4; i++) { E.X[i] = c.g.X[i]; E.dep[i] = 0; E.nbv[i] = 0; }
   E.Vh = c.g.Vh; E.parity = parity; E.ndir = (int)c.halo.size();
   E.seq = c.halo_seq; E.wait = c.p2p ? 1 : 0; E.err = c.d_err;
@@ -519,13 +563,7 @@ static int exterior(const Gauge& g, int parity, double2* r, double scale, const 
   const int end = fill_ext(g, parity, r, scale, bx, dot_out, dot_interior, E);
   if (end == 0) return 0;
   const int grid = (end + SWEEP_BLOCK - 1) / SWEEP_BLOCK;
-  if (g.nlinks == 8) {
-    if (dot_out) k_exterior<2, true><<<grid, SWEEP_BLOCK, 0, c.stream>>>(E);
-    else k_exterior<2, false><<<grid, SWEEP_BLOCK, 0, c.stream>>>(E);
-  } else {
-    if (dot_out) k_exterior<1, true><<<grid, SWEEP_BLOCK, 0, c.stream>>>(E);
-    else k_exterior<1, false><<<grid, SWEEP_BLOCK, 0, c.stream>>>(E);
-  }
+  QB_DISPATCH(g, dot_out != nullptr, k_exterior<NL, RC, DOT><<<grid, SWEEP_BLOCK, 0, c.stream>>>(E));
   count_launch();
   QB_CUDA(cudaGetLastError());
   return 0;
@@ -538,7 +576,7 @@ int sweep(const Gauge& g, int parity, double2* r, const double2* x, const double
   const bool multi = c.g.comm_mask != 0;
 
   SweepArgs A;
-  A.u = g.d; A.x = x; A.r = r; A.bx = bx ? bx : r;
+  A.L = g.links(); A.x = x; A.r = r; A.bx = bx ? bx : r;
   A.a = a; A.b = bx ? b : 0.0; A.sgn = sgn; A.post = post;
   for (int i = 0; i < 4; i++) A.X[i] = c.g.X[i];
   A.Vh = c.g.Vh; A.parity = parity; A.comm_mask = c.g.comm_mask;
@@ -557,29 +595,32 @@ int sweep(const Gauge& g, int parity, double2* r, const double2* x, const double
     F.nint = grid;
     const int total = F.npack + F.nint + (nbd + SWEEP_BLOCK - 1) / SWEEP_BLOCK;
     if ((size_t)total > c.npart) return fail("sweep: %d blocks exceed the %zu reduction slots", total, c.npart);
-    if (g.nlinks == 8) {
-      if (fused_dot) k_sweep_fused<2, true><<<total, SWEEP_BLOCK, 0, c.stream>>>(F);
-      else k_sweep_fused<2, false><<<total, SWEEP_BLOCK, 0, c.stream>>>(F);
-    } else {
-      if (fused_dot) k_sweep_fused<1, true><<<total, SWEEP_BLOCK, 0, c.stream>>>(F);
-      else k_sweep_fused<1, false><<<total, SWEEP_BLOCK, 0, c.stream>>>(F);
-    }
+    QB_DISPATCH(g, fused_dot, k_sweep_fused<NL, RC, DOT><<<total, SWEEP_BLOCK, 0, c.stream>>>(F));
     count_launch();
     QB_CUDA(cudaGetLastError());
     return 0;
   }
 
+  const int tune = getenv("QEXB200_SWEEP_TUNE") ? atoi(getenv("QEXB200_SWEEP_TUNE")) : 0;
+  if (!multi && !fused_dot && tune > 0) {
+#define QB_T(ID, BLOCK, MINB)                                                               \
+    if (tune == ID) {                                                                         \
+      const int gr = (c.g.Vh + BLOCK - 1) / BLOCK;                                            \
+      if (g.nlinks == 8) k_sweep_t<2, BLOCK, MINB><<<gr, BLOCK, 0, c.stream>>>(A);            \
+      else k_sweep_t<1, BLOCK, MINB><<<gr, BLOCK, 0, c.stream>>>(A);                          \
+    }
+    QB_T(1, 128, 8) QB_T(2, 128, 6) QB_T(3, 128, 4) QB_T(4, 256, 4) QB_T(5, 256, 3) QB_T(6, 64, 16)
+    QB_T(7, 64, 12) QB_T(8, 96, 8) QB_T(9, 128, 10) QB_T(10, 256, 2) QB_T(11, 64, 8) QB_T(12, 32, 24)
+#undef QB_T
+    count_launch();
+    QB_CUDA(cudaGetLastError());
+    return 0;
+  }
   if (multi) QB_CHECK(halo_start(g, parity, x));
   // NCCL path: the interior part of the dot goes to a scratch scalar, k_exterior finishes it
   double* dot_interior = c.d_scal + 48;
   if (multi) A.result = dot_interior;
-  if (g.nlinks == 8) {
-    if (fused_dot) k_sweep<2, true><<<grid, SWEEP_BLOCK, 0, c.stream>>>(A);
-    else k_sweep<2, false><<<grid, SWEEP_BLOCK, 0, c.stream>>>(A);
-  } else {
-    if (fused_dot) k_sweep<1, true><<<grid, SWEEP_BLOCK, 0, c.stream>>>(A);
-    else k_sweep<1, false><<<grid, SWEEP_BLOCK, 0, c.stream>>>(A);
-  }
+  QB_DISPATCH(g, fused_dot, k_sweep<NL, RC, DOT><<<grid, SWEEP_BLOCK, 0, c.stream>>>(A));
   count_launch();
   QB_CUDA(cudaGetLastError());
   if (multi) {

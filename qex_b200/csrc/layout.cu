@@ -180,7 +180,7 @@ int upload_links(Gauge& g, const double* const* links) {
   }
   QB_CUDA(cudaStreamSynchronize(c.stream));
   g.loaded = true;
-  return 0;
+  return compress_links(g);
 }
 
 // Staggered.rephase (stagD.nim:72-80): setBC (gaugeUtils.nim:124-131) then
@@ -205,6 +205,169 @@ __global__ void __launch_bounds__(LB) k_rephase(double2* u, int Vh, int X0, int 
   }
 }
 
+// ---- 12-real link storage -------------------------------------------------------------------
+// A link class (one-hop / three-hop) whose matrices are s * W, W in SU(3), with one |s| for the
+// whole field is also stored as rows 0 and 1 (96 B instead of 144 B per link); the sweeps rebuild
+// row 2 = (sigma/|s|) conj(row0 x row1).  Naive links with staggered phases and antiperiodic BC
+// are +-SU(3); Naik links are c * (product of three unitarised links).  Fat7-smeared links are not
+// of this form and stay at 18 reals.  k_compress writes the rows, the sign bits and the evidence
+// (max deviation of the rebuilt matrix, spread of |s|^2) the host decides on.
+__device__ __forceinline__ double warp_max(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ double warp_min(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmin(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+template <int NL>
+__global__ void __launch_bounds__(LB) k_compress(const double2* __restrict__ u, double2* __restrict__ u12_0,
+                                                  double2* __restrict__ u12_1, unsigned short* __restrict__ sgn,
+                                                  unsigned long long* stats, int Vh) {
+  const int ds = blockIdx.x * LB + threadIdx.x;
+  const bool live = ds < 2 * Vh;
+  const int par = live ? ds / Vh : 0, idx = live ? ds - par * Vh : 0;
+  double dev[2] = {0.0, 0.0}, smin[2] = {1e300, 1e300}, smax[2] = {0.0, 0.0};
+  unsigned int bits = 0;
+  if (live) {
+#pragma unroll
+    for (int mu = 0; mu < 4; mu++) {
+#pragma unroll
+      for (int j = 0; j < NL; j++) {
+        const double2* p = u + ((size_t)((mu * NL + j) * 2 + par) * 9) * Vh + idx;
+        double2 U[9];
+#pragma unroll
+        for (int e = 0; e < 9; e++) U[e] = p[(size_t)e * Vh];
+        double2* o = (j == 0 ? u12_0 : u12_1) + ((size_t)(mu * 2 + par) * 6) * Vh + idx;
+#pragma unroll
+        for (int e = 0; e < 6; e++) o[(size_t)e * Vh] = U[e];
+        const double s2 = U[0].x * U[0].x + U[0].y * U[0].y + U[1].x * U[1].x + U[1].y * U[1].y +
+                          U[2].x * U[2].x + U[2].y * U[2].y;
+        const double t2 = U[3].x * U[3].x + U[3].y * U[3].y + U[4].x * U[4].x + U[4].y * U[4].y +
+                          U[5].x * U[5].x + U[5].y * U[5].y;
+        double2 ov = {0, 0};   // <row0, row1>
+#pragma unroll
+        for (int e = 0; e < 3; e++) {
+          ov.x += U[e].x * U[3 + e].x + U[e].y * U[3 + e].y;
+          ov.y += U[e].x * U[3 + e].y - U[e].y * U[3 + e].x;
+        }
+        double2 c[3];          // conj(row0 x row1)
+        c[0].x = U[1].x * U[5].x - U[1].y * U[5].y - (U[2].x * U[4].x - U[2].y * U[4].y);
+        c[0].y = -(U[1].x * U[5].y + U[1].y * U[5].x - (U[2].x * U[4].y + U[2].y * U[4].x));
+        c[1].x = U[2].x * U[3].x - U[2].y * U[3].y - (U[0].x * U[5].x - U[0].y * U[5].y);
+        c[1].y = -(U[2].x * U[3].y + U[2].y * U[3].x - (U[0].x * U[5].y + U[0].y * U[5].x));
+        c[2].x = U[0].x * U[4].x - U[0].y * U[4].y - (U[1].x * U[3].x - U[1].y * U[3].y);
+        c[2].y = -(U[0].x * U[4].y + U[0].y * U[4].x - (U[1].x * U[3].y + U[1].y * U[3].x));
+        double re = 0.0;       // Re <c, row2> = sigma |c|^2 / |s|
+#pragma unroll
+        for (int e = 0; e < 3; e++) re += c[e].x * U[6 + e].x + c[e].y * U[6 + e].y;
+        const bool neg = re < 0.0;
+        if (neg) bits |= 1u << (2 * mu + j);
+        const double inv = s2 > 0.0 ? rsqrt(s2) : 0.0;
+        const double f = neg ? -inv : inv;
+        double d = fmax(fabs(t2 - s2), sqrt(ov.x * ov.x + ov.y * ov.y)) * inv * inv;
+#pragma unroll
+        for (int e = 0; e < 3; e++)
+          d = fmax(d, fmax(fabs(U[6 + e].x - f * c[e].x), fabs(U[6 + e].y - f * c[e].y)) * inv);
+        if (!(s2 > 0.0)) d = 1.0;
+        dev[j] = fmax(dev[j], d);
+        smin[j] = fmin(smin[j], s2);
+        smax[j] = fmax(smax[j], s2);
+      }
+    }
+    sgn[ds] = (unsigned short)bits;
+  }
+#pragma unroll
+  for (int j = 0; j < NL; j++) {
+    const double a = warp_max(dev[j]), b = warp_min(smin[j]), cmax = warp_max(smax[j]);
+    if ((threadIdx.x & 31) == 0) {   // non-negative doubles order like their bit patterns
+      atomicMax(stats + j, (unsigned long long)__double_as_longlong(a));
+      atomicMin(stats + 2 + j, (unsigned long long)__double_as_longlong(b));
+      atomicMax(stats + 4 + j, (unsigned long long)__double_as_longlong(cmax));
+    }
+  }
+}
+
+// high byte of sgn: the sign bits of the links the BACKWARD hops read, U_{mu,j}(s - h_j mu)
+template <int NL>
+__global__ void __launch_bounds__(LB) k_sign_bwd(unsigned short* sgn, int Vh, int X0, int X1, int X2, int X3) {
+  const int ds = blockIdx.x * LB + threadIdx.x;
+  if (ds >= 2 * Vh) return;
+  const int par = ds / Vh, idx = ds - par * Vh;
+  const int X[4] = {X0, X1, X2, X3};
+  const Site s = site_from_idx(idx, par, X);
+  unsigned int bits = sgn[ds] & 0xffu;
+#pragma unroll
+  for (int mu = 0; mu < 4; mu++) {
+    const int st = stride_of(mu, X);
+#pragma unroll
+    for (int j = 0; j < NL; j++) {
+      const int h = (j == 0) ? 1 : 3;
+      int ln = s.lex - h * st;
+      if (s.x[mu] - h < 0) ln += X[mu] * st;   // local wrap; off-rank hops never read this bit
+      const unsigned int nb = sgn[(size_t)(1 - par) * Vh + (ln >> 1)];
+      bits |= ((nb >> (2 * mu + j)) & 1u) << (8 + 2 * mu + j);
+    }
+  }
+  sgn[ds] = (unsigned short)bits;
+}
+
+void free_compressed(Gauge& g) {
+  for (int j = 0; j < 2; j++) {
+    if (g.d12[j]) cudaFree(g.d12[j]);
+    g.d12[j] = nullptr; g.recon[j] = 18; g.inv[j] = 1.0;
+  }
+  if (g.sgn) cudaFree(g.sgn);
+  g.sgn = nullptr;
+}
+
+// Tolerances of the 12-real form: rebuilt matrix within 2e-14 |s| of the stored one, |s|^2 equal
+// over the field to 1e-13 relative (the Dslash parity bar is 1e-13).
+constexpr double RECON_DEV_TOL = 2e-14;
+constexpr double RECON_SCALE_TOL = 1e-13;
+
+int compress_links(Gauge& g) {
+  Context& c = ctx();
+  QB_CUDA(cudaStreamSynchronize(c.stream));
+  free_compressed(g);
+  if (!g.want12 || !g.loaded) return 0;
+  const int nl = g.nlinks / 4;
+  const size_t n12 = (size_t)4 * 2 * 6 * c.g.Vh;
+  for (int j = 0; j < nl; j++) QB_CUDA(cudaMalloc(&g.d12[j], sizeof(double2) * n12));
+  QB_CUDA(cudaMalloc(&g.sgn, sizeof(unsigned short) * 2 * (size_t)c.g.Vh));
+  unsigned long long* stats = reinterpret_cast<unsigned long long*>(c.d_scal + 56);
+  unsigned long long init[6] = {0, 0, 0x7ff0000000000000ull, 0x7ff0000000000000ull, 0, 0};
+  QB_CUDA(cudaMemcpyAsync(stats, init, sizeof init, cudaMemcpyHostToDevice, c.stream));
+  const int grid = (2 * c.g.Vh + LB - 1) / LB;
+  if (nl == 2) k_compress<2><<<grid, LB, 0, c.stream>>>(g.d, g.d12[0], g.d12[1], g.sgn, stats, c.g.Vh);
+  else k_compress<1><<<grid, LB, 0, c.stream>>>(g.d, g.d12[0], nullptr, g.sgn, stats, c.g.Vh);
+  count_launch();
+  if (nl == 2) k_sign_bwd<2><<<grid, LB, 0, c.stream>>>(g.sgn, c.g.Vh, c.g.X[0], c.g.X[1], c.g.X[2], c.g.X[3]);
+  else k_sign_bwd<1><<<grid, LB, 0, c.stream>>>(g.sgn, c.g.Vh, c.g.X[0], c.g.X[1], c.g.X[2], c.g.X[3]);
+  count_launch();
+  QB_CUDA(cudaGetLastError());
+  double hs[6];
+  QB_CHECK(fetch_scalars(c.d_scal + 56, hs, 6));
+  bool any = false;
+  for (int j = 0; j < nl; j++) {
+    const double dev = hs[j], smin = hs[2 + j], smax = hs[4 + j];
+    g.dev[j] = dev;
+    const bool ok = ((g.want12 >> j) & 1) && dev <= RECON_DEV_TOL && smin > 0.0 && (smax - smin) <= RECON_SCALE_TOL * smax;
+    if (ok) {
+      g.recon[j] = 12;
+      g.inv[j] = 1.0 / sqrt(0.5 * (smin + smax));
+      any = true;
+    } else {
+      cudaFree(g.d12[j]); g.d12[j] = nullptr; g.recon[j] = 18;
+    }
+  }
+  if (!any) { cudaFree(g.sgn); g.sgn = nullptr; }
+  return 0;
+}
+
 int rephase(Gauge& g) {
   Context& c = ctx();
   if (g.nlinks != 4) return fail("gauge_rephase: only one-hop link sets (nlinks=4) carry phases here");
@@ -215,7 +378,7 @@ int rephase(Gauge& g) {
                                        G.rc[1] * G.X[1], G.rc[2] * G.X[2], G.rc[3] * G.X[3], G.lat[3]);
   count_launch();
   QB_CUDA(cudaGetLastError());
-  return 0;
+  return compress_links(g);   // the signs changed: refresh the 12-real copy if one is wanted
 }
 
 }  // namespace qb

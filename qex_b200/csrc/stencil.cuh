@@ -59,6 +59,34 @@ __device__ __forceinline__ void load_link(double2 (&U)[9], const double2* __rest
 #pragma unroll
   for (int e = 0; e < 9; e++) U[e] = __ldcs(p + (size_t)e * Vh);
 }
+// Link U_{mu,j}(par, idx) of a set with NL classes; RC bit j set: class j is read as 12 reals and
+// the third row rebuilt (neg = its sign bit).  j is a compile-time constant after unrolling.
+template <int NL, int RC>
+__device__ __forceinline__ void load_link_k(double2 (&U)[9], const Links& L, int mu, int j, int par,
+                                            int idx, int Vh, unsigned int neg) {
+  if ((RC >> j) & 1) {
+    const double2* __restrict__ p = L.u12[j] + ((size_t)(mu * 2 + par) * 6) * Vh + idx;
+#pragma unroll
+    for (int e = 0; e < 6; e++) U[e] = __ldcs(p + (size_t)e * Vh);
+    const double f = neg ? -L.inv[j] : L.inv[j];
+    // row2 = f * conj(row0 x row1)
+    double2 c;
+    c.x = U[1].x * U[5].x - U[1].y * U[5].y - (U[2].x * U[4].x - U[2].y * U[4].y);
+    c.y = U[1].x * U[5].y + U[1].y * U[5].x - (U[2].x * U[4].y + U[2].y * U[4].x);
+    U[6] = make_double2(f * c.x, -f * c.y);
+    c.x = U[2].x * U[3].x - U[2].y * U[3].y - (U[0].x * U[5].x - U[0].y * U[5].y);
+    c.y = U[2].x * U[3].y + U[2].y * U[3].x - (U[0].x * U[5].y + U[0].y * U[5].x);
+    U[7] = make_double2(f * c.x, -f * c.y);
+    c.x = U[0].x * U[4].x - U[0].y * U[4].y - (U[1].x * U[3].x - U[1].y * U[3].y);
+    c.y = U[0].x * U[4].y + U[0].y * U[4].x - (U[1].x * U[3].y + U[1].y * U[3].x);
+    U[8] = make_double2(f * c.x, -f * c.y);
+  } else {
+    const double2* __restrict__ p = L.u + ((size_t)((mu * NL + j) * 2 + par) * 9) * Vh + idx;
+#pragma unroll
+    for (int e = 0; e < 9; e++) U[e] = __ldcs(p + (size_t)e * Vh);
+  }
+}
+
 // vectors are re-read by up to 16 neighbours: keep them cached
 __device__ __forceinline__ void load_vec(double2 (&v)[3], const double2* __restrict__ p, int Vh) {
 #pragma unroll

@@ -60,11 +60,11 @@ def cpu_plan_check(L, G, nlinks, rank, world, dist):
     return True
 
 
-def gpu_case(L, G, nlinks, inner, rank, world, local_rank, dist, transport="nccl"):
+def gpu_case(L, G, nlinks, inner, rank, world, local_rank, dist, transport="nccl", recon=18):
     import torch
     import oracle
     import qex_b200 as qb
-    from util import make_inputs, rel_l2
+    from util import make_inputs, make_exact_inputs, rel_l2
     torch.cuda.set_device(local_rank)
     idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
     if transport == "nccl":
@@ -76,11 +76,14 @@ def gpu_case(L, G, nlinks, inner, rank, world, local_rank, dist, transport="nccl
         qb.p2p_attach_torch(dist)
         assert qb.p2p_active()
     qb.set_host_layout(inner)
-    lat, g, (x, b) = make_inputs(L, nlinks)
+    lat, g, (x, b) = (make_exact_inputs if recon == 12 else make_inputs)(L, nlinks)
     lo = oracle.QexLayout(L, G, inner)
     mine = lambda f: lo.scatter(f)[rank]
     s = qb.Staggered([mine(g[k]) for k in range(nlinks)])
     res = {}
+    if recon == 12:
+        got_rc, dev = s.recon(12)
+        assert got_rc == ([12, 12] if nlinks == 8 else [12, 18]), (got_rc, dev)
     # Dslash, all flavours
     for parity in (0, 1):
         want = b.copy()
@@ -139,6 +142,7 @@ def main():
     ap.add_argument("--inner", default="1,1,1,1")
     ap.add_argument("--nlinks", type=int, default=4)
     ap.add_argument("--transport", default="nccl", choices=["nccl", "p2p"])
+    ap.add_argument("--recon", type=int, default=18, choices=[12, 18])
     a = ap.parse_args()
     import torch.distributed as dist
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
@@ -154,7 +158,7 @@ def main():
     else:
         import torch
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-        out = gpu_case(L, G, a.nlinks, inner, rank, world, local_rank, dist, a.transport)
+        out = gpu_case(L, G, a.nlinks, inner, rank, world, local_rank, dist, a.transport, a.recon)
     dist.barrier()
     if rank == 0:
         print("MULTI_OK " + json.dumps(out))

@@ -7,6 +7,14 @@ from test_dist_cpu import launch
 pytestmark = pytest.mark.gpu
 
 
+def run_case(nproc, lat, rg, inner, nlinks, transport, recon=18):
+    if ngpus() < nproc:
+        pytest.skip("needs %d GPUs" % nproc)
+    r = launch(nproc, ["--lat", lat, "--rankgeom", rg, "--inner", inner, "--nlinks", str(nlinks),
+                       "--transport", transport, "--recon", str(recon)], timeout=600)
+    assert r.returncode == 0 and "MULTI_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+
+
 def ngpus():
     import torch
     return torch.cuda.device_count()
@@ -25,8 +33,15 @@ def ngpus():
 def test_multi_gpu_parity(nproc, lat, rg, inner, nlinks, transport):
     """transport p2p: NVLink stores into the neighbours' windows + in-kernel cross-rank sums;
     nccl: ncclSend/ncclRecv + ncclAllReduce."""
-    if ngpus() < nproc:
-        pytest.skip("needs %d GPUs" % nproc)
-    r = launch(nproc, ["--lat", lat, "--rankgeom", rg, "--inner", inner, "--nlinks", str(nlinks),
-                       "--transport", transport], timeout=600)
-    assert r.returncode == 0 and "MULTI_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+    run_case(nproc, lat, rg, inner, nlinks, transport)
+
+
+@pytest.mark.parametrize("nproc,lat,rg,nlinks,transport", [
+    (2, "8,8,8,16", "1,1,1,2", 4, "p2p"),
+    (2, "8,8,12,8", "1,1,2,1", 8, "p2p"),
+    (2, "8,8,8,16", "1,1,1,2", 8, "nccl"),
+    (4, "8,8,16,16", "1,1,2,2", 8, "p2p"),
+])
+def test_multi_gpu_parity_recon12(nproc, lat, rg, nlinks, transport):
+    """Same checks with the 12-real link storage (sign bits of off-rank hops come from the packer)."""
+    run_case(nproc, lat, rg, "1,1,1,1", nlinks, transport, recon=12)

@@ -4,7 +4,7 @@ CG iterations within +-1 and true residual <= requested."""
 import numpy as np
 import pytest
 
-from util import make_inputs, rel_l2
+from util import make_inputs, make_exact_inputs, rel_l2
 
 pytestmark = pytest.mark.gpu
 
@@ -87,6 +87,87 @@ def test_D_Ddag_D2ee_parity(orc, ctx_factory, L, nlinks, inner):
     got = xq.copy()
     s.eoReconstruct(got, lo.scatter(b)[0], m)
     assert rel_l2(lo.gather([got]), want) <= DSLASH_TOL
+    s.free()
+
+
+@pytest.mark.parametrize("L,nlinks,inner", [CASES[0], CASES[2], CASES[4], CASES[6]])
+def test_recon12_parity(orc, ctx_factory, L, nlinks, inner):
+    """12-real link storage (rows 0,1 + rebuilt third row, include/qex_b200.h qexb200_gauge_recon):
+    phased +-SU(3) one-hop links and 0.1*SU(3) three-hop links qualify, the Dslash stays within the
+    1e-13 bar of the 18-real oracle and the CG iteration count within +-1."""
+    qb = ctx_factory(L, inner)
+    lat, g, (x, r0) = make_exact_inputs(L, nlinks)
+    lo = orc.QexLayout(L, (1, 1, 1, 1), inner)
+    s = qb.Staggered([lo.scatter(g[k])[0] for k in range(nlinks)])
+    got_rc, dev = s.recon(12)
+    assert got_rc == ([12, 12] if nlinks == 8 else [12, 18]), (got_rc, dev)
+    assert max(dev[:nlinks // 4]) <= 2e-14
+    for parity in (0, 1):
+        want = r0.copy()
+        lat.stagD2(g, want, x, 0.7, -0.3, parity)
+        got = lo.scatter(r0)[0]
+        qb.stagD2(s, parity, got, lo.scatter(x)[0], 0.7, -0.3)
+        got = lo.gather([got])
+        sl = slice(0, lat.half) if parity == 0 else slice(lat.half, lat.vol)
+        assert rel_l2(got[sl], want[sl]) <= DSLASH_TOL
+    m, r2req = 0.1, 1e-10
+    want = lat.vector()
+    it_o, _ = lat.solveXX(g, want, x, m, 0, r2req, 10000)
+    got = lo.scatter(lat.vector())[0]
+    sp = qb.SolverParams(r2req=r2req, maxits=10000)
+    s.solveEE(got, lo.scatter(x)[0], m, sp)
+    assert abs(sp.iterations - it_o) <= 1, (sp.iterations, it_o)
+    assert rel_l2(lo.gather([got])[:lat.half], want[:lat.half]) <= 10 * np.sqrt(r2req)
+    # back to 18 reals: bit-identical to a set that never was compressed
+    assert s.recon(18)[0] == [18, 18]
+    a = lo.scatter(r0)[0]
+    qb.stagD2(s, 0, a, lo.scatter(x)[0], 0.0, 0.0)
+    s2 = qb.Staggered([lo.scatter(g[k])[0] for k in range(nlinks)])
+    b = lo.scatter(r0)[0]
+    qb.stagD2(s2, 0, b, lo.scatter(x)[0], 0.0, 0.0)
+    assert np.array_equal(a, b)
+    s.free()
+    s2.free()
+
+
+def test_recon12_refuses_non_unitary_links(orc, ctx_factory):
+    """Smeared (non-unitary) fat links must stay at 18 reals while the Naik class compresses; device
+    rephase keeps the request (sticky) and re-derives the sign bits."""
+    L = (8, 8, 8, 8)
+    qb = ctx_factory(L)
+    # QEX's own projectSU output is unitary to ~1e-11 only: above the 2e-14 bar, so it is refused
+    # (reading it as 12 reals would cost the 1e-13 parity with the 18-real reference)
+    lat, g, (x, _) = make_inputs(L, 4)
+    s = qb.Staggered([g[k] for k in range(4)])
+    got_rc, dev = s.recon(12)
+    assert got_rc == [18, 18] and 2e-14 < dev[0] < 1e-8, (got_rc, dev)
+    s.free()
+    lat, g, (x, _) = make_exact_inputs(L, 8)
+    rs = np.random.default_rng(5)
+    g = g.copy()
+    g[0::2] += 0.05 * rs.standard_normal(g[0::2].shape)     # "fat" links: no longer s*SU(3)
+    s = qb.Staggered([g[k] for k in range(8)])
+    got_rc, dev = s.recon(12)
+    assert got_rc == [18, 12] and dev[0] > 1e-3
+    assert s.recon(1218)[0] == [18, 18] and s.recon(1812)[0] == [18, 12]
+    want, got = lat.vector(), lat.vector()
+    lat.D(g, want, x, 0.1)
+    s.D(got, x, 0.1)
+    assert rel_l2(got, want) <= DSLASH_TOL
+    s.free()
+    # sticky across rephase: plain SU(3) in, phases applied on the device
+    from qex_b200.synth import random_su3_links
+    g0 = np.ascontiguousarray(np.stack(random_su3_links(lat.vol, 4, seed=9)))
+    g1 = g0.copy()
+    lat.setBC(g1)
+    lat.stagPhase(g1)
+    s = qb.newStag([g0[k] for k in range(4)])
+    assert s.recon(12)[0][0] == 12
+    s.rephase()
+    lat.D(g1, want, x, 0.0)
+    s.D(got, x, 0.0)
+    assert rel_l2(got, want) <= DSLASH_TOL
+    assert s.recon(12)[0][0] == 12
     s.free()
 
 

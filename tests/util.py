@@ -26,6 +26,25 @@ def make_inputs(L, nlinks=4, seed=SEED, nvec=2, long_scale=0.1):
     return lat, np.ascontiguousarray(g), vecs
 
 
+def make_exact_inputs(L, nlinks=4, seed=5, nvec=2, long_scale=0.1):
+    """Like make_inputs, but the SU(3) links come from a Gram-Schmidt in numpy and are unitary to
+    machine precision (QEX's projectSU goes through a closed-form eigen-decomposition and leaves
+    ~1e-11, src/maths/matrixFunctions.nim:126-181) -- the inputs the 12-real link storage is for."""
+    from qex_b200.synth import random_su3_links, gaussian_vector
+    lat = oracle.Lattice(L)
+    g = np.ascontiguousarray(np.stack(random_su3_links(lat.vol, 4, seed=seed)))
+    lat.setBC(g)
+    lat.stagPhase(g)
+    if nlinks == 8:
+        g3 = np.stack(random_su3_links(lat.vol, 4, seed=seed + 1, scale=[long_scale] * 4))
+        gg = np.zeros((8,) + g.shape[1:])
+        gg[0::2] = g
+        gg[1::2] = g3
+        g = gg
+    vecs = [gaussian_vector(lat.vol, seed + i) for i in range(nvec)]
+    return lat, np.ascontiguousarray(g), vecs
+
+
 def rel_l2(a, b):
     return float(np.linalg.norm((a - b).ravel()) / max(np.linalg.norm(b.ravel()), 1e-300))
 

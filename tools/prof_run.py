@@ -16,12 +16,14 @@ for nlinks in (4, 8):
     s = qb.Staggered(links)
     del links
     fb, fx = qb.DeviceField(gaussian_vector(vol)), qb.DeviceField()
-    for _ in range(4):
-        s.dev_stagD2(0, fx, fb, 0.0, 0.0)
-        s.dev_stagD2(1, fx, fb, 0.0, 0.0)
-    sp = qb.SolverParams(r2req=0.0, maxits=10)
-    s.dev_solveXX(fx, fb, 0.1, sp)
-    qb.sync()
-    print("nlinks", nlinks, "iterations", sp.iterations, "launches", qb.launch_count())
+    for mode in (18, 12 if nlinks == 4 else 1812):
+        rc, dev = s.recon(mode)
+        for _ in range(4):
+            s.dev_stagD2(0, fx, fb, 0.0, 0.0)
+            s.dev_stagD2(1, fx, fb, 0.0, 0.0)
+        sp = qb.SolverParams(r2req=0.0, maxits=10)
+        s.dev_solveXX(fx, fb, 0.1, sp)
+        qb.sync()
+        print("nlinks", nlinks, "links", rc, "iterations", sp.iterations, "launches", qb.launch_count())
     fb.free(); fx.free(); s.free()
 qb.finalize()
