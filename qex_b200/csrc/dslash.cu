@@ -358,8 +358,8 @@ struct FusedArgs {
   int npack, nint;
 };
 
-template <int NL, int RC, bool DOT>
-__global__ void __launch_bounds__(SWEEP_BLOCK, SWEEP_MINB) k_sweep_fused(const FusedArgs F) {
+template <int NL, int RC, bool DOT, int MINB>
+__global__ void __launch_bounds__(SWEEP_BLOCK, MINB) k_sweep_fused(const FusedArgs F) {
   const SweepArgs& A = F.A;
   const int bid = blockIdx.x;
   double dot = 0.0;
@@ -595,7 +595,8 @@ int sweep(const Gauge& g, int parity, double2* r, const double2* x, const double
     F.nint = grid;
     const int total = F.npack + F.nint + (nbd + SWEEP_BLOCK - 1) / SWEEP_BLOCK;
     if ((size_t)total > c.npart) return fail("sweep: %d blocks exceed the %zu reduction slots", total, c.npart);
-    QB_DISPATCH(g, fused_dot, k_sweep_fused<NL, RC, DOT><<<total, SWEEP_BLOCK, 0, c.stream>>>(F));
+    // residency 6 blocks/SM measured best for every variant (tools/tune_fused.py: 5, 4, 3 are 1-20 % slower)
+    QB_DISPATCH(g, fused_dot, k_sweep_fused<NL, RC, DOT, SWEEP_MINB><<<total, SWEEP_BLOCK, 0, c.stream>>>(F));
     count_launch();
     QB_CUDA(cudaGetLastError());
     return 0;
