@@ -143,6 +143,19 @@ int qexb200_solveXX(qexb200_gauge_t g, int parity, double* r, const double* x, d
 int qexb200_solve(qexb200_gauge_t g, double* x, const double* b, double m,
                   qexb200_solver_params* sp);
 
+/* ---- multi-shift solves (src/solvers/cgm.nim:84-316, src/physics/stagSolve.nim:296-446) ---- */
+
+/* solveXX(s, xs, b, ms, sp0, subset): (A + sigma_k) xs[k] = b on `parity`, A = stagD2ee/oo(shifts[0]^2),
+ * sigma_0 = 0, sigma_k = shifts[k] for k > 0 (the caller passes shifts[0] = m_0, shifts[k] =
+ * 4 (m_k^2 - m_0^2), stagSolve.nim:391-394).  xs[k] is zeroed on the subset, the other parity is
+ * left alone.  sp->iterations = iterations of the unshifted system; sp->r2 = 0 like the reference. */
+int qexb200_solveXX_multi(qexb200_gauge_t g, int parity, double* const* xs, const double* b,
+                          const double* shifts, int nmass, qexb200_solver_params* sp);
+/* solve(s, xs, b, ms, sp0): xs[k] = Ddag(m_k) (D Ddag)(m_k)^-1 b through the even/odd multi-shift
+ * solve with the true-residual loop on mass ms[0] (stagSolve.nim:347-446). */
+int qexb200_solve_multi(qexb200_gauge_t g, double* const* xs, const double* b, const double* ms,
+                        int nmass, qexb200_solver_params* sp);
+
 /* ---- device-resident fields (callers that keep vectors on the GPU) ------- */
 
 int qexb200_field_create(qexb200_field_t* f);
@@ -166,6 +179,10 @@ int qexb200_dev_solveXX(qexb200_gauge_t g, int parity, qexb200_field_t r, qexb20
                         double m, qexb200_solver_params* sp);
 int qexb200_dev_solve(qexb200_gauge_t g, qexb200_field_t x, qexb200_field_t b, double m,
                       qexb200_solver_params* sp);
+int qexb200_dev_solveXX_multi(qexb200_gauge_t g, int parity, const qexb200_field_t* xs, qexb200_field_t b,
+                              const double* shifts, int nmass, qexb200_solver_params* sp);
+int qexb200_dev_solve_multi(qexb200_gauge_t g, const qexb200_field_t* xs, qexb200_field_t b,
+                            const double* ms, int nmass, qexb200_solver_params* sp);
 
 /* ---- halo plan (pure host arithmetic, usable without a GPU) ---------------- */
 

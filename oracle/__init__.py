@@ -82,6 +82,10 @@ def lib():
         L.orc_solveXX.argtypes = [vp, C.c_int, dp, dp, dp, C.c_double, C.c_int, C.c_double, C.c_int, dp]
         L.orc_solve.argtypes = [vp, C.c_int, dp, dp, dp, C.c_double, C.c_double, C.c_int, C.c_int,
                                 C.POINTER(SolveStats)]
+        L.orc_cgm_xx.restype = C.c_int
+        L.orc_cgm_xx.argtypes = [vp, C.c_int, dp, dp, dp, C.c_double, dp, C.c_int, C.c_int, C.c_double, C.c_int, dp, dp]
+        L.orc_solve_multi.restype = C.c_int
+        L.orc_solve_multi.argtypes = [vp, C.c_int, dp, dp, dp, dp, C.c_int, C.c_double, C.c_int, C.POINTER(SolveStats)]
         L.orc_layout_setup.argtypes = [C.POINTER(OrcLayout), ip, ip, ip]
         L.orc_layout_index.argtypes = [C.POINTER(OrcLayout), ip, ip, ip]
         L.orc_layout_coord.argtypes = [C.POINTER(OrcLayout), C.c_int, C.c_int, ip]
@@ -208,6 +212,24 @@ class Lattice:
     def solve(self, g, x, b, m, r2req, maxits=50000, usePrevSoln=False):
         st = SolveStats()
         lib().orc_solve(self.h, g.shape[0], _dp(g), _dp(x), _dp(b), m, r2req, maxits, int(usePrevSoln), C.byref(st))
+        return st
+
+    def cgm_xx(self, g, xs, b, m2, sigmas, parity, r2req, maxits):
+        """Multi-shift CG (cgm.nim:84-316): xs float64[nmass, vol, 3, 2]; returns (iterations, r2, b2)."""
+        sg = np.ascontiguousarray(sigmas, dtype=np.float64)
+        r2, b2 = C.c_double(), C.c_double()
+        it = lib().orc_cgm_xx(self.h, g.shape[0], _dp(g), _dp(xs), _dp(b), m2, _dp(sg), len(sg), parity, r2req,
+                              maxits, C.byref(r2), C.byref(b2))
+        return it, r2.value, b2.value
+
+    def solve_multi(self, g, xs, b, ms, r2req, maxits=50000):
+        """solve(s, xs, b, ms, sp) (stagSolve.nim:347-446)."""
+        m = np.ascontiguousarray(ms, dtype=np.float64)
+        st = SolveStats()
+        rc = lib().orc_solve_multi(self.h, g.shape[0], _dp(g), _dp(xs), _dp(b), _dp(m), len(m), r2req, maxits,
+                                   C.byref(st))
+        if rc != 0:
+            raise RuntimeError("solve_multi: no subset qualifies for a solve")
         return st
 
 

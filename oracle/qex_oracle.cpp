@@ -675,6 +675,126 @@ void orc_solve(void* lat, int nd, const double* g, double* x, const double* b, d
   if (st) { st->iterations = its; st->calls = calls; st->r2 = (b2 > 0 ? r2 / b2 : 0.0); st->b2 = b2; }
 }
 
+// ---------------------------------------------------------------------------
+// Multi-shift CG  (src/solvers/cgm.nim:84-316, cpNone: z=r, q=ps[0], LAp=Ap), new solution
+// (b2 < 0 branch, :166-172).  Solves (A + sigma_k) xs[k] = b on `parity`, A = stagD2xx(m2),
+// sg[0] = 0, sg[k>0] = sigmas[k] (:107-110).  xs: nmass full-lattice vectors, contiguous.
+// Returns iterations; *r2out = final r2 of the unshifted system, *b2out = |b|^2 on the subset.
+// ---------------------------------------------------------------------------
+int orc_cgm_xx(void* lat, int nd, const double* g, double* xs, const double* b, double m2,
+               const double* sigmas, int nmass, int parity, double r2req, int maxits,
+               double* r2out, double* b2out) {
+  Lat* l = (Lat*)lat;
+  const size_t n = (size_t)l->vol * 6;
+  size_t lo, hi; sub_range(l, parity, lo, hi);
+  std::vector<double> r(n, 0.0), Ap(n, 0.0), t(n, 0.0), ps((size_t)nmass * n, 0.0);
+  std::vector<double> sg(nmass), zi(nmass, 1.0), zim1(nmass, 1.0);
+  for (int m = 0; m < nmass; m++) sg[m] = (m == 0) ? 0.0 : sigmas[m];
+#pragma omp parallel for
+  for (size_t i = lo; i < hi; i++) r[i] = b[i];                              // :168
+  for (int m = 0; m < nmass; m++)
+    for (size_t i = lo; i < hi; i++) xs[(size_t)m * n + i] = 0.0;            // :169
+  const double b2 = orc_norm2(lat, b, parity);
+  double r2 = b2;
+  const double r2stop = r2req * b2;                                          // :184
+  int itn = 0;
+  if (r2 > r2stop) {
+    double alpha = 0, beta = 0, alphaim1 = -1.0, betaim1 = 0.0, r2i = r2, r2ip1 = 0, r2r = 0;   // :199-211
+    double* p = ps.data();
+    for (int m = 0; m < nmass; m++)
+      for (size_t i = lo; i < hi; i++) ps[(size_t)m * n + i] = r[i];         // q := z ; ps[m] := p  (:205-218)
+    bool continuing = true;
+    while (continuing) {                                                     // :223
+      for (int m = 0; m < nmass; m++) {
+        if (m == 0) {
+          orc_stagD2xx(lat, nd, g, Ap.data(), p, m2, parity, t.data());      // :228
+          itn++;
+          const double qLAp = orc_redot(lat, p, Ap.data(), parity);          // :233
+          alpha = (qLAp != 0.0) ? r2i / qLAp : 0.0;
+          double* x = xs;
+#pragma omp parallel for
+          for (size_t i = lo; i < hi; i++) { r[i] -= alpha * Ap[i]; x[i] += alpha * p[i]; }   // :237-239
+          r2ip1 = orc_norm2(lat, r.data(), parity);                          // :245-248
+          r2r = r2ip1;
+          beta = (r2i != 0.0) ? r2ip1 / r2i : 0.0;                           // :252-254
+          continuing = (itn < maxits) && (r2r > r2stop);                     // :256
+          if (continuing) {
+#pragma omp parallel for
+            for (size_t i = lo; i < hi; i++) p[i] = r[i] + beta * p[i];      // :258
+          }
+        } else {                                                             // :260-274
+          double zip1d = alpha * betaim1 * (zim1[m] - zi[m]);
+          zip1d += zim1[m] * alphaim1 * (1.0 + sg[m] * alpha);
+          const double zip1 = (zip1d != 0.0) ? zi[m] * zim1[m] * alphaim1 / zip1d : 0.0;
+          const double zr = (zi[m] != 0.0) ? zip1 / zi[m] : 0.0;
+          double* xm = xs + (size_t)m * n;
+          double* pm = ps.data() + (size_t)m * n;
+          const double cx = alpha * zr;
+#pragma omp parallel for
+          for (size_t i = lo; i < hi; i++) xm[i] += cx * pm[i];
+          if (continuing) {
+            const double cp = beta * zr * zr;
+#pragma omp parallel for
+            for (size_t i = lo; i < hi; i++) pm[i] = zip1 * r[i] + cp * pm[i];
+            zim1[m] = zi[m]; zi[m] = zip1;
+          }
+        }
+      }
+      alphaim1 = alpha; betaim1 = beta; r2i = r2ip1;                          // :276
+      r2 = r2r;
+    }
+  }
+  if (r2out) *r2out = r2;
+  if (b2out) *b2out = b2;
+  return itn;
+}
+
+// solve(s, xs, b, ms, sp0), stagSolve.nim:347-446: xs[k] = Ddag(m_k) (D Ddag)^-1 b through the
+// even (or odd) multi-shift solve; shifts[0] = ms[0], shifts[k] = 4 (ms[k]^2 - ms[0]^2).
+// Returns -1 if neither parity qualifies for a solve (the reference would raise on subset "").
+int orc_solve_multi(void* lat, int nd, const double* g, double* xs, const double* b, const double* ms,
+                    int nmass, double r2req0, int maxits0, OrcSolveStats* st) {
+  Lat* l = (Lat*)lat;
+  const size_t n = (size_t)l->vol * 6, nh = (size_t)l->half * 6;
+  const double mass = ms[0];
+  double b2 = orc_norm2(lat, b, 2), b2e = orc_norm2(lat, b, 0), b2o = orc_norm2(lat, b, 1);
+  std::vector<double> r(b, b + n), ys((size_t)nmass * n, 0.0), xt(n, 0.0), shifts(nmass);
+  double r2 = b2e + b2o;
+  const double r2stop = r2req0 * b2;
+  for (int m = 0; m < nmass; m++) shifts[m] = (m == 0) ? ms[m] : 4.0 * (ms[m] * ms[m] - mass * mass);
+  memset(xs, 0, sizeof(double) * n * nmass);
+  int its = 0, calls = 0, subset = -1;
+  while (r2 > r2stop) {
+    const int maxits = maxits0 - its;
+    if (maxits <= 0) break;
+    double r2req = r2stop;
+    const double r2stop2 = 0.5 * r2req;
+    const double r2stope = (b2o <= r2stop2) ? r2req - b2o : r2stop2;
+    const double r2stopo = (b2e <= r2stop2) ? r2req - b2e : r2stop2;
+    if (b2e > r2stope) { r2req = r2stope / b2e; subset = 0; }
+    else if (b2o > r2stopo) { r2req = r2stopo / b2o; subset = 1; }
+    if (subset < 0) return -1;
+    std::fill(ys.begin(), ys.end(), 0.0);
+    its += orc_cgm_xx(lat, nd, g, ys.data(), r.data(), mass * mass, shifts.data(), nmass, subset, r2req, maxits,
+                      nullptr, nullptr);
+    calls++;
+    const size_t lo = subset == 0 ? 0 : nh, hi = subset == 0 ? nh : n;
+    for (int m = 0; m < nmass; m++)
+      for (size_t i = lo; i < hi; i++) xs[(size_t)m * n + i] += 4.0 * ys[(size_t)m * n + i];
+    orc_Ddag(lat, nd, g, xt.data(), xs, mass);
+    orc_D(lat, nd, g, r.data(), xt.data(), mass);
+    for (size_t i = 0; i < n; i++) r[i] = b[i] - r[i];
+    b2e = orc_norm2(lat, r.data(), 0); b2o = orc_norm2(lat, r.data(), 1);
+    r2 = b2e + b2o;
+  }
+  for (int m = 0; m < nmass; m++) {                                          // :431-437
+    if (m != 0 || calls == 0) orc_Ddag(lat, nd, g, xt.data(), xs + (size_t)m * n, ms[m]);
+    memcpy(xs + (size_t)m * n, xt.data(), sizeof(double) * n);
+  }
+  if (st) { st->iterations = its; st->calls = calls; st->r2 = (b2 > 0 ? r2 / b2 : 0.0); st->b2 = b2; }
+  return 0;
+}
+
 int orc_num_threads() { return omp_get_max_threads(); }
 void orc_set_num_threads(int n) { omp_set_num_threads(n); }
 

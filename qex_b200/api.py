@@ -67,6 +67,10 @@ def lib():
         L.qexb200_eoReconstruct.argtypes = [C.c_int, dp, dp, C.c_double]
         L.qexb200_solveXX.argtypes = [C.c_int, C.c_int, dp, dp, C.c_double, spp]
         L.qexb200_solve.argtypes = [C.c_int, dp, dp, C.c_double, spp]
+        L.qexb200_solveXX_multi.argtypes = [C.c_int, C.c_int, C.POINTER(dp), dp, dp, C.c_int, spp]
+        L.qexb200_solve_multi.argtypes = [C.c_int, C.POINTER(dp), dp, dp, C.c_int, spp]
+        L.qexb200_dev_solveXX_multi.argtypes = [C.c_int, C.c_int, ip, C.c_int, dp, C.c_int, spp]
+        L.qexb200_dev_solve_multi.argtypes = [C.c_int, ip, C.c_int, dp, C.c_int, spp]
         L.qexb200_field_create.argtypes = [ip]
         L.qexb200_field_destroy.argtypes = [C.c_int]
         L.qexb200_field_upload.argtypes = [C.c_int, dp]
@@ -331,6 +335,36 @@ class Staggered:
         _ck(lib().qexb200_solve(self.h, _dp(x), _dp(b), m, C.byref(c)))
         sp._addStats(c)
         return sp
+
+    # multi-shift (solveXX(s, xs, b, ms, ...) / solve(s, xs, b, ms, sp), stagSolve.nim:296-446)
+    def solveXX_multi(self, xs, b, shifts, sp, parEven=True):
+        arr = (C.POINTER(C.c_double) * len(xs))(*[_dp(x) for x in xs])
+        sh = (C.c_double * len(xs))(*[float(t) for t in shifts])
+        c = sp._c()
+        _ck(lib().qexb200_solveXX_multi(self.h, EVEN if parEven else ODD, arr, _dp(b), sh, len(xs), C.byref(c)))
+        sp._addStats(c)
+
+    def solve_multi(self, xs, b, ms, sp):
+        arr = (C.POINTER(C.c_double) * len(xs))(*[_dp(x) for x in xs])
+        mm = (C.c_double * len(xs))(*[float(t) for t in ms])
+        c = sp._c()
+        _ck(lib().qexb200_solve_multi(self.h, arr, _dp(b), mm, len(xs), C.byref(c)))
+        sp._addStats(c)
+        return sp
+
+    def dev_solveXX_multi(self, xs, b, shifts, sp, parEven=True):
+        hs = (C.c_int * len(xs))(*[x.h for x in xs])
+        sh = (C.c_double * len(xs))(*[float(t) for t in shifts])
+        c = sp._c()
+        _ck(lib().qexb200_dev_solveXX_multi(self.h, EVEN if parEven else ODD, hs, b.h, sh, len(xs), C.byref(c)))
+        sp._addStats(c)
+
+    def dev_solve_multi(self, xs, b, ms, sp):
+        hs = (C.c_int * len(xs))(*[x.h for x in xs])
+        mm = (C.c_double * len(xs))(*[float(t) for t in ms])
+        c = sp._c()
+        _ck(lib().qexb200_dev_solve_multi(self.h, hs, b.h, mm, len(xs), C.byref(c)))
+        sp._addStats(c)
 
     # device-field operators
     def dev_D(self, r, x, m):

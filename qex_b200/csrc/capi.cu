@@ -238,6 +238,103 @@ static int op_solve(const Gauge& g, Field& x, const Field& b, double m, qexb200_
   return 0;
 }
 
+// solveXX(s, xs, b, ms, sp0, subset) with the multi-shift CG, stagSolve.nim:296-345.  shifts[0] is
+// the base mass m0 (A = stagD2xx(m0^2)), shifts[k>0] = sigma_k.  xs are zeroed on the subset only
+// (cgm.nim:169).
+static int op_solveXX_multi(const Gauge& g, int parity, Field* const* xs, const Field& b, const double* shifts,
+                            int nmass, qexb200_solver_params* sp) {
+  const double t0 = now_s();
+  std::vector<double2*> xp(nmass);
+  for (int m = 0; m < nmass; m++) xp[m] = hf(*xs[m], parity);
+  CgResult res;
+  QB_CHECK(cgm_xx(g, parity, xp.data(), hf(b, parity), shifts[0] * shifts[0], shifts, nmass, sp->r2req, sp->maxits, &res));
+  sp->calls = 1;
+  sp->iterations = res.iterations;
+  sp->iterations_max = res.iterations;
+  sp->seconds = now_s() - t0;
+  const double neven = (double)g_ctx.g.Vh * g_ctx.g.nranks;
+  sp->flops = (double)(g.nlinks * 4 * 72 + 60) * neven * res.iterations;   // stagSolve.nim:334
+  sp->r2 = 0.0;                                                             // sp.r2.push 0.0, :343
+  return 0;
+}
+
+struct MultiWork { std::vector<Field> ys, hx; Field xt; bool ok = false; int Vh = 0; };
+static MultiWork g_mw;
+static int multi_work(int nmass, bool host) {
+  if (g_mw.Vh != g_ctx.g.Vh) {
+    for (auto& f : g_mw.ys) cudaFree(f.d);
+    for (auto& f : g_mw.hx) cudaFree(f.d);
+    if (g_mw.ok) cudaFree(g_mw.xt.d);
+    g_mw = MultiWork();
+  }
+  if (!g_mw.ok) { QB_CHECK(new_field(&g_mw.xt)); g_mw.ok = true; g_mw.Vh = g_ctx.g.Vh; }
+  while ((int)g_mw.ys.size() < nmass) { Field f; QB_CHECK(new_field(&f)); g_mw.ys.push_back(f); }
+  while (host && (int)g_mw.hx.size() < nmass) { Field f; QB_CHECK(new_field(&f)); g_mw.hx.push_back(f); }
+  return 0;
+}
+
+// solve(s, xs, b, ms, sp0), stagSolve.nim:347-446: xs[k] = Ddag(m_k) y_k with (D Ddag)(m_k) y_k = b
+static int op_solve_multi(const Gauge& g, Field* const* xs, const Field& b, const double* ms, int nmass,
+                          qexb200_solver_params* sp0) {
+  const double t0 = now_s();
+  QB_CHECK(solve_work());
+  QB_CHECK(multi_work(nmass, false));
+  Field &r = g_sw.r, &xt = g_mw.xt;
+  const size_t nfull = 2 * nhalf();
+  const double mass = ms[0];
+  double b2, b2e, b2o;
+  QB_CHECK(norm2_host(b, QEXB200_ALL, &b2));
+  QB_CHECK(norm2_host(b, QEXB200_EVEN, &b2e));
+  QB_CHECK(norm2_host(b, QEXB200_ODD, &b2o));
+  QB_CHECK(blas_copy(r.d, b.d, nfull));
+  double r2 = b2e + b2o;
+  const double r2stop = sp0->r2req * b2;
+  std::vector<double> shifts(nmass);
+  std::vector<Field*> ys(nmass);
+  for (int m = 0; m < nmass; m++) {
+    shifts[m] = (m == 0) ? ms[m] : 4.0 * (ms[m] * ms[m] - mass * mass);   // :391-394
+    ys[m] = &g_mw.ys[m];
+    QB_CHECK(blas_zero(xs[m]->d, nfull));
+    QB_CHECK(blas_zero(ys[m]->d, nfull));
+  }
+  int its = 0, itsmax = 0, calls = 0, subset = -1;
+  while (r2 > r2stop) {
+    qexb200_solver_params sp = *sp0;
+    sp.maxits = sp0->maxits - its;
+    if (sp.maxits <= 0) break;
+    sp.r2req = r2stop;
+    const double r2stop2 = 0.5 * sp.r2req;
+    const double r2stope = (b2o <= r2stop2) ? sp.r2req - b2o : r2stop2;
+    const double r2stopo = (b2e <= r2stop2) ? sp.r2req - b2e : r2stop2;
+    if (b2e > r2stope) { sp.r2req = r2stope / b2e; subset = 0; }
+    else if (b2o > r2stopo) { sp.r2req = r2stopo / b2o; subset = 1; }
+    if (subset < 0) return fail("solve (multi-shift): no subset qualifies for a solve");   // reference: qexError, :323
+    QB_CHECK(op_solveXX_multi(g, subset, ys.data(), r, shifts.data(), nmass, &sp));
+    its += sp.iterations;
+    if (sp.iterations > itsmax) itsmax = sp.iterations;
+    calls++;
+    for (int m = 0; m < nmass; m++) QB_CHECK(blas_axpy(hf(*xs[m], subset), 4.0, hf(*ys[m], subset), nhalf()));
+    QB_CHECK(op_Ddag(g, xt, *xs[0], mass));
+    QB_CHECK(op_D(g, r, xt, mass));
+    QB_CHECK(blas_xmy(r.d, b.d, r.d, nfull));
+    QB_CHECK(norm2_host(r, QEXB200_EVEN, &b2e));
+    QB_CHECK(norm2_host(r, QEXB200_ODD, &b2o));
+    r2 = b2e + b2o;
+  }
+  for (int m = 0; m < nmass; m++) {                                        // :431-437
+    if (m != 0 || calls == 0) QB_CHECK(op_Ddag(g, xt, *xs[m], ms[m]));
+    QB_CHECK(blas_copy(xs[m]->d, xt.d, nfull));
+  }
+  sp0->calls = 1;
+  sp0->iterations = its;
+  sp0->iterations_max = itsmax;
+  sp0->seconds = now_s() - t0;
+  const double neven = (double)g_ctx.g.Vh * g_ctx.g.nranks;
+  sp0->flops = (double)(g.nlinks * 4 * 72 + 60) * neven * its + (double)(g.nlinks * 4 * 72 + 24) * neven;  // :334,444
+  sp0->r2 = b2 > 0 ? r2 / b2 : 0.0;
+  return 0;
+}
+
 // Local geometry of one rank; ranks are lexicographic with dimension 0 slowest (qlayout.nim:94-113).
 int make_geom(const int latsize[4], const int rankgeom[4], int myrank, Geom* gp) {
   Geom& g = *gp;
@@ -336,6 +433,9 @@ int qexb200_plan_halo(const int latsize[4], const int rankgeom[4], int myrank, i
   return 0;
 }
 
+struct HostTmp { Field a, b; bool ok = false; int Vh = 0; };
+static HostTmp g_ht;
+
 int qexb200_p2p_export(void* out64) {
   QB_CHECK(need_ctx());
   return p2p_export(out64);
@@ -354,6 +454,11 @@ int qexb200_finalize(void) {
   for (auto& kv : g_fields) cudaFree(kv.second.d);
   g_gauges.clear(); g_fields.clear();
   if (g_sw.ok) { cudaFree(g_sw.r.d); cudaFree(g_sw.y.d); cudaFree(g_sw.d.d); g_sw = SolveWork(); }
+  for (auto& f : g_mw.ys) cudaFree(f.d);
+  for (auto& f : g_mw.hx) cudaFree(f.d);
+  if (g_mw.ok) cudaFree(g_mw.xt.d);
+  g_mw = MultiWork();
+  if (g_ht.ok) { cudaFree(g_ht.a.d); cudaFree(g_ht.b.d); g_ht = HostTmp(); }
   cg_free();
   halo_free();
   p2p_free();
@@ -520,10 +625,9 @@ int qexb200_dev_solve(qexb200_gauge_t hg, qexb200_field_t x, qexb200_field_t b, 
 }
 
 // ---- host-buffer entry points: H2D, device op, D2H ---------------------------
-struct HostTmp { Field a, b; bool ok = false; int Vh = 0; };
-static HostTmp g_ht;
 static int host_tmp() {
   if (g_ht.ok && g_ht.Vh == g_ctx.g.Vh) return 0;
+  if (g_ht.ok) { cudaFree(g_ht.a.d); cudaFree(g_ht.b.d); g_ht = HostTmp(); }
   QB_CHECK(new_field(&g_ht.a)); QB_CHECK(new_field(&g_ht.b));
   g_ht.ok = true; g_ht.Vh = g_ctx.g.Vh;
   return 0;
@@ -596,6 +700,63 @@ int qexb200_solve(qexb200_gauge_t hg, double* x, const double* b, double m, qexb
   QB_CHECK(upload_vector(X, b));
   QB_CHECK(op_solve(*g, R, X, m, sp));
   QB_CHECK(download_vector(R, x));
+  sp->seconds = now_s() - t0;
+  return 0;
+}
+
+// ---- multi-shift solves -----------------------------------------------------------------------
+static int get_fields(const qexb200_field_t* hs, int n, std::vector<Field*>& out) {
+  out.resize(n);
+  for (int i = 0; i < n; i++) QB_CHECK(get_field(hs[i], &out[i]));
+  return 0;
+}
+int qexb200_dev_solveXX_multi(qexb200_gauge_t hg, int parity, const qexb200_field_t* xs, qexb200_field_t b,
+                              const double* shifts, int nmass, qexb200_solver_params* sp) {
+  QB_CHECK(need_ctx());
+  Gauge* g; QB_CHECK(get_gauge(hg, &g));
+  if (parity != 0 && parity != 1) return fail("solveXX (multi-shift): parity must be 0 or 1");
+  if (nmass < 1) return fail("solveXX (multi-shift): nmass must be >= 1");
+  std::vector<Field*> fx; QB_CHECK(get_fields(xs, nmass, fx));
+  Field* fb; QB_CHECK(get_field(b, &fb));
+  return op_solveXX_multi(*g, parity, fx.data(), *fb, shifts, nmass, sp);
+}
+int qexb200_dev_solve_multi(qexb200_gauge_t hg, const qexb200_field_t* xs, qexb200_field_t b, const double* ms,
+                            int nmass, qexb200_solver_params* sp) {
+  QB_CHECK(need_ctx());
+  Gauge* g; QB_CHECK(get_gauge(hg, &g));
+  if (nmass < 1) return fail("solve (multi-shift): nmass must be >= 1");
+  std::vector<Field*> fx; QB_CHECK(get_fields(xs, nmass, fx));
+  Field* fb; QB_CHECK(get_field(b, &fb));
+  return op_solve_multi(*g, fx.data(), *fb, ms, nmass, sp);
+}
+int qexb200_solveXX_multi(qexb200_gauge_t hg, int parity, double* const* xs, const double* b, const double* shifts,
+                          int nmass, qexb200_solver_params* sp) {
+  HOST_PROLOGUE(hg);
+  (void)R;
+  if (parity != 0 && parity != 1) return fail("solveXX (multi-shift): parity must be 0 or 1");
+  if (nmass < 1) return fail("solveXX (multi-shift): nmass must be >= 1");
+  const double t0 = now_s();
+  QB_CHECK(multi_work(nmass, true));
+  std::vector<Field*> fx(nmass);
+  for (int m = 0; m < nmass; m++) { fx[m] = &g_mw.hx[m]; QB_CHECK(upload_vector(*fx[m], xs[m])); }   // other parity is preserved
+  QB_CHECK(upload_vector(X, b));
+  QB_CHECK(op_solveXX_multi(*g, parity, fx.data(), X, shifts, nmass, sp));
+  for (int m = 0; m < nmass; m++) QB_CHECK(download_vector(*fx[m], xs[m]));
+  sp->seconds = now_s() - t0;
+  return 0;
+}
+int qexb200_solve_multi(qexb200_gauge_t hg, double* const* xs, const double* b, const double* ms, int nmass,
+                        qexb200_solver_params* sp) {
+  HOST_PROLOGUE(hg);
+  (void)R;
+  if (nmass < 1) return fail("solve (multi-shift): nmass must be >= 1");
+  const double t0 = now_s();
+  QB_CHECK(multi_work(nmass, true));
+  std::vector<Field*> fx(nmass);
+  for (int m = 0; m < nmass; m++) fx[m] = &g_mw.hx[m];
+  QB_CHECK(upload_vector(X, b));
+  QB_CHECK(op_solve_multi(*g, fx.data(), X, ms, nmass, sp));
+  for (int m = 0; m < nmass; m++) QB_CHECK(download_vector(*fx[m], xs[m]));
   sp->seconds = now_s() - t0;
   return 0;
 }

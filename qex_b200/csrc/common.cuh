@@ -218,6 +218,8 @@ int check_device_error();
 struct CgResult { int iterations; double r2, b2; };
 int cg_xx(const Gauge& g, int parity, double2* x, const double2* b, double m2, double r2req,
           int maxits, bool x_is_zero, CgResult* res);
+int cgm_xx(const Gauge& g, int parity, double2* const* xs, const double2* b, double m2, const double* sigmas,
+           int nmass, double r2req, int maxits, CgResult* res);
 int apply_xx_public(const Gauge& g, int parity, double2* out, const double2* x, double m2);
 int cg_free();
 

@@ -281,6 +281,87 @@ def test_solve_parity(orc, ctx_factory, L, nlinks, m, r2req):
     s.free()
 
 
+@pytest.mark.parametrize("L,nlinks,ms,r2req", [
+    ((8, 8, 8, 8), 4, (0.1, 0.2, 0.5), 1e-12),
+    ((8, 8, 8, 16), 8, (0.05, 0.1, 0.3, 1.0), 1e-10),
+    ((4, 6, 8, 10), 4, (0.2,), 1e-16),                 # a single mass: plain CG through the multi-shift code
+])
+def test_multishift_solveXX_parity(orc, ctx_factory, L, nlinks, ms, r2req):
+    """solveXX(s, xs, b, ms, sp, subset) (stagSolve.nim:296-345, cgm.nim:84-316): same iteration count
+    (+-1) and solutions as the oracle's multi-shift CG, on both subsets; every xs[k] satisfies its own
+    shifted system; the untouched parity of xs is preserved."""
+    qb = ctx_factory(L)
+    lat, g, (b, junk) = make_inputs(L, nlinks)
+    s = qb.Staggered([g[k] for k in range(nlinks)])
+    shifts = [ms[0]] + [4.0 * (m * m - ms[0] ** 2) for m in ms[1:]]
+    for par_even in (True, False):
+        parity = 0 if par_even else 1
+        sl = slice(0, lat.half) if par_even else slice(lat.half, lat.vol)
+        osl = slice(lat.half, lat.vol) if par_even else slice(0, lat.half)
+        want = np.zeros((len(ms),) + b.shape)
+        it_o, r2_o, b2_o = lat.cgm_xx(g, want, b, ms[0] ** 2, shifts, parity, r2req, 10000)
+        got = [junk.copy() for _ in ms]
+        sp = qb.SolverParams(r2req=r2req, maxits=10000)
+        s.solveXX_multi(got, b, shifts, sp, parEven=par_even)
+        assert abs(sp.iterations - it_o) <= 1, (sp.iterations, it_o)
+        assert sp.flops == (nlinks * 4 * 72 + 60) * lat.half * sp.iterations
+        for k, m in enumerate(ms):
+            assert np.array_equal(got[k][osl], junk[osl])
+            assert rel_l2(got[k][sl], want[k][sl]) <= 10 * np.sqrt(r2req)
+            Ax = lat.vector()
+            lat.stagD2xx(g, Ax, got[k], m * m, parity)
+            tr = float(((Ax - b)[sl] ** 2).sum() / (b[sl] ** 2).sum())
+            assert tr <= 1.01 * r2req, (k, tr)
+    # maxits is honoured, and every shifted solution still gets that iteration's update
+    got = [lat.vector() for _ in ms]
+    want = np.zeros((len(ms),) + b.shape)
+    lat.cgm_xx(g, want, b, ms[0] ** 2, shifts, 0, 1e-30, 5)
+    sp = qb.SolverParams(r2req=1e-30, maxits=5)
+    s.solveXX_multi(got, b, shifts, sp)
+    assert sp.iterations == 5
+    for k in range(len(ms)):
+        assert rel_l2(got[k][:lat.half], want[k][:lat.half]) <= 1e-11
+    s.free()
+
+
+@pytest.mark.parametrize("L,nlinks,ms,r2req", [
+    ((8, 8, 8, 8), 4, (0.1, 0.2, 0.5), 1e-12),
+    ((8, 8, 8, 8), 8, (0.05, 0.25), 1e-10),
+])
+def test_multishift_solve_parity(orc, ctx_factory, L, nlinks, ms, r2req):
+    """solve(s, xs, b, ms, sp) (stagSolve.nim:347-446) and the reference's own check of it
+    (stagSolve.nim:651-661): multi-shift result == repeated single-mass solves."""
+    qb = ctx_factory(L)
+    lat, g, (b, _) = make_inputs(L, nlinks)
+    s = qb.Staggered([g[k] for k in range(nlinks)])
+    want = np.zeros((len(ms),) + b.shape)
+    st = lat.solve_multi(g, want, b, ms, r2req, 20000)
+    got = [lat.vector() for _ in ms]
+    sp = qb.SolverParams(r2req=r2req, maxits=20000)
+    s.solve_multi(got, b, ms, sp)
+    assert abs(sp.iterations - st.iterations) <= max(1, st.calls), (sp.iterations, st.iterations)
+    assert sp.r2 <= r2req
+    for k, m in enumerate(ms):
+        assert rel_l2(got[k], want[k]) <= 10 * np.sqrt(r2req)
+        Dx = lat.vector()
+        lat.D(g, Dx, got[k], m)
+        assert lat.norm2(Dx - b) / lat.norm2(b) <= 2 * r2req
+        single = lat.vector()
+        s.solve(single, b, m, qb.SolverParams(r2req=r2req, maxits=20000))
+        assert rel_l2(got[k], single) <= 20 * np.sqrt(r2req)
+    # device-resident entry point gives the same numbers
+    fb = qb.DeviceField(b)
+    fxs = [qb.DeviceField() for _ in ms]
+    sp2 = qb.SolverParams(r2req=r2req, maxits=20000)
+    s.dev_solve_multi(fxs, fb, ms, sp2)
+    assert sp2.iterations == sp.iterations
+    for k in range(len(ms)):
+        assert np.array_equal(fxs[k].download(lat.vector()), got[k])
+        fxs[k].free()
+    fb.free()
+    s.free()
+
+
 def test_solve_structural_identities(orc, ctx_factory):
     """solve(D x0) == x0 (stagSolve.nim:556-574); usePrevSoln restart converges in 0 iterations;
     zero source gives zero (cg.nim:139-144); maxits is honoured."""
