@@ -345,6 +345,8 @@ def run_ours(args):
             "cg_gflops": rr["gflops"], "time_to_solution_ms": rr["ms_per_step"], "cg_iterations": rr["iterations"],
             "e2e_gflops": rr["e2e_gflops"], "roofline": roof(rr, nlinks)}
     line["variants"] = variants
+    if world == 1:
+        line["link_pipeline"] = link_pipeline_leg(qb, nsites, peak, rank, cpu=not args.no_cpu)
     if world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_reference_leg(lat_shape, 4, args.ref_solves)
     else:
@@ -354,6 +356,48 @@ def run_ours(args):
         dist.destroy_process_group()
     if rank == 0:
         print(json.dumps(line))
+
+
+# Compulsory HBM traffic of the device link pipeline in matrix passes (144 B per site each): every
+# distinct field a launch reads counted once, every field it writes once.
+HYP_PASSES = 12 * 3 + 12 * 6 + 4 * 8
+HISQ_PASSES = 4 * (3 * (5 + 10 + 6) - 1) + 4 * (3 * (5 + 10 + 8) - 1) + 4 * 2 + 4 * 2
+
+
+def link_pipeline_leg(qb, nsites, peak, rank, cpu=True, reps=3):
+    """HisqCoefs.smear and HypCoefs.smear on resident links (what an HMC force step does before
+    its solves), timed with CUDA events on the library's stream; the oracle's CPU time per site beside."""
+    from qex_b200.synth import random_su3_links
+    g = qb.DeviceGauge(random_su3_links(nsites, 4, seed=5 + rank))
+    fl, ll = qb.DeviceGauge(nlinks=4), qb.DeviceGauge(nlinks=4)
+    hc, yc = qb.HisqCoefs().init(), qb.HypCoefs(0.4, 0.5, 0.5)
+    out = {"unit": "ms per smear of the whole lattice", "sites": nsites}
+    for name, fn, passes in (("hisq", lambda: hc.smear(g, fl, ll), HISQ_PASSES), ("nhyp", lambda: yc.smear(g, fl), HYP_PASSES)):
+        fn()
+        qb.sync()
+        qb.launch_count(reset=True)
+        qb.timer_start()
+        for _ in range(reps):
+            fn()
+        ms = qb.timer_stop() / reps
+        gbs = 1e-9 * nsites * passes * 144 / (1e-3 * ms)
+        out[name] = {"ms": ms, "launches": qb.launch_count() // reps, "algorithmic_bytes_per_site": passes * 144,
+                     "achieved_gbs": gbs, "frac_of_hbm_peak": gbs / peak}
+    out["plaq_fat"] = [float(t) for t in fl.plaq()]
+    for d in (g, fl, ll):
+        d.free()
+    if cpu:
+        import oracle
+        Ls = (16, 16, 16, 16)
+        lat = oracle.Lattice(Ls)
+        gg = lat.random_gauge(lat.new_rng(1))
+        t0 = time.perf_counter(); lat.hisq_smear(gg, oracle.hisq_coefs()); t1 = time.perf_counter()
+        lat.hyp_smear(gg, (0.4, 0.5, 0.5)); t2 = time.perf_counter()
+        scale = nsites / lat.vol
+        out["cpu_port"] = {"sample": "oracle (C++/OpenMP restatement) on 16^4, scaled by sites to this lattice",
+                           "cores": oracle.num_threads(), "hisq_ms": 1e3 * (t1 - t0) * scale,
+                           "nhyp_ms": 1e3 * (t2 - t1) * scale}
+    return out
 
 
 def ncu_traffic(nlinks, recon):

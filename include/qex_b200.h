@@ -116,6 +116,42 @@ int qexb200_gauge_recon(qexb200_gauge_t g, int want, int got[2], double dev[2]);
  * (stagD.nim:72-80,509-522; gauge/gaugeUtils.nim:124-131).  One-hop links only. */
 int qexb200_gauge_rephase(qexb200_gauge_t g);
 
+/* ---- device link pipeline ------------------------------------
+ * The smearing steps QEX runs on the CPU before every solve of an HMC force step
+ * (src/stagg_pv_hmc/staghmc_spv.nim:367-386; src/physics/hisqLinks.nim:32-39), on the resident links:
+ * thin links are uploaded once with qexb200_gauge_load, smeared, rephased and solved on without
+ * leaving the GPU.  All handles here hold 4 link fields unless stated.  Single rank for now: on a
+ * lattice split over ranks these return an error (no silent host path). */
+typedef struct {   /* Fat7lCoefs, src/gauge/fat7l.nim:5-10 */
+  double one_link, three_staple, five_staple, seven_staple, lepage;
+} qexb200_fat7l_coefs;
+typedef struct {   /* HisqCoefs, src/physics/hisqLinks.nim:4-8 */
+  qexb200_fat7l_coefs fat7first, fat7second;
+  double naik;
+} qexb200_hisq_coefs;
+typedef struct {   /* HypCoefs, src/gauge/hypsmear.nim:16-19 */
+  double alpha1, alpha2, alpha3;
+} qexb200_hyp_coefs;
+/* HisqCoefs.init (hisqLinks.nim:17-24) */
+void qexb200_hisq_coefs_init(qexb200_hisq_coefs* c);
+/* makeImpLinks(fl, gf, coef, ll, gfLong, naik) (fat7l.nim:78-162).  naik == 0: ll / gfLong are
+ * ignored (pass -1), the 4-argument overload of fat7l.nim:164-165. */
+int qexb200_gauge_makeImpLinks(qexb200_gauge_t fl, qexb200_gauge_t gf, const qexb200_fat7l_coefs* coef,
+                               qexb200_gauge_t ll, qexb200_gauge_t gfLong, double naik);
+/* HisqCoefs.smear(g, fl, ll) (hisqLinks.nim:32-43): fat7 -> projectU -> fat7 + Lepage + Naik */
+int qexb200_gauge_smear_hisq(qexb200_gauge_t fl, qexb200_gauge_t ll, qexb200_gauge_t g,
+                             const qexb200_hisq_coefs* coef);
+/* HypCoefs.smear(g, fl) (hypsmear.nim:49-162,269-273): three levels of projected staples */
+int qexb200_gauge_smear_hyp(qexb200_gauge_t fl, qexb200_gauge_t g, const qexb200_hyp_coefs* coef);
+/* dst[mu][x] = projectU(src[mu][x]) (src/maths/matrixFunctions.nim:301-312); same link count */
+int qexb200_gauge_projectU(qexb200_gauge_t dst, qexb200_gauge_t src);
+/* plaq (src/gauge/gaugeUtils.nim:213-284) of the one-hop links: pl[mu(mu-1)/2 + nu], nu < mu */
+int qexb200_gauge_plaq(qexb200_gauge_t g, double pl[6]);
+/* newStag3(fl, ll) (stagD.nim:552-564): out (8 link fields) = {fl[0], ll[0], fl[1], ll[1], ...} */
+int qexb200_gauge_join3(qexb200_gauge_t out, qexb200_gauge_t fl, qexb200_gauge_t ll);
+/* device links -> native QEX host memory, links[k] as in qexb200_gauge_load */
+int qexb200_gauge_download(qexb200_gauge_t g, double* const* links);
+
 /* ---- operator on HOST fields (each call: H2D, kernels, D2H) --------------- */
 
 /* stagD2 (stagD.nim:348-395): r[p] = a*r + b*x + sum_k [U_k x(+h_k) - U_k^+ x(-h_k)] */

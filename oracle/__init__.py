@@ -86,6 +86,10 @@ def lib():
         L.orc_cgm_xx.argtypes = [vp, C.c_int, dp, dp, dp, C.c_double, dp, C.c_int, C.c_int, C.c_double, C.c_int, dp, dp]
         L.orc_solve_multi.restype = C.c_int
         L.orc_solve_multi.argtypes = [vp, C.c_int, dp, dp, dp, dp, C.c_int, C.c_double, C.c_int, C.POINTER(SolveStats)]
+        L.orc_makeImpLinks.argtypes = [vp, dp, dp, dp, dp, C.c_double, dp]
+        L.orc_projectU_field.argtypes = [vp, dp, dp, C.c_int]
+        L.orc_hisq_smear.argtypes = [vp, dp, dp, dp, dp]
+        L.orc_hyp_smear.argtypes = [vp, dp, dp, dp]
         L.orc_layout_setup.argtypes = [C.POINTER(OrcLayout), ip, ip, ip]
         L.orc_layout_index.argtypes = [C.POINTER(OrcLayout), ip, ip, ip]
         L.orc_layout_coord.argtypes = [C.POINTER(OrcLayout), C.c_int, C.c_int, ip]
@@ -168,6 +172,39 @@ class Lattice:
 
     def stagPhase(self, g):
         lib().orc_stagphase(self.h, _dp(g))
+
+    # -- link smearing -----------------------------------------------------
+    def makeImpLinks(self, gf, coef, gfLong=None, naik=0.0):
+        """makeImpLinks (fat7l.nim:78-162). coef = (oneLink, threeStaple, fiveStaple, sevenStaple, lepage).
+        Returns fl, or (fl, ll) when naik != 0."""
+        c = np.ascontiguousarray(coef, dtype=np.float64)
+        fl = self.gauge(4)
+        if naik != 0.0:
+            ll = self.gauge(4)
+            lib().orc_makeImpLinks(self.h, _dp(gf), _dp(c), _dp(fl), _dp(gfLong), naik, _dp(ll))
+            return fl, ll
+        lib().orc_makeImpLinks(self.h, _dp(gf), _dp(c), _dp(fl), None, 0.0, None)
+        return fl
+
+    def projectU(self, g):
+        out = np.zeros_like(g)
+        lib().orc_projectU_field(self.h, _dp(g), _dp(out), g.shape[0])
+        return out
+
+    def hisq_smear(self, g, coefs):
+        """HisqCoefs.smear (hisqLinks.nim:32-39); coefs = fat7first[5] + fat7second[5] + [naik]."""
+        c = np.ascontiguousarray(coefs, dtype=np.float64)
+        assert c.shape == (11,)
+        fl, ll = self.gauge(4), self.gauge(4)
+        lib().orc_hisq_smear(self.h, _dp(g), _dp(c), _dp(fl), _dp(ll))
+        return fl, ll
+
+    def hyp_smear(self, g, alpha):
+        """HypCoefs.smear (hypsmear.nim:49-162); alpha = (alpha1, alpha2, alpha3)."""
+        a = np.ascontiguousarray(alpha, dtype=np.float64)
+        fl = self.gauge(4)
+        lib().orc_hyp_smear(self.h, _dp(g), _dp(a), _dp(fl))
+        return fl
 
     # -- operator ----------------------------------------------------------
     def stagD2(self, g, r, x, a, b, parity):
@@ -308,6 +345,13 @@ class QexLayout:
         c = (C.c_int * 4)()
         lib().orc_layout_coord(C.byref(self.s), rank, index, c)
         return tuple(c)
+
+
+def hisq_coefs(f7lf=0.0, naik=1.0):
+    """HisqCoefs.init + setHisqFat7 (hisqLinks.nim:10-24) as the flat 11-vector hisq_smear takes."""
+    def fat7(f, n):
+        return [(1.0 + 3.0 * f + n) / 8.0, -1.0 / 16.0, 1.0 / 64.0, -1.0 / 384.0, -f / 16.0]
+    return np.array(fat7(f7lf, 0.0) + fat7(2.0 - f7lf, naik) + [-naik / 24.0])
 
 
 def set_gauss_variant(v):

@@ -795,6 +795,196 @@ int orc_solve_multi(void* lat, int nd, const double* g, double* xs, const double
   return 0;
 }
 
+// ---------------------------------------------------------------------------
+// Link smearing: fat7 + Lepage + Naik (src/gauge/fat7l.nim:24-162), HISQ
+// (src/physics/hisqLinks.nim:9-43), nHYP (src/gauge/hypsmear.nim:49-162,
+// src/gauge/smearutil.nim:3-22).  Matrix fields are [vol] of M3; a link set is
+// 4 contiguous fields [mu][vol][18].  The restatement keeps the reference's
+// structure: shifted copies first (Shifter ^*), then site-local products.
+// ---------------------------------------------------------------------------
+typedef std::vector<M3> MF;
+static MF mf_load(Lat* l, const double* p) {
+  MF f(l->vol);
+#pragma omp parallel for
+  for (int i = 0; i < l->vol; i++) f[i] = m3_load(p + (size_t)i * 18);
+  return f;
+}
+static void mf_store(Lat* l, double* p, const MF& f) {
+#pragma omp parallel for
+  for (int i = 0; i < l->vol; i++) m3_store(p + (size_t)i * 18, f[i]);
+}
+// newShifter(f, mu, +1) ^* f : r(x) = f(x + mu);  len = -1 : r(x) = f(x - mu)
+static MF mf_shift(Lat* l, const MF& f, int mu, int len) {
+  MF r(l->vol);
+  const std::vector<int>& t = len > 0 ? l->fwd[mu][0] : l->bwd[mu][0];
+#pragma omp parallel for
+  for (int i = 0; i < l->vol; i++) r[i] = f[t[i]];
+  return r;
+}
+static inline void m3_axpy(M3& y, double a, const M3& x) {
+  for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) y.e[i][j] += a * x.e[i][j];
+}
+static inline M3 m3_scale(double a, const M3& x) {
+  M3 r; for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) r.e[i][j] = a * x.e[i][j]; return r;
+}
+
+// computeGenStaple, fat7l.nim:24-76.  staple == nullptr: the `bool` overload (not saved).
+static void gen_staple(Lat* l, MF* staple, int mu, int nu, const MF& link, bool link_is_gauge_mu, double coef,
+                       const MF* gauge, MF& flmu) {
+  (void)link_is_gauge_mu;
+  const MF ts0 = mf_shift(l, link, nu, +1);        // link(x+nu)
+  const MF ts1 = mf_shift(l, gauge[nu], mu, +1);   // gauge[nu](x+mu)
+  MF tmat2(l->vol);
+#pragma omp parallel for
+  for (int i = 0; i < l->vol; i++) {
+    const M3 up = m3_mul(m3_mul(gauge[nu][i], ts0[i]), m3_adj(ts1[i]));       // :43,48
+    if (staple) (*staple)[i] = up; else m3_axpy(flmu[i], coef, up);
+    tmat2[i] = m3_mul(m3_mul(m3_adj(gauge[nu][i]), link[i]), ts1[i]);         // :54
+  }
+  const MF ts2 = mf_shift(l, tmat2, nu, -1);                                  // :55
+#pragma omp parallel for
+  for (int i = 0; i < l->vol; i++) {
+    if (staple) { m3_axpy((*staple)[i], 1.0, ts2[i]); m3_axpy(flmu[i], coef, (*staple)[i]); }   // :60-61
+    else m3_axpy(flmu[i], coef, ts2[i]);                                      // :64
+  }
+}
+
+// makeImpLinks, fat7l.nim:78-162.  coef = {oneLink, threeStaple, fiveStaple, sevenStaple, lepage}.
+// gfl / ll may be NULL when naik == 0.
+void orc_makeImpLinks(void* lat, const double* gf_, const double* coef, double* fl_, const double* gfl_, double naik,
+                      double* ll_) {
+  Lat* l = (Lat*)lat;
+  const size_t fs = (size_t)l->vol * 18;
+  MF gf[4], fl[4];
+  for (int d = 0; d < 4; d++) gf[d] = mf_load(l, gf_ + d * fs);
+  double coef1 = coef[0];
+  const double coef3 = coef[1], coef5 = coef[2], coef7 = coef[3], coefL = coef[4];
+  const bool have5 = coef5 != 0.0 || coef7 != 0.0 || coefL != 0.0;
+  const bool have3 = coef3 != 0.0 || have5;
+  coef1 -= 6.0 * coefL;                                                       // :108
+  for (int dir = 0; dir < 4; dir++) {
+    fl[dir].resize(l->vol);
+#pragma omp parallel for
+    for (int i = 0; i < l->vol; i++) fl[dir][i] = m3_scale(coef1, gf[dir][i]);  // :135
+    if (!have3) continue;
+    for (int nu = 0; nu < 4; nu++) {
+      if (nu == dir) continue;
+      MF staple(l->vol), tempmat1(l->vol);
+      gen_staple(l, &staple, dir, nu, gf[dir], true, coef3, gf, fl[dir]);     // :139
+      if (coefL != 0.0) gen_staple(l, nullptr, dir, nu, staple, false, coefL, gf, fl[dir]);  // :141-143
+      if (coef5 != 0.0 || coef7 != 0.0) {
+        for (int rho = 0; rho < 4; rho++) {
+          if (rho == dir || rho == nu) continue;
+          gen_staple(l, &tempmat1, dir, rho, staple, false, coef5, gf, fl[dir]);  // :147
+          if (coef7 != 0.0) {
+            for (int sig = 0; sig < 4; sig++) {
+              if (sig == dir || sig == nu || sig == rho) continue;
+              gen_staple(l, nullptr, dir, sig, tempmat1, false, coef7, gf, fl[dir]);  // :152
+            }
+          }
+        }
+      }
+    }
+  }
+  if (naik != 0.0) {                                                          // :156-167
+    for (int dir = 0; dir < 4; dir++) {
+      const MF w = mf_load(l, gfl_ + dir * fs);
+      const MF s1 = mf_shift(l, w, dir, +1);
+      MF t(l->vol);
+#pragma omp parallel for
+      for (int i = 0; i < l->vol; i++) t[i] = m3_mul(w[i], s1[i]);
+      const MF s2 = mf_shift(l, t, dir, +1);
+      MF r(l->vol);
+#pragma omp parallel for
+      for (int i = 0; i < l->vol; i++) r[i] = m3_scale(naik, m3_mul(w[i], s2[i]));
+      mf_store(l, ll_ + dir * fs, r);
+    }
+  }
+  for (int d = 0; d < 4; d++) mf_store(l, fl_ + d * fs, fl[d]);
+}
+
+// projectU of every site of n fields (hisqLinks.nim:35-37, hypsmear.nim:28-34)
+void orc_projectU_field(void* lat, const double* in, double* out, int nfields) {
+  Lat* l = (Lat*)lat;
+  const size_t n = (size_t)l->vol * nfields;
+#pragma omp parallel for
+  for (size_t i = 0; i < n; i++) m3_store(out + i * 18, projectU(m3_load(in + i * 18)));
+}
+
+// HisqCoefs.smear, hisqLinks.nim:32-39.  c = {fat7first[5], fat7second[5], naik}.
+void orc_hisq_smear(void* lat, const double* g, const double* c, double* fl, double* ll) {
+  Lat* l = (Lat*)lat;
+  const size_t n = (size_t)l->vol * 18 * 4;
+  std::vector<double> t1(n), t2(n);
+  orc_makeImpLinks(lat, g, c, t1.data(), nullptr, 0.0, nullptr);
+  orc_projectU_field(lat, t1.data(), t2.data(), 4);
+  orc_makeImpLinks(lat, t2.data(), c + 5, fl, t2.data(), c[10], ll);
+}
+
+// symStaple, smearutil.nim:3-22: s += alp*[ g1 * s2 * s1^+  +  (g1^+ g2 s1)(x - d1) ],
+// s1 = g1 shifted from +d2, s2 = g2 shifted from +d1 (d1 / d2 = direction of g1 / g2).
+static void sym_staple(Lat* l, MF& s, double alp, const MF& g1, int d1, const MF& g2, int d2) {
+  const MF s1 = mf_shift(l, g1, d2, +1), s2 = mf_shift(l, g2, d1, +1);
+  MF tm(l->vol);
+#pragma omp parallel for
+  for (int i = 0; i < l->vol; i++) tm[i] = m3_mul(m3_mul(m3_adj(g1[i]), g2[i]), s1[i]);
+  const MF sm = mf_shift(l, tm, d1, -1);
+#pragma omp parallel for
+  for (int i = 0; i < l->vol; i++) {
+    m3_axpy(s[i], alp, m3_mul(m3_mul(g1[i], s2[i]), m3_adj(s1[i])));
+    m3_axpy(s[i], alp, sm[i]);
+  }
+}
+static void mf_project(MF& r, const MF& x) {
+#pragma omp parallel for
+  for (size_t i = 0; i < x.size(); i++) r[i] = projectU(x[i]);
+}
+
+// HypCoefs.smear = forward part of smearGetForce, hypsmear.nim:49-162.  alpha = {alpha1, alpha2, alpha3}.
+// Optional outputs (may be NULL): l1o/l2o [4][4][vol][18] projected level-1/2 links (diagonal unused).
+void orc_hyp_smear(void* lat, const double* g, const double* alpha, double* fl_) {
+  Lat* l = (Lat*)lat;
+  const size_t fs = (size_t)l->vol * 18;
+  MF gf[4], l1[4][4], l2[4][4];
+  for (int d = 0; d < 4; d++) gf[d] = mf_load(l, g + d * fs);
+  const double alp1 = alpha[0] / 2.0, alp2 = alpha[1] / 4.0, alp3 = alpha[2] / 6.0;
+  const double ma1 = 1 - alpha[0], ma2 = 1 - alpha[1], ma3 = 1 - alpha[2];
+  for (int mu = 0; mu < 4; mu++) for (int nu = 0; nu < 4; nu++) {
+    if (nu == mu) continue;
+    MF x(l->vol);
+#pragma omp parallel for
+    for (int i = 0; i < l->vol; i++) x[i] = m3_scale(ma1, gf[mu][i]);        // :107
+    sym_staple(l, x, alp1, gf[nu], nu, gf[mu], mu);                           // :108-109
+    l1[mu][nu].resize(l->vol);
+    mf_project(l1[mu][nu], x);
+  }
+  for (int mu = 0; mu < 4; mu++) for (int nu = 0; nu < 4; nu++) {
+    if (nu == mu) continue;
+    MF x(l->vol);
+#pragma omp parallel for
+    for (int i = 0; i < l->vol; i++) x[i] = m3_scale(ma2, gf[mu][i]);        // :117
+    for (int a = 0; a < 4; a++) {
+      if (a == mu || a == nu) continue;
+      const int b = 1 + 2 + 3 - mu - nu - a;
+      sym_staple(l, x, alp2, l1[a][b], a, l1[mu][b], mu);                     // :129-130
+    }
+    l2[mu][nu].resize(l->vol);
+    mf_project(l2[mu][nu], x);
+  }
+  for (int mu = 0; mu < 4; mu++) {
+    MF x(l->vol);
+#pragma omp parallel for
+    for (int i = 0; i < l->vol; i++) x[i] = m3_scale(ma3, gf[mu][i]);        // :136
+    for (int nu = 0; nu < 4; nu++) {
+      if (nu == mu) continue;
+      sym_staple(l, x, alp3, l2[nu][mu], nu, l2[mu][nu], mu);                 // :147-148
+    }
+    MF r(l->vol);
+    mf_project(r, x);
+    mf_store(l, fl_ + mu * fs, r);
+  }
+}
+
 int orc_num_threads() { return omp_get_max_threads(); }
 void orc_set_num_threads(int n) { omp_set_num_threads(n); }
 

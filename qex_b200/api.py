@@ -33,6 +33,32 @@ class HaloDir(C.Structure):
                 ("off_b", C.c_longlong), ("n_b", C.c_longlong)]
 
 
+class Fat7lCoefs(C.Structure):
+    """Fat7lCoefs (src/gauge/fat7l.nim:5-10)."""
+    _fields_ = [("oneLink", C.c_double), ("threeStaple", C.c_double), ("fiveStaple", C.c_double),
+                ("sevenStaple", C.c_double), ("lepage", C.c_double)]
+
+
+class HisqCoefs(C.Structure):
+    """HisqCoefs (src/physics/hisqLinks.nim:4-43): init() sets the HISQ defaults, smear(g, fl, ll)."""
+    _fields_ = [("fat7first", Fat7lCoefs), ("fat7second", Fat7lCoefs), ("naik", C.c_double)]
+
+    def init(self):
+        lib().qexb200_hisq_coefs_init(C.byref(self))
+        return self
+
+    def smear(self, g, fl, ll):
+        _ck(lib().qexb200_gauge_smear_hisq(fl.h, ll.h, g.h, C.byref(self)))
+
+
+class HypCoefs(C.Structure):
+    """HypCoefs (src/gauge/hypsmear.nim:16-19,269-273): smear(g, fl)."""
+    _fields_ = [("alpha1", C.c_double), ("alpha2", C.c_double), ("alpha3", C.c_double)]
+
+    def smear(self, g, fl):
+        _ck(lib().qexb200_gauge_smear_hyp(fl.h, g.h, C.byref(self)))
+
+
 def lib_path():
     return _LIBPATH
 
@@ -59,6 +85,15 @@ def lib():
         L.qexb200_gauge_destroy.argtypes = [C.c_int]
         L.qexb200_gauge_rephase.argtypes = [C.c_int]
         L.qexb200_gauge_recon.argtypes = [C.c_int, C.c_int, ip, dp]
+        L.qexb200_hisq_coefs_init.restype = None
+        L.qexb200_hisq_coefs_init.argtypes = [C.POINTER(HisqCoefs)]
+        L.qexb200_gauge_makeImpLinks.argtypes = [C.c_int, C.c_int, C.POINTER(Fat7lCoefs), C.c_int, C.c_int, C.c_double]
+        L.qexb200_gauge_smear_hisq.argtypes = [C.c_int, C.c_int, C.c_int, C.POINTER(HisqCoefs)]
+        L.qexb200_gauge_smear_hyp.argtypes = [C.c_int, C.c_int, C.POINTER(HypCoefs)]
+        L.qexb200_gauge_projectU.argtypes = [C.c_int, C.c_int]
+        L.qexb200_gauge_plaq.argtypes = [C.c_int, dp]
+        L.qexb200_gauge_join3.argtypes = [C.c_int, C.c_int, C.c_int]
+        L.qexb200_gauge_download.argtypes = [C.c_int, C.POINTER(dp)]
         L.qexb200_stagD2.argtypes = [C.c_int, C.c_int, dp, dp, C.c_double, C.c_double]
         L.qexb200_stagD.argtypes = [C.c_int, C.c_int, dp, dp, C.c_double, C.c_double, C.c_double]
         L.qexb200_D.argtypes = [C.c_int, dp, dp, C.c_double]
@@ -275,23 +310,40 @@ class DeviceField:
         self.h = None
 
 
-# ---- Staggered (src/physics/stagD.nim:15-22,522-586; stagSolve.nim) ---------------
-class Staggered:
-    """Staggered[G,T]: holds the link set (device resident) and offers D/Ddag/solve."""
+# ---- device link sets ---------------------------------------------------------------
+class DeviceGauge:
+    """A device-resident link set (4 or 8 link fields): lo.newGauge() + the link pipeline of
+    src/gauge/fat7l.nim, src/physics/hisqLinks.nim, src/gauge/hypsmear.nim on the GPU."""
 
-    def __init__(self, links):
-        self.nlinks = len(links)
+    def __init__(self, links=None, nlinks=4):
+        self.nlinks = len(links) if links is not None else int(nlinks)
         h = C.c_int()
         _ck(lib().qexb200_gauge_create(self.nlinks, C.byref(h)))
         self.h = h.value
-        self.load(links)
+        self._owner = True
+        if links is not None:
+            self.load(links)
 
     def load(self, links):
         arr = (C.POINTER(C.c_double) * self.nlinks)(*[_dp(l) for l in links])
         _ck(lib().qexb200_gauge_load(self.h, arr))
 
+    def download(self, links):
+        arr = (C.POINTER(C.c_double) * self.nlinks)(*[_dp(l) for l in links])
+        _ck(lib().qexb200_gauge_download(self.h, arr))
+        return links
+
     def rephase(self):
         _ck(lib().qexb200_gauge_rephase(self.h))
+
+    def plaq(self):
+        """plaq (src/gauge/gaugeUtils.nim:213-284) of the one-hop links."""
+        pl = np.zeros(6)
+        _ck(lib().qexb200_gauge_plaq(self.h, _dp(pl)))
+        return pl
+
+    def projectU(self, src):
+        _ck(lib().qexb200_gauge_projectU(self.h, src.h))
 
     def recon(self, want=12):
         """Ask for 12-real (rows 0,1 + rebuilt third row) or 18-real link storage; returns
@@ -301,9 +353,27 @@ class Staggered:
         return [got[0], got[1]], [dev[0], dev[1]]
 
     def free(self):
-        if self.h is not None and is_initialized():
+        if self.h is not None and self._owner and is_initialized():
             lib().qexb200_gauge_destroy(self.h)
         self.h = None
+
+
+def makeImpLinks(fl, gf, coef, ll=None, gfLong=None, naik=0.0):
+    """makeImpLinks(fl, gf, coef[, ll, gfLong, naik]) (src/gauge/fat7l.nim:78-165) on DeviceGauges."""
+    _ck(lib().qexb200_gauge_makeImpLinks(fl.h, gf.h, C.byref(coef), ll.h if ll is not None else -1,
+                                         gfLong.h if gfLong is not None else -1, float(naik)))
+
+
+# ---- Staggered (src/physics/stagD.nim:15-22,522-586; stagSolve.nim) ---------------
+class Staggered(DeviceGauge):
+    """Staggered[G,T]: holds the link set (device resident) and offers D/Ddag/solve.  Built from host
+    link fields (uploaded) or from a DeviceGauge (shared by reference, like newStag keeps `g`)."""
+
+    def __init__(self, links):
+        if isinstance(links, DeviceGauge):
+            self.nlinks, self.h, self._owner = links.nlinks, links.h, False
+        else:
+            DeviceGauge.__init__(self, links)
 
     # host-field operators
     def D(self, r, x, m):
@@ -395,6 +465,10 @@ class Staggered:
 
 def newStag(g):
     """newStag(g) (stagD.nim:533-542): naive one-hop operator from 4 link fields."""
+    if isinstance(g, DeviceGauge):
+        if g.nlinks != 4:
+            raise QexB200Error("newStag needs 4 link fields")
+        return Staggered(g)
     if len(g) != 4:
         raise QexB200Error("newStag needs 4 link fields")
     return Staggered(list(g))
@@ -403,6 +477,12 @@ def newStag(g):
 def newStag3(g, g3=None):
     """newStag3(g, g3) (stagD.nim:552-564): links interleaved as [fat0, long0, fat1, long1, ...];
     newStag3(g) with 8 fields takes them already interleaved (stagD.nim:543-551)."""
+    if isinstance(g, DeviceGauge) and isinstance(g3, DeviceGauge):
+        out = DeviceGauge(nlinks=8)
+        _ck(lib().qexb200_gauge_join3(out.h, g.h, g3.h))
+        s = Staggered(out)
+        s._owner, out._owner = True, False
+        return s
     if g3 is None:
         if len(g) != 8:
             raise QexB200Error("newStag3(g) needs 8 interleaved link fields")

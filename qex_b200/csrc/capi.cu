@@ -460,6 +460,7 @@ int qexb200_finalize(void) {
   g_mw = MultiWork();
   if (g_ht.ok) { cudaFree(g_ht.a.d); cudaFree(g_ht.b.d); g_ht = HostTmp(); }
   cg_free();
+  smear_free();
   halo_free();
   p2p_free();
   if (g_ctx.h_err) cudaFreeHost(g_ctx.h_err);
@@ -532,6 +533,120 @@ int qexb200_gauge_rephase(qexb200_gauge_t h) {
   QB_CHECK(need_ctx());
   Gauge* g; QB_CHECK(get_gauge(h, &g));
   return rephase(*g);
+}
+
+// ---- device link pipeline (smear.cu) -----------------------------------------
+static inline double2* link_field(Gauge* g, int k) { return g->d + (size_t)k * 18 * g_ctx.g.Vh; }
+// the four one-hop fields of a set (nlinks 4: k = mu; nlinks 8: k = 2 mu, stagD.nim:552-564)
+static void one_hop(Gauge* g, double2* out[4]) {
+  for (int mu = 0; mu < 4; mu++) out[mu] = link_field(g, g->nlinks == 8 ? 2 * mu : mu);
+}
+static int links_written(Gauge* g) {
+  g->loaded = true;
+  return compress_links(*g);
+}
+static int get_gauge4(int h, Gauge** g, const char* who, bool must_be_loaded) {
+  QB_CHECK(get_gauge(h, g));
+  if ((*g)->nlinks != 4) return fail("%s: gauge handle %d must hold 4 link fields (has %d)", who, h, (*g)->nlinks);
+  if (must_be_loaded && !(*g)->loaded) return fail("%s: gauge handle %d holds no links", who, h);
+  return 0;
+}
+
+void qexb200_hisq_coefs_init(qexb200_hisq_coefs* c) {   // HisqCoefs.init + setHisqFat7, hisqLinks.nim:10-24
+  const double f7lf = 0.0, naik = 1.0;
+  auto set = [](qexb200_fat7l_coefs& k, double f, double n) {
+    k.one_link = (1.0 + 3.0 * f + n) / 8.0; k.three_staple = -1.0 / 16.0; k.five_staple = 1.0 / 64.0;
+    k.seven_staple = -1.0 / 384.0; k.lepage = -f / 16.0;
+  };
+  set(c->fat7first, f7lf, 0.0);
+  set(c->fat7second, 2.0 - f7lf, naik);
+  c->naik = -naik / 24.0;
+}
+int qexb200_gauge_download(qexb200_gauge_t h, double* const* links) {
+  QB_CHECK(need_ctx());
+  Gauge* g; QB_CHECK(get_gauge(h, &g));
+  return download_links(*g, links);
+}
+int qexb200_gauge_plaq(qexb200_gauge_t h, double pl[6]) {
+  QB_CHECK(need_ctx());
+  Gauge* g; QB_CHECK(get_gauge(h, &g));
+  if (!g->loaded) return fail("gauge_plaq: gauge holds no links");
+  double2* u[4]; one_hop(g, u);
+  return plaq_links(u, pl);
+}
+int qexb200_gauge_projectU(qexb200_gauge_t hdst, qexb200_gauge_t hsrc) {
+  QB_CHECK(need_ctx());
+  Gauge *d, *s;
+  QB_CHECK(get_gauge(hdst, &d)); QB_CHECK(get_gauge(hsrc, &s));
+  if (d->nlinks != s->nlinks) return fail("gauge_projectU: link counts differ (%d vs %d)", d->nlinks, s->nlinks);
+  if (!s->loaded) return fail("gauge_projectU: source holds no links");
+  QB_CHECK(project_fields(d->d, s->d, s->nlinks));
+  return links_written(d);
+}
+int qexb200_gauge_makeImpLinks(qexb200_gauge_t hfl, qexb200_gauge_t hgf, const qexb200_fat7l_coefs* coef,
+                               qexb200_gauge_t hll, qexb200_gauge_t hgfl, double naik) {
+  QB_CHECK(need_ctx());
+  Gauge *fl, *gf, *ll = nullptr, *gfl = nullptr;
+  QB_CHECK(get_gauge4(hfl, &fl, "makeImpLinks(fl)", false));
+  QB_CHECK(get_gauge4(hgf, &gf, "makeImpLinks(gf)", true));
+  if (fl == gf) return fail("makeImpLinks: fl and gf must be different link sets");
+  const double c[5] = {coef->one_link, coef->three_staple, coef->five_staple, coef->seven_staple, coef->lepage};
+  double2 *pfl[4], *pgf[4], *pll[4], *pgl[4];
+  one_hop(fl, pfl); one_hop(gf, pgf);
+  if (naik != 0.0) {
+    QB_CHECK(get_gauge4(hll, &ll, "makeImpLinks(ll)", false));
+    QB_CHECK(get_gauge4(hgfl, &gfl, "makeImpLinks(gfLong)", true));
+    if (ll == gfl || ll == gf || ll == fl) return fail("makeImpLinks: ll must be its own link set");
+    one_hop(ll, pll); one_hop(gfl, pgl);
+  }
+  QB_CHECK(make_imp_links(pfl, pgf, c, ll ? pll : nullptr, gfl ? pgl : nullptr, naik));
+  QB_CHECK(links_written(fl));
+  if (ll) QB_CHECK(links_written(ll));
+  return 0;
+}
+int qexb200_gauge_smear_hisq(qexb200_gauge_t hfl, qexb200_gauge_t hll, qexb200_gauge_t hg,
+                             const qexb200_hisq_coefs* coef) {
+  QB_CHECK(need_ctx());
+  Gauge *fl, *ll, *g;
+  QB_CHECK(get_gauge4(hfl, &fl, "smear_hisq(fl)", false));
+  QB_CHECK(get_gauge4(hll, &ll, "smear_hisq(ll)", false));
+  QB_CHECK(get_gauge4(hg, &g, "smear_hisq(g)", true));
+  if (fl == ll) return fail("smear_hisq: fl and ll must be different link sets");
+  const qexb200_fat7l_coefs &a = coef->fat7first, &b = coef->fat7second;
+  const double c[11] = {a.one_link, a.three_staple, a.five_staple, a.seven_staple, a.lepage,
+                        b.one_link, b.three_staple, b.five_staple, b.seven_staple, b.lepage, coef->naik};
+  double2 *pfl[4], *pll[4], *pg[4];
+  one_hop(fl, pfl); one_hop(ll, pll); one_hop(g, pg);
+  QB_CHECK(hisq_smear(pfl, pll, pg, c));
+  QB_CHECK(links_written(fl));
+  return links_written(ll);
+}
+int qexb200_gauge_smear_hyp(qexb200_gauge_t hfl, qexb200_gauge_t hg, const qexb200_hyp_coefs* coef) {
+  QB_CHECK(need_ctx());
+  Gauge *fl, *g;
+  QB_CHECK(get_gauge4(hfl, &fl, "smear_hyp(fl)", false));
+  QB_CHECK(get_gauge4(hg, &g, "smear_hyp(g)", true));
+  if (fl == g) return fail("smear_hyp: fl and g must be different link sets");
+  const double al[3] = {coef->alpha1, coef->alpha2, coef->alpha3};
+  double2 *pfl[4], *pg[4];
+  one_hop(fl, pfl); one_hop(g, pg);
+  QB_CHECK(hyp_smear(pfl, pg, al));
+  return links_written(fl);
+}
+// newStag3(fl, ll) (stagD.nim:552-564): g[2 mu] = fl[mu], g[2 mu + 1] = ll[mu]
+int qexb200_gauge_join3(qexb200_gauge_t hout, qexb200_gauge_t hfl, qexb200_gauge_t hll) {
+  QB_CHECK(need_ctx());
+  Gauge *o, *fl, *ll;
+  QB_CHECK(get_gauge(hout, &o));
+  if (o->nlinks != 8) return fail("gauge_join3: output must hold 8 link fields");
+  QB_CHECK(get_gauge4(hfl, &fl, "gauge_join3(fl)", true));
+  QB_CHECK(get_gauge4(hll, &ll, "gauge_join3(ll)", true));
+  const size_t n = (size_t)18 * g_ctx.g.Vh;
+  for (int mu = 0; mu < 4; mu++) {
+    QB_CUDA(cudaMemcpyAsync(link_field(o, 2 * mu), link_field(fl, mu), sizeof(double2) * n, cudaMemcpyDeviceToDevice, g_ctx.stream));
+    QB_CUDA(cudaMemcpyAsync(link_field(o, 2 * mu + 1), link_field(ll, mu), sizeof(double2) * n, cudaMemcpyDeviceToDevice, g_ctx.stream));
+  }
+  return links_written(o);
 }
 
 // ---- device fields -----------------------------------------------------------

@@ -228,9 +228,19 @@ int ensure_perm();
 int upload_vector(Field& f, const double* host);
 int download_vector(const Field& f, double* host);
 int upload_links(Gauge& g, const double* const* links);
+int download_links(const Gauge& g, double* const* links);
 int rephase(Gauge& g);
 int compress_links(Gauge& g);      // honours g.want12; sets g.recon
 void free_compressed(Gauge& g);
+
+// ---- smear.cu (device link pipeline; matrix field = double2[2][9][Vh]) -------
+int make_imp_links(double2* const fl[4], const double2* const gf[4], const double coef[5], double2* const ll[4],
+                   const double2* const gfl[4], double naik);
+int hisq_smear(double2* const fl[4], double2* const ll[4], const double2* const g[4], const double c[11]);
+int hyp_smear(double2* const fl[4], const double2* const g[4], const double alpha[3]);
+int project_fields(double2* out, const double2* in, int nfields);
+int plaq_links(const double2* const u[4], double pl[6]);
+int smear_free();
 
 // ---- comm.cu ----------------------------------------------------------------
 int halo_setup();

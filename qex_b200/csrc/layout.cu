@@ -183,6 +183,28 @@ int upload_links(Gauge& g, const double* const* links) {
   return compress_links(g);
 }
 
+// Device links back to native QEX host memory (the inverse of upload_links): what a caller needs
+// after smearing on the device, e.g. to measure or to save the smeared links.
+int download_links(const Gauge& g, double* const* links) {
+  Context& c = ctx();
+  QB_CHECK(ensure_perm());
+  if (!g.loaded) return fail("gauge_download: gauge holds no links");
+  const size_t bytes = sizeof(double) * 18 * (size_t)c.g.V;
+  QB_CHECK(ensure_stage(bytes));
+  const int grid = (c.g.V + LB - 1) / LB;
+  for (int k = 0; k < g.nlinks; k++) {
+    if (!links[k]) return fail("gauge_download: links[%d] is NULL", k);
+    const double2* src = g.d + (size_t)k * 2 * 9 * c.g.Vh;
+    k_scatter<9><<<grid, LB, 0, c.stream>>>(c.d_stage, src, c.d_perm, c.g.V, c.permV, (size_t)c.g.Vh,
+                                            (size_t)9 * c.g.Vh, c.g.Vh);
+    count_launch();
+    QB_CUDA(cudaGetLastError());
+    QB_CUDA(cudaMemcpyAsync(links[k], c.d_stage, bytes, cudaMemcpyDeviceToHost, c.stream));
+    QB_CUDA(cudaStreamSynchronize(c.stream));
+  }
+  return 0;
+}
+
 // Staggered.rephase (stagD.nim:72-80): setBC (gaugeUtils.nim:124-131) then
 // stagPhase with phases {8,9,11,0} (stagD.nim:509-522), on GLOBAL coordinates.
 __global__ void __launch_bounds__(LB) k_rephase(double2* u, int Vh, int X0, int X1, int X2, int X3,

@@ -1,0 +1,202 @@
+// Per-site arithmetic of the device link pipeline: 3x3 complex products, the staple
+// of one (side link, middle link) pair gathered straight from the checkerboarded fields, projectU.
+// Everything here is QB_HD so that tests/emu_links.cpp can run the very same site functions on the
+// host against the oracle before GPU time is spent (test harness only; the library never does).
+//
+// A "matrix field" is double2 f[2 parity][9 (row,col)][Vh]; a link set stores nlinks of them.
+#pragma once
+#include <cuda_runtime.h>
+#include <math.h>
+
+#if defined(__CUDACC__)
+#define QB_HD __host__ __device__ __forceinline__
+#else
+#define QB_HD inline
+#endif
+
+namespace qb {
+
+struct M3 {
+  double2 e[9];
+};
+
+struct LSite {   // local coordinates + parity + checkerboard index
+  int x[4];
+  int par, idx;
+};
+
+QB_HD LSite lsite(int idx, int par, const int* X) {
+  LSite s;
+  int t = idx;
+  const int xh = X[0] >> 1;
+  const int x0h = t % xh; t /= xh;
+  s.x[1] = t % X[1]; t /= X[1];
+  s.x[2] = t % X[2];
+  s.x[3] = t / X[2];
+  s.x[0] = 2 * x0h + ((par + s.x[1] + s.x[2] + s.x[3]) & 1);
+  s.par = par; s.idx = idx;
+  return s;
+}
+// one hop of d = +-1 (or +-k) in direction mu with local wrap-around (single rank: periodic)
+QB_HD LSite lhop(LSite s, int mu, int d, const int* X) {
+  int c = s.x[mu] + d;
+  if (c >= X[mu]) c -= X[mu];
+  if (c < 0) c += X[mu];
+  s.x[mu] = c;
+  if (d & 1) s.par ^= 1;
+  s.idx = (((s.x[3] * X[2] + s.x[2]) * X[1] + s.x[1]) * X[0] + s.x[0]) >> 1;
+  return s;
+}
+
+QB_HD M3 m3_ld(const double2* f, const LSite& s, int Vh) {
+  M3 m;
+  const double2* p = f + (size_t)s.par * 9 * Vh + s.idx;
+#pragma unroll
+  for (int e = 0; e < 9; e++) m.e[e] = p[(size_t)e * Vh];
+  return m;
+}
+QB_HD void m3_st(double2* f, const LSite& s, int Vh, const M3& m) {
+  double2* p = f + (size_t)s.par * 9 * Vh + s.idx;
+#pragma unroll
+  for (int e = 0; e < 9; e++) p[(size_t)e * Vh] = m.e[e];
+}
+
+QB_HD double2 c_mul(double2 a, double2 b) { return make_double2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
+
+// a * b
+QB_HD M3 m3_mul(const M3& a, const M3& b) {
+  M3 r;
+#pragma unroll
+  for (int i = 0; i < 3; i++)
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+      double re = 0.0, im = 0.0;
+#pragma unroll
+      for (int k = 0; k < 3; k++) {
+        const double2 p = a.e[i * 3 + k], q = b.e[k * 3 + j];
+        re += p.x * q.x - p.y * q.y;
+        im += p.x * q.y + p.y * q.x;
+      }
+      r.e[i * 3 + j] = make_double2(re, im);
+    }
+  return r;
+}
+// a * b^+
+QB_HD M3 m3_mul_na(const M3& a, const M3& b) {
+  M3 r;
+#pragma unroll
+  for (int i = 0; i < 3; i++)
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+      double re = 0.0, im = 0.0;
+#pragma unroll
+      for (int k = 0; k < 3; k++) {
+        const double2 p = a.e[i * 3 + k], q = b.e[j * 3 + k];   // conj(q)
+        re += p.x * q.x + p.y * q.y;
+        im += p.y * q.x - p.x * q.y;
+      }
+      r.e[i * 3 + j] = make_double2(re, im);
+    }
+  return r;
+}
+// a^+ * b
+QB_HD M3 m3_mul_an(const M3& a, const M3& b) {
+  M3 r;
+#pragma unroll
+  for (int i = 0; i < 3; i++)
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+      double re = 0.0, im = 0.0;
+#pragma unroll
+      for (int k = 0; k < 3; k++) {
+        const double2 p = a.e[k * 3 + i], q = b.e[k * 3 + j];   // conj(p)
+        re += p.x * q.x + p.y * q.y;
+        im += p.x * q.y - p.y * q.x;
+      }
+      r.e[i * 3 + j] = make_double2(re, im);
+    }
+  return r;
+}
+QB_HD void m3_axpy(M3& y, double a, const M3& x) {
+#pragma unroll
+  for (int e = 0; e < 9; e++) { y.e[e].x += a * x.e[e].x; y.e[e].y += a * x.e[e].y; }
+}
+QB_HD M3 m3_zero() {
+  M3 r;
+#pragma unroll
+  for (int e = 0; e < 9; e++) r.e[e] = make_double2(0.0, 0.0);
+  return r;
+}
+
+// The two staples of middle link L (direction dL) with side link G (direction dG) at site s:
+//   G(x) L(x+dG) G(x+dL)^+  +  G(x-dG)^+ L(x-dG) G(x-dG+dL)
+// = computeGenStaple's staple (src/gauge/fat7l.nim:24-76, gauge[nu] = G, link = L, mu = dL, nu = dG)
+// = symStaple's bracket (src/gauge/smearutil.nim:3-17, g1 = G, g2 = L).
+// The reference forms the lower staple at x-dG and shifts it; here it is gathered in place.
+QB_HD M3 staple_pair(const double2* G, const double2* L, int dG, int dL, const LSite& s, const int* X, int Vh) {
+  const LSite sG = lhop(s, dG, +1, X);
+  const LSite sL = lhop(s, dL, +1, X);
+  M3 r = m3_mul_na(m3_mul(m3_ld(G, s, Vh), m3_ld(L, sG, Vh)), m3_ld(G, sL, Vh));
+  const LSite sb = lhop(s, dG, -1, X);
+  const LSite sbL = lhop(sb, dL, +1, X);
+  const M3 lo = m3_mul(m3_mul_an(m3_ld(G, sb, Vh), m3_ld(L, sb, Vh)), m3_ld(G, sbL, Vh));
+  m3_axpy(r, 1.0, lo);
+  return r;
+}
+
+// ---- projectU (src/maths/matrixFunctions.nim:79-181,301-312) --------------------------------
+// eigenvalues of a Hermitian 3x3 from tr, tr(x^2), det: eigs3, :79-111
+QB_HD void eigs3(double& e0, double& e1, double& e2, double tr, double p2, double det) {
+  const double tr3 = (1.0 / 3.0) * tr;
+  const double p23 = (1.0 / 3.0) * p2;
+  const double tr32 = tr3 * tr3;
+  const double q = fabs(0.5 * (p23 - tr32));
+  const double r = 0.25 * tr3 * (5 * tr32 - p2) - 0.5 * det;
+  const double sq = sqrt(q);
+  const double sq3 = q * sq;
+  const double isq3 = 1.0 / sq3;
+  const double isq3c = fmin(3e38, fmax(-3e38, isq3));
+  const double rsq3c = r * isq3c;
+  const double rsq3 = fmin(1.0, fmax(-1.0, rsq3c));
+  const double t = (1.0 / 3.0) * acos(rsq3);
+  const double st = sin(t), ct = cos(t);
+  const double sqc = sq * ct;
+  const double sqs = 1.73205080756887729352 * sq * st;
+  const double ll = tr3 + sqc;
+  e0 = tr3 - 2 * sqc; e1 = ll + sqs; e2 = ll - sqs;
+}
+QB_HD double m3_det_re(const M3& x) {
+  const double2 a = c_mul(x.e[0], x.e[4]), b = c_mul(x.e[1], x.e[3]);
+  const double2 c = c_mul(x.e[2], x.e[3]), d = c_mul(x.e[0], x.e[5]);
+  const double2 f = c_mul(x.e[1], x.e[5]), g = c_mul(x.e[2], x.e[4]);
+  const double2 t0 = c_mul(make_double2(a.x - b.x, a.y - b.y), x.e[8]);
+  const double2 t1 = c_mul(make_double2(c.x - d.x, c.y - d.y), x.e[7]);
+  const double2 t2 = c_mul(make_double2(f.x - g.x, f.y - g.y), x.e[6]);
+  return t0.x + t1.x + t2.x;
+}
+// x (x^+ x + 1e-20)^(-1/2): projectU :301-312 through rsqrtPHM3 :126-181
+QB_HD M3 project_u(const M3& x) {
+  M3 h = m3_mul_an(x, x);
+  h.e[0].x += 1e-20; h.e[4].x += 1e-20; h.e[8].x += 1e-20;
+  const double tr = h.e[0].x + h.e[4].x + h.e[8].x;
+  const M3 h2 = m3_mul(h, h);
+  const double p2 = h2.e[0].x + h2.e[4].x + h2.e[8].x;
+  const double det = m3_det_re(h);
+  double l0, l1, l2;
+  eigs3(l0, l1, l2, tr, p2, det);
+  const double sl0 = sqrt(fabs(l0)), sl1 = sqrt(fabs(l1)), sl2 = sqrt(fabs(l2));
+  const double u = sl0 + sl1 + sl2;
+  const double w = sl0 * sl1 * sl2;
+  const double d = w * (sl0 + sl1) * (sl0 + sl2) * (sl1 + sl2);
+  const double di = 1.0 / d;
+  const double c0 = (w * u * u + l0 * sl0 * (l1 + l2) + l1 * sl1 * (l0 + l2) + l2 * sl2 * (l0 + l1)) * di;
+  const double c1 = -(tr * u + w) * di;
+  const double c2 = u * di;
+  M3 rs;
+#pragma unroll
+  for (int e = 0; e < 9; e++) rs.e[e] = make_double2(c1 * h.e[e].x + c2 * h2.e[e].x, c1 * h.e[e].y + c2 * h2.e[e].y);
+  rs.e[0].x += c0; rs.e[4].x += c0; rs.e[8].x += c0;
+  return m3_mul(x, rs);
+}
+
+}  // namespace qb

@@ -1,0 +1,382 @@
+// Device link pipeline: fat7 + Lepage + Naik links (makeImpLinks,
+// src/gauge/fat7l.nim:78-162), HISQ (src/physics/hisqLinks.nim:32-39), nHYP
+// (src/gauge/hypsmear.nim:49-162), projectU (src/maths/matrixFunctions.nim:301-312) and plaq
+// (src/gauge/gaugeUtils.nim:213-284) on the resident link fields.
+//
+// The reference builds every staple from pre-shifted copies of whole fields (Shifter ^*, three
+// extra passes per staple) and projects in separate sweeps.  Here ONE kernel shape does all of it:
+// a thread owns a site, gathers the six matrices of each staple pair from the checkerboarded
+// fields by coordinate arithmetic, sums up to three weighted pairs onto `cbase*base + acc`,
+// optionally projects, and writes once.  nHYP is then 12 + 12 + 4 launches (one per output
+// field, projection fused), fat7 is 10 launches per (mu, nu) pair reduced to 4.
+// HBM-bound streaming of 144-byte matrices; fp64 FMA pipe is the secondary limit.
+#include "linkops.cuh"
+#include "stencil.cuh"
+
+namespace qb {
+
+constexpr int SB = 128;
+
+// ---- pool of matrix-field temporaries (kept across calls: HMC smears every force step) -------
+struct MatPool {
+  std::vector<double2*> free_list, all;
+  size_t elems = 0;
+};
+static MatPool g_pool;
+
+static int pool_get(double2** out) {
+  Context& c = ctx();
+  const size_t n = (size_t)18 * c.g.Vh;
+  if (g_pool.elems != n) {
+    for (double2* p : g_pool.all) cudaFree(p);
+    g_pool.all.clear(); g_pool.free_list.clear(); g_pool.elems = n;
+  }
+  if (!g_pool.free_list.empty()) { *out = g_pool.free_list.back(); g_pool.free_list.pop_back(); return 0; }
+  double2* p = nullptr;
+  QB_CUDA(cudaMalloc(&p, sizeof(double2) * n));
+  g_pool.all.push_back(p);
+  *out = p;
+  return 0;
+}
+static void pool_put(double2* p) { if (p) g_pool.free_list.push_back(p); }
+int smear_free() {
+  for (double2* p : g_pool.all) cudaFree(p);
+  g_pool.all.clear(); g_pool.free_list.clear(); g_pool.elems = 0;
+  return 0;
+}
+struct Tmp {   // RAII handle of one pooled field
+  double2* p = nullptr;
+  ~Tmp() { pool_put(p); }
+  int get() { return p ? 0 : pool_get(&p); }
+  void drop() { pool_put(p); p = nullptr; }
+};
+
+// ---- the staple kernel ----------------------------------------------------------------------
+struct StapleTerm {
+  const double2* G;   // side link field (direction dG)
+  const double2* L;   // middle link field (direction dL of the launch)
+  int dG;
+  double coef;
+};
+struct StapleArgs {
+  StapleTerm t[3];
+  int dL;
+  const double2* base;  // out = cbase*base + acc + sum_k coef_k * pair_k   (base / acc may be null)
+  double cbase;
+  const double2* acc;   // may alias out
+  double2* out;         // projected when PROJ
+  double2* save;        // NS == 1: the bare pair of term 0 (computeGenStaple's saved staple), may be null
+  double2* raw;         // PROJ: the unprojected sum (hypsmear's l1x/l2x/flx, needed by the force), may be null
+  int X[4];
+  int Vh;
+};
+
+template <int NS, bool PROJ>
+__global__ void __launch_bounds__(SB) k_staple(const StapleArgs a) {
+  const int ds = blockIdx.x * SB + threadIdx.x;
+  if (ds >= 2 * a.Vh) return;
+  const int par = ds / a.Vh, idx = ds - par * a.Vh;
+  const LSite s = lsite(idx, par, a.X);
+  M3 r = m3_zero();
+  if (a.base) m3_axpy(r, a.cbase, m3_ld(a.base, s, a.Vh));
+  if (a.acc) m3_axpy(r, 1.0, m3_ld(a.acc, s, a.Vh));
+#pragma unroll
+  for (int k = 0; k < NS; k++) {
+    const M3 st = staple_pair(a.t[k].G, a.t[k].L, a.t[k].dG, a.dL, s, a.X, a.Vh);
+    if (NS == 1 && a.save) m3_st(a.save, s, a.Vh, st);
+    m3_axpy(r, a.t[k].coef, st);
+  }
+  if (PROJ) {
+    if (a.raw) m3_st(a.raw, s, a.Vh, r);
+    r = project_u(r);
+  }
+  m3_st(a.out, s, a.Vh, r);
+}
+
+static int launch_staple(const StapleArgs& a, int ns, bool proj) {
+  Context& c = ctx();
+  const int grid = (c.g.V + SB - 1) / SB;
+  if (proj) {
+    if (ns == 1) k_staple<1, true><<<grid, SB, 0, c.stream>>>(a);
+    else if (ns == 2) k_staple<2, true><<<grid, SB, 0, c.stream>>>(a);
+    else k_staple<3, true><<<grid, SB, 0, c.stream>>>(a);
+  } else {
+    if (ns == 1) k_staple<1, false><<<grid, SB, 0, c.stream>>>(a);
+    else if (ns == 2) k_staple<2, false><<<grid, SB, 0, c.stream>>>(a);
+    else k_staple<3, false><<<grid, SB, 0, c.stream>>>(a);
+  }
+  count_launch();
+  QB_CUDA(cudaGetLastError());
+  return 0;
+}
+static StapleArgs staple_args(int dL) {
+  StapleArgs a = {};
+  const Geom& g = ctx().g;
+  for (int d = 0; d < 4; d++) a.X[d] = g.X[d];
+  a.Vh = g.Vh; a.dL = dL;
+  return a;
+}
+
+// out = projectU(in) / out = c * in, n matrix fields back to back
+template <bool PROJ>
+__global__ void __launch_bounds__(SB) k_sitewise(double2* out, const double2* in, double c, int Vh, size_t nsites) {
+  const size_t t = (size_t)blockIdx.x * SB + threadIdx.x;
+  if (t >= nsites) return;
+  const size_t blk = t / Vh;            // (field, parity) block of 9*Vh
+  const int idx = (int)(t - blk * Vh);
+  const double2* p = in + blk * 9 * Vh + idx;
+  M3 m;
+#pragma unroll
+  for (int e = 0; e < 9; e++) m.e[e] = p[(size_t)e * Vh];
+  if (PROJ) m = project_u(m);
+  else {
+#pragma unroll
+    for (int e = 0; e < 9; e++) { m.e[e].x *= c; m.e[e].y *= c; }
+  }
+  double2* q = out + blk * 9 * Vh + idx;
+#pragma unroll
+  for (int e = 0; e < 9; e++) q[(size_t)e * Vh] = m.e[e];
+}
+
+int project_fields(double2* out, const double2* in, int nfields) {
+  Context& c = ctx();
+  const size_t ns = (size_t)nfields * c.g.V;
+  k_sitewise<true><<<(unsigned)((ns + SB - 1) / SB), SB, 0, c.stream>>>(out, in, 1.0, c.g.Vh, ns);
+  count_launch();
+  QB_CUDA(cudaGetLastError());
+  return 0;
+}
+static int scale_field(double2* out, const double2* in, double s) {
+  Context& c = ctx();
+  const size_t ns = (size_t)c.g.V;
+  k_sitewise<false><<<(unsigned)((ns + SB - 1) / SB), SB, 0, c.stream>>>(out, in, s, c.g.Vh, ns);
+  count_launch();
+  QB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// Naik link, fat7l.nim:156-167: ll(x) = naik * W(x) W(x+mu) W(x+2mu)
+__global__ void __launch_bounds__(SB) k_naik(double2* ll, const double2* w, int mu, double naik, int X0, int X1,
+                                              int X2, int X3, int Vh) {
+  const int ds = blockIdx.x * SB + threadIdx.x;
+  if (ds >= 2 * Vh) return;
+  const int X[4] = {X0, X1, X2, X3};
+  const int par = ds / Vh, idx = ds - par * Vh;
+  const LSite s = lsite(idx, par, X);
+  const LSite s1 = lhop(s, mu, +1, X), s2 = lhop(s1, mu, +1, X);
+  const M3 t = m3_mul(m3_ld(w, s1, Vh), m3_ld(w, s2, Vh));   // the reference multiplies right to left too
+  M3 r = m3_mul(m3_ld(w, s, Vh), t);
+#pragma unroll
+  for (int e = 0; e < 9; e++) { r.e[e].x *= naik; r.e[e].y *= naik; }
+  m3_st(ll, s, Vh, r);
+}
+
+// ---- plaq, gaugeUtils.nim:213-284 ------------------------------------------------------------
+// pl[mu(mu-1)/2 + nu] = sum_x Re tr[(U_nu(x) U_mu(x+nu))^+ (U_mu(x) U_nu(x+mu))] / (6 * 3 * vol), nu < mu
+struct PlaqArgs {
+  const double2* u[4];
+  double* partials;   // [grid][6]
+  int X[4];
+  int Vh;
+};
+__global__ void __launch_bounds__(SB) k_plaq(const PlaqArgs a) {
+  __shared__ double sm[SB / 32][6];
+  const int ds = blockIdx.x * SB + threadIdx.x;
+  double v[6] = {0, 0, 0, 0, 0, 0};
+  if (ds < 2 * a.Vh) {
+    const int par = ds / a.Vh, idx = ds - par * a.Vh;
+    const LSite s = lsite(idx, par, a.X);
+    M3 U[4];
+#pragma unroll
+    for (int mu = 0; mu < 4; mu++) U[mu] = m3_ld(a.u[mu], s, a.Vh);
+#pragma unroll
+    for (int mu = 1; mu < 4; mu++) {
+      const LSite smu = lhop(s, mu, +1, a.X);
+#pragma unroll
+      for (int nu = 0; nu < mu; nu++) {
+        const LSite snu = lhop(s, nu, +1, a.X);
+        const M3 p = m3_mul(U[nu], m3_ld(a.u[mu], snu, a.Vh));
+        const M3 q = m3_mul(U[mu], m3_ld(a.u[nu], smu, a.Vh));
+        double d = 0.0;
+#pragma unroll
+        for (int e = 0; e < 9; e++) d += q.e[e].x * p.e[e].x + q.e[e].y * p.e[e].y;
+        v[(mu * (mu - 1)) / 2 + nu] = d;
+      }
+    }
+  }
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < 6; k++) {
+    double t = v[k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) t += __shfl_down_sync(0xffffffffu, t, o);
+    if (lane == 0) sm[w][k] = t;
+  }
+  __syncthreads();
+  if (threadIdx.x < 6) {
+    double t = 0.0;
+    for (int i = 0; i < SB / 32; i++) t += sm[i][threadIdx.x];
+    a.partials[(size_t)blockIdx.x * 6 + threadIdx.x] = t;
+  }
+}
+// fixed-order final sum: one block, thread k < 6 * 32 handles plane k / 32 with stride 32
+__global__ void __launch_bounds__(192) k_plaq_final(const double* partials, int nblocks, double norm, double* out) {
+  const int k = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  double t = 0.0;
+  for (int i = lane; i < nblocks; i += 32) t += partials[(size_t)i * 6 + k];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) t += __shfl_down_sync(0xffffffffu, t, o);
+  if (lane == 0) out[k] = t * norm;
+}
+
+int plaq_links(const double2* const u[4], double pl[6]) {
+  Context& c = ctx();
+  if (c.g.nranks > 1) return fail("gauge_plaq: not available on a lattice split over ranks yet");
+  Tmp part;
+  QB_CHECK(part.get());
+  PlaqArgs a;
+  for (int d = 0; d < 4; d++) { a.u[d] = u[d]; a.X[d] = c.g.X[d]; }
+  a.Vh = c.g.Vh;
+  a.partials = reinterpret_cast<double*>(part.p);
+  const int grid = (c.g.V + SB - 1) / SB;
+  k_plaq<<<grid, SB, 0, c.stream>>>(a);
+  count_launch();
+  k_plaq_final<<<1, 192, 0, c.stream>>>(a.partials, grid, 1.0 / (18.0 * (double)c.g.V), c.d_scal + 40);
+  count_launch();
+  QB_CUDA(cudaGetLastError());
+  return fetch_scalars(c.d_scal + 40, pl, 6);
+}
+
+// ---- makeImpLinks, fat7l.nim:78-162 ------------------------------------------------------------
+// coef = {oneLink, threeStaple, fiveStaple, sevenStaple, lepage}.  fl, gf: 4 fields each; ll / gfl
+// may be null when naik == 0.  fl must not alias gf.  Per (dir, nu): the 3-staple (saved), the two
+// 5-staples built on it (saved), then ONE launch adding Lepage + both 7-staples.
+int make_imp_links(double2* const fl[4], const double2* const gf[4], const double coef[5], double2* const ll[4],
+                   const double2* const gfl[4], double naik) {
+  Context& c = ctx();
+  if (c.g.nranks > 1) return fail("makeImpLinks: not available on a lattice split over ranks yet");
+  for (int d = 0; d < 4; d++)
+    if (c.g.X[d] < 4) return fail("makeImpLinks: local extent %d in direction %d is below 4", c.g.X[d], d);
+  double coef1 = coef[0];
+  const double coef3 = coef[1], coef5 = coef[2], coef7 = coef[3], coefL = coef[4];
+  const bool have5 = coef5 != 0.0 || coef7 != 0.0 || coefL != 0.0;
+  const bool have3 = coef3 != 0.0 || have5;
+  coef1 -= 6.0 * coefL;   // :108
+  Tmp s3, s5[2];
+  for (int dir = 0; dir < 4; dir++) {
+    if (!have3) { QB_CHECK(scale_field(fl[dir], gf[dir], coef1)); continue; }
+    QB_CHECK(s3.get());
+    bool first = true;
+    for (int nu = 0; nu < 4; nu++) {
+      if (nu == dir) continue;
+      {   // :139 computeGenStaple(staple, dir, nu, gf[dir], coef3)
+        StapleArgs a = staple_args(dir);
+        a.t[0] = {gf[nu], gf[dir], nu, coef3};
+        if (first) { a.base = gf[dir]; a.cbase = coef1; } else a.acc = fl[dir];
+        a.out = fl[dir]; a.save = s3.p;
+        QB_CHECK(launch_staple(a, 1, false));
+        first = false;
+      }
+      StapleArgs tail = staple_args(dir);
+      tail.acc = fl[dir]; tail.out = fl[dir];
+      int nt = 0;
+      if (coefL != 0.0) tail.t[nt++] = {gf[nu], s3.p, nu, coefL};   // :141-143
+      if (coef5 != 0.0 || coef7 != 0.0) {
+        int k = 0;
+        for (int rho = 0; rho < 4; rho++) {
+          if (rho == dir || rho == nu) continue;
+          QB_CHECK(s5[k].get());
+          StapleArgs a = staple_args(dir);   // :147
+          a.t[0] = {gf[rho], s3.p, rho, coef5};
+          a.acc = fl[dir]; a.out = fl[dir]; a.save = s5[k].p;
+          QB_CHECK(launch_staple(a, 1, false));
+          if (coef7 != 0.0) {
+            const int sig = 6 - dir - nu - rho;   // :150-153
+            tail.t[nt++] = {gf[sig], s5[k].p, sig, coef7};
+          }
+          k++;
+        }
+      }
+      if (nt) QB_CHECK(launch_staple(tail, nt, false));
+    }
+  }
+  if (naik != 0.0) {
+    if (!ll || !gfl) return fail("makeImpLinks: naik != 0 needs long-link input and output");
+    for (int d = 0; d < 4; d++)
+      if (c.g.X[d] < 4) return fail("makeImpLinks: Naik links need local extent >= 4");
+    const int grid = (c.g.V + SB - 1) / SB;
+    for (int dir = 0; dir < 4; dir++) {
+      k_naik<<<grid, SB, 0, c.stream>>>(ll[dir], gfl[dir], dir, naik, c.g.X[0], c.g.X[1], c.g.X[2], c.g.X[3], c.g.Vh);
+      count_launch();
+    }
+    QB_CUDA(cudaGetLastError());
+  }
+  return 0;
+}
+
+// ---- HisqCoefs.smear, hisqLinks.nim:32-39 -------------------------------------------------------
+// c = {fat7first[5], fat7second[5], naik}
+int hisq_smear(double2* const fl[4], double2* const ll[4], const double2* const g[4], const double c[11]) {
+  Tmp t1[4], t2[4];
+  double2* p1[4]; const double2* cp2[4];
+  for (int d = 0; d < 4; d++) { QB_CHECK(t1[d].get()); p1[d] = t1[d].p; }
+  QB_CHECK(make_imp_links(p1, g, c, nullptr, nullptr, 0.0));
+  for (int d = 0; d < 4; d++) {
+    QB_CHECK(t2[d].get());
+    QB_CHECK(project_fields(t2[d].p, t1[d].p, 1));
+    t1[d].drop();
+    cp2[d] = t2[d].p;
+  }
+  return make_imp_links(fl, cp2, c + 5, ll, cp2, c[10]);
+}
+
+// ---- HypCoefs.smear, hypsmear.nim:49-162 --------------------------------------------------------
+// L1[mu][nu] = P((1-a1) g[mu] + a1/2 S(g[nu], g[mu]));  L2[mu][nu] = P((1-a2) g[mu] + a2/4 sum_a S(L1[a][b], L1[mu][b]));
+// fl[mu] = P((1-a3) g[mu] + a3/6 sum_nu S(L2[nu][mu], L2[mu][nu])).  One launch per output field.
+int hyp_smear(double2* const fl[4], const double2* const g[4], const double alpha[3]) {
+  Context& c = ctx();
+  if (c.g.nranks > 1) return fail("hyp smear: not available on a lattice split over ranks yet");
+  for (int d = 0; d < 4; d++)
+    if (c.g.X[d] < 4) return fail("hyp smear: local extent %d in direction %d is below 4", c.g.X[d], d);
+  const double alp1 = alpha[0] / 2.0, alp2 = alpha[1] / 4.0, alp3 = alpha[2] / 6.0;
+  const double ma1 = 1 - alpha[0], ma2 = 1 - alpha[1], ma3 = 1 - alpha[2];
+  Tmp l1[4][4], l2[4][4];
+  for (int mu = 0; mu < 4; mu++) for (int nu = 0; nu < 4; nu++) {
+    if (nu == mu) continue;
+    QB_CHECK(l1[mu][nu].get());
+    StapleArgs a = staple_args(mu);   // :107-111
+    a.base = g[mu]; a.cbase = ma1;
+    a.t[0] = {g[nu], g[mu], nu, alp1};
+    a.out = l1[mu][nu].p;
+    QB_CHECK(launch_staple(a, 1, true));
+  }
+  for (int mu = 0; mu < 4; mu++) for (int nu = 0; nu < 4; nu++) {
+    if (nu == mu) continue;
+    QB_CHECK(l2[mu][nu].get());
+    StapleArgs a = staple_args(mu);   // :117-133
+    a.base = g[mu]; a.cbase = ma2;
+    int nt = 0;
+    for (int s = 0; s < 4; s++) {
+      if (s == mu || s == nu) continue;
+      const int b = 6 - mu - nu - s;
+      a.t[nt++] = {l1[s][b].p, l1[mu][b].p, s, alp2};
+    }
+    a.out = l2[mu][nu].p;
+    QB_CHECK(launch_staple(a, nt, true));
+  }
+  for (int mu = 0; mu < 4; mu++) for (int nu = 0; nu < 4; nu++) l1[mu][nu].drop();
+  for (int mu = 0; mu < 4; mu++) {
+    StapleArgs a = staple_args(mu);   // :136-150
+    a.base = g[mu]; a.cbase = ma3;
+    int nt = 0;
+    for (int nu = 0; nu < 4; nu++) {
+      if (nu == mu) continue;
+      a.t[nt++] = {l2[nu][mu].p, l2[mu][nu].p, nu, alp3};
+    }
+    a.out = fl[mu];
+    QB_CHECK(launch_staple(a, nt, true));
+  }
+  return 0;
+}
+
+}  // namespace qb

@@ -1,0 +1,35 @@
+// TEST HARNESS ONLY: runs the per-site functions of qex_b200/csrc/linkops.cuh on the host (they are
+// __host__ __device__) over a whole field, so the coordinate arithmetic and the 3x3 algebra of the
+// device link pipeline can be checked against the oracle on a machine without a GPU.  Compiled by
+// tests/test_links_emu.py with g++; never part of libqex_b200.so.
+#include "../../qex_b200/csrc/linkops.cuh"
+
+using namespace qb;
+
+extern "C" {
+// fields in the DEVICE layout double2[2][9][Vh]
+void emu_staple_field(const double* G, const double* L, int dG, int dL, const int* X, double* out) {
+  const int Vh = X[0] * X[1] * X[2] * X[3] / 2;
+  for (int par = 0; par < 2; par++)
+    for (int idx = 0; idx < Vh; idx++) {
+      const LSite s = lsite(idx, par, X);
+      const M3 st = staple_pair((const double2*)G, (const double2*)L, dG, dL, s, X, Vh);
+      m3_st((double2*)out, s, Vh, st);
+    }
+}
+void emu_project_field(const double* in, const int* X, double* out) {
+  const int Vh = X[0] * X[1] * X[2] * X[3] / 2;
+  for (int par = 0; par < 2; par++)
+    for (int idx = 0; idx < Vh; idx++) {
+      const LSite s = lsite(idx, par, X);
+      m3_st((double2*)out, s, Vh, project_u(m3_ld((const double2*)in, s, Vh)));
+    }
+}
+// coordinates of (par, idx) and the index of its neighbour: out[6] = x0..x3, par', idx'
+void emu_hop(int idx, int par, int mu, int d, const int* X, int* out) {
+  const LSite s = lsite(idx, par, X);
+  const LSite t = lhop(s, mu, d, X);
+  for (int k = 0; k < 4; k++) out[k] = s.x[k];
+  out[4] = t.par; out[5] = t.idx;
+}
+}

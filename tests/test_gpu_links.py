@@ -1,0 +1,214 @@
+"""GPU parity of the device link pipeline through the C ABI: makeImpLinks
+(src/gauge/fat7l.nim:78-162), HISQ (src/physics/hisqLinks.nim:32-39), nHYP (src/gauge/hypsmear.nim:49-162),
+projectU, plaq -- against the oracle on the same seeded links.  Bar: rel-L2 <= 1e-13 per link field."""
+import numpy as np
+import pytest
+
+import oracle
+from util import SEED, rel_l2
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-13
+
+
+@pytest.fixture()
+def ctx_factory(qb):
+    def make(L, inner=(1, 1, 1, 1)):
+        if qb.is_initialized():
+            qb.finalize()
+        qb.init(L)
+        qb.set_host_layout(inner)
+        return qb
+    yield make
+    if qb.is_initialized():
+        qb.finalize()
+
+
+def thin_links(L, phases=True, seed=SEED):
+    lat = oracle.Lattice(L)
+    g = lat.random_gauge(lat.new_rng(seed), 4)
+    if phases:
+        lat.setBC(g)
+        lat.stagPhase(g)
+    return lat, g
+
+
+def up(qb, lo, g):
+    return qb.DeviceGauge([lo.scatter(g[k])[0] for k in range(g.shape[0])])
+
+
+def down(lat, lo, dg):
+    parts = [lo.scatter(lat.gauge(1)[0])[0] for _ in range(dg.nlinks)]
+    dg.download(parts)
+    return np.stack([lo.gather([p]) for p in parts])
+
+
+GEOMS = [((8, 8, 8, 8), (1, 1, 1, 1)), ((4, 6, 8, 10), (1, 1, 1, 1)), ((8, 8, 8, 8), (1, 2, 2, 2))]
+
+
+@pytest.mark.parametrize("L,inner", GEOMS)
+def test_plaq_and_roundtrip(ctx_factory, L, inner):
+    qb = ctx_factory(L, inner)
+    lat, g = thin_links(L, phases=False)
+    lo = oracle.QexLayout(L, (1, 1, 1, 1), inner)
+    dg = up(qb, lo, g)
+    assert np.allclose(dg.plaq(), lat.plaq(g), rtol=0, atol=1e-14)
+    assert np.array_equal(down(lat, lo, dg), g)       # upload -> download is a pure permutation
+    dg.free()
+
+
+def test_fat7_unit_gauge_known_answer(ctx_factory):
+    """The reference's own check (fat7l.nim:185-214): on the unit gauge every plaquette of the fat links
+    is c^4/6 with c = oneLink + 6 threeStaple + 24 fiveStaple + 48 sevenStaple + 6 lepage."""
+    L = (4, 4, 4, 4)
+    qb = ctx_factory(L)
+    lat = oracle.Lattice(L)
+    lo = oracle.QexLayout(L)
+    dg = up(qb, lo, lat.unit_gauge())
+    fl = qb.DeviceGauge(nlinks=4)
+    for c in [(1, 0, 0, 0, 0), (0, 1, 0, 0, 0), (0, 0, 1, 0, 0), (0, 0, 0, 1, 0), (0, 0, 0, 0, 1), (1, 1, 1, 1, 1)]:
+        qb.makeImpLinks(fl, dg, qb.Fat7lCoefs(*[float(t) for t in c]))
+        cc = c[0] + 6 * c[1] + 24 * c[2] + 48 * c[3] + 6 * c[4]
+        want = cc ** 4 / 6.0
+        assert np.allclose(fl.plaq(), want, rtol=1e-13), (c, fl.plaq(), want)
+    fl.free(); dg.free()
+
+
+COEFS = [
+    (0.3, -0.2, 0.0, 0.0, 0.0),                          # 3-staple only
+    (0.3, -0.2, 0.0, 0.0, 0.15),                         # + Lepage
+    (0.3, -0.2, 0.11, 0.0, 0.0),                         # + 5-staple, no 7
+    (0.625, -1 / 16., 1 / 64., -1 / 384., 0.0),          # HISQ first level
+    (1.0, -1 / 16., 1 / 64., -1 / 384., -1 / 8.),        # HISQ second level (all five terms)
+    (0.5, 0.0, 0.0, 0.0, 0.0),                           # one-link only
+]
+
+
+@pytest.mark.parametrize("L,inner", GEOMS[:2])
+def test_makeImpLinks_parity(ctx_factory, L, inner):
+    qb = ctx_factory(L, inner)
+    lat, g = thin_links(L)
+    lo = oracle.QexLayout(L, (1, 1, 1, 1), inner)
+    dg = up(qb, lo, g)
+    fl, ll = qb.DeviceGauge(nlinks=4), qb.DeviceGauge(nlinks=4)
+    for c in COEFS:
+        want = lat.makeImpLinks(g, c)
+        qb.makeImpLinks(fl, dg, qb.Fat7lCoefs(*c))
+        got = down(lat, lo, fl)
+        for mu in range(4):
+            assert rel_l2(got[mu], want[mu]) <= TOL, (c, mu)
+    # with Naik links (fat7l.nim:156-167)
+    c = COEFS[4]
+    wfl, wll = lat.makeImpLinks(g, c, gfLong=g, naik=-1 / 24.)
+    qb.makeImpLinks(fl, dg, qb.Fat7lCoefs(*c), ll, dg, -1 / 24.)
+    gfl, gll = down(lat, lo, fl), down(lat, lo, ll)
+    for mu in range(4):
+        assert rel_l2(gfl[mu], wfl[mu]) <= TOL
+        assert rel_l2(gll[mu], wll[mu]) <= TOL
+    for d in (dg, fl, ll):
+        d.free()
+
+
+@pytest.mark.parametrize("L,inner", GEOMS)
+def test_projectU_parity(ctx_factory, L, inner):
+    qb = ctx_factory(L, inner)
+    lat, g = thin_links(L)
+    fat = lat.makeImpLinks(g, COEFS[3])
+    lo = oracle.QexLayout(L, (1, 1, 1, 1), inner)
+    src, dst = up(qb, lo, fat), qb.DeviceGauge(nlinks=4)
+    dst.projectU(src)
+    got, want = down(lat, lo, dst), lat.projectU(fat)
+    for mu in range(4):
+        assert rel_l2(got[mu], want[mu]) <= TOL
+    m = got[..., 0] + 1j * got[..., 1]
+    assert np.abs(np.einsum("kxab,kxcb->kxac", m, m.conj()) - np.eye(3)).max() < 1e-12
+    src.free(); dst.free()
+
+
+@pytest.mark.parametrize("L,inner", GEOMS)
+def test_hisq_smear_parity_and_solve(ctx_factory, L, inner):
+    """HisqCoefs.smear on the device = the oracle's, and the operator built from the device-resident
+    result (newStag3(fl, ll), src/physics/hisqLinks.nim:47-72 / tests/examples/testStagProp.nim:28-36) gives the
+    oracle's Dslash and CG on the oracle's HISQ links."""
+    qb = ctx_factory(L, inner)
+    lat, g = thin_links(L)
+    lo = oracle.QexLayout(L, (1, 1, 1, 1), inner)
+    wfl, wll = lat.hisq_smear(g, oracle.hisq_coefs())
+    dg = up(qb, lo, g)
+    fl, ll = qb.DeviceGauge(nlinks=4), qb.DeviceGauge(nlinks=4)
+    qb.HisqCoefs().init().smear(dg, fl, ll)
+    gfl, gll = down(lat, lo, fl), down(lat, lo, ll)
+    for mu in range(4):
+        assert rel_l2(gfl[mu], wfl[mu]) <= TOL, mu
+        assert rel_l2(gll[mu], wll[mu]) <= TOL, mu
+    assert np.allclose(fl.plaq(), lat.plaq(wfl), rtol=1e-12, atol=1e-15)
+    s = qb.newStag3(fl, ll)
+    gg = np.zeros((8,) + wfl.shape[1:])
+    gg[0::2], gg[1::2] = wfl, wll
+    x = lat.gaussian_vector(lat.new_rng(11))
+    want, got = lat.vector(), lo.scatter(lat.vector())[0]
+    lat.D(gg, want, x, 0.05)
+    s.D(got, lo.scatter(x)[0], 0.05)
+    assert rel_l2(lo.gather([got]), want) <= TOL
+    sol, ref = lo.scatter(lat.vector())[0], lat.vector()
+    sp = qb.SolverParams(r2req=1e-10)
+    s.solve(sol, lo.scatter(x)[0], 0.05, sp)
+    st = lat.solve(gg, ref, x, 0.05, 1e-10)
+    assert abs(sp.iterations - st.iterations) <= 1
+    assert rel_l2(lo.gather([sol]), ref) < 1e-4
+    for d in (s, dg, fl, ll):
+        d.free()
+
+
+@pytest.mark.parametrize("L,inner", GEOMS)
+def test_hyp_smear_parity_and_solve(ctx_factory, L, inner):
+    """nHYP as staghmc_spv uses it (src/stagg_pv_hmc/staghmc_spv.nim:367-386): smear the thin links, then
+    setBC + stagPhase on the smeared set, then solve -- all on the device."""
+    qb = ctx_factory(L, inner)
+    lat, g = thin_links(L, phases=False)
+    lo = oracle.QexLayout(L, (1, 1, 1, 1), inner)
+    alpha = (0.4, 0.5, 0.5)                      # tests/extra/staghmc_sh/ref.0:62-66
+    want = lat.hyp_smear(g, alpha)
+    dg, fl = up(qb, lo, g), qb.DeviceGauge(nlinks=4)
+    qb.HypCoefs(*alpha).smear(dg, fl)
+    got = down(lat, lo, fl)
+    for mu in range(4):
+        assert rel_l2(got[mu], want[mu]) <= TOL, mu
+    assert np.allclose(fl.plaq(), lat.plaq(want), rtol=1e-12, atol=1e-15)
+    fl.rephase()
+    lat.setBC(want)
+    lat.stagPhase(want)
+    s = qb.newStag(fl)
+    x = lat.gaussian_vector(lat.new_rng(3))
+    sol, ref = lo.scatter(lat.vector())[0], lat.vector()
+    sp = qb.SolverParams(r2req=1e-12)
+    s.solve(sol, lo.scatter(x)[0], 0.1, sp)
+    st = lat.solve(want, ref, x, 0.1, 1e-12)
+    assert abs(sp.iterations - st.iterations) <= 1
+    assert rel_l2(lo.gather([sol]), ref) < 1e-5
+    for d in (s, dg, fl):
+        d.free()
+
+
+def test_hyp_unit_gauge_is_fixed_point(ctx_factory):
+    L = (4, 4, 4, 4)
+    qb = ctx_factory(L)
+    lat, lo = oracle.Lattice(L), oracle.QexLayout(L)
+    dg, fl = up(qb, lo, lat.unit_gauge()), qb.DeviceGauge(nlinks=4)
+    qb.HypCoefs(0.4, 0.5, 0.5).smear(dg, fl)
+    assert np.abs(down(lat, lo, fl) - lat.unit_gauge()).max() < 1e-14
+    dg.free(); fl.free()
+
+
+def test_link_pipeline_errors(ctx_factory):
+    qb = ctx_factory((4, 4, 4, 4))
+    lat, lo = oracle.Lattice((4, 4, 4, 4)), oracle.QexLayout((4, 4, 4, 4))
+    dg, empty = up(qb, lo, lat.unit_gauge()), qb.DeviceGauge(nlinks=4)
+    with pytest.raises(qb.QexB200Error):
+        qb.makeImpLinks(dg, dg, qb.Fat7lCoefs(1, 0, 0, 0, 0))      # in place is refused
+    with pytest.raises(qb.QexB200Error):
+        qb.HypCoefs(0.4, 0.5, 0.5).smear(empty, dg)                # source holds no links
+    with pytest.raises(qb.QexB200Error):
+        empty.plaq()
+    dg.free(); empty.free()

@@ -1,0 +1,103 @@
+"""Host emulation of the device link pipeline's per-site functions (qex_b200/csrc/linkops.cuh compiled
+with g++) against the oracle: index arithmetic of the staple gather, 3x3 algebra, projectU.  No GPU."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import oracle
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+SO = os.path.join(HERE, "emu", "_emu_links.so")
+
+
+@pytest.fixture(scope="module")
+def emu():
+    src = os.path.join(HERE, "emu", "emu_links.cpp")
+    hdr = os.path.join(HERE, "..", "qex_b200", "csrc", "linkops.cuh")
+    if not os.path.exists(SO) or os.path.getmtime(SO) < max(os.path.getmtime(src), os.path.getmtime(hdr)):
+        subprocess.check_call(["/usr/bin/g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-x", "c++",
+                               "-I/usr/local/cuda/include", src, "-o", SO])
+    lib = C.CDLL(SO)
+    dp, ip = C.POINTER(C.c_double), C.POINTER(C.c_int)
+    lib.emu_staple_field.argtypes = [dp, dp, C.c_int, C.c_int, ip, dp]
+    lib.emu_project_field.argtypes = [dp, ip, dp]
+    lib.emu_hop.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, ip, ip]
+    return lib
+
+
+def to_dev(f):
+    """oracle field [vol,3,3,2] -> device layout [2][9][Vh][2]"""
+    vol = f.shape[0]
+    return np.ascontiguousarray(f.reshape(2, vol // 2, 9, 2).transpose(0, 2, 1, 3))
+
+
+def from_dev(d):
+    vh = d.shape[2]
+    return np.ascontiguousarray(d.transpose(0, 2, 1, 3)).reshape(2 * vh, 3, 3, 2)
+
+
+def dp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_double))
+
+
+L = (4, 6, 4, 8)
+
+
+def test_hop_matches_oracle_coords(emu):
+    lat = oracle.Lattice(L)
+    X = (C.c_int * 4)(*L)
+    co = lat.coords
+    vh = lat.half
+    out = (C.c_int * 6)()
+    rng = np.random.default_rng(1)
+    for i in rng.integers(0, lat.vol, 300):
+        par, idx = divmod(int(i), vh)
+        for mu in range(4):
+            for d in (+1, -1, +3, -3):
+                emu.emu_hop(idx, par, mu, d, X, out)
+                assert tuple(out[:4]) == tuple(int(co[k][i]) for k in range(4))
+                y = [int(co[k][i]) for k in range(4)]
+                y[mu] = (y[mu] + d) % L[mu]
+                j = out[4] * vh + out[5]
+                assert tuple(int(co[k][j]) for k in range(4)) == tuple(y)
+
+
+def test_staple_pair_matches_makeImpLinks(emu):
+    """threeStaple-only makeImpLinks = sum over nu of the staple pair (fat7l.nim:24-76,139)."""
+    lat = oracle.Lattice(L)
+    g = lat.random_gauge(lat.new_rng(987654321))
+    want = lat.makeImpLinks(g, (0.0, 1.0, 0.0, 0.0, 0.0))
+    X = (C.c_int * 4)(*L)
+    gd = [to_dev(g[mu]) for mu in range(4)]
+    for mu in range(4):
+        acc = np.zeros_like(gd[0])
+        for nu in range(4):
+            if nu == mu:
+                continue
+            out = np.zeros_like(gd[0])
+            emu.emu_staple_field(dp(gd[nu]), dp(gd[mu]), nu, mu, X, dp(out))
+            acc += out
+        got = from_dev(acc)
+        err = np.linalg.norm(got - want[mu]) / np.linalg.norm(want[mu])
+        assert err < 1e-14, (mu, err)
+
+
+def test_project_u_matches_oracle(emu):
+    lat = oracle.Lattice(L)
+    g = lat.random_gauge(lat.new_rng(5))
+    fat = lat.makeImpLinks(g, (0.625, -1.0 / 16, 1.0 / 64, -1.0 / 384, 0.0))
+    want = lat.projectU(fat)
+    X = (C.c_int * 4)(*L)
+    for mu in range(4):
+        out = np.zeros_like(to_dev(fat[mu]))
+        emu.emu_project_field(dp(to_dev(fat[mu])), X, dp(out))
+        got = from_dev(out)
+        err = np.linalg.norm(got - want[mu]) / np.linalg.norm(want[mu])
+        assert err < 1e-13, (mu, err)
+        # and the result is unitary
+        m = got[..., 0] + 1j * got[..., 1]
+        dev = np.abs(np.einsum("xab,xcb->xac", m, m.conj()) - np.eye(3)).max()
+        assert dev < 1e-12
