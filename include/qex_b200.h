@@ -220,6 +220,24 @@ int qexb200_dev_solveXX_multi(qexb200_gauge_t g, int parity, const qexb200_field
 int qexb200_dev_solve_multi(qexb200_gauge_t g, const qexb200_field_t* xs, qexb200_field_t b,
                             const double* ms, int nmass, qexb200_solver_params* sp);
 
+/* ---- fermion-force outer products (src/physics/stagD.nim:588-664) -----------------
+ * Link-shaped outputs live in gauge handles with the operator's link count (4, or 8 with the three-hop
+ * fields at 2 mu + 1).  Single rank for now (error on a split lattice). */
+int qexb200_gauge_zero(qexb200_gauge_t g);            /* f[mu] := 0 */
+int qexb200_gauge_scale(qexb200_gauge_t g, double c); /* g[mu] *= c (src/hmc/agradOps.nim:513-520) */
+/* stagDeriv(s, f, x) (stagD.nim:635-664): f[mu](e) += x(e) (x) x(e+mu)^+, f[mu](o) -= x(o) (x) x(o+mu)^+,
+ * then s.rephase f.  4 link fields. */
+int qexb200_dev_stagDeriv(qexb200_gauge_t s, qexb200_gauge_t f, qexb200_field_t x);
+int qexb200_stagDeriv(qexb200_gauge_t s, double* const* f, const double* x);
+/* stagD2deriv(s, g, c, x) (stagD.nim:588-633) = (d/dg) redot[(2D) x, c]:
+ * g[k] += c (x) x(+h_k)^+ - x (x) c(+h_k)^+ on all sites. */
+int qexb200_dev_stagD2deriv(qexb200_gauge_t s, qexb200_gauge_t g, qexb200_field_t c, qexb200_field_t x);
+int qexb200_stagD2deriv(qexb200_gauge_t s, double* const* g, const double* c, const double* x);
+/* The force loop of src/stagg_pv_hmc/staghmc_spv.nim:826-850:
+ * f[k](x) (+)= (x even ? scale_even : scale_odd) * a(x) (x) b(x+h_k)^+; accumulate == 0 overwrites. */
+int qexb200_dev_outer(qexb200_gauge_t f, qexb200_field_t a, qexb200_field_t b, double scale_even,
+                      double scale_odd, int accumulate);
+
 /* ---- halo plan (pure host arithmetic, usable without a GPU) ---------------- */
 
 /* One entry per direction split over ranks: what this rank sends each parity sweep.  It is the

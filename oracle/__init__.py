@@ -90,6 +90,9 @@ def lib():
         L.orc_projectU_field.argtypes = [vp, dp, dp, C.c_int]
         L.orc_hisq_smear.argtypes = [vp, dp, dp, dp, dp]
         L.orc_hyp_smear.argtypes = [vp, dp, dp, dp]
+        L.orc_outer.argtypes = [vp, C.c_int, dp, dp, dp, C.c_double, C.c_double, C.c_int]
+        L.orc_stagDeriv.argtypes = [vp, C.c_int, dp, dp]
+        L.orc_stagD2deriv.argtypes = [vp, C.c_int, dp, dp, dp]
         L.orc_layout_setup.argtypes = [C.POINTER(OrcLayout), ip, ip, ip]
         L.orc_layout_index.argtypes = [C.POINTER(OrcLayout), ip, ip, ip]
         L.orc_layout_coord.argtypes = [C.POINTER(OrcLayout), C.c_int, C.c_int, ip]
@@ -205,6 +208,19 @@ class Lattice:
         fl = self.gauge(4)
         lib().orc_hyp_smear(self.h, _dp(g), _dp(a), _dp(fl))
         return fl
+
+    # -- fermion-force outer products --------------------------------------
+    def outer(self, f, a, b, ce=1.0, co=1.0, accumulate=True):
+        """f[k](x) (+)= (ce|co) a(x) (x) b(x+h_k)^+  (staghmc_spv.nim:833-850)."""
+        lib().orc_outer(self.h, f.shape[0], _dp(f), _dp(a), _dp(b), ce, co, int(accumulate))
+
+    def stagDeriv(self, f, x):
+        """stagDeriv (stagD.nim:635-664)."""
+        lib().orc_stagDeriv(self.h, f.shape[0], _dp(f), _dp(x))
+
+    def stagD2deriv(self, g, c, x):
+        """stagD2deriv (stagD.nim:588-633)."""
+        lib().orc_stagD2deriv(self.h, g.shape[0], _dp(g), _dp(c), _dp(x))
 
     # -- operator ----------------------------------------------------------
     def stagD2(self, g, r, x, a, b, parity):

@@ -985,6 +985,44 @@ void orc_hyp_smear(void* lat, const double* g, const double* alpha, double* fl_)
   }
 }
 
+// ---------------------------------------------------------------------------
+// Fermion-force outer products (src/physics/stagD.nim:588-664; peqOuter/meqOuter
+// src/maths/matrixConcept.nim:717-724: r[i][j] +-= x[i] * conj(y[j])).
+// f = nd contiguous link-shaped fields [k][vol][18], hop of field k as in the operator.
+// ---------------------------------------------------------------------------
+static inline void outer_acc(double* f, const double* a, const double* b, double s) {
+  for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) {
+    const double ar = a[2 * i], ai = a[2 * i + 1], br = b[2 * j], bi = b[2 * j + 1];
+    f[(i * 3 + j) * 2] += s * (ar * br + ai * bi);
+    f[(i * 3 + j) * 2 + 1] += s * (ai * br - ar * bi);
+  }
+}
+// f[k](x) (+)= (x even ? ce : co) * a(x) (x) b(x + h_k)^+ ; accumulate == 0 overwrites
+// (the loop of staghmc_spv.nim:833-850 with frc_ind == 0 / > 0)
+void orc_outer(void* lat, int nd, double* f, const double* a, const double* b, double ce, double co, int accumulate) {
+  Lat* l = (Lat*)lat;
+  const size_t fs = (size_t)l->vol * 18;
+  for (int k = 0; k < nd; k++) {
+    const int mu = nd == 8 ? k / 2 : k, h = (nd == 8 && (k & 1)) ? 1 : 0;
+#pragma omp parallel for
+    for (int i = 0; i < l->vol; i++) {
+      double* fk = f + k * fs + (size_t)i * 18;
+      if (!accumulate) for (int e = 0; e < 18; e++) fk[e] = 0.0;
+      outer_acc(fk, a + (size_t)i * 6, b + (size_t)l->fwd[mu][h][i] * 6, i < l->half ? ce : co);
+    }
+  }
+}
+// stagDeriv, stagD.nim:635-664: even sites +=, odd sites -=, then s.rephase f (nd == 4)
+void orc_stagDeriv(void* lat, int nd, double* f, const double* x) {
+  orc_outer(lat, nd, f, x, x, 1.0, -1.0, 1);
+  if (nd == 4) { orc_setbc(lat, f); orc_stagphase(lat, f); }
+}
+// stagD2deriv, stagD.nim:588-633: g += c (x) x(+h)^+ ; g -= x (x) c(+h)^+  on all sites
+void orc_stagD2deriv(void* lat, int nd, double* g, const double* c, const double* x) {
+  orc_outer(lat, nd, g, c, x, 1.0, 1.0, 1);
+  orc_outer(lat, nd, g, x, c, -1.0, -1.0, 1);
+}
+
 int orc_num_threads() { return omp_get_max_threads(); }
 void orc_set_num_threads(int n) { omp_set_num_threads(n); }
 

@@ -94,6 +94,13 @@ def lib():
         L.qexb200_gauge_plaq.argtypes = [C.c_int, dp]
         L.qexb200_gauge_join3.argtypes = [C.c_int, C.c_int, C.c_int]
         L.qexb200_gauge_download.argtypes = [C.c_int, C.POINTER(dp)]
+        L.qexb200_gauge_zero.argtypes = [C.c_int]
+        L.qexb200_gauge_scale.argtypes = [C.c_int, C.c_double]
+        L.qexb200_dev_stagDeriv.argtypes = [C.c_int, C.c_int, C.c_int]
+        L.qexb200_stagDeriv.argtypes = [C.c_int, C.POINTER(dp), dp]
+        L.qexb200_dev_stagD2deriv.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int]
+        L.qexb200_stagD2deriv.argtypes = [C.c_int, C.POINTER(dp), dp, dp]
+        L.qexb200_dev_outer.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_int]
         L.qexb200_stagD2.argtypes = [C.c_int, C.c_int, dp, dp, C.c_double, C.c_double]
         L.qexb200_stagD.argtypes = [C.c_int, C.c_int, dp, dp, C.c_double, C.c_double, C.c_double]
         L.qexb200_D.argtypes = [C.c_int, dp, dp, C.c_double]
@@ -345,6 +352,16 @@ class DeviceGauge:
     def projectU(self, src):
         _ck(lib().qexb200_gauge_projectU(self.h, src.h))
 
+    def zero(self):
+        _ck(lib().qexb200_gauge_zero(self.h))
+
+    def scale(self, c):
+        _ck(lib().qexb200_gauge_scale(self.h, float(c)))
+
+    def outer(self, a, b, scale_even=1.0, scale_odd=1.0, accumulate=True):
+        """f[mu](x) (+)= scale * a(x) (x) b(x+mu)^+ on DeviceFields (staghmc_spv.nim:826-850)."""
+        _ck(lib().qexb200_dev_outer(self.h, a.h, b.h, float(scale_even), float(scale_odd), int(accumulate)))
+
     def recon(self, want=12):
         """Ask for 12-real (rows 0,1 + rebuilt third row) or 18-real link storage; returns
         ([recon of one-hop class, recon of three-hop class], [measured deviation per class])."""
@@ -511,3 +528,21 @@ def stagD2ee(s, r, x, m2):
 def stagD2oo(s, r, x, m2):
     """stagD2oo (stagD.nim:467-469)."""
     _ck(lib().qexb200_stagD2xx(s.h, ODD, _dp(r), _dp(x), m2))
+
+
+def stagDeriv(s, f, x):
+    """stagDeriv(s, f, x) (stagD.nim:635-664).  f: DeviceGauge + x: DeviceField, or host link fields + host vector."""
+    if isinstance(f, DeviceGauge):
+        _ck(lib().qexb200_dev_stagDeriv(s.h, f.h, x.h))
+    else:
+        arr = (C.POINTER(C.c_double) * len(f))(*[_dp(t) for t in f])
+        _ck(lib().qexb200_stagDeriv(s.h, arr, _dp(x)))
+
+
+def stagD2deriv(s, g, c, x):
+    """stagD2deriv(s, g, c, x) (stagD.nim:588-633): g += (d/dg) redot[(2D) x, c]."""
+    if isinstance(g, DeviceGauge):
+        _ck(lib().qexb200_dev_stagD2deriv(s.h, g.h, c.h, x.h))
+    else:
+        arr = (C.POINTER(C.c_double) * len(g))(*[_dp(t) for t in g])
+        _ck(lib().qexb200_stagD2deriv(s.h, arr, _dp(c), _dp(x)))

@@ -53,6 +53,7 @@ int nccl_load() {
 }
 
 static std::map<int, Gauge> g_gauges;
+static Gauge g_hf;   // staging link set of the host-field force calls
 static std::map<int, Field> g_fields;
 static int g_next_handle = 1;
 
@@ -461,6 +462,7 @@ int qexb200_finalize(void) {
   if (g_ht.ok) { cudaFree(g_ht.a.d); cudaFree(g_ht.b.d); g_ht = HostTmp(); }
   cg_free();
   smear_free();
+  if (g_hf.d) { cudaFree(g_hf.d); g_hf = Gauge(); }
   halo_free();
   p2p_free();
   if (g_ctx.h_err) cudaFreeHost(g_ctx.h_err);
@@ -739,6 +741,70 @@ int qexb200_dev_solve(qexb200_gauge_t hg, qexb200_field_t x, qexb200_field_t b, 
   return op_solve(*g, *f1, *f2, m, sp);
 }
 
+// ---- fermion-force outer products (force.cu) ----------------------
+static int op_outer(Gauge& f, const Field& a, const Field& b, double ce, double co, bool acc) {
+  const OuterPair p = {a.d, b.d, ce, co};
+  QB_CHECK(outer_products(f, &p, 1, acc));
+  f.loaded = true;
+  return 0;
+}
+// stagDeriv(s, f, x), stagD.nim:635-664: f[mu] += x (x) x(+mu)^+ on even sites, -= on odd sites, then s.rephase f
+static int op_stagDeriv(Gauge& f, const Field& x) {
+  if (f.nlinks != 4) return fail("stagDeriv: the force field must hold 4 link fields (s.rephase f, stagD.nim:664)");
+  QB_CHECK(op_outer(f, x, x, 1.0, -1.0, true));
+  return rephase(f);
+}
+// stagD2deriv(s, g, c, x), stagD.nim:588-633: g[mu] += c (x) x(+h)^+ - x (x) c(+h)^+
+static int op_stagD2deriv(Gauge& g, const Field& c, const Field& x) {
+  const OuterPair p[2] = {{c.d, x.d, 1.0, 1.0}, {x.d, c.d, -1.0, -1.0}};
+  QB_CHECK(outer_products(g, p, 2, true));
+  g.loaded = true;
+  return 0;
+}
+static int same_links(const Gauge* s, const Gauge* f, const char* who) {
+  if (s->nlinks != f->nlinks) return fail("%s: operator has %d link fields, force field %d", who, s->nlinks, f->nlinks);
+  return 0;
+}
+int qexb200_gauge_zero(qexb200_gauge_t h) {
+  QB_CHECK(need_ctx());
+  Gauge* g; QB_CHECK(get_gauge(h, &g));
+  QB_CUDA(cudaMemsetAsync(g->d, 0, sizeof(double2) * (size_t)g->nlinks * 18 * g_ctx.g.Vh, g_ctx.stream));
+  g->loaded = true;
+  free_compressed(*g);
+  return 0;
+}
+int qexb200_gauge_scale(qexb200_gauge_t h, double c) {
+  QB_CHECK(need_ctx());
+  Gauge* g; QB_CHECK(get_gauge(h, &g));
+  if (!g->loaded) return fail("gauge_scale: gauge holds no links");
+  QB_CHECK(blas_scale(g->d, c, (size_t)g->nlinks * 18 * g_ctx.g.Vh));
+  return compress_links(*g);
+}
+int qexb200_dev_outer(qexb200_gauge_t hf, qexb200_field_t ha, qexb200_field_t hb, double scale_even,
+                      double scale_odd, int accumulate) {
+  QB_CHECK(need_ctx());
+  Gauge* f; QB_CHECK(get_gauge(hf, &f));
+  Field *a, *b; QB_CHECK(get_field(ha, &a)); QB_CHECK(get_field(hb, &b));
+  if (accumulate && !f->loaded) return fail("outer: accumulating into a link set that holds nothing");
+  return op_outer(*f, *a, *b, scale_even, scale_odd, accumulate != 0);
+}
+int qexb200_dev_stagDeriv(qexb200_gauge_t hs, qexb200_gauge_t hf, qexb200_field_t hx) {
+  QB_CHECK(need_ctx());
+  Gauge *s, *f; QB_CHECK(get_gauge(hs, &s)); QB_CHECK(get_gauge(hf, &f));
+  Field* x; QB_CHECK(get_field(hx, &x));
+  QB_CHECK(same_links(s, f, "stagDeriv"));
+  if (!f->loaded) return fail("stagDeriv: f holds nothing (zero it first, the reference accumulates)");
+  return op_stagDeriv(*f, *x);
+}
+int qexb200_dev_stagD2deriv(qexb200_gauge_t hs, qexb200_gauge_t hg, qexb200_field_t hc, qexb200_field_t hx) {
+  QB_CHECK(need_ctx());
+  Gauge *s, *g; QB_CHECK(get_gauge(hs, &s)); QB_CHECK(get_gauge(hg, &g));
+  Field *c, *x; QB_CHECK(get_field(hc, &c)); QB_CHECK(get_field(hx, &x));
+  QB_CHECK(same_links(s, g, "stagD2deriv"));
+  if (!g->loaded) return fail("stagD2deriv: g holds nothing (zero it first, the reference accumulates)");
+  return op_stagD2deriv(*g, *c, *x);
+}
+
 // ---- host-buffer entry points: H2D, device op, D2H ---------------------------
 static int host_tmp() {
   if (g_ht.ok && g_ht.Vh == g_ctx.g.Vh) return 0;
@@ -797,6 +863,32 @@ int qexb200_eoReconstruct(qexb200_gauge_t hg, double* r, const double* b, double
   QB_CHECK(upload_vector(X, b));
   QB_CHECK(op_eoReconstruct(*g, R, X, m));
   return download_vector(R, r);
+}
+// stagDeriv / stagD2deriv on HOST fields: f (nd link fields, accumulated into) and the vectors in native QEX memory
+static int host_force_tmp(int nlinks) {
+  if (g_hf.d && g_hf.nlinks == nlinks) return 0;
+  if (g_hf.d) { cudaFree(g_hf.d); g_hf = Gauge(); }
+  g_hf.nlinks = nlinks;
+  QB_CUDA(cudaMalloc(&g_hf.d, sizeof(double2) * (size_t)nlinks * 18 * g_ctx.g.Vh));
+  return 0;
+}
+int qexb200_stagDeriv(qexb200_gauge_t hg, double* const* f, const double* x) {
+  HOST_PROLOGUE(hg);
+  (void)R;
+  QB_CHECK(host_force_tmp(g->nlinks));
+  QB_CHECK(upload_links(g_hf, f));
+  QB_CHECK(upload_vector(X, x));
+  QB_CHECK(op_stagDeriv(g_hf, X));
+  return download_links(g_hf, f);
+}
+int qexb200_stagD2deriv(qexb200_gauge_t hg, double* const* gr, const double* c, const double* x) {
+  HOST_PROLOGUE(hg);
+  QB_CHECK(host_force_tmp(g->nlinks));
+  QB_CHECK(upload_links(g_hf, gr));
+  QB_CHECK(upload_vector(R, c));
+  QB_CHECK(upload_vector(X, x));
+  QB_CHECK(op_stagD2deriv(g_hf, R, X));
+  return download_links(g_hf, gr);
 }
 int qexb200_solveXX(qexb200_gauge_t hg, int parity, double* r, const double* x, double m, qexb200_solver_params* sp) {
   HOST_PROLOGUE(hg);

@@ -242,6 +242,14 @@ int project_fields(double2* out, const double2* in, int nfields);
 int plaq_links(const double2* const u[4], double pl[6]);
 int smear_free();
 
+// ---- force.cu (fermion-force outer products) ---------------------------------
+struct OuterPair {
+  const double2* a;   // full field [2][3][Vh], taken at x
+  const double2* b;   // full field, taken at x + h
+  double ce, co;      // weight on even / odd sites x
+};
+int outer_products(Gauge& f, const OuterPair* pairs, int np, bool accumulate);
+
 // ---- comm.cu ----------------------------------------------------------------
 int halo_setup();
 int plan_halo(const Geom& g, int nl, std::vector<HaloDir>& dirs, size_t* total);
