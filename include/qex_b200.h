@@ -220,6 +220,20 @@ int qexb200_dev_solveXX_multi(qexb200_gauge_t g, int parity, const qexb200_field
 int qexb200_dev_solve_multi(qexb200_gauge_t g, const qexb200_field_t* xs, qexb200_field_t b,
                             const double* ms, int nmass, qexb200_solver_params* sp);
 
+/* ---- gauge import straight into the device layout --------------------------------
+ * loadGauge (src/gauge/gaugeUtils.nim:87-106) through Reader.read (src/io/readerQiolite.nim:108-165): the
+ * rank's hypercube of the record goes to the GPU as raw bytes; byte swap, float -> double and the
+ * permutation into the device layout are one kernel.  4 link fields. */
+/* getFileLattice (readerQiolite.nim:11-17); pure host, needs no GPU */
+int qexb200_scidac_lattice(const char* filename, int dims[4]);
+/* First lattice record of a SciDAC (or ILDG) file -> g.  sums (may be NULL) = {file suma, file sumb, this rank's
+ * partial suma, partial sumb}: a single rank verifies the checksum itself (mismatch = error); several ranks
+ * each read their own hypercube and the caller XORs the partials over the ranks. */
+int qexb200_gauge_read_scidac(qexb200_gauge_t g, const char* filename, unsigned int sums[4]);
+/* Site-major host array [local site, lexicographic x0 fastest][mu][3][3][re,im] of 4- or 8-byte reals, e.g. the
+ * MILC-order arrays the QUDA wrapper builds (src/quda/qudaWrapperImpl.nim:216-240) or a reader's raw record. */
+int qexb200_gauge_load_sitemajor(qexb200_gauge_t g, const void* data, int precision_bytes, int big_endian);
+
 /* ---- fermion-force outer products (src/physics/stagD.nim:588-664) -----------------
  * Link-shaped outputs live in gauge handles with the operator's link count (4, or 8 with the three-hop
  * fields at 2 mu + 1).  Single rank for now (error on a split lattice). */

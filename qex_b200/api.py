@@ -101,6 +101,9 @@ def lib():
         L.qexb200_dev_stagD2deriv.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int]
         L.qexb200_stagD2deriv.argtypes = [C.c_int, C.POINTER(dp), dp, dp]
         L.qexb200_dev_outer.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_int]
+        L.qexb200_scidac_lattice.argtypes = [C.c_char_p, ip]
+        L.qexb200_gauge_read_scidac.argtypes = [C.c_int, C.c_char_p, C.POINTER(C.c_uint)]
+        L.qexb200_gauge_load_sitemajor.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_int]
         L.qexb200_stagD2.argtypes = [C.c_int, C.c_int, dp, dp, C.c_double, C.c_double]
         L.qexb200_stagD.argtypes = [C.c_int, C.c_int, dp, dp, C.c_double, C.c_double, C.c_double]
         L.qexb200_D.argtypes = [C.c_int, dp, dp, C.c_double]
@@ -216,6 +219,13 @@ def finalize():
 
 def is_initialized():
     return _lib is not None and bool(_lib.qexb200_is_initialized())
+
+
+def getFileLattice(fn):
+    """getFileLattice (src/io/readerQiolite.nim:11-17)."""
+    d = (C.c_int * 4)()
+    _ck(lib().qexb200_scidac_lattice(os.fsencode(fn), d))
+    return list(d)
 
 
 def set_host_layout(innergeom):
@@ -342,6 +352,18 @@ class DeviceGauge:
 
     def rephase(self):
         _ck(lib().qexb200_gauge_rephase(self.h))
+
+    def loadGauge(self, fn):
+        """loadGauge(g, fn) (src/gauge/gaugeUtils.nim:87-106): first lattice record of a SciDAC/ILDG file.
+        Returns (file suma, file sumb, this rank's suma, this rank's sumb)."""
+        sums = (C.c_uint * 4)()
+        _ck(lib().qexb200_gauge_read_scidac(self.h, os.fsencode(fn), sums))
+        return tuple(int(t) for t in sums)
+
+    def load_sitemajor(self, data, big_endian=False):
+        """Site-major array [site lex][mu][3][3][2] (float32 or float64), e.g. MILC order."""
+        a = np.ascontiguousarray(data)
+        _ck(lib().qexb200_gauge_load_sitemajor(self.h, a.ctypes.data_as(C.c_void_p), a.dtype.itemsize, int(big_endian)))
 
     def plaq(self):
         """plaq (src/gauge/gaugeUtils.nim:213-284) of the one-hop links."""

@@ -462,6 +462,7 @@ int qexb200_finalize(void) {
   if (g_ht.ok) { cudaFree(g_ht.a.d); cudaFree(g_ht.b.d); g_ht = HostTmp(); }
   cg_free();
   smear_free();
+  io_free();
   if (g_hf.d) { cudaFree(g_hf.d); g_hf = Gauge(); }
   halo_free();
   p2p_free();
@@ -649,6 +650,25 @@ int qexb200_gauge_join3(qexb200_gauge_t hout, qexb200_gauge_t hfl, qexb200_gauge
     QB_CUDA(cudaMemcpyAsync(link_field(o, 2 * mu + 1), link_field(ll, mu), sizeof(double2) * n, cudaMemcpyDeviceToDevice, g_ctx.stream));
   }
   return links_written(o);
+}
+
+// ---- gauge import (io.cu) ------------------------------------------
+int qexb200_gauge_load_sitemajor(qexb200_gauge_t h, const void* data, int precision_bytes, int big_endian) {
+  QB_CHECK(need_ctx());
+  Gauge* g; QB_CHECK(get_gauge(h, &g));
+  if (!data) return fail("gauge_load_sitemajor: data is NULL");
+  return import_sitemajor(*g, data, precision_bytes, big_endian);
+}
+int qexb200_gauge_read_scidac(qexb200_gauge_t h, const char* filename, unsigned int sums[4]) {
+  QB_CHECK(need_ctx());
+  Gauge* g; QB_CHECK(get_gauge(h, &g));
+  if (!filename) return fail("gauge_read_scidac: filename is NULL");
+  return read_scidac(*g, filename, sums);
+}
+int qexb200_scidac_lattice(const char* filename, int dims[4]) {
+  clear_error();
+  if (!filename) return fail("scidac_lattice: filename is NULL");
+  return scidac_lattice(filename, dims);
 }
 
 // ---- device fields -----------------------------------------------------------

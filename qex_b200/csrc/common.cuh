@@ -250,6 +250,12 @@ struct OuterPair {
 };
 int outer_products(Gauge& f, const OuterPair* pairs, int np, bool accumulate);
 
+// ---- io.cu (SciDAC/LIME and site-major import into the device layout) -------
+int import_sitemajor(Gauge& g, const void* data, int prec, int big_endian);
+int read_scidac(Gauge& g, const char* fn, unsigned sums[4]);
+int scidac_lattice(const char* fn, int dims[4]);
+int io_free();
+
 // ---- comm.cu ----------------------------------------------------------------
 int halo_setup();
 int plan_halo(const Geom& g, int nl, std::vector<HaloDir>& dirs, size_t* total);
