@@ -451,7 +451,7 @@ int qexb200_finalize(void) {
   if (!g_ctx.live) return 0;
   cudaStreamSynchronize(g_ctx.stream);
   cudaStreamSynchronize(g_ctx.comm_stream);
-  for (auto& kv : g_gauges) { cudaFree(kv.second.d); free_compressed(kv.second); }
+  for (auto& kv : g_gauges) { links_free(kv.second.d, kv.second.nlinks, kv.second.arena); free_compressed(kv.second); }
   for (auto& kv : g_fields) cudaFree(kv.second.d);
   g_gauges.clear(); g_fields.clear();
   if (g_sw.ok) { cudaFree(g_sw.r.d); cudaFree(g_sw.y.d); cudaFree(g_sw.d.d); g_sw = SolveWork(); }
@@ -463,7 +463,7 @@ int qexb200_finalize(void) {
   cg_free();
   smear_free();
   io_free();
-  if (g_hf.d) { cudaFree(g_hf.d); g_hf = Gauge(); }
+  if (g_hf.d) { links_free(g_hf.d, g_hf.nlinks, g_hf.arena); g_hf = Gauge(); }
   halo_free();
   p2p_free();
   if (g_ctx.h_err) cudaFreeHost(g_ctx.h_err);
@@ -502,7 +502,7 @@ int qexb200_gauge_create(int nlinks, qexb200_gauge_t* out) {
   if (nlinks != 4 && nlinks != 8) return fail("gauge_create: nlinks must be 4 (naive) or 8 (fat+Naik), got %d", nlinks);
   Gauge g;
   g.nlinks = nlinks;
-  QB_CUDA(cudaMalloc(&g.d, sizeof(double2) * (size_t)nlinks * 18 * g_ctx.g.Vh));
+  QB_CHECK(links_alloc(nlinks, &g.d, &g.arena));
   const int h = g_next_handle++;
   g_gauges[h] = g;
   *out = h;
@@ -517,7 +517,7 @@ int qexb200_gauge_destroy(qexb200_gauge_t h) {
   QB_CHECK(need_ctx());
   Gauge* g; QB_CHECK(get_gauge(h, &g));
   cudaStreamSynchronize(g_ctx.stream);
-  cudaFree(g->d);
+  links_free(g->d, g->nlinks, g->arena);
   free_compressed(*g);
   g_gauges.erase(h);
   return 0;
@@ -887,10 +887,9 @@ int qexb200_eoReconstruct(qexb200_gauge_t hg, double* r, const double* b, double
 // stagDeriv / stagD2deriv on HOST fields: f (nd link fields, accumulated into) and the vectors in native QEX memory
 static int host_force_tmp(int nlinks) {
   if (g_hf.d && g_hf.nlinks == nlinks) return 0;
-  if (g_hf.d) { cudaFree(g_hf.d); g_hf = Gauge(); }
+  if (g_hf.d) { links_free(g_hf.d, g_hf.nlinks, g_hf.arena); g_hf = Gauge(); }
   g_hf.nlinks = nlinks;
-  QB_CUDA(cudaMalloc(&g_hf.d, sizeof(double2) * (size_t)nlinks * 18 * g_ctx.g.Vh));
-  return 0;
+  return links_alloc(nlinks, &g_hf.d, &g_hf.arena);
 }
 int qexb200_stagDeriv(qexb200_gauge_t hg, double* const* f, const double* x) {
   HOST_PROLOGUE(hg);

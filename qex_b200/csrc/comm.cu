@@ -6,7 +6,7 @@
 //                        the product is formed at the source like stagD.nim:359-361)
 // All messages of a sweep go out in one ncclGroup on a dedicated stream so the
 // interior kernel overlaps the transfer; the exterior kernels wait on an event.
-#include "common.cuh"
+#include "stencil.cuh"
 #include <cstdlib>
 #include <cstring>
 
@@ -91,10 +91,81 @@ int p2p_alloc() {
     if (((c.g.comm_mask >> mu) & 1) && c.g.X[mu] < 3) naik_ok = false;
   QB_CHECK(plan_halo(c.g, naik_ok ? 2 : 1, dirs, &cap));
   c.halo_cap = cap;
-  c.win_bytes = WIN_HDR + 2 * cap * sizeof(double2);
-  QB_CUDA(cudaMalloc(&c.win, c.win_bytes));
-  QB_CUDA(cudaMemset(c.win, 0, c.win_bytes));
+  const size_t head = ((WIN_HDR + 2 * cap * sizeof(double2) + 255) / 256) * 256;
+  // arena of link-shaped fields for the multi-rank link pipeline / force (QEXB200_ARENA_FIELDS matrix fields;
+  // an nHYP smear holds 4 + 4 + 24, a HISQ smear 4 + 4 + 4 + 11)
+  int units = 64;
+  if (const char* ev = getenv("QEXB200_ARENA_FIELDS")) units = atoi(ev) < 0 ? 0 : atoi(ev);
+  c.arena_unit = sizeof(double2) * 18 * (size_t)c.g.Vh;
+  c.arena_off = head;
+  c.win_bytes = head + (size_t)units * c.arena_unit;
+  cudaError_t e = cudaMalloc(&c.win, c.win_bytes);
+  if (e != cudaSuccess) return fail("p2p window of %zu bytes (%d arena fields, QEXB200_ARENA_FIELDS): %s", c.win_bytes, units, cudaGetErrorString(e));
+  c.arena_units = units;
+  c.arena_used.assign((size_t)units, 0);
+  QB_CUDA(cudaMemset(c.win, 0, head));
   QB_CUDA(cudaDeviceSynchronize());
+  return 0;
+}
+
+bool in_arena(const void* p) {
+  Context& c = ctx();
+  const char* q = static_cast<const char*>(p);
+  return c.win && q >= c.win + c.arena_off && q < c.win + c.win_bytes;
+}
+// first fit over unit slots: deterministic, so ranks making the same calls get the same offsets
+int links_alloc(int nfields, double2** out, bool* arena) {
+  Context& c = ctx();
+  *arena = false;
+  if (c.g.nranks > 1 && c.win && c.arena_units > 0) {
+    for (int i = 0; i + nfields <= c.arena_units; i++) {
+      int j = 0;
+      while (j < nfields && !c.arena_used[(size_t)(i + j)]) j++;
+      if (j == nfields) {
+        for (j = 0; j < nfields; j++) c.arena_used[(size_t)(i + j)] = 1;
+        *out = reinterpret_cast<double2*>(c.win + c.arena_off + (size_t)i * c.arena_unit);
+        *arena = true;
+        return 0;
+      }
+      i += j;
+    }
+    return fail("the peer arena (%d matrix fields) is full: raise QEXB200_ARENA_FIELDS", c.arena_units);
+  }
+  QB_CUDA(cudaMalloc(out, sizeof(double2) * 18 * (size_t)c.g.Vh * nfields));
+  return 0;
+}
+void links_free(double2* p, int nfields, bool arena) {
+  Context& c = ctx();
+  if (!p) return;
+  if (!arena) { cudaFree(p); return; }
+  if (!c.win) return;   // window already gone (finalize)
+  const size_t i = (size_t)(reinterpret_cast<char*>(p) - (c.win + c.arena_off)) / c.arena_unit;
+  for (int j = 0; j < nfields && i + j < c.arena_used.size(); j++) c.arena_used[i + j] = 0;
+}
+int peers_fill(Peers* pr) {
+  Context& c = ctx();
+  if (!c.p2p) return fail("this operation on a lattice split over ranks needs the peer-memory transport (qexb200_p2p_attach)");
+  memset(pr, 0, sizeof *pr);
+  for (int r = 0; r < c.g.nranks; r++) pr->base[r] = c.peer_win[r] + c.arena_off;
+  pr->me = c.g.rank;
+  for (int nb = 0; nb < 81; nb++) {
+    int t = nb, r = 0, rc[4];
+    for (int d = 0; d < 4; d++) { const int disp = t % 3 - 1; t /= 3; rc[d] = ((c.g.rc[d] + disp) % c.g.G[d] + c.g.G[d]) % c.g.G[d]; }
+    for (int d = 0; d < 4; d++) r = r * c.g.G[d] + rc[d];   // dimension 0 slowest (qlayout.nim:94-113)
+    pr->peer_of[nb] = (unsigned char)r;
+  }
+  return 0;
+}
+// Cross-rank barrier on the compute stream: one warp pushes a sequence word into every peer's LL slot and
+// waits for everybody's (xrank_sum of zeros).  Kernel boundaries order it after this rank's earlier kernels.
+__global__ void k_xbarrier(XRank* xr) { (void)xrank_sum(xr, 0.0); }
+int xbarrier() {
+  Context& c = ctx();
+  if (c.g.nranks < 2) return 0;
+  if (!c.p2p) return fail("cross-rank barrier needs the peer-memory transport (qexb200_p2p_attach)");
+  k_xbarrier<<<1, 32, 0, c.stream>>>(c.d_xr);
+  count_launch();
+  QB_CUDA(cudaGetLastError());
   return 0;
 }
 
@@ -157,6 +228,7 @@ int p2p_free() {
   if (c.win) cudaFree(c.win);
   if (c.d_xr) cudaFree(c.d_xr);
   c.win = nullptr; c.d_xr = nullptr; c.p2p = false; c.win_bytes = 0; c.halo_cap = 0;
+  c.arena_units = 0; c.arena_used.clear(); c.arena_off = 0;
   return 0;
 }
 

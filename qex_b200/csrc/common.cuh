@@ -7,6 +7,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <nccl.h>
+#include "linkops.cuh"
 #include <cstdint>
 #include <cstdio>
 #include <string>
@@ -121,6 +122,11 @@ struct Context {
   int* h_err = nullptr;             // mapped pinned error word
   int* d_err = nullptr;             // its device alias
   unsigned int halo_seq = 0;        // parity sweeps exchanged so far (identical on all ranks)
+  // symmetric arena inside the window: link-shaped fields of multi-rank contexts live here, at the same
+  // offsets on every rank (SPMD call order), so kernels can read a neighbour's copy over NVLink
+  size_t arena_off = 0, arena_unit = 0; // byte offset inside the window; bytes of one matrix field (18 Vh double2)
+  int arena_units = 0;
+  std::vector<char> arena_used;     // one flag per unit
   unsigned long long p2p_timeout_ns = 120ull * 1000000000ull;  // QEXB200_P2P_TIMEOUT_S
 };
 
@@ -173,6 +179,7 @@ struct Gauge {
   int nlinks = 0;        // 4 or 8
   double2* d = nullptr;  // [nlinks][2][9][Vh]
   bool loaded = false;
+  bool arena = false;    // d lives in the peer-mapped arena (multi-rank contexts)
   // 12-real compression (layout.cu compress_links)
   int want12 = 0;                 // sticky request (bit j: class j), re-applied after every load / rephase
   int recon[2] = {18, 18};        // what the sweeps read per link class
@@ -265,6 +272,12 @@ int p2p_alloc();                       // allocate the window (multi-rank contex
 int p2p_export(void* out64);
 int p2p_attach(const void* handles);   // nranks * 64 bytes, rank order
 int p2p_free();
+// matrix-field storage: the peer-mapped arena on multi-rank contexts with a window, cudaMalloc otherwise
+int links_alloc(int nfields, double2** out, bool* in_arena);
+void links_free(double2* p, int nfields, bool in_arena);
+bool in_arena(const void* p);
+int peers_fill(Peers* pr);          // kernel-side view of the arena (needs qexb200_p2p_attach)
+int xbarrier();                     // all ranks' earlier work on the compute stream is complete and visible
 int halo_begin(const Gauge& g);
 // Start the exchange for a sweep that outputs `parity`: pack, then send/recv on comm_stream.
 int halo_start(const Gauge& g, int parity, const double2* x);

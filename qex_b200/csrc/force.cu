@@ -19,7 +19,10 @@ struct OuterArgs {
   int accumulate;
   int X[4];
   int Vh;
+  Peers pr;
 };
+int pool_acquire(double2** out);   // smear.cu: pooled matrix-field temporaries (arena-backed on split lattices)
+void pool_release(double2* p);
 
 __device__ __forceinline__ void ld_vec(double2 (&v)[3], const double2* f, const LSite& s, int Vh) {
   const double2* p = f + (size_t)s.par * 3 * Vh + s.idx;
@@ -27,7 +30,17 @@ __device__ __forceinline__ void ld_vec(double2 (&v)[3], const double2* f, const 
   for (int c = 0; c < 3; c++) v[c] = __ldg(p + (size_t)c * Vh);
 }
 
-template <int NL, int NP>
+// neighbour vector on a split lattice: from the owner's arena copy over NVLink
+__device__ __forceinline__ void ld_vec_peer(double2 (&v)[3], const double2* f, const LSite& s, int Vh, const Peers& pr) {
+  const int peer = s.nb == NB_HOME ? pr.me : pr.peer_of[s.nb];
+  if (peer == pr.me) { ld_vec(v, f, s, Vh); return; }
+  const double2* p = reinterpret_cast<const double2*>(pr.base[peer] + (reinterpret_cast<const char*>(f) - pr.base[pr.me])) +
+                     (size_t)s.par * 3 * Vh + s.idx;
+#pragma unroll
+  for (int c = 0; c < 3; c++) v[c] = ld_peer(p + (size_t)c * Vh);
+}
+
+template <int NL, int NP, bool MR>
 __global__ void __launch_bounds__(FB) k_outer(const OuterArgs a) {
   const int ds = blockIdx.x * FB + threadIdx.x;
   if (ds >= 2 * a.Vh) return;
@@ -56,7 +69,8 @@ __global__ void __launch_bounds__(FB) k_outer(const OuterArgs a) {
 #pragma unroll
       for (int q = 0; q < NP; q++) {
         double2 vb[3];
-        ld_vec(vb, a.p[q].b, t, a.Vh);
+        if (MR) ld_vec_peer(vb, a.p[q].b, t, a.Vh, a.pr);
+        else ld_vec(vb, a.p[q].b, t, a.Vh);
 #pragma unroll
         for (int i = 0; i < 3; i++)
 #pragma unroll
@@ -71,10 +85,11 @@ __global__ void __launch_bounds__(FB) k_outer(const OuterArgs a) {
   }
 }
 
-// f[k](x) (+)= sum_q w_q(x) a_q(x) (x) b_q(x + h_k)^+, np = 1 or 2 pairs
+// f[k](x) (+)= sum_q w_q(x) a_q(x) (x) b_q(x + h_k)^+, np = 1 or 2 pairs.  On a split lattice the shifted
+// operands are first copied into arena temporaries (vectors live in ordinary allocations), a cross-rank
+// barrier follows, and the kernel reads the off-rank neighbours from the owners' copies.
 int outer_products(Gauge& f, const OuterPair* pairs, int np, bool accumulate) {
   Context& c = ctx();
-  if (c.g.nranks > 1) return fail("force outer products: not available on a lattice split over ranks yet");
   if (np < 1 || np > 2) return fail("outer_products: 1 or 2 pairs");
   const int nl = f.nlinks / 4;
   for (int d = 0; d < 4; d++)
@@ -84,12 +99,34 @@ int outer_products(Gauge& f, const OuterPair* pairs, int np, bool accumulate) {
   a.f = f.d; a.accumulate = accumulate ? 1 : 0; a.Vh = c.g.Vh;
   for (int d = 0; d < 4; d++) a.X[d] = c.g.X[d];
   const int grid = (c.g.V + FB - 1) / FB;
-  if (nl == 1 && np == 1) k_outer<1, 1><<<grid, FB, 0, c.stream>>>(a);
-  else if (nl == 1) k_outer<1, 2><<<grid, FB, 0, c.stream>>>(a);
-  else if (np == 1) k_outer<2, 1><<<grid, FB, 0, c.stream>>>(a);
-  else k_outer<2, 2><<<grid, FB, 0, c.stream>>>(a);
+  const bool mr = c.g.nranks > 1;
+  double2* tmp[2] = {nullptr, nullptr};
+  if (mr) {
+    QB_CHECK(peers_fill(&a.pr));
+    for (int q = 0; q < np; q++) {
+      if (q == 1 && pairs[1].b == pairs[0].b) { a.p[1].b = a.p[0].b; continue; }
+      QB_CHECK(pool_acquire(&tmp[q]));
+      if (!in_arena(tmp[q])) return fail("force outer products on a split lattice need the peer arena (QEXB200_ARENA_FIELDS > 0)");
+      QB_CUDA(cudaMemcpyAsync(tmp[q], pairs[q].b, sizeof(double2) * 6 * (size_t)c.g.Vh, cudaMemcpyDeviceToDevice, c.stream));
+      a.p[q].b = tmp[q];
+    }
+    QB_CHECK(xbarrier());
+  }
+#define QB_OUTER(MRV)                                                              \
+  do {                                                                             \
+    if (nl == 1 && np == 1) k_outer<1, 1, MRV><<<grid, FB, 0, c.stream>>>(a);      \
+    else if (nl == 1) k_outer<1, 2, MRV><<<grid, FB, 0, c.stream>>>(a);            \
+    else if (np == 1) k_outer<2, 1, MRV><<<grid, FB, 0, c.stream>>>(a);            \
+    else k_outer<2, 2, MRV><<<grid, FB, 0, c.stream>>>(a);                         \
+  } while (0)
+  if (mr) QB_OUTER(true); else QB_OUTER(false);
+#undef QB_OUTER
   count_launch();
   QB_CUDA(cudaGetLastError());
+  if (mr) {
+    QB_CHECK(xbarrier());   // the peers have finished reading the temporaries
+    for (int q = 0; q < 2; q++) pool_release(tmp[q]);
+  }
   return 0;
 }
 

@@ -23,6 +23,17 @@ struct M3 {
 struct LSite {   // local coordinates + parity + checkerboard index
   int x[4];
   int par, idx;
+  int nb;        // rank displacement of the site: sum_d (disp_d + 1) 3^d, NB_HOME = this rank
+};
+constexpr int NB_HOME = 40;
+
+// Peer view of the symmetric arena (multi-rank link pipeline): every rank allocates its link-shaped fields
+// at the same offsets of an IPC-mapped arena, so the neighbour's copy of field f is at
+// base[peer] + (f - base[me]).  peer_of[nb] = rank owning displacement nb (periodic in the rank grid).
+struct Peers {
+  char* base[16];
+  unsigned char peer_of[81];
+  int me;
 };
 
 QB_HD LSite lsite(int idx, int par, const int* X) {
@@ -34,14 +45,15 @@ QB_HD LSite lsite(int idx, int par, const int* X) {
   s.x[2] = t % X[2];
   s.x[3] = t / X[2];
   s.x[0] = 2 * x0h + ((par + s.x[1] + s.x[2] + s.x[3]) & 1);
-  s.par = par; s.idx = idx;
+  s.par = par; s.idx = idx; s.nb = NB_HOME;
   return s;
 }
 // one hop of d = +-1 (or +-k) in direction mu with local wrap-around (single rank: periodic)
 QB_HD LSite lhop(LSite s, int mu, int d, const int* X) {
   int c = s.x[mu] + d;
-  if (c >= X[mu]) c -= X[mu];
-  if (c < 0) c += X[mu];
+  const int p3 = mu == 0 ? 1 : (mu == 1 ? 3 : (mu == 2 ? 9 : 27));
+  if (c >= X[mu]) { c -= X[mu]; s.nb += p3; }
+  if (c < 0) { c += X[mu]; s.nb -= p3; }
   s.x[mu] = c;
   if (d & 1) s.par ^= 1;
   s.idx = (((s.x[3] * X[2] + s.x[2]) * X[1] + s.x[1]) * X[0] + s.x[0]) >> 1;
@@ -53,6 +65,29 @@ QB_HD M3 m3_ld(const double2* f, const LSite& s, int Vh) {
   const double2* p = f + (size_t)s.par * 9 * Vh + s.idx;
 #pragma unroll
   for (int e = 0; e < 9; e++) m.e[e] = p[(size_t)e * Vh];
+  return m;
+}
+// 16-byte load of peer memory: system scope, never served from a stale L1 line
+QB_HD double2 ld_peer(const double2* p) {
+#if defined(__CUDA_ARCH__)
+  double2 v;
+  asm volatile("ld.relaxed.sys.global.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p) : "memory");
+  return v;
+#else
+  return *p;
+#endif
+}
+// MR: a site that left the rank (s.nb != NB_HOME) is read from the owner's arena over NVLink
+template <bool MR>
+QB_HD M3 m3_ldx(const double2* f, const LSite& s, int Vh, const Peers& pr) {
+  if (!MR) return m3_ld(f, s, Vh);
+  const int peer = s.nb == NB_HOME ? pr.me : pr.peer_of[s.nb];
+  if (peer == pr.me) return m3_ld(f, s, Vh);
+  const double2* p = reinterpret_cast<const double2*>(pr.base[peer] + (reinterpret_cast<const char*>(f) - pr.base[pr.me])) +
+                     (size_t)s.par * 9 * Vh + s.idx;
+  M3 m;
+#pragma unroll
+  for (int e = 0; e < 9; e++) m.e[e] = ld_peer(p + (size_t)e * Vh);
   return m;
 }
 QB_HD void m3_st(double2* f, const LSite& s, int Vh, const M3& m) {
@@ -133,15 +168,22 @@ QB_HD M3 m3_zero() {
 // = computeGenStaple's staple (src/gauge/fat7l.nim:24-76, gauge[nu] = G, link = L, mu = dL, nu = dG)
 // = symStaple's bracket (src/gauge/smearutil.nim:3-17, g1 = G, g2 = L).
 // The reference forms the lower staple at x-dG and shifts it; here it is gathered in place.
-QB_HD M3 staple_pair(const double2* G, const double2* L, int dG, int dL, const LSite& s, const int* X, int Vh) {
+template <bool MR>
+QB_HD M3 staple_pair_x(const double2* G, const double2* L, int dG, int dL, const LSite& s, const int* X, int Vh,
+                       const Peers& pr) {
   const LSite sG = lhop(s, dG, +1, X);
   const LSite sL = lhop(s, dL, +1, X);
-  M3 r = m3_mul_na(m3_mul(m3_ld(G, s, Vh), m3_ld(L, sG, Vh)), m3_ld(G, sL, Vh));
+  M3 r = m3_mul_na(m3_mul(m3_ld(G, s, Vh), m3_ldx<MR>(L, sG, Vh, pr)), m3_ldx<MR>(G, sL, Vh, pr));
   const LSite sb = lhop(s, dG, -1, X);
   const LSite sbL = lhop(sb, dL, +1, X);
-  const M3 lo = m3_mul(m3_mul_an(m3_ld(G, sb, Vh), m3_ld(L, sb, Vh)), m3_ld(G, sbL, Vh));
+  const M3 lo = m3_mul(m3_mul_an(m3_ldx<MR>(G, sb, Vh, pr), m3_ldx<MR>(L, sb, Vh, pr)), m3_ldx<MR>(G, sbL, Vh, pr));
   m3_axpy(r, 1.0, lo);
   return r;
+}
+QB_HD M3 staple_pair(const double2* G, const double2* L, int dG, int dL, const LSite& s, const int* X, int Vh) {
+  Peers none;
+  none.me = 0;
+  return staple_pair_x<false>(G, L, dG, dL, s, X, Vh, none);
 }
 
 // ---- projectU (src/maths/matrixFunctions.nim:79-181,301-312) --------------------------------

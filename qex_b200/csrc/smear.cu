@@ -21,30 +21,44 @@ namespace qb {
 constexpr int SB = QB_SB;
 
 // ---- pool of matrix-field temporaries (kept across calls: HMC smears every force step) -------
+// On a multi-rank context with a peer window the fields come from the symmetric arena (links_alloc), in the
+// same order on every rank, so a neighbour's temporary sits at the same arena offset.
 struct MatPool {
-  std::vector<double2*> free_list, all;
+  std::vector<double2*> free_list;          // LIFO: deterministic across ranks
+  std::vector<std::pair<double2*, bool>> all;
   size_t elems = 0;
 };
 static MatPool g_pool;
 
+int smear_free() {
+  for (auto& e : g_pool.all) links_free(e.first, 1, e.second);
+  g_pool.all.clear(); g_pool.free_list.clear(); g_pool.elems = 0;
+  return 0;
+}
 static int pool_get(double2** out) {
   Context& c = ctx();
   const size_t n = (size_t)18 * c.g.Vh;
-  if (g_pool.elems != n) {
-    for (double2* p : g_pool.all) cudaFree(p);
-    g_pool.all.clear(); g_pool.free_list.clear(); g_pool.elems = n;
-  }
+  if (g_pool.elems != n) { smear_free(); g_pool.elems = n; }
   if (!g_pool.free_list.empty()) { *out = g_pool.free_list.back(); g_pool.free_list.pop_back(); return 0; }
   double2* p = nullptr;
-  QB_CUDA(cudaMalloc(&p, sizeof(double2) * n));
-  g_pool.all.push_back(p);
+  bool arena = false;
+  QB_CHECK(links_alloc(1, &p, &arena));
+  g_pool.all.push_back(std::make_pair(p, arena));
   *out = p;
   return 0;
 }
 static void pool_put(double2* p) { if (p) g_pool.free_list.push_back(p); }
-int smear_free() {
-  for (double2* p : g_pool.all) cudaFree(p);
-  g_pool.all.clear(); g_pool.free_list.clear(); g_pool.elems = 0;
+int pool_acquire(double2** out) { return pool_get(out); }
+void pool_release(double2* p) { pool_put(p); }
+
+// Multi-rank: every launch of the pipeline is preceded by a cross-rank barrier (what it reads remotely was
+// written by the peers' previous launches; what it overwrites may still be read by their previous launch).
+static inline bool multi() { return ctx().g.nranks > 1; }
+static int mr_begin(Peers* pr, std::initializer_list<const void*> fields) {
+  if (!multi()) { pr->me = 0; return 0; }
+  QB_CHECK(peers_fill(pr));
+  for (const void* f : fields)
+    if (f && !in_arena(f)) return fail("link pipeline on a split lattice: a link set lives outside the peer arena (create gauges after qexb200_p2p_attach)");
   return 0;
 }
 struct Tmp {   // RAII handle of one pooled field
@@ -72,6 +86,7 @@ struct StapleArgs {
   double2* raw;         // PROJ: the unprojected sum (hypsmear's l1x/l2x/flx, needed by the force), may be null
   int X[4];
   int Vh;
+  Peers pr;             // multi-rank: where the neighbours' copies of the fields are
 };
 
 // Blocks alternate parity (block b: parity b & 1, sites (b >> 1) * SB ...): the even and the odd sites of
@@ -80,7 +95,7 @@ struct StapleArgs {
 #ifndef QB_STAPLE_MINB
 #define QB_STAPLE_MINB 6
 #endif
-template <int NS, bool PROJ>
+template <int NS, bool PROJ, bool MR>
 __global__ void __launch_bounds__(SB, QB_STAPLE_MINB) k_staple(const StapleArgs a) {
   const int par = blockIdx.x & 1, idx = (blockIdx.x >> 1) * SB + threadIdx.x;
   if (idx >= a.Vh) return;
@@ -90,7 +105,7 @@ __global__ void __launch_bounds__(SB, QB_STAPLE_MINB) k_staple(const StapleArgs 
   if (a.acc) m3_axpy(r, 1.0, m3_ld(a.acc, s, a.Vh));
 #pragma unroll
   for (int k = 0; k < NS; k++) {
-    const M3 st = staple_pair(a.t[k].G, a.t[k].L, a.t[k].dG, a.dL, s, a.X, a.Vh);
+    const M3 st = staple_pair_x<MR>(a.t[k].G, a.t[k].L, a.t[k].dG, a.dL, s, a.X, a.Vh, a.pr);
     if (NS == 1 && a.save) m3_st(a.save, s, a.Vh, st);
     m3_axpy(r, a.t[k].coef, st);
   }
@@ -103,27 +118,40 @@ __global__ void __launch_bounds__(SB, QB_STAPLE_MINB) k_staple(const StapleArgs 
 
 static inline int grid_par(int Vh, int block) { return 2 * ((Vh + block - 1) / block); }
 
+template <bool MR>
+static void launch_staple_t(const StapleArgs& a, int ns, bool proj, int grid, cudaStream_t st) {
+  if (proj) {
+    if (ns == 1) k_staple<1, true, MR><<<grid, SB, 0, st>>>(a);
+    else if (ns == 2) k_staple<2, true, MR><<<grid, SB, 0, st>>>(a);
+    else k_staple<3, true, MR><<<grid, SB, 0, st>>>(a);
+  } else {
+    if (ns == 1) k_staple<1, false, MR><<<grid, SB, 0, st>>>(a);
+    else if (ns == 2) k_staple<2, false, MR><<<grid, SB, 0, st>>>(a);
+    else k_staple<3, false, MR><<<grid, SB, 0, st>>>(a);
+  }
+}
 static int launch_staple(const StapleArgs& a, int ns, bool proj) {
   Context& c = ctx();
   const int grid = grid_par(c.g.Vh, SB);
-  if (proj) {
-    if (ns == 1) k_staple<1, true><<<grid, SB, 0, c.stream>>>(a);
-    else if (ns == 2) k_staple<2, true><<<grid, SB, 0, c.stream>>>(a);
-    else k_staple<3, true><<<grid, SB, 0, c.stream>>>(a);
+  if (multi()) {
+    for (int k = 0; k < ns; k++)
+      if (!in_arena(a.t[k].G) || !in_arena(a.t[k].L)) return fail("link pipeline on a split lattice: a field lives outside the peer arena");
+    QB_CHECK(xbarrier());
+    launch_staple_t<true>(a, ns, proj, grid, c.stream);
   } else {
-    if (ns == 1) k_staple<1, false><<<grid, SB, 0, c.stream>>>(a);
-    else if (ns == 2) k_staple<2, false><<<grid, SB, 0, c.stream>>>(a);
-    else k_staple<3, false><<<grid, SB, 0, c.stream>>>(a);
+    launch_staple_t<false>(a, ns, proj, grid, c.stream);
   }
   count_launch();
   QB_CUDA(cudaGetLastError());
   return 0;
 }
+static Peers g_peers = {};   // filled by mr_begin at the start of every pipeline entry point
 static StapleArgs staple_args(int dL) {
   StapleArgs a = {};
   const Geom& g = ctx().g;
   for (int d = 0; d < 4; d++) a.X[d] = g.X[d];
   a.Vh = g.Vh; a.dL = dL;
+  a.pr = g_peers;
   return a;
 }
 
@@ -166,14 +194,15 @@ static int scale_field(double2* out, const double2* in, double s) {
 }
 
 // Naik link, fat7l.nim:156-167: ll(x) = naik * W(x) W(x+mu) W(x+2mu)
+template <bool MR>
 __global__ void __launch_bounds__(SB) k_naik(double2* ll, const double2* w, int mu, double naik, int X0, int X1,
-                                              int X2, int X3, int Vh) {
+                                              int X2, int X3, int Vh, const Peers pr) {
   const int par = blockIdx.x & 1, idx = (blockIdx.x >> 1) * SB + threadIdx.x;
   if (idx >= Vh) return;
   const int X[4] = {X0, X1, X2, X3};
   const LSite s = lsite(idx, par, X);
   const LSite s1 = lhop(s, mu, +1, X), s2 = lhop(s1, mu, +1, X);
-  const M3 t = m3_mul(m3_ld(w, s1, Vh), m3_ld(w, s2, Vh));   // the reference multiplies right to left too
+  const M3 t = m3_mul(m3_ldx<MR>(w, s1, Vh, pr), m3_ldx<MR>(w, s2, Vh, pr));   // the reference multiplies right to left too
   M3 r = m3_mul(m3_ld(w, s, Vh), t);
 #pragma unroll
   for (int e = 0; e < 9; e++) { r.e[e].x *= naik; r.e[e].y *= naik; }
@@ -187,7 +216,9 @@ struct PlaqArgs {
   double* partials;   // [grid][6]
   int X[4];
   int Vh;
+  Peers pr;
 };
+template <bool MR>
 __global__ void __launch_bounds__(SB) k_plaq(const PlaqArgs a) {
   __shared__ double sm[SB / 32][6];
   const int par = blockIdx.x & 1, idx = (blockIdx.x >> 1) * SB + threadIdx.x;
@@ -203,8 +234,8 @@ __global__ void __launch_bounds__(SB) k_plaq(const PlaqArgs a) {
 #pragma unroll
       for (int nu = 0; nu < mu; nu++) {
         const LSite snu = lhop(s, nu, +1, a.X);
-        const M3 p = m3_mul(U[nu], m3_ld(a.u[mu], snu, a.Vh));
-        const M3 q = m3_mul(U[mu], m3_ld(a.u[nu], smu, a.Vh));
+        const M3 p = m3_mul(U[nu], m3_ldx<MR>(a.u[mu], snu, a.Vh, a.pr));
+        const M3 q = m3_mul(U[mu], m3_ldx<MR>(a.u[nu], smu, a.Vh, a.pr));
         double d = 0.0;
 #pragma unroll
         for (int e = 0; e < 9; e++) d += q.e[e].x * p.e[e].x + q.e[e].y * p.e[e].y;
@@ -228,31 +259,49 @@ __global__ void __launch_bounds__(SB) k_plaq(const PlaqArgs a) {
   }
 }
 // fixed-order final sum: one block, thread k < 6 * 32 handles plane k / 32 with stride 32
-__global__ void __launch_bounds__(192) k_plaq_final(const double* partials, int nblocks, double norm, double* out) {
+// xr != nullptr: the six sums are then added over the ranks in rank order (xrank_sum, one warp)
+__global__ void __launch_bounds__(192) k_plaq_final(const double* partials, int nblocks, double norm, double* out,
+                                                     XRank* xr) {
+  __shared__ double sm[6];
   const int k = threadIdx.x >> 5, lane = threadIdx.x & 31;
   double t = 0.0;
   for (int i = lane; i < nblocks; i += 32) t += partials[(size_t)i * 6 + k];
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) t += __shfl_down_sync(0xffffffffu, t, o);
-  if (lane == 0) out[k] = t * norm;
+  if (lane == 0) sm[k] = t;
+  __syncthreads();
+  if (k == 0) {
+    for (int j = 0; j < 6; j++) {
+      double v = sm[j];
+      if (xr) v = xrank_sum(xr, v);
+      if (lane == 0) out[j] = v * norm;
+    }
+  }
 }
 
 int plaq_links(const double2* const u[4], double pl[6]) {
   Context& c = ctx();
-  if (c.g.nranks > 1) return fail("gauge_plaq: not available on a lattice split over ranks yet");
   Tmp part;
   QB_CHECK(part.get());
   PlaqArgs a;
   for (int d = 0; d < 4; d++) { a.u[d] = u[d]; a.X[d] = c.g.X[d]; }
   a.Vh = c.g.Vh;
   a.partials = reinterpret_cast<double*>(part.p);
+  QB_CHECK(mr_begin(&a.pr, {u[0], u[1], u[2], u[3]}));
   const int grid = grid_par(c.g.Vh, SB);
-  k_plaq<<<grid, SB, 0, c.stream>>>(a);
+  const double norm = 1.0 / (18.0 * (double)c.g.V * c.g.nranks);
+  if (multi()) {
+    QB_CHECK(xbarrier());
+    k_plaq<true><<<grid, SB, 0, c.stream>>>(a);
+  } else {
+    k_plaq<false><<<grid, SB, 0, c.stream>>>(a);
+  }
   count_launch();
-  k_plaq_final<<<1, 192, 0, c.stream>>>(a.partials, grid, 1.0 / (18.0 * (double)c.g.V), c.d_scal + 40);
+  k_plaq_final<<<1, 192, 0, c.stream>>>(a.partials, grid, norm, c.d_scal + 40, xrank());
   count_launch();
   QB_CUDA(cudaGetLastError());
-  return fetch_scalars(c.d_scal + 40, pl, 6);
+  QB_CHECK(fetch_scalars(c.d_scal + 40, pl, 6));
+  return xbarrier();   // peers may still be reading these links
 }
 
 // ---- makeImpLinks, fat7l.nim:78-162 ------------------------------------------------------------
@@ -262,7 +311,7 @@ int plaq_links(const double2* const u[4], double pl[6]) {
 int make_imp_links(double2* const fl[4], const double2* const gf[4], const double coef[5], double2* const ll[4],
                    const double2* const gfl[4], double naik) {
   Context& c = ctx();
-  if (c.g.nranks > 1) return fail("makeImpLinks: not available on a lattice split over ranks yet");
+  QB_CHECK(mr_begin(&g_peers, {gf[0], gf[1], gf[2], gf[3], fl[0], fl[1], fl[2], fl[3]}));
   for (int d = 0; d < 4; d++)
     if (c.g.X[d] < 4) return fail("makeImpLinks: local extent %d in direction %d is below 4", c.g.X[d], d);
   double coef1 = coef[0];
@@ -314,12 +363,18 @@ int make_imp_links(double2* const fl[4], const double2* const gf[4], const doubl
       if (c.g.X[d] < 4) return fail("makeImpLinks: Naik links need local extent >= 4");
     const int grid = grid_par(c.g.Vh, SB);
     for (int dir = 0; dir < 4; dir++) {
-      k_naik<<<grid, SB, 0, c.stream>>>(ll[dir], gfl[dir], dir, naik, c.g.X[0], c.g.X[1], c.g.X[2], c.g.X[3], c.g.Vh);
+      if (multi()) {
+        if (!in_arena(gfl[dir])) return fail("makeImpLinks on a split lattice: gfLong lives outside the peer arena");
+        QB_CHECK(xbarrier());
+        k_naik<true><<<grid, SB, 0, c.stream>>>(ll[dir], gfl[dir], dir, naik, c.g.X[0], c.g.X[1], c.g.X[2], c.g.X[3], c.g.Vh, g_peers);
+      } else {
+        k_naik<false><<<grid, SB, 0, c.stream>>>(ll[dir], gfl[dir], dir, naik, c.g.X[0], c.g.X[1], c.g.X[2], c.g.X[3], c.g.Vh, g_peers);
+      }
       count_launch();
     }
     QB_CUDA(cudaGetLastError());
   }
-  return 0;
+  return xbarrier();   // the peers may still be reading what the caller overwrites next
 }
 
 // ---- HisqCoefs.smear, hisqLinks.nim:32-39 -------------------------------------------------------
@@ -343,7 +398,7 @@ int hisq_smear(double2* const fl[4], double2* const ll[4], const double2* const 
 // fl[mu] = P((1-a3) g[mu] + a3/6 sum_nu S(L2[nu][mu], L2[mu][nu])).  One launch per output field.
 int hyp_smear(double2* const fl[4], const double2* const g[4], const double alpha[3]) {
   Context& c = ctx();
-  if (c.g.nranks > 1) return fail("hyp smear: not available on a lattice split over ranks yet");
+  QB_CHECK(mr_begin(&g_peers, {g[0], g[1], g[2], g[3], fl[0], fl[1], fl[2], fl[3]}));
   for (int d = 0; d < 4; d++)
     if (c.g.X[d] < 4) return fail("hyp smear: local extent %d in direction %d is below 4", c.g.X[d], d);
   const double alp1 = alpha[0] / 2.0, alp2 = alpha[1] / 4.0, alp3 = alpha[2] / 6.0;
@@ -384,7 +439,7 @@ int hyp_smear(double2* const fl[4], const double2* const g[4], const double alph
     a.out = fl[mu];
     QB_CHECK(launch_staple(a, nt, true));
   }
-  return 0;
+  return xbarrier();
 }
 
 }  // namespace qb

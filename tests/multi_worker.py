@@ -134,6 +134,98 @@ def gpu_case(L, G, nlinks, inner, rank, world, local_rank, dist, transport="nccl
     return res
 
 
+def links_case(L, G, inner, rank, world, local_rank, dist):
+    """Device link pipeline, force outer products and plaq on a lattice split over ranks (peer arena + NVLink
+    reads of the neighbours' fields): every rank compares its block with the oracle's global result."""
+    import torch
+    import oracle
+    import qex_b200 as qb
+    from util import make_inputs, rel_l2, SEED
+    torch.cuda.set_device(local_rank)
+    qb.init(L, G, rank, local_rank, None)
+    qb.p2p_attach_torch(dist)
+    qb.set_host_layout(inner)
+    lat = oracle.Lattice(L)
+    g = lat.random_gauge(lat.new_rng(SEED), 4)
+    lo = oracle.QexLayout(L, G, inner)
+    mine = lambda f: lo.scatter(f)[rank]
+
+    def down(dg):
+        parts = [np.zeros_like(mine(g[0])) for _ in range(dg.nlinks)]
+        dg.download(parts)
+        return parts
+    res = {}
+    dg = qb.DeviceGauge([mine(g[k]) for k in range(4)])
+    res["plaq"] = float(np.abs(dg.plaq() - lat.plaq(g)).max())
+    assert res["plaq"] < 1e-14
+    # nHYP, then rephase, then a solve on the smeared links (staghmc_spv.nim:367-386)
+    want = lat.hyp_smear(g, (0.4, 0.5, 0.5))
+    fl = qb.DeviceGauge(nlinks=4)
+    qb.HypCoefs(0.4, 0.5, 0.5).smear(dg, fl)
+    got = down(fl)
+    res["nhyp"] = max(rel_l2(got[mu], mine(want[mu])) for mu in range(4))
+    assert res["nhyp"] <= 1e-13, res
+    assert np.abs(fl.plaq() - lat.plaq(want)).max() < 1e-13
+    fl.rephase()
+    lat.setBC(want); lat.stagPhase(want)
+    s = qb.newStag(fl)
+    x = lat.gaussian_vector(lat.new_rng(3))
+    ref, sol = lat.vector(), np.zeros_like(mine(x))
+    st = lat.solve(want, ref, x, 0.1, 1e-10)
+    sp = qb.SolverParams(r2req=1e-10)
+    s.solve(sol, mine(x), 0.1, sp)
+    assert abs(sp.iterations - st.iterations) <= 1
+    assert rel_l2(sol, mine(ref)) < 1e-4
+    # HISQ on phased thin links (testStagProp.nim:24-36); bar follows the oracle's conditioning
+    gp = g.copy(); lat.setBC(gp); lat.stagPhase(gp)
+    wfl, wll = lat.hisq_smear(gp, oracle.hisq_coefs())
+    sgn = np.random.default_rng(0).choice([-1.0, 1.0], size=gp.shape)
+    pfl, pll = lat.hisq_smear(gp * (1.0 + 1.1e-16 * sgn), oracle.hisq_coefs())
+    tol = max(1e-13, 4 * max(rel_l2(pfl[mu], wfl[mu]) for mu in range(4)), 4 * max(rel_l2(pll[mu], wll[mu]) for mu in range(4)))
+    dgp = qb.DeviceGauge([mine(gp[k]) for k in range(4)])
+    hfl, hll = qb.DeviceGauge(nlinks=4), qb.DeviceGauge(nlinks=4)
+    qb.HisqCoefs().init().smear(dgp, hfl, hll)
+    gfl, gll = down(hfl), down(hll)
+    res["hisq_fat"] = max(rel_l2(gfl[mu], mine(wfl[mu])) for mu in range(4))
+    res["hisq_long"] = max(rel_l2(gll[mu], mine(wll[mu])) for mu in range(4))
+    assert res["hisq_fat"] <= tol and res["hisq_long"] <= tol, (res, tol)
+    # fat + Lepage only (all five coefficients), tight bar: no projection in between
+    c5 = (1.0, -1 / 16., 1 / 64., -1 / 384., -1 / 8.)
+    w5, w5l = lat.makeImpLinks(gp, c5, gfLong=gp, naik=-1 / 24.)
+    qb.makeImpLinks(hfl, dgp, qb.Fat7lCoefs(*c5), hll, dgp, -1 / 24.)
+    gfl, gll = down(hfl), down(hll)
+    res["fat7"] = max(rel_l2(gfl[mu], mine(w5[mu])) for mu in range(4))
+    res["naik"] = max(rel_l2(gll[mu], mine(w5l[mu])) for mu in range(4))
+    assert res["fat7"] <= 1e-13 and res["naik"] <= 1e-13, res
+    for d in (s, dg, fl, dgp, hfl, hll):
+        d.free()
+    # force outer products, one-hop and one+three-hop
+    for nl in (4, 8):
+        _, gg, (xv, cv) = make_inputs(L, nl)
+        sop = qb.Staggered([mine(gg[k]) for k in range(nl)])
+        start = 0.25 * gg
+        wantf = start.copy()
+        lat.stagD2deriv(wantf, cv, xv)
+        gr = qb.DeviceGauge([mine(start[k]) for k in range(nl)])
+        dc, dx = qb.DeviceField(mine(cv)), qb.DeviceField(mine(xv))
+        qb.stagD2deriv(sop, gr, dc, dx)
+        gotf = down(gr)
+        res["stagD2deriv_%d" % nl] = max(rel_l2(gotf[k], mine(wantf[k])) for k in range(nl))
+        assert res["stagD2deriv_%d" % nl] <= 1e-13, res
+        if nl == 4:
+            wd = lat.gauge(4)
+            lat.stagDeriv(wd, xv)
+            gr.zero()
+            qb.stagDeriv(sop, gr, dx)
+            gotf = down(gr)
+            res["stagDeriv"] = max(rel_l2(gotf[k], mine(wd[k])) for k in range(4))
+            assert res["stagDeriv"] <= 1e-13, res
+        for d in (sop, gr, dc, dx):
+            d.free()
+    qb.finalize()
+    return res
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--cpu", action="store_true")
@@ -143,6 +235,7 @@ def main():
     ap.add_argument("--nlinks", type=int, default=4)
     ap.add_argument("--transport", default="nccl", choices=["nccl", "p2p"])
     ap.add_argument("--recon", type=int, default=18, choices=[12, 18])
+    ap.add_argument("--links", action="store_true", help="link pipeline / force case instead of the Dslash + CG case")
     a = ap.parse_args()
     import torch.distributed as dist
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
@@ -158,7 +251,10 @@ def main():
     else:
         import torch
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-        out = gpu_case(L, G, a.nlinks, inner, rank, world, local_rank, dist, a.transport, a.recon)
+        if a.links:
+            out = links_case(L, G, inner, rank, world, local_rank, dist)
+        else:
+            out = gpu_case(L, G, a.nlinks, inner, rank, world, local_rank, dist, a.transport, a.recon)
     dist.barrier()
     if rank == 0:
         print("MULTI_OK " + json.dumps(out))

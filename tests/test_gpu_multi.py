@@ -45,3 +45,20 @@ def test_multi_gpu_parity(nproc, lat, rg, inner, nlinks, transport):
 def test_multi_gpu_parity_recon12(nproc, lat, rg, nlinks, transport):
     """Same checks with the 12-real link storage (sign bits of off-rank hops come from the packer)."""
     run_case(nproc, lat, rg, "1,1,1,1", nlinks, transport, recon=12)
+
+
+@pytest.mark.parametrize("nproc,lat,rg,inner", [
+    (2, "8,8,8,16", "1,1,1,2", "1,1,1,1"),
+    (2, "8,8,8,8", "1,1,1,2", "1,2,2,1"),        # local extent 4: the 3-hop and the staples leave the rank both ways
+    (2, "8,8,12,8", "1,1,2,1", "1,1,1,1"),
+    (4, "8,8,16,16", "1,1,2,2", "1,1,1,1"),      # the lower staple's corner x - nu + mu crosses two ranks
+    (4, "16,8,8,8", "4,1,1,1", "1,1,1,1"),
+    (8, "8,16,16,16", "1,2,2,2", "1,1,1,1"),
+])
+def test_multi_gpu_links_and_force(nproc, lat, rg, inner):
+    """nHYP / HISQ / fat7+Naik smearing, plaq, stagDeriv / stagD2deriv on a lattice split over ranks: link-shaped
+    fields live in the IPC-mapped arena and off-rank neighbours are read over NVLink (csrc/smear.cu, force.cu)."""
+    if ngpus() < nproc:
+        pytest.skip("needs %d GPUs" % nproc)
+    r = launch(nproc, ["--lat", lat, "--rankgeom", rg, "--inner", inner, "--links"], timeout=600)
+    assert r.returncode == 0 and "MULTI_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
