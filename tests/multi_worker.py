@@ -178,17 +178,17 @@ def links_case(L, G, inner, rank, world, local_rank, dist):
     assert rel_l2(sol, mine(ref)) < 1e-4
     # HISQ on phased thin links (testStagProp.nim:24-36); bar follows the oracle's conditioning
     gp = g.copy(); lat.setBC(gp); lat.stagPhase(gp)
-    wfl, wll = lat.hisq_smear(gp, oracle.hisq_coefs())
-    sgn = np.random.default_rng(0).choice([-1.0, 1.0], size=gp.shape)
-    pfl, pll = lat.hisq_smear(gp * (1.0 + 1.1e-16 * sgn), oracle.hisq_coefs())
-    tol = max(1e-13, 4 * max(rel_l2(pfl[mu], wfl[mu]) for mu in range(4)), 4 * max(rel_l2(pll[mu], wll[mu]) for mu in range(4)))
+    from util import hisq_reference, hisq_bar
+    wfl, wll, efl, ell = hisq_reference(lat, gp, oracle.hisq_coefs())
     dgp = qb.DeviceGauge([mine(gp[k]) for k in range(4)])
     hfl, hll = qb.DeviceGauge(nlinks=4), qb.DeviceGauge(nlinks=4)
     qb.HisqCoefs().init().smear(dgp, hfl, hll)
     gfl, gll = down(hfl), down(hll)
     res["hisq_fat"] = max(rel_l2(gfl[mu], mine(wfl[mu])) for mu in range(4))
     res["hisq_long"] = max(rel_l2(gll[mu], mine(wll[mu])) for mu in range(4))
-    assert res["hisq_fat"] <= tol and res["hisq_long"] <= tol, (res, tol)
+    for mu in range(4):   # bar = 4x the oracle's own distance from the exact-projection chain on this block
+        assert rel_l2(gfl[mu], mine(wfl[mu])) <= hisq_bar(mine(wfl[mu]), mine(efl[mu])), (mu, res)
+        assert rel_l2(gll[mu], mine(wll[mu])) <= hisq_bar(mine(wll[mu]), mine(ell[mu])), (mu, res)
     # fat + Lepage only (all five coefficients), tight bar: no projection in between
     c5 = (1.0, -1 / 16., 1 / 64., -1 / 384., -1 / 8.)
     w5, w5l = lat.makeImpLinks(gp, c5, gfLong=gp, naik=-1 / 24.)

@@ -56,3 +56,25 @@ def to_qex(lo, f):
 
 def from_qex(lo, a):
     return lo.gather([a])
+
+
+def hisq_reference(lat, g, coefs):
+    """The oracle's HISQ links plus the SAME chain with the projection done exactly (polar factor from numpy's SVD,
+    good to ~1e-15).  QEX's projectU takes the closed-form eigenvalue route (matrixFunctions.nim:79-181), which on
+    random links is only ~1e-13 from the exact polar factor in L2 with a heavy tail (single sites at 1e-11 where
+    U^+U is nearly singular); two correct implementations of it therefore differ by a few times that distance.
+    Returns (fl, ll, fl_exact, ll_exact)."""
+    fl, ll = lat.hisq_smear(g, coefs)
+    t1 = lat.makeImpLinks(g, coefs[:5])
+    m = t1[..., 0] + 1j * t1[..., 1]
+    u, _, vh = np.linalg.svd(m)
+    w = u @ vh
+    p = np.ascontiguousarray(np.stack([w.real, w.imag], axis=-1))
+    fle, lle = lat.makeImpLinks(p, coefs[5:10], gfLong=p, naik=float(coefs[10]))
+    return fl, ll, fle, lle
+
+
+def hisq_bar(want, exact, base=1e-13, factor=4.0):
+    """Parity bar for a HISQ link field (or a rank's block of it): `factor` times the oracle's own distance from
+    the exact-projection result, never below `base`."""
+    return max(base, factor * rel_l2(want, exact))
