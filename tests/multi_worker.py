@@ -186,9 +186,12 @@ def links_case(L, G, inner, rank, world, local_rank, dist):
     gfl, gll = down(hfl), down(hll)
     res["hisq_fat"] = max(rel_l2(gfl[mu], mine(wfl[mu])) for mu in range(4))
     res["hisq_long"] = max(rel_l2(gll[mu], mine(wll[mu])) for mu in range(4))
-    for mu in range(4):   # bar = 4x the oracle's own distance from the exact-projection chain on this block
-        assert rel_l2(gfl[mu], mine(wfl[mu])) <= hisq_bar(mine(wfl[mu]), mine(efl[mu])), (mu, res)
-        assert rel_l2(gll[mu], mine(wll[mu])) <= hisq_bar(mine(wll[mu]), mine(ell[mu])), (mu, res)
+    bar_f, bar_l = hisq_bar(wfl, efl), hisq_bar(wll, ell)   # 10x the oracle's own distance from the exact-projection chain
+    assert res["hisq_fat"] <= bar_f and res["hisq_long"] <= bar_l, (res, bar_f, bar_l)
+    for mu in range(4):   # site by site the typical deviation is at rounding level
+        w = mine(wfl[mu])
+        site = np.linalg.norm((gfl[mu] - w).reshape(w.shape[0], -1), axis=1) / np.linalg.norm(w.reshape(w.shape[0], -1), axis=1)
+        assert np.median(site) < 1e-14, (mu, float(np.median(site)))
     # fat + Lepage only (all five coefficients), tight bar: no projection in between
     c5 = (1.0, -1 / 16., 1 / 64., -1 / 384., -1 / 8.)
     w5, w5l = lat.makeImpLinks(gp, c5, gfLong=gp, naik=-1 / 24.)
