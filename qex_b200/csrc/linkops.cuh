@@ -108,9 +108,9 @@ QB_HD M3 m3_mul(const M3& a, const M3& b) {
       double re = 0.0, im = 0.0;
 #pragma unroll
       for (int k = 0; k < 3; k++) {
-        const double2 p = a.e[i * 3 + k], q = b.e[k * 3 + j];
-        re += p.x * q.x - p.y * q.y;
-        im += p.x * q.y + p.y * q.x;
+        const double2 p = a.e[i * 3 + k], q = b.e[k * 3 + j];   // 4 FMAs per complex multiply-add
+        re = fma(p.x, q.x, re); re = fma(-p.y, q.y, re);
+        im = fma(p.x, q.y, im); im = fma(p.y, q.x, im);
       }
       r.e[i * 3 + j] = make_double2(re, im);
     }
@@ -127,8 +127,8 @@ QB_HD M3 m3_mul_na(const M3& a, const M3& b) {
 #pragma unroll
       for (int k = 0; k < 3; k++) {
         const double2 p = a.e[i * 3 + k], q = b.e[j * 3 + k];   // conj(q)
-        re += p.x * q.x + p.y * q.y;
-        im += p.y * q.x - p.x * q.y;
+        re = fma(p.x, q.x, re); re = fma(p.y, q.y, re);
+        im = fma(p.y, q.x, im); im = fma(-p.x, q.y, im);
       }
       r.e[i * 3 + j] = make_double2(re, im);
     }
@@ -145,8 +145,8 @@ QB_HD M3 m3_mul_an(const M3& a, const M3& b) {
 #pragma unroll
       for (int k = 0; k < 3; k++) {
         const double2 p = a.e[k * 3 + i], q = b.e[k * 3 + j];   // conj(p)
-        re += p.x * q.x + p.y * q.y;
-        im += p.x * q.y - p.y * q.x;
+        re = fma(p.x, q.x, re); re = fma(p.y, q.y, re);
+        im = fma(p.x, q.y, im); im = fma(-p.y, q.x, im);
       }
       r.e[i * 3 + j] = make_double2(re, im);
     }
