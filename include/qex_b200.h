@@ -120,8 +120,10 @@ int qexb200_gauge_rephase(qexb200_gauge_t g);
  * The smearing steps QEX runs on the CPU before every solve of an HMC force step
  * (src/stagg_pv_hmc/staghmc_spv.nim:367-386; src/physics/hisqLinks.nim:32-39), on the resident links:
  * thin links are uploaded once with qexb200_gauge_load, smeared, rephased and solved on without
- * leaving the GPU.  All handles here hold 4 link fields unless stated.  Single rank for now: on a
- * lattice split over ranks these return an error (no silent host path). */
+ * leaving the GPU.  All handles here hold 4 link fields unless stated.  On a lattice split over ranks the
+ * peer-memory transport is required (qexb200_p2p_attach BEFORE the gauges are created): link-shaped fields then
+ * live in an arena of the peer window (QEXB200_ARENA_FIELDS matrix fields, default 64) and off-rank neighbours
+ * are read over NVLink; with NCCL only these return an error (no silent host path). */
 typedef struct {   /* Fat7lCoefs, src/gauge/fat7l.nim:5-10 */
   double one_link, three_staple, five_staple, seven_staple, lepage;
 } qexb200_fat7l_coefs;
@@ -236,7 +238,7 @@ int qexb200_gauge_load_sitemajor(qexb200_gauge_t g, const void* data, int precis
 
 /* ---- fermion-force outer products (src/physics/stagD.nim:588-664) -----------------
  * Link-shaped outputs live in gauge handles with the operator's link count (4, or 8 with the three-hop
- * fields at 2 mu + 1).  Single rank for now (error on a split lattice). */
+ * fields at 2 mu + 1).  Split lattices: as the link pipeline above (peer-memory transport). */
 int qexb200_gauge_zero(qexb200_gauge_t g);            /* f[mu] := 0 */
 int qexb200_gauge_scale(qexb200_gauge_t g, double c); /* g[mu] *= c (src/hmc/agradOps.nim:513-520) */
 /* stagDeriv(s, f, x) (stagD.nim:635-664): f[mu](e) += x(e) (x) x(e+mu)^+, f[mu](o) -= x(o) (x) x(o+mu)^+,

@@ -10,6 +10,9 @@
 // optionally projects, and writes once.  nHYP is then 12 + 12 + 4 launches (one per output
 // field, projection fused), fat7 is 10 launches per (mu, nu) pair reduced to 4.
 // HBM-bound streaming of 144-byte matrices; fp64 FMA pipe is the secondary limit.
+// On a lattice split over ranks the fields live in a symmetric peer-mapped arena and a site's off-rank
+// neighbours are read straight from the owner's memory over NVLink (linkops.cuh m3_ldx<MR>), with a
+// one-warp cross-rank barrier between dependent launches: no packing, no exchange buffers, no NCCL.
 #include "linkops.cuh"
 #include "stencil.cuh"
 
