@@ -145,6 +145,23 @@ int qexb200_gauge_smear_hisq(qexb200_gauge_t fl, qexb200_gauge_t ll, qexb200_gau
                              const qexb200_hisq_coefs* coef);
 /* HypCoefs.smear(g, fl) (hypsmear.nim:49-162,269-273): three levels of projected staples */
 int qexb200_gauge_smear_hyp(qexb200_gauge_t fl, qexb200_gauge_t g, const qexb200_hyp_coefs* coef);
+/* smearGetForce (hypsmear.nim:49-162): like qexb200_gauge_smear_hyp, and keeps the projected and unprojected
+ * fields of the three levels in a state handle (52 matrix fields).  The state refers to g: g must stay unchanged
+ * and alive until the state is destroyed (hypsmear.nim:51-53). */
+typedef int qexb200_hyp_t;
+int qexb200_hyp_smear_get_force(qexb200_gauge_t fl, qexb200_gauge_t g, const qexb200_hyp_coefs* coef,
+                                qexb200_hyp_t* state);
+/* smearedForce(f, chain) (hypsmear.nim:163-262): the chain rule through projectU (projectUderiv,
+ * src/maths/matrixFunctions.nim:321-357) and the staples (symStapleDeriv, src/gauge/smearutil.nim:24-54) of the three
+ * levels: chain = derivative with respect to the smeared links, f = with respect to the thin links.  f may be the
+ * same handle as chain (f.smeared_force(f), src/stagg_pv_hmc/staghmc_spv.nim:745).  On a split lattice it needs
+ * QEXB200_ARENA_FIELDS >= 100. */
+int qexb200_hyp_smeared_force(qexb200_hyp_t state, qexb200_gauge_t f, qexb200_gauge_t chain);
+int qexb200_hyp_destroy(qexb200_hyp_t state);
+/* projTAH(f, g, adj) (src/stagg_pv_hmc/staghmc_spv_gforce.nim:256-291): f[mu] := projectTAH(f[mu] g[mu]^+)
+ * (adj = 0, matter force) or projectTAH(g[mu] f[mu]^+) (adj != 0, gauge force); projectTAH = traceless
+ * anti-Hermitian part (src/maths/matrixFunctions.nim:375-380). */
+int qexb200_gauge_projTAH(qexb200_gauge_t f, qexb200_gauge_t g, int adj);
 /* dst[mu][x] = projectU(src[mu][x]) (src/maths/matrixFunctions.nim:301-312); same link count */
 int qexb200_gauge_projectU(qexb200_gauge_t dst, qexb200_gauge_t src);
 /* plaq (src/gauge/gaugeUtils.nim:213-284) of the one-hop links: pl[mu(mu-1)/2 + nu], nu < mu */

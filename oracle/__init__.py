@@ -90,6 +90,9 @@ def lib():
         L.orc_projectU_field.argtypes = [vp, dp, dp, C.c_int]
         L.orc_hisq_smear.argtypes = [vp, dp, dp, dp, dp]
         L.orc_hyp_smear.argtypes = [vp, dp, dp, dp]
+        L.orc_sym_staple_deriv.argtypes = [vp, dp, dp, dp, C.c_int, dp, C.c_int, dp]
+        L.orc_hyp_force.argtypes = [vp, dp, dp, dp, dp, dp]
+        L.orc_projectUderiv.argtypes = [dp, dp, dp]
         L.orc_outer.argtypes = [vp, C.c_int, dp, dp, dp, C.c_double, C.c_double, C.c_int]
         L.orc_stagDeriv.argtypes = [vp, C.c_int, dp, dp]
         L.orc_stagD2deriv.argtypes = [vp, C.c_int, dp, dp, dp]
@@ -208,6 +211,26 @@ class Lattice:
         fl = self.gauge(4)
         lib().orc_hyp_smear(self.h, _dp(g), _dp(a), _dp(fl))
         return fl
+
+    def sym_staple_deriv(self, f1, f2, g1, d1, g2, d2, c):
+        """symStapleDeriv (smearutil.nim:24-54): f1, f2 accumulate the derivatives wrt g1 (dir d1), g2 (dir d2)."""
+        lib().orc_sym_staple_deriv(self.h, _dp(f1), _dp(f2), _dp(g1), d1, _dp(g2), d2, _dp(c))
+
+    def projectUderiv(self, x, chain):
+        """projectUderiv(r, x, c) site by site (matrixFunctions.nim:321-357); x, chain: [n, 3, 3, 2]."""
+        out = np.zeros_like(x)
+        xf, cf, of = x.reshape(-1, 18), chain.reshape(-1, 18), out.reshape(-1, 18)
+        for i in range(xf.shape[0]):
+            lib().orc_projectUderiv(_dp(xf[i]), _dp(cf[i]), _dp(of[i]))
+        return out
+
+    def hyp_force(self, g, alpha, chain, want_fl=False):
+        """smearGetForce -> smearedForce(f, chain) (hypsmear.nim:49-262): the chain rule through the three nHYP levels."""
+        a = np.ascontiguousarray(alpha, dtype=np.float64)
+        f = self.gauge(4)
+        fl = self.gauge(4) if want_fl else None
+        lib().orc_hyp_force(self.h, _dp(g), _dp(a), _dp(chain), _dp(f), _dp(fl) if want_fl else None)
+        return (f, fl) if want_fl else f
 
     # -- fermion-force outer products --------------------------------------
     def outer(self, f, a, b, ce=1.0, co=1.0, accumulate=True):

@@ -986,6 +986,185 @@ void orc_hyp_smear(void* lat, const double* g, const double* alpha, double* fl_)
 }
 
 // ---------------------------------------------------------------------------
+// nHYP smearing force: smearGetForce's smearedForce (src/gauge/hypsmear.nim:163-262),
+// symStapleDeriv (src/gauge/smearutil.nim:24-54), projectUderiv (src/maths/matrixFunctions.nim:321-357),
+// inverse (src/maths/matinv.nim:89-113), adjugate + sylsolve (src/maths/projUderiv.nim:8-38,96-148).
+// ---------------------------------------------------------------------------
+static inline M3 m3_add(const M3& a, const M3& b) { M3 r = a; m3_axpy(r, 1.0, b); return r; }
+static inline M3 m3_inverse(const M3& x) {   // matinv.nim:89-113
+  const cplx x00 = x.e[0][0], x01 = x.e[0][1], x02 = x.e[0][2], x10 = x.e[1][0], x11 = x.e[1][1], x12 = x.e[1][2],
+             x20 = x.e[2][0], x21 = x.e[2][1], x22 = x.e[2][2];
+  const cplx det0 = x00 * x11 - x01 * x10, det1 = x02 * x10 - x00 * x12, det2 = x01 * x12 - x02 * x11;
+  const cplx det = det0 * x22 + det1 * x21 + det2 * x20;
+  const cplx idet = 1.0 / det;
+  M3 r;
+  r.e[0][0] = idet * (x11 * x22 - x12 * x21); r.e[0][1] = idet * (x21 * x02 - x22 * x01); r.e[0][2] = idet * det2;
+  r.e[1][0] = idet * (x12 * x20 - x10 * x22); r.e[1][1] = idet * (x22 * x00 - x20 * x02); r.e[1][2] = idet * det1;
+  r.e[2][0] = idet * (x10 * x21 - x11 * x20); r.e[2][1] = idet * (x20 * x01 - x21 * x00); r.e[2][2] = idet * det0;
+  return r;
+}
+static inline M3 m3_adjugate(const M3& x) {  // projUderiv.nim:17-35
+  M3 r;
+  r.e[0][0] = x.e[1][1] * x.e[2][2] - x.e[1][2] * x.e[2][1]; r.e[0][1] = x.e[2][1] * x.e[0][2] - x.e[2][2] * x.e[0][1];
+  r.e[0][2] = x.e[0][1] * x.e[1][2] - x.e[0][2] * x.e[1][1]; r.e[1][0] = x.e[1][2] * x.e[2][0] - x.e[1][0] * x.e[2][2];
+  r.e[1][1] = x.e[2][2] * x.e[0][0] - x.e[2][0] * x.e[0][2]; r.e[1][2] = x.e[0][2] * x.e[1][0] - x.e[0][0] * x.e[1][2];
+  r.e[2][0] = x.e[1][0] * x.e[2][1] - x.e[1][1] * x.e[2][0]; r.e[2][1] = x.e[2][0] * x.e[0][1] - x.e[2][1] * x.e[0][0];
+  r.e[2][2] = x.e[0][0] * x.e[1][1] - x.e[0][1] * x.e[1][0];
+  return r;
+}
+// solves A X + X A = C, projUderiv.nim:122-146
+static inline M3 m3_sylsolve(const M3& a, const M3& c) {
+  const M3 ad = m3_adjugate(a);
+  const cplx t = a.e[0][0] + a.e[1][1] + a.e[2][2];
+  const cplx s = ad.e[0][0] + ad.e[1][1] + ad.e[2][2];
+  const cplx r = a.e[0][0] * ad.e[0][0] + a.e[0][1] * ad.e[1][0] + a.e[0][2] * ad.e[2][0];
+  const M3 ac = m3_mul(a, c), ca = m3_mul(c, a), aca = m3_mul(ac, a), adc = m3_mul(ad, c), cad = m3_mul(c, ad),
+           adcad = m3_mul(adc, ad);
+  const cplx c2 = 1.0 / (2.0 * (s * t - r)), c0 = c2 * (s + t * t), c1 = c2 * (t / r), c4 = c2 * t;
+  M3 x;
+  for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++)
+    x.e[i][j] = c0 * c.e[i][j] + c1 * adcad.e[i][j] + c2 * (aca.e[i][j] - adc.e[i][j] - cad.e[i][j]) -
+                c4 * (ac.e[i][j] + ca.e[i][j]);
+  return x;
+}
+// projectUderiv(r, u, x, chain), matrixFunctions.nim:329-351
+static inline M3 projectUderiv(const M3& u, const M3& x, const M3& chain) {
+  M3 t = m3_mul(m3_adj(x), x);
+  for (int i = 0; i < 3; i++) t.e[i][i] += 1e-20;
+  const M3 z = rsqrtPH3(t);
+  const M3 y = m3_inverse(z);
+  M3 r = m3_mul(chain, z);
+  const M3 t1 = m3_mul(m3_adj(u), r);
+  const M3 t2 = m3_sylsolve(y, t1);
+  const M3 t3 = m3_add(t2, m3_adj(t2));
+  m3_axpy(r, -1.0, m3_mul(x, t3));
+  return r;
+}
+void orc_projectUderiv(const double* x, const double* chain, double* out) {   // :353-357
+  const M3 X = m3_load(x);
+  m3_store(out, projectUderiv(projectU(X), X, m3_load(chain)));
+}
+// symStapleDeriv, smearutil.nim:24-54.  d1 / d2 = direction of g1 / g2; c = chain (direction d2).
+static void sym_staple_deriv(Lat* l, MF& f1, MF& f2, const MF& g1, int d1, const MF& g2, int d2, const MF& c) {
+  const MF s1 = mf_shift(l, g1, d2, +1), s2 = mf_shift(l, g2, d1, +1), s = mf_shift(l, c, d1, +1);
+  MF tm1(l->vol), tm2(l->vol);
+#pragma omp parallel for
+  for (int i = 0; i < l->vol; i++) {
+    tm1[i] = m3_mul(m3_mul(m3_adj(g1[i]), c[i]), s1[i]);
+    tm2[i] = m3_add(m3_mul(m3_mul(m3_adj(g2[i]), g1[i]), s[i]), m3_mul(m3_mul(m3_adj(c[i]), g1[i]), s2[i]));
+  }
+  const MF sm1 = mf_shift(l, tm1, d1, -1), sm2 = mf_shift(l, tm2, d2, -1);
+#pragma omp parallel for
+  for (int i = 0; i < l->vol; i++) {
+    m3_axpy(f1[i], 1.0, m3_mul(m3_mul(g2[i], s1[i]), m3_adj(s[i])));
+    m3_axpy(f1[i], 1.0, m3_mul(m3_mul(c[i], s1[i]), m3_adj(s2[i])));
+    m3_axpy(f2[i], 1.0, m3_mul(m3_mul(g1[i], s[i]), m3_adj(s1[i])));
+    m3_axpy(f2[i], 1.0, sm1[i]);
+    m3_axpy(f1[i], 1.0, sm2[i]);
+  }
+}
+// test hook: f1, f2 += symStapleDeriv(g1 (dir d1), g2 (dir d2), chain c)
+void orc_sym_staple_deriv(void* lat, double* f1_, double* f2_, const double* g1_, int d1, const double* g2_, int d2,
+                          const double* c_) {
+  Lat* l = (Lat*)lat;
+  MF f1 = mf_load(l, f1_), f2 = mf_load(l, f2_);
+  sym_staple_deriv(l, f1, f2, mf_load(l, g1_), d1, mf_load(l, g2_), d2, mf_load(l, c_));
+  mf_store(l, f1_, f1); mf_store(l, f2_, f2);
+}
+static void mf_scale(MF& f, double a) {
+#pragma omp parallel for
+  for (size_t i = 0; i < f.size(); i++) f[i] = m3_scale(a, f[i]);
+}
+static void mf_axpy(MF& y, double a, const MF& x) {
+#pragma omp parallel for
+  for (size_t i = 0; i < y.size(); i++) m3_axpy(y[i], a, x[i]);
+}
+
+// smear (forward, keepProj branch) + smearedForce(f, chain), hypsmear.nim:49-262.  fl_ (may be NULL) gets the
+// smeared links; f_ the force with respect to the thin links.
+void orc_hyp_force(void* lat, const double* g, const double* alpha, const double* chain_, double* f_, double* fl_) {
+  Lat* l = (Lat*)lat;
+  const size_t fs = (size_t)l->vol * 18;
+  const int V = l->vol;
+  MF gf[4], l1[4][4], l2[4][4], l1x[4][4], l2x[4][4], flx[4];
+  for (int d = 0; d < 4; d++) gf[d] = mf_load(l, g + d * fs);
+  const double alp1 = alpha[0] / 2.0, alp2 = alpha[1] / 4.0, alp3 = alpha[2] / 6.0;
+  const double ma1 = 1 - alpha[0], ma2 = 1 - alpha[1], ma3 = 1 - alpha[2];
+  auto scaled = [&](double a, const MF& x) { MF r(V); for (int i = 0; i < V; i++) r[i] = m3_scale(a, x[i]); return r; };
+  for (int mu = 0; mu < 4; mu++) for (int nu = 0; nu < 4; nu++) {
+    if (nu == mu) continue;
+    l1x[mu][nu] = scaled(ma1, gf[mu]);
+    sym_staple(l, l1x[mu][nu], alp1, gf[nu], nu, gf[mu], mu);
+    l1[mu][nu].resize(V); mf_project(l1[mu][nu], l1x[mu][nu]);
+  }
+  for (int mu = 0; mu < 4; mu++) for (int nu = 0; nu < 4; nu++) {
+    if (nu == mu) continue;
+    l2x[mu][nu] = scaled(ma2, gf[mu]);
+    for (int a = 0; a < 4; a++) {
+      if (a == mu || a == nu) continue;
+      const int b = 6 - mu - nu - a;
+      sym_staple(l, l2x[mu][nu], alp2, l1[a][b], a, l1[mu][b], mu);
+    }
+    l2[mu][nu].resize(V); mf_project(l2[mu][nu], l2x[mu][nu]);
+  }
+  for (int mu = 0; mu < 4; mu++) {
+    flx[mu] = scaled(ma3, gf[mu]);
+    for (int nu = 0; nu < 4; nu++) if (nu != mu) sym_staple(l, flx[mu], alp3, l2[nu][mu], nu, l2[mu][nu], mu);
+    if (fl_) { MF r(V); mf_project(r, flx[mu]); mf_store(l, fl_ + mu * fs, r); }
+  }
+  // ---- smearedForce, :163-262 ----
+  MF f[4], fc[4], fl1[4][4], fl2[4][4];
+  const M3 zero = m3_scale(0.0, gf[0][0]);
+  for (int mu = 0; mu < 4; mu++) for (int nu = 0; nu < 4; nu++) if (nu != mu) { fl1[mu][nu].assign(V, zero); fl2[mu][nu].assign(V, zero); }
+  for (int mu = 0; mu < 4; mu++) {                                             // :185-186
+    const MF ch = mf_load(l, chain_ + mu * fs);
+    fc[mu].resize(V);
+#pragma omp parallel for
+    for (int i = 0; i < V; i++) fc[mu][i] = projectUderiv(projectU(flx[mu][i]), flx[mu][i], ch[i]);
+  }
+  for (int mu = 0; mu < 4; mu++) { f[mu] = scaled(ma3, fc[mu]); mf_scale(fc[mu], alp3); }   // :188-190
+  for (int mu = 0; mu < 4; mu++) for (int nu = 0; nu < 4; nu++) {                          // :191-205
+    if (nu == mu) continue;
+    sym_staple_deriv(l, fl2[nu][mu], fl2[mu][nu], l2[nu][mu], nu, l2[mu][nu], mu, fc[mu]);
+  }
+  for (int mu = 0; mu < 4; mu++) for (int nu = 0; nu < 4; nu++) {                          // :209-215
+    if (nu == mu) continue;
+    MF& x = fl2[mu][nu];
+#pragma omp parallel for
+    for (int i = 0; i < V; i++) x[i] = projectUderiv(l2[mu][nu][i], l2x[mu][nu][i], x[i]);
+  }
+  for (int mu = 0; mu < 4; mu++) for (int nu = 0; nu < 4; nu++) {                          // :217-221
+    if (nu == mu) continue;
+    mf_axpy(f[mu], ma2, fl2[mu][nu]);
+    mf_scale(fl2[mu][nu], alp2);
+  }
+  for (int mu = 0; mu < 4; mu++) for (int nu = 0; nu < 4; nu++) {                          // :222-240
+    if (nu == mu) continue;
+    for (int a = 0; a < 4; a++) {
+      if (a == mu || a == nu) continue;
+      const int b = 6 - mu - nu - a;
+      sym_staple_deriv(l, fl1[a][b], fl1[mu][b], l1[a][b], a, l1[mu][b], mu, fl2[mu][nu]);
+    }
+  }
+  for (int mu = 0; mu < 4; mu++) for (int nu = 0; nu < 4; nu++) {                          // :244-251
+    if (nu == mu) continue;
+    MF& x = fl1[mu][nu];
+#pragma omp parallel for
+    for (int i = 0; i < V; i++) x[i] = projectUderiv(l1[mu][nu][i], l1x[mu][nu][i], x[i]);
+  }
+  for (int mu = 0; mu < 4; mu++) for (int nu = 0; nu < 4; nu++) {                          // :253-257
+    if (nu == mu) continue;
+    mf_axpy(f[mu], ma1, fl1[mu][nu]);
+    mf_scale(fl1[mu][nu], alp1);
+  }
+  for (int mu = 0; mu < 4; mu++) for (int nu = 0; nu < 4; nu++) {                          // :258-264
+    if (nu == mu) continue;
+    sym_staple_deriv(l, f[nu], f[mu], gf[nu], nu, gf[mu], mu, fl1[mu][nu]);
+  }
+  for (int mu = 0; mu < 4; mu++) mf_store(l, f_ + mu * fs, f[mu]);
+}
+
+// ---------------------------------------------------------------------------
 // Fermion-force outer products (src/physics/stagD.nim:588-664; peqOuter/meqOuter
 // src/maths/matrixConcept.nim:717-724: r[i][j] +-= x[i] * conj(y[j])).
 // f = nd contiguous link-shaped fields [k][vol][18], hop of field k as in the operator.

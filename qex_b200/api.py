@@ -58,6 +58,21 @@ class HypCoefs(C.Structure):
     def smear(self, g, fl):
         _ck(lib().qexb200_gauge_smear_hyp(fl.h, g.h, C.byref(self)))
 
+    def smearGetForce(self, g, fl):
+        """smearGetForce(gf, fl) (hypsmear.nim:49-162): smears and returns smearedForce(f, chain) as a callable
+        (its .free() releases the kept fields; g must stay unchanged meanwhile)."""
+        h = C.c_int()
+        _ck(lib().qexb200_hyp_smear_get_force(fl.h, g.h, C.byref(self), C.byref(h)))
+
+        def smearedForce(f, chain):
+            _ck(lib().qexb200_hyp_smeared_force(h.value, f.h, chain.h))
+
+        def free():
+            if is_initialized():
+                lib().qexb200_hyp_destroy(h.value)
+        smearedForce.free = free
+        return smearedForce
+
 
 def lib_path():
     return _LIBPATH
@@ -91,6 +106,10 @@ def lib():
         L.qexb200_gauge_smear_hisq.argtypes = [C.c_int, C.c_int, C.c_int, C.POINTER(HisqCoefs)]
         L.qexb200_gauge_smear_hyp.argtypes = [C.c_int, C.c_int, C.POINTER(HypCoefs)]
         L.qexb200_gauge_projectU.argtypes = [C.c_int, C.c_int]
+        L.qexb200_hyp_smear_get_force.argtypes = [C.c_int, C.c_int, C.POINTER(HypCoefs), ip]
+        L.qexb200_hyp_smeared_force.argtypes = [C.c_int, C.c_int, C.c_int]
+        L.qexb200_hyp_destroy.argtypes = [C.c_int]
+        L.qexb200_gauge_projTAH.argtypes = [C.c_int, C.c_int, C.c_int]
         L.qexb200_gauge_plaq.argtypes = [C.c_int, dp]
         L.qexb200_gauge_join3.argtypes = [C.c_int, C.c_int, C.c_int]
         L.qexb200_gauge_download.argtypes = [C.c_int, C.POINTER(dp)]
@@ -373,6 +392,10 @@ class DeviceGauge:
 
     def projectU(self, src):
         _ck(lib().qexb200_gauge_projectU(self.h, src.h))
+
+    def projTAH(self, g, adj="no_adj"):
+        """projTAH(f, g, adj) (src/stagg_pv_hmc/staghmc_spv_gforce.nim:256-291)."""
+        _ck(lib().qexb200_gauge_projTAH(self.h, g.h, int(adj == "adj")))
 
     def zero(self):
         _ck(lib().qexb200_gauge_zero(self.h))

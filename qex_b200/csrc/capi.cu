@@ -54,6 +54,7 @@ int nccl_load() {
 
 static std::map<int, Gauge> g_gauges;
 static Gauge g_hf;   // staging link set of the host-field force calls
+static std::map<int, HypState> g_hyps;
 static std::map<int, Field> g_fields;
 static int g_next_handle = 1;
 
@@ -460,6 +461,8 @@ int qexb200_finalize(void) {
   if (g_mw.ok) cudaFree(g_mw.xt.d);
   g_mw = MultiWork();
   if (g_ht.ok) { cudaFree(g_ht.a.d); cudaFree(g_ht.b.d); g_ht = HostTmp(); }
+  for (auto& kv : g_hyps) hyp_state_free(&kv.second);
+  g_hyps.clear();
   cg_free();
   smear_free();
   io_free();
@@ -635,6 +638,60 @@ int qexb200_gauge_smear_hyp(qexb200_gauge_t hfl, qexb200_gauge_t hg, const qexb2
   one_hop(fl, pfl); one_hop(g, pg);
   QB_CHECK(hyp_smear(pfl, pg, al));
   return links_written(fl);
+}
+// smearGetForce (hypsmear.nim:49-162): smear AND keep what smearedForce needs
+int qexb200_hyp_smear_get_force(qexb200_gauge_t hfl, qexb200_gauge_t hg, const qexb200_hyp_coefs* coef, qexb200_hyp_t* out) {
+  QB_CHECK(need_ctx());
+  Gauge *fl, *g;
+  QB_CHECK(get_gauge4(hfl, &fl, "smearGetForce(fl)", false));
+  QB_CHECK(get_gauge4(hg, &g, "smearGetForce(g)", true));
+  if (fl == g) return fail("smearGetForce: fl and g must be different link sets");
+  const double al[3] = {coef->alpha1, coef->alpha2, coef->alpha3};
+  double2 *pfl[4], *pg[4];
+  one_hop(fl, pfl); one_hop(g, pg);
+  HypState st;
+  const int rc = hyp_smear(pfl, pg, al, &st);
+  if (rc) { hyp_state_free(&st); return rc; }
+  st.gauge_handle = hg;
+  QB_CHECK(links_written(fl));
+  const int h = g_next_handle++;
+  g_hyps[h] = st;
+  *out = h;
+  return 0;
+}
+// smearedForce(f, chain) (hypsmear.nim:163-262); f may be the same handle as chain (staghmc_spv.nim:745)
+int qexb200_hyp_smeared_force(qexb200_hyp_t hs, qexb200_gauge_t hf, qexb200_gauge_t hchain) {
+  QB_CHECK(need_ctx());
+  auto it = g_hyps.find(hs);
+  if (it == g_hyps.end()) return fail("invalid smearing-state handle %d", hs);
+  Gauge *f, *ch, *g;
+  QB_CHECK(get_gauge4(hf, &f, "smearedForce(f)", false));
+  QB_CHECK(get_gauge4(hchain, &ch, "smearedForce(chain)", true));
+  if (get_gauge(it->second.gauge_handle, &g) != 0 || link_field(g, 0) != it->second.g[0])
+    return fail("smearedForce: the thin links the state was built from are gone");
+  double2 *pf[4], *pc[4];
+  one_hop(f, pf); one_hop(ch, pc);
+  QB_CHECK(hyp_force(it->second, pf, pc));
+  f->loaded = true;
+  return 0;
+}
+int qexb200_hyp_destroy(qexb200_hyp_t hs) {
+  QB_CHECK(need_ctx());
+  auto it = g_hyps.find(hs);
+  if (it == g_hyps.end()) return fail("invalid smearing-state handle %d", hs);
+  cudaStreamSynchronize(g_ctx.stream);
+  hyp_state_free(&it->second);
+  g_hyps.erase(it);
+  return 0;
+}
+// projTAH(f, g, adj) (stagg_pv_hmc/staghmc_spv_gforce.nim:256-291)
+int qexb200_gauge_projTAH(qexb200_gauge_t hf, qexb200_gauge_t hg, int adj) {
+  QB_CHECK(need_ctx());
+  Gauge *f, *g;
+  QB_CHECK(get_gauge(hf, &f)); QB_CHECK(get_gauge(hg, &g));
+  if (f->nlinks != g->nlinks) return fail("projTAH: link counts differ (%d vs %d)", f->nlinks, g->nlinks);
+  if (!f->loaded || !g->loaded) return fail("projTAH: a link set holds nothing");
+  return proj_tah(f->d, g->d, f->nlinks, adj != 0);
 }
 // newStag3(fl, ll) (stagD.nim:552-564): g[2 mu] = fl[mu], g[2 mu + 1] = ll[mu]
 int qexb200_gauge_join3(qexb200_gauge_t hout, qexb200_gauge_t hfl, qexb200_gauge_t hll) {

@@ -244,7 +244,18 @@ void free_compressed(Gauge& g);
 int make_imp_links(double2* const fl[4], const double2* const gf[4], const double coef[5], double2* const ll[4],
                    const double2* const gfl[4], double naik);
 int hisq_smear(double2* const fl[4], double2* const ll[4], const double2* const g[4], const double c[11]);
-int hyp_smear(double2* const fl[4], const double2* const g[4], const double alpha[3]);
+// what smearGetForce keeps for smearedForce (hypsmear.nim:62-75): projected and unprojected fields of each level
+struct HypState {
+  double2 *l1[4][4] = {}, *l2[4][4] = {}, *l1x[4][4] = {}, *l2x[4][4] = {}, *flx[4] = {};
+  const double2* g[4] = {};    // the thin links the state was built from (must stay unchanged, hypsmear.nim:51-53)
+  double alpha[3] = {0, 0, 0};
+  int gauge_handle = -1;
+  bool live = false;
+};
+int hyp_smear(double2* const fl[4], const double2* const g[4], const double alpha[3], HypState* st = nullptr);
+int hyp_force(const HypState& st, double2* const f[4], const double2* const chain[4]);
+void hyp_state_free(HypState* st);
+int proj_tah(double2* f, const double2* g, int nfields, bool adj);
 int project_fields(double2* out, const double2* in, int nfields);
 int plaq_links(const double2* const u[4], double pl[6]);
 int smear_free();

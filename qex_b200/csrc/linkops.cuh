@@ -216,8 +216,8 @@ QB_HD double m3_det_re(const M3& x) {
   const double2 t2 = c_mul(make_double2(f.x - g.x, f.y - g.y), x.e[6]);
   return t0.x + t1.x + t2.x;
 }
-// x (x^+ x + 1e-20)^(-1/2): projectU :301-312 through rsqrtPHM3 :126-181
-QB_HD M3 project_u(const M3& x) {
+// (x^+ x + 1e-20)^(-1/2): projectUrsqrt :301-306 through rsqrtPHM3 :126-181
+QB_HD M3 project_u_rsqrt(const M3& x) {
   M3 h = m3_mul_an(x, x);
   h.e[0].x += 1e-20; h.e[4].x += 1e-20; h.e[8].x += 1e-20;
   const double tr = h.e[0].x + h.e[4].x + h.e[8].x;
@@ -238,7 +238,122 @@ QB_HD M3 project_u(const M3& x) {
 #pragma unroll
   for (int e = 0; e < 9; e++) rs.e[e] = make_double2(c1 * h.e[e].x + c2 * h2.e[e].x, c1 * h.e[e].y + c2 * h2.e[e].y);
   rs.e[0].x += c0; rs.e[4].x += c0; rs.e[8].x += c0;
-  return m3_mul(x, rs);
+  return rs;
+}
+// x (x^+ x + 1e-20)^(-1/2): projectU :308-312
+QB_HD M3 project_u(const M3& x) { return m3_mul(x, project_u_rsqrt(x)); }
+
+// ---- projectUderiv (src/maths/matrixFunctions.nim:321-357) ----------------------------------------
+QB_HD double2 c_sub(double2 a, double2 b) { return make_double2(a.x - b.x, a.y - b.y); }
+QB_HD double2 c_add(double2 a, double2 b) { return make_double2(a.x + b.x, a.y + b.y); }
+QB_HD double2 c_inv(double2 a) { const double n = 1.0 / (a.x * a.x + a.y * a.y); return make_double2(a.x * n, -a.y * n); }
+// adjugate, src/maths/projUderiv.nim:17-35
+QB_HD M3 m3_adjugate(const M3& x) {
+  M3 r;
+  r.e[0] = c_sub(c_mul(x.e[4], x.e[8]), c_mul(x.e[5], x.e[7]));
+  r.e[1] = c_sub(c_mul(x.e[7], x.e[2]), c_mul(x.e[8], x.e[1]));
+  r.e[2] = c_sub(c_mul(x.e[1], x.e[5]), c_mul(x.e[2], x.e[4]));
+  r.e[3] = c_sub(c_mul(x.e[5], x.e[6]), c_mul(x.e[3], x.e[8]));
+  r.e[4] = c_sub(c_mul(x.e[8], x.e[0]), c_mul(x.e[6], x.e[2]));
+  r.e[5] = c_sub(c_mul(x.e[2], x.e[3]), c_mul(x.e[0], x.e[5]));
+  r.e[6] = c_sub(c_mul(x.e[3], x.e[7]), c_mul(x.e[4], x.e[6]));
+  r.e[7] = c_sub(c_mul(x.e[6], x.e[1]), c_mul(x.e[7], x.e[0]));
+  r.e[8] = c_sub(c_mul(x.e[0], x.e[4]), c_mul(x.e[1], x.e[3]));
+  return r;
+}
+// inverse, src/maths/matinv.nim:89-113 (adjugate / determinant)
+QB_HD M3 m3_inverse(const M3& x) {
+  const M3 ad = m3_adjugate(x);
+  const double2 det = c_add(c_add(c_mul(ad.e[8], x.e[8]), c_mul(ad.e[5], x.e[7])), c_mul(ad.e[2], x.e[6]));
+  const double2 idet = c_inv(det);
+  M3 r;
+#pragma unroll
+  for (int e = 0; e < 9; e++) r.e[e] = c_mul(idet, ad.e[e]);
+  return r;
+}
+// A X + X A = C for X, src/maths/projUderiv.nim:122-146
+QB_HD M3 m3_sylsolve(const M3& a, const M3& c) {
+  const M3 ad = m3_adjugate(a);
+  const double2 t = c_add(c_add(a.e[0], a.e[4]), a.e[8]);
+  const double2 s = c_add(c_add(ad.e[0], ad.e[4]), ad.e[8]);
+  const double2 r = c_add(c_add(c_mul(a.e[0], ad.e[0]), c_mul(a.e[1], ad.e[3])), c_mul(a.e[2], ad.e[6]));
+  const M3 ac = m3_mul(a, c), ca = m3_mul(c, a), aca = m3_mul(ac, a), adc = m3_mul(ad, c), cad = m3_mul(c, ad),
+           adcad = m3_mul(adc, ad);
+  const double2 st = c_sub(c_mul(s, t), r);
+  const double2 c2 = c_inv(make_double2(2.0 * st.x, 2.0 * st.y));
+  const double2 c0 = c_mul(c2, c_add(s, c_mul(t, t)));
+  const double2 c1 = c_mul(c2, c_mul(t, c_inv(r)));
+  const double2 c4 = c_mul(c2, t);
+  M3 x;
+#pragma unroll
+  for (int e = 0; e < 9; e++) {
+    const double2 v = c_add(c_add(c_mul(c0, c.e[e]), c_mul(c1, adcad.e[e])),
+                            c_mul(c2, c_sub(c_sub(aca.e[e], adc.e[e]), cad.e[e])));
+    x.e[e] = c_sub(v, c_mul(c4, c_add(ac.e[e], ca.e[e])));
+  }
+  return x;
+}
+// projectUderiv(r, u, x, chain) :329-351 with u = x z formed from the same z (the 3-argument form :353-357)
+QB_HD M3 project_u_deriv(const M3& x, const M3& chain) {
+  const M3 z = project_u_rsqrt(x);
+  const M3 u = m3_mul(x, z);
+  const M3 y = m3_inverse(z);
+  M3 r = m3_mul(chain, z);
+  const M3 t1 = m3_mul_an(u, r);
+  const M3 t2 = m3_sylsolve(y, t1);
+  M3 t3;
+#pragma unroll
+  for (int i = 0; i < 3; i++)
+#pragma unroll
+    for (int j = 0; j < 3; j++)
+      t3.e[i * 3 + j] = make_double2(t2.e[i * 3 + j].x + t2.e[j * 3 + i].x, t2.e[i * 3 + j].y - t2.e[j * 3 + i].y);
+  m3_axpy(r, -1.0, m3_mul(x, t3));
+  return r;
+}
+
+// ---- symStapleDeriv (src/gauge/smearutil.nim:24-54), gathered in place --------------------------------
+// g1: side link (direction d1), g2: middle link (d2), c: chain of the smeared link (direction d2).
+//   f1(x) += g2(x) g1(x+d2) c(x+d1)^+ + c(x) g1(x+d2) g2(x+d1)^+ + [g2^+ g1 c(+d1) + c^+ g1 g2(+d1)](x-d2)
+//   f2(x) += g1(x) c(x+d1) g1(x+d2)^+ + [g1^+ c g1(+d2)](x-d1)
+template <bool MR>
+QB_HD void staple_deriv_x(M3& f1, M3& f2, const double2* g1, int d1, const double2* g2, int d2, const double2* c,
+                          const LSite& s, const int* X, int Vh, const Peers& pr) {
+  const LSite s1 = lhop(s, d1, +1, X), s2 = lhop(s, d2, +1, X);
+  const M3 G1x2 = m3_ldx<MR>(g1, s2, Vh, pr), Cx1 = m3_ldx<MR>(c, s1, Vh, pr);
+  {
+    const M3 t = m3_mul_na(m3_mul(m3_ld(g2, s, Vh), G1x2), Cx1);
+    m3_axpy(f1, 1.0, t);
+    const M3 v = m3_mul_na(m3_mul(m3_ld(c, s, Vh), G1x2), m3_ldx<MR>(g2, s1, Vh, pr));
+    m3_axpy(f1, 1.0, v);
+    const M3 w = m3_mul_na(m3_mul(m3_ld(g1, s, Vh), Cx1), G1x2);
+    m3_axpy(f2, 1.0, w);
+  }
+  {
+    const LSite y = lhop(s, d2, -1, X), y1 = lhop(y, d1, +1, X);
+    const M3 G1y = m3_ldx<MR>(g1, y, Vh, pr);
+    const M3 a = m3_mul(m3_mul_an(m3_ldx<MR>(g2, y, Vh, pr), G1y), m3_ldx<MR>(c, y1, Vh, pr));
+    m3_axpy(f1, 1.0, a);
+    const M3 b = m3_mul(m3_mul_an(m3_ldx<MR>(c, y, Vh, pr), G1y), m3_ldx<MR>(g2, y1, Vh, pr));
+    m3_axpy(f1, 1.0, b);
+  }
+  {
+    const LSite y = lhop(s, d1, -1, X), y2 = lhop(y, d2, +1, X);
+    const M3 a = m3_mul(m3_mul_an(m3_ldx<MR>(g1, y, Vh, pr), m3_ldx<MR>(c, y, Vh, pr)), m3_ldx<MR>(g1, y2, Vh, pr));
+    m3_axpy(f2, 1.0, a);
+  }
+}
+// projectTAH, src/maths/matrixFunctions.nim:375-380: (x - x^+)/2 minus its trace / 3
+QB_HD M3 project_tah(const M3& x) {
+  M3 r;
+#pragma unroll
+  for (int i = 0; i < 3; i++)
+#pragma unroll
+    for (int j = 0; j < 3; j++)
+      r.e[i * 3 + j] = make_double2(0.5 * (x.e[i * 3 + j].x - x.e[j * 3 + i].x), 0.5 * (x.e[i * 3 + j].y + x.e[j * 3 + i].y));
+  const double d = (r.e[0].y + r.e[4].y + r.e[8].y) * (1.0 / 3.0);   // the trace is purely imaginary
+  r.e[0].y -= d; r.e[4].y -= d; r.e[8].y -= d;
+  r.e[0].x = 0.0; r.e[4].x = 0.0; r.e[8].x = 0.0;
+  return r;
 }
 
 }  // namespace qb

@@ -396,53 +396,234 @@ int hisq_smear(double2* const fl[4], double2* const ll[4], const double2* const 
   return make_imp_links(fl, cp2, c + 5, ll, cp2, c[10]);
 }
 
-// ---- HypCoefs.smear, hypsmear.nim:49-162 --------------------------------------------------------
+// ---- HypCoefs.smear / smearGetForce, hypsmear.nim:49-162 ---------------------------------------------
 // L1[mu][nu] = P((1-a1) g[mu] + a1/2 S(g[nu], g[mu]));  L2[mu][nu] = P((1-a2) g[mu] + a2/4 sum_a S(L1[a][b], L1[mu][b]));
 // fl[mu] = P((1-a3) g[mu] + a3/6 sum_nu S(L2[nu][mu], L2[mu][nu])).  One launch per output field.
-int hyp_smear(double2* const fl[4], const double2* const g[4], const double alpha[3]) {
+// st != nullptr (smearGetForce): the projected and unprojected fields of every level are kept for smearedForce.
+static int state_alloc(HypState* st) {
+  for (int mu = 0; mu < 4; mu++) {
+    QB_CHECK(pool_get(&st->flx[mu]));
+    for (int nu = 0; nu < 4; nu++) {
+      if (nu == mu) continue;
+      QB_CHECK(pool_get(&st->l1[mu][nu])); QB_CHECK(pool_get(&st->l2[mu][nu]));
+      QB_CHECK(pool_get(&st->l1x[mu][nu])); QB_CHECK(pool_get(&st->l2x[mu][nu]));
+    }
+  }
+  st->live = true;
+  return 0;
+}
+void hyp_state_free(HypState* st) {
+  if (!st->live) return;
+  for (int mu = 3; mu >= 0; mu--) {   // reverse order: the pool is LIFO
+    for (int nu = 3; nu >= 0; nu--) {
+      if (nu == mu) continue;
+      pool_put(st->l2x[mu][nu]); pool_put(st->l1x[mu][nu]); pool_put(st->l2[mu][nu]); pool_put(st->l1[mu][nu]);
+    }
+    pool_put(st->flx[mu]);
+  }
+  *st = HypState();
+}
+
+int hyp_smear(double2* const fl[4], const double2* const g[4], const double alpha[3], HypState* st) {
   Context& c = ctx();
   QB_CHECK(mr_begin(&g_peers, {g[0], g[1], g[2], g[3], fl[0], fl[1], fl[2], fl[3]}));
   for (int d = 0; d < 4; d++)
     if (c.g.X[d] < 4) return fail("hyp smear: local extent %d in direction %d is below 4", c.g.X[d], d);
   const double alp1 = alpha[0] / 2.0, alp2 = alpha[1] / 4.0, alp3 = alpha[2] / 6.0;
   const double ma1 = 1 - alpha[0], ma2 = 1 - alpha[1], ma3 = 1 - alpha[2];
-  Tmp l1[4][4], l2[4][4];
+  Tmp t1[4][4], t2[4][4];
+  double2 *l1[4][4] = {}, *l2[4][4] = {};
+  if (st) {
+    if (st->live) hyp_state_free(st);
+    QB_CHECK(state_alloc(st));
+    for (int d = 0; d < 3; d++) st->alpha[d] = alpha[d];
+    for (int d = 0; d < 4; d++) st->g[d] = g[d];
+  }
   for (int mu = 0; mu < 4; mu++) for (int nu = 0; nu < 4; nu++) {
     if (nu == mu) continue;
-    QB_CHECK(l1[mu][nu].get());
+    if (st) { l1[mu][nu] = st->l1[mu][nu]; l2[mu][nu] = st->l2[mu][nu]; }
+    else { QB_CHECK(t1[mu][nu].get()); l1[mu][nu] = t1[mu][nu].p; }
+  }
+  for (int mu = 0; mu < 4; mu++) for (int nu = 0; nu < 4; nu++) {
+    if (nu == mu) continue;
     StapleArgs a = staple_args(mu);   // :107-111
     a.base = g[mu]; a.cbase = ma1;
     a.t[0] = {g[nu], g[mu], nu, alp1};
-    a.out = l1[mu][nu].p;
+    a.out = l1[mu][nu];
+    if (st) a.raw = st->l1x[mu][nu];
     QB_CHECK(launch_staple(a, 1, true));
   }
   for (int mu = 0; mu < 4; mu++) for (int nu = 0; nu < 4; nu++) {
     if (nu == mu) continue;
-    QB_CHECK(l2[mu][nu].get());
+    if (!st) { QB_CHECK(t2[mu][nu].get()); l2[mu][nu] = t2[mu][nu].p; }
     StapleArgs a = staple_args(mu);   // :117-133
     a.base = g[mu]; a.cbase = ma2;
     int nt = 0;
     for (int s = 0; s < 4; s++) {
       if (s == mu || s == nu) continue;
       const int b = 6 - mu - nu - s;
-      a.t[nt++] = {l1[s][b].p, l1[mu][b].p, s, alp2};
+      a.t[nt++] = {l1[s][b], l1[mu][b], s, alp2};
     }
-    a.out = l2[mu][nu].p;
+    a.out = l2[mu][nu];
+    if (st) a.raw = st->l2x[mu][nu];
     QB_CHECK(launch_staple(a, nt, true));
   }
-  for (int mu = 0; mu < 4; mu++) for (int nu = 0; nu < 4; nu++) l1[mu][nu].drop();
+  for (int mu = 0; mu < 4; mu++) for (int nu = 0; nu < 4; nu++) t1[mu][nu].drop();
   for (int mu = 0; mu < 4; mu++) {
     StapleArgs a = staple_args(mu);   // :136-150
     a.base = g[mu]; a.cbase = ma3;
     int nt = 0;
     for (int nu = 0; nu < 4; nu++) {
       if (nu == mu) continue;
-      a.t[nt++] = {l2[nu][mu].p, l2[mu][nu].p, nu, alp3};
+      a.t[nt++] = {l2[nu][mu], l2[mu][nu], nu, alp3};
     }
     a.out = fl[mu];
+    if (st) a.raw = st->flx[mu];
     QB_CHECK(launch_staple(a, nt, true));
   }
   return xbarrier();
+}
+
+// ---- smearedForce, hypsmear.nim:163-262 ---------------------------------------------------------------
+// r = projectUderiv(x, chain) (matrixFunctions.nim:321-357); keep = s_keep * r (may alias chain: the next level's
+// chain, already weighted by alpha/n); f = (acc ? f : 0) + s_f * r -- the `f[mu] := ma*fc; fc *= alp` pairs of
+// :188-190,217-221,253-257 folded into the projection kernel.
+struct ProjDerivArgs {
+  const double2* x; const double2* chain;
+  double2* keep; double s_keep;
+  double2* f; double s_f; int acc;
+  int Vh;
+};
+__global__ void __launch_bounds__(SB) k_proj_deriv(const ProjDerivArgs a) {
+  const int t = blockIdx.x * SB + threadIdx.x;
+  if (t >= 2 * a.Vh) return;
+  LSite s; s.par = t / a.Vh; s.idx = t - s.par * a.Vh; s.nb = NB_HOME;
+  const M3 r = project_u_deriv(m3_ld(a.x, s, a.Vh), m3_ld(a.chain, s, a.Vh));
+  M3 o = m3_zero();
+  if (a.acc) o = m3_ld(a.f, s, a.Vh);
+  m3_axpy(o, a.s_f, r);
+  m3_st(a.f, s, a.Vh, o);
+  M3 k = m3_zero();
+  m3_axpy(k, a.s_keep, r);
+  m3_st(a.keep, s, a.Vh, k);
+}
+static int launch_proj_deriv(const double2* x, const double2* chain, double2* keep, double s_keep, double2* f, double s_f,
+                             bool acc) {
+  Context& c = ctx();
+  const ProjDerivArgs a = {x, chain, keep, s_keep, f, s_f, acc ? 1 : 0, c.g.Vh};
+  k_proj_deriv<<<(c.g.V + SB - 1) / SB, SB, 0, c.stream>>>(a);
+  count_launch();
+  QB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// symStapleDeriv, smearutil.nim:24-54: f1 (wrt g1, direction d1) and f2 (wrt g2, direction d2) accumulate
+struct DerivArgs {
+  double2 *f1, *f2;
+  const double2 *g1, *g2, *c;
+  int d1, d2;
+  int X[4];
+  int Vh;
+  Peers pr;
+};
+template <bool MR>
+__global__ void __launch_bounds__(SB, 4) k_staple_deriv(const DerivArgs a) {
+  const int par = blockIdx.x & 1, idx = (blockIdx.x >> 1) * SB + threadIdx.x;
+  if (idx >= a.Vh) return;
+  const LSite s = lsite(idx, par, a.X);
+  M3 f1 = m3_ld(a.f1, s, a.Vh), f2 = m3_ld(a.f2, s, a.Vh);
+  staple_deriv_x<MR>(f1, f2, a.g1, a.d1, a.g2, a.d2, a.c, s, a.X, a.Vh, a.pr);
+  m3_st(a.f1, s, a.Vh, f1);
+  m3_st(a.f2, s, a.Vh, f2);
+}
+static int launch_deriv(double2* f1, double2* f2, const double2* g1, int d1, const double2* g2, int d2, const double2* ch) {
+  Context& c = ctx();
+  DerivArgs a;
+  a.f1 = f1; a.f2 = f2; a.g1 = g1; a.g2 = g2; a.c = ch; a.d1 = d1; a.d2 = d2; a.Vh = c.g.Vh; a.pr = g_peers;
+  for (int d = 0; d < 4; d++) a.X[d] = c.g.X[d];
+  const int grid = grid_par(c.g.Vh, SB);
+  if (multi()) {
+    if (!in_arena(g1) || !in_arena(g2) || !in_arena(ch)) return fail("smeared force on a split lattice: a field lives outside the peer arena");
+    QB_CHECK(xbarrier());
+    k_staple_deriv<true><<<grid, SB, 0, c.stream>>>(a);
+  } else {
+    k_staple_deriv<false><<<grid, SB, 0, c.stream>>>(a);
+  }
+  count_launch();
+  QB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// f[mu] = d/dU of sum Re tr(chain^+ V(U)) through the three levels; f may alias chain (staghmc_spv.nim:745).
+int hyp_force(const HypState& st, double2* const f[4], const double2* const chain[4]) {
+  Context& c = ctx();
+  if (!st.live) return fail("smeared force: the smearing state is empty");
+  QB_CHECK(mr_begin(&g_peers, {st.g[0], st.g[1], st.g[2], st.g[3], f[0], f[1], f[2], f[3]}));
+  const double alp1 = st.alpha[0] / 2.0, alp2 = st.alpha[1] / 4.0, alp3 = st.alpha[2] / 6.0;
+  const double ma1 = 1 - st.alpha[0], ma2 = 1 - st.alpha[1], ma3 = 1 - st.alpha[2];
+  const size_t bytes = sizeof(double2) * 18 * (size_t)c.g.Vh;
+  Tmp fc[4], fl1[4][4], fl2[4][4];
+  for (int mu = 0; mu < 4; mu++) {
+    QB_CHECK(fc[mu].get());
+    for (int nu = 0; nu < 4; nu++) {
+      if (nu == mu) continue;
+      QB_CHECK(fl1[mu][nu].get()); QB_CHECK(fl2[mu][nu].get());
+      QB_CUDA(cudaMemsetAsync(fl1[mu][nu].p, 0, bytes, c.stream));     // :178-182
+      QB_CUDA(cudaMemsetAsync(fl2[mu][nu].p, 0, bytes, c.stream));
+    }
+  }
+  for (int mu = 0; mu < 4; mu++)                                            // :185-190
+    QB_CHECK(launch_proj_deriv(st.flx[mu], chain[mu], fc[mu].p, alp3, f[mu], ma3, false));
+  for (int mu = 0; mu < 4; mu++) for (int nu = 0; nu < 4; nu++) {           // :191-205
+    if (nu == mu) continue;
+    QB_CHECK(launch_deriv(fl2[nu][mu].p, fl2[mu][nu].p, st.l2[nu][mu], nu, st.l2[mu][nu], mu, fc[mu].p));
+  }
+  for (int mu = 0; mu < 4; mu++) for (int nu = 0; nu < 4; nu++) {           // :209-221
+    if (nu == mu) continue;
+    QB_CHECK(launch_proj_deriv(st.l2x[mu][nu], fl2[mu][nu].p, fl2[mu][nu].p, alp2, f[mu], ma2, true));
+  }
+  for (int mu = 0; mu < 4; mu++) for (int nu = 0; nu < 4; nu++) {           // :222-240
+    if (nu == mu) continue;
+    for (int a = 0; a < 4; a++) {
+      if (a == mu || a == nu) continue;
+      const int b = 6 - mu - nu - a;
+      QB_CHECK(launch_deriv(fl1[a][b].p, fl1[mu][b].p, st.l1[a][b], a, st.l1[mu][b], mu, fl2[mu][nu].p));
+    }
+  }
+  for (int mu = 0; mu < 4; mu++) for (int nu = 0; nu < 4; nu++) {           // :244-257
+    if (nu == mu) continue;
+    QB_CHECK(launch_proj_deriv(st.l1x[mu][nu], fl1[mu][nu].p, fl1[mu][nu].p, alp1, f[mu], ma1, true));
+  }
+  for (int mu = 0; mu < 4; mu++) for (int nu = 0; nu < 4; nu++) {           // :258-264
+    if (nu == mu) continue;
+    QB_CHECK(launch_deriv(f[nu], f[mu], st.g[nu], nu, st.g[mu], mu, fl1[mu][nu].p));
+  }
+  return xbarrier();
+}
+
+// projTAH(f, g, adj) (src/stagg_pv_hmc/staghmc_spv_gforce.nim:256-291): f[mu] := projectTAH(f[mu] g[mu]^+), or of
+// g[mu] f[mu]^+ with adj
+__global__ void __launch_bounds__(SB) k_proj_tah(double2* f, const double2* g, int adj, int Vh, size_t nsites) {
+  const size_t t = (size_t)blockIdx.x * SB + threadIdx.x;
+  if (t >= nsites) return;
+  const size_t blk = t / Vh;
+  const int idx = (int)(t - blk * Vh);
+  double2* fp = f + blk * 9 * Vh + idx;
+  const double2* gp = g + blk * 9 * Vh + idx;
+  M3 F, G;
+#pragma unroll
+  for (int e = 0; e < 9; e++) { F.e[e] = fp[(size_t)e * Vh]; G.e[e] = gp[(size_t)e * Vh]; }
+  const M3 r = project_tah(adj ? m3_mul_na(G, F) : m3_mul_na(F, G));
+#pragma unroll
+  for (int e = 0; e < 9; e++) fp[(size_t)e * Vh] = r.e[e];
+}
+int proj_tah(double2* f, const double2* g, int nfields, bool adj) {
+  Context& c = ctx();
+  const size_t ns = (size_t)nfields * c.g.V;
+  k_proj_tah<<<(unsigned)((ns + SB - 1) / SB), SB, 0, c.stream>>>(f, g, adj ? 1 : 0, c.g.Vh, ns);
+  count_launch();
+  QB_CUDA(cudaGetLastError());
+  return 0;
 }
 
 }  // namespace qb

@@ -25,6 +25,37 @@ void emu_project_field(const double* in, const int* X, double* out) {
       m3_st((double2*)out, s, Vh, project_u(m3_ld((const double2*)in, s, Vh)));
     }
 }
+// out = projectUderiv(x, chain) site by site
+void emu_project_u_deriv_field(const double* x, const double* chain, const int* X, double* out) {
+  const int Vh = X[0] * X[1] * X[2] * X[3] / 2;
+  for (int par = 0; par < 2; par++)
+    for (int idx = 0; idx < Vh; idx++) {
+      const LSite s = lsite(idx, par, X);
+      m3_st((double2*)out, s, Vh, project_u_deriv(m3_ld((const double2*)x, s, Vh), m3_ld((const double2*)chain, s, Vh)));
+    }
+}
+// f1, f2 += symStapleDeriv(g1 (d1), g2 (d2), c)
+void emu_staple_deriv_field(double* f1, double* f2, const double* g1, int d1, const double* g2, int d2, const double* c,
+                            const int* X) {
+  const int Vh = X[0] * X[1] * X[2] * X[3] / 2;
+  Peers none; none.me = 0;
+  for (int par = 0; par < 2; par++)
+    for (int idx = 0; idx < Vh; idx++) {
+      const LSite s = lsite(idx, par, X);
+      M3 a = m3_ld((const double2*)f1, s, Vh), b = m3_ld((const double2*)f2, s, Vh);
+      staple_deriv_x<false>(a, b, (const double2*)g1, d1, (const double2*)g2, d2, (const double2*)c, s, X, Vh, none);
+      m3_st((double2*)f1, s, Vh, a);
+      m3_st((double2*)f2, s, Vh, b);
+    }
+}
+void emu_project_tah_field(const double* in, const int* X, double* out) {
+  const int Vh = X[0] * X[1] * X[2] * X[3] / 2;
+  for (int par = 0; par < 2; par++)
+    for (int idx = 0; idx < Vh; idx++) {
+      const LSite s = lsite(idx, par, X);
+      m3_st((double2*)out, s, Vh, project_tah(m3_ld((const double2*)in, s, Vh)));
+    }
+}
 // coordinates of (par, idx) and the index of its neighbour: out[6] = x0..x3, par', idx'
 void emu_hop(int idx, int par, int mu, int d, const int* X, int* out) {
   const LSite s = lsite(idx, par, X);

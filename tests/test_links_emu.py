@@ -25,6 +25,9 @@ def emu():
     lib.emu_staple_field.argtypes = [dp, dp, C.c_int, C.c_int, ip, dp]
     lib.emu_project_field.argtypes = [dp, ip, dp]
     lib.emu_hop.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, ip, ip]
+    lib.emu_project_u_deriv_field.argtypes = [dp, dp, ip, dp]
+    lib.emu_staple_deriv_field.argtypes = [dp, dp, dp, C.c_int, dp, C.c_int, dp, ip]
+    lib.emu_project_tah_field.argtypes = [dp, ip, dp]
     return lib
 
 
@@ -101,3 +104,50 @@ def test_project_u_matches_oracle(emu):
         m = got[..., 0] + 1j * got[..., 1]
         dev = np.abs(np.einsum("xab,xcb->xac", m, m.conj()) - np.eye(3)).max()
         assert dev < 1e-12
+
+
+def test_project_u_deriv_matches_oracle(emu):
+    """projectUderiv (matrixFunctions.nim:321-357: rsqrt, inverse, sylsolve) on smeared, non-unitary links."""
+    lat = oracle.Lattice(L)
+    g = lat.random_gauge(lat.new_rng(5))
+    x = lat.makeImpLinks(g, (0.5, 0.25 / 6, 0.0, 0.0, 0.0))[0]           # like (1-a) U + a/6 staples
+    chain = np.random.default_rng(1).standard_normal(x.shape)
+    want = lat.projectUderiv(x, chain)
+    X = (C.c_int * 4)(*L)
+    out = np.zeros_like(to_dev(x))
+    emu.emu_project_u_deriv_field(dp(to_dev(x)), dp(to_dev(chain)), X, dp(out))
+    err = np.linalg.norm(from_dev(out) - want) / np.linalg.norm(want)
+    assert err < 1e-12, err
+
+
+def test_staple_deriv_matches_oracle(emu):
+    """symStapleDeriv (smearutil.nim:24-54) gathered in place, all direction pairs, accumulating."""
+    lat = oracle.Lattice(L)
+    g = lat.random_gauge(lat.new_rng(9))
+    rng = np.random.default_rng(2)
+    c = rng.standard_normal(g[0].shape)
+    X = (C.c_int * 4)(*L)
+    for d1 in range(4):
+        for d2 in range(4):
+            if d1 == d2:
+                continue
+            f1, f2 = rng.standard_normal(c.shape), rng.standard_normal(c.shape)
+            w1, w2 = f1.copy(), f2.copy()
+            lat.sym_staple_deriv(w1, w2, g[d1], d1, g[d2], d2, c)
+            e1, e2 = to_dev(f1), to_dev(f2)
+            emu.emu_staple_deriv_field(dp(e1), dp(e2), dp(to_dev(g[d1])), d1, dp(to_dev(g[d2])), d2, dp(to_dev(c)), X)
+            assert np.linalg.norm(from_dev(e1) - w1) / np.linalg.norm(w1) < 1e-14, (d1, d2)
+            assert np.linalg.norm(from_dev(e2) - w2) / np.linalg.norm(w2) < 1e-14, (d1, d2)
+
+
+def test_project_tah(emu):
+    rng = np.random.default_rng(3)
+    lat = oracle.Lattice(L)
+    x = rng.standard_normal((lat.vol, 3, 3, 2))
+    out = np.zeros_like(to_dev(x))
+    emu.emu_project_tah_field(dp(to_dev(x)), (C.c_int * 4)(*L), dp(out))
+    m = x[..., 0] + 1j * x[..., 1]
+    w = 0.5 * (m - m.conj().transpose(0, 2, 1))
+    w = w - np.einsum("xaa->x", w)[:, None, None] / 3.0 * np.eye(3)
+    got = from_dev(out)
+    assert np.abs(got[..., 0] + 1j * got[..., 1] - w).max() < 1e-15
