@@ -349,7 +349,7 @@ def run_ours(args):
         # on several GPUs: link-shaped fields in the peer-mapped arena, neighbours read over NVLink (csrc/smear.cu)
         try:
             lp = link_pipeline_leg(qb, nsites, peak, rank, cpu=(world == 1 and not args.no_cpu))
-            for k in ("hisq", "nhyp"):
+            for k in ("hisq", "nhyp", "nhyp_force"):
                 lp[k]["ms"] = maxreduce(lp[k]["ms"])
                 gbs = 1e-9 * nsites * lp[k]["algorithmic_bytes_per_site"] / (1e-3 * lp[k]["ms"])
                 lp[k]["achieved_gbs"], lp[k]["frac_of_hbm_peak"] = gbs, gbs / peak
@@ -372,6 +372,7 @@ def run_ours(args):
 # Compulsory HBM traffic of the device link pipeline in matrix passes (144 B per site each): every
 # distinct field a launch reads counted once, every field it writes once.
 HYP_PASSES = 12 * 3 + 12 * 6 + 4 * 8
+HYP_FORCE_PASSES = 24 + 4 * 4 + 12 * 7 + 12 * 5 + 24 * 7 + 12 * 5 + 12 * 7     # smearedForce alone
 HISQ_PASSES = 4 * (3 * (5 + 10 + 6) - 1) + 4 * (3 * (5 + 10 + 8) - 1) + 4 * 2 + 4 * 2
 
 
@@ -394,6 +395,18 @@ def link_pipeline_leg(qb, nsites, peak, rank, cpu=True, reps=3):
         gbs = 1e-9 * nsites * passes * 144 / (1e-3 * ms)
         out[name] = {"ms": ms, "launches": qb.launch_count() // reps, "algorithmic_bytes_per_site": passes * 144,
                      "achieved_gbs": gbs, "frac_of_hbm_peak": gbs / peak}
+    # smearGetForce + smearedForce (hypsmear.nim:49-262): what every nHYP force step adds after the solves
+    force = yc.smearGetForce(g, fl)
+    ll.zero()
+    for it in range(reps + 1):
+        if it == 1:
+            qb.sync(); qb.launch_count(reset=True); qb.timer_start()
+        force(ll, fl)
+    ms = qb.timer_stop() / reps
+    gbs = 1e-9 * nsites * HYP_FORCE_PASSES * 144 / (1e-3 * ms)
+    out["nhyp_force"] = {"ms": ms, "launches": qb.launch_count() // reps, "algorithmic_bytes_per_site": HYP_FORCE_PASSES * 144,
+                         "achieved_gbs": gbs, "frac_of_hbm_peak": gbs / peak}
+    force.free()
     out["plaq_fat"] = [float(t) for t in fl.plaq()]
     for d in (g, fl, ll):
         d.free()

@@ -166,6 +166,19 @@ def links_case(L, G, inner, rank, world, local_rank, dist):
     res["nhyp"] = max(rel_l2(got[mu], mine(want[mu])) for mu in range(4))
     assert res["nhyp"] <= 1e-13, res
     assert np.abs(fl.plaq() - lat.plaq(want)).max() < 1e-13
+    if int(os.environ.get("QEXB200_ARENA_FIELDS", "64")) >= 100:
+        # smearGetForce / smearedForce on the split lattice (hypsmear.nim:49-262), in place like staghmc_spv.nim:745
+        chain = np.random.default_rng(4).standard_normal(g.shape)
+        wantf = lat.hyp_force(g, (0.4, 0.5, 0.5), chain)
+        fl2 = qb.DeviceGauge(nlinks=4)
+        dc = qb.DeviceGauge([mine(chain[k]) for k in range(4)])
+        force = qb.HypCoefs(0.4, 0.5, 0.5).smearGetForce(dg, fl2)
+        force(dc, dc)
+        gotf = down(dc)
+        res["nhyp_force"] = max(rel_l2(gotf[mu], mine(wantf[mu])) for mu in range(4))
+        assert res["nhyp_force"] <= 1e-11, res
+        dc.projTAH(dg)
+        force.free(); fl2.free(); dc.free()
     fl.rephase()
     lat.setBC(want); lat.stagPhase(want)
     s = qb.newStag(fl)

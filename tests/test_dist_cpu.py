@@ -18,11 +18,12 @@ def free_port():
     return p
 
 
-def launch(nproc, extra, timeout=300):
+def launch(nproc, extra, timeout=300, env_extra=None):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(nproc),
            "--master-addr", "127.0.0.1", "--master-port", str(free_port()),
            os.path.join(HERE, "multi_worker.py")] + extra
     env = dict(os.environ, OMP_NUM_THREADS="2")
+    env.update(env_extra or {})
     return subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, env=env)
 
 

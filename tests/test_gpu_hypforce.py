@@ -10,8 +10,8 @@ from util import SEED, rel_l2, make_inputs
 
 pytestmark = pytest.mark.gpu
 ALPHA = (0.4, 0.5, 0.5)
-BAR = 1e-11          # projectUderiv solves a Sylvester equation in closed form: conditioning like projectU's
-SITE_BAR = 1e-13     # median per-site deviation
+BAR = 1e-13          # nHYP's projected sums are well conditioned (measured 2e-15 on 2 ranks)
+SITE_BAR = 1e-14     # median per-site deviation
 
 
 @pytest.fixture()

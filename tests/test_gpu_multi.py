@@ -60,5 +60,7 @@ def test_multi_gpu_links_and_force(nproc, lat, rg, inner):
     fields live in the IPC-mapped arena and off-rank neighbours are read over NVLink (csrc/smear.cu, force.cu)."""
     if ngpus() < nproc:
         pytest.skip("needs %d GPUs" % nproc)
-    r = launch(nproc, ["--lat", lat, "--rankgeom", rg, "--inner", inner, "--links"], timeout=600)
+    # the nHYP force keeps 52 fields and works in 28 more: a larger arena than the default 64
+    r = launch(nproc, ["--lat", lat, "--rankgeom", rg, "--inner", inner, "--links"], timeout=600,
+               env_extra={"QEXB200_ARENA_FIELDS": "128"})
     assert r.returncode == 0 and "MULTI_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
