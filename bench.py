@@ -194,6 +194,8 @@ def run_ours(args):
             dist.broadcast(idt, 0)
             nccl_id = bytes(idt.cpu().tolist())
     lat_shape, rankgeom = WEAK[world]
+    if world > 1:   # room in the peer arena for the nHYP force state (52 fields) and its work fields (28)
+        os.environ.setdefault("QEXB200_ARENA_FIELDS", "128")
     qb.init(lat_shape, rankgeom, rank, local_rank, nccl_id)
     if world > 1 and args.transport == "p2p":
         qb.p2p_attach_torch(dist)     # halos and scalar sums over NVLink stores (csrc/comm.cu)
@@ -407,7 +409,7 @@ def link_pipeline_leg(qb, nsites, peak, rank, cpu=True, reps=3):
     out["nhyp_force"] = {"ms": ms, "launches": qb.launch_count() // reps, "algorithmic_bytes_per_site": HYP_FORCE_PASSES * 144,
                          "achieved_gbs": gbs, "frac_of_hbm_peak": gbs / peak}
     force.free()
-    out["plaq_fat"] = [float(t) for t in fl.plaq()]
+    out["plaq_smeared"] = [float(t) for t in fl.plaq()]
     for d in (g, fl, ll):
         d.free()
     if cpu:

@@ -158,6 +158,20 @@ int qexb200_hyp_smear_get_force(qexb200_gauge_t fl, qexb200_gauge_t g, const qex
  * QEXB200_ARENA_FIELDS >= 100. */
 int qexb200_hyp_smeared_force(qexb200_hyp_t state, qexb200_gauge_t f, qexb200_gauge_t chain);
 int qexb200_hyp_destroy(qexb200_hyp_t state);
+/* fat7lDeriv(deriv, gauge, mid, coef, llderiv, llgauge, llmid, naik) (src/gauge/fat7lderiv.nim:122-335): the derivative
+ * of makeImpLinks, mid / llmid = chain with respect to the fat / long links; deriv and llderiv ACCUMULATE (zero them
+ * first where the reference passes fresh fields).  naik == 0: the ll* handles are ignored (pass -1). */
+int qexb200_gauge_fat7lDeriv(qexb200_gauge_t deriv, qexb200_gauge_t gauge, qexb200_gauge_t mid,
+                             const qexb200_fat7l_coefs* coef, qexb200_gauge_t llderiv, qexb200_gauge_t llgauge,
+                             qexb200_gauge_t llmid, double naik);
+/* HisqCoefs.smearGetForce(u, su, sul) (src/gauge/hisqsmear.nim:51-84): smears like qexb200_gauge_smear_hisq and keeps
+ * the first-level fat links and their projection; smearedForce(dsdu, dsdsu, dsdsul) then runs second fat7 + Naik
+ * derivative -> projectUderiv -> first fat7 derivative, ACCUMULATING into dsdu (examples/hisqhmc.nim:496-530). */
+typedef int qexb200_hisq_t;
+int qexb200_hisq_smear_get_force(qexb200_gauge_t su, qexb200_gauge_t sul, qexb200_gauge_t u,
+                                 const qexb200_hisq_coefs* coef, qexb200_hisq_t* state);
+int qexb200_hisq_smeared_force(qexb200_hisq_t state, qexb200_gauge_t dsdu, qexb200_gauge_t dsdsu, qexb200_gauge_t dsdsul);
+int qexb200_hisq_destroy(qexb200_hisq_t state);
 /* projTAH(f, g, adj) (src/stagg_pv_hmc/staghmc_spv_gforce.nim:256-291): f[mu] := projectTAH(f[mu] g[mu]^+)
  * (adj = 0, matter force) or projectTAH(g[mu] f[mu]^+) (adj != 0, gauge force); projectTAH = traceless
  * anti-Hermitian part (src/maths/matrixFunctions.nim:375-380). */

@@ -90,6 +90,8 @@ def lib():
         L.orc_projectU_field.argtypes = [vp, dp, dp, C.c_int]
         L.orc_hisq_smear.argtypes = [vp, dp, dp, dp, dp]
         L.orc_hyp_smear.argtypes = [vp, dp, dp, dp]
+        L.orc_fat7l_deriv.argtypes = [vp, dp, dp, dp, dp, dp, dp, dp, C.c_double]
+        L.orc_hisq_force.argtypes = [vp, dp, dp, dp, dp, dp]
         L.orc_sym_staple_deriv.argtypes = [vp, dp, dp, dp, C.c_int, dp, C.c_int, dp]
         L.orc_hyp_force.argtypes = [vp, dp, dp, dp, dp, dp]
         L.orc_projectUderiv.argtypes = [dp, dp, dp]
@@ -211,6 +213,22 @@ class Lattice:
         fl = self.gauge(4)
         lib().orc_hyp_smear(self.h, _dp(g), _dp(a), _dp(fl))
         return fl
+
+    def fat7lDeriv(self, deriv, gauge, mid, coef, llderiv=None, llgauge=None, llmid=None, naik=0.0):
+        """fat7lDeriv (fat7lderiv.nim:122-335); deriv (and llderiv) accumulate."""
+        c = np.ascontiguousarray(coef, dtype=np.float64)
+        if naik != 0.0:
+            lib().orc_fat7l_deriv(self.h, _dp(deriv), _dp(gauge), _dp(mid), _dp(c), _dp(llderiv), _dp(llgauge), _dp(llmid), naik)
+        else:
+            lib().orc_fat7l_deriv(self.h, _dp(deriv), _dp(gauge), _dp(mid), _dp(c), None, None, None, 0.0)
+
+    def hisq_force(self, u, coefs, dsdsu, dsdsul, dsdu=None):
+        """HisqCoefs.smearGetForce -> smearedForce(dsdu, dsdsu, dsdsul) (hisqsmear.nim:51-84); dsdu accumulates."""
+        c = np.ascontiguousarray(coefs, dtype=np.float64)
+        if dsdu is None:
+            dsdu = self.gauge(4)
+        lib().orc_hisq_force(self.h, _dp(u), _dp(c), _dp(dsdsu), _dp(dsdsul), _dp(dsdu))
+        return dsdu
 
     def sym_staple_deriv(self, f1, f2, g1, d1, g2, d2, c):
         """symStapleDeriv (smearutil.nim:24-54): f1, f2 accumulate the derivatives wrt g1 (dir d1), g2 (dir d2)."""

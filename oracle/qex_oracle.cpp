@@ -1165,6 +1165,131 @@ void orc_hyp_force(void* lat, const double* g, const double* alpha, const double
 }
 
 // ---------------------------------------------------------------------------
+// fat7 + Lepage + Naik derivative (src/gauge/fat7lderiv.nim:122-335) and the HISQ smearing force
+// (src/gauge/hisqsmear.nim:51-84).  Built, like the reference, from symStaple / symStapleDeriv.
+// deriv / llderiv ACCUMULATE (the reference's `+=`).
+// ---------------------------------------------------------------------------
+static void fat7l_deriv(Lat* l, MF* deriv, const MF* gauge, const MF* mid, const double* coef, MF* llderiv,
+                        const MF* llgauge, const MF* llmid, double naik) {
+  const int V = l->vol;
+  const double coefL = coef[4], coef1 = coef[0] - 6 * coefL, coef3 = coef[1], coef5 = coef[2], coef7 = coef[3];
+  const bool have5 = coef5 != 0.0 || coef7 != 0.0 || coefL != 0.0;
+  const bool have3 = coef3 != 0.0 || have5;
+  const M3 zero = m3_scale(0.0, gauge[0][0]);
+  MF stpl3[4], mid5[4];
+  for (int sig = 0; sig < 4; sig++) {
+    if (have5) {
+      for (int mu = 0; mu < 4; mu++) {
+        if (mu == sig) continue;
+        stpl3[mu].assign(V, zero);
+        sym_staple(l, stpl3[mu], 1.0, gauge[mu], mu, gauge[sig], sig);      // :185-186
+        mid5[mu].assign(V, zero);
+      }
+      for (int rho = 0; rho < 4; rho++) {
+        if (rho == sig) continue;
+        MF stpl5(V, zero), mid3(V, zero);
+        if (coef7 != 0.0) {
+          for (int mu = 0; mu < 4; mu++) {
+            if (mu == sig || mu == rho) continue;
+            for (int nu = 0; nu < 4; nu++) {
+              if (nu == sig || nu == rho || nu == mu) continue;
+              sym_staple(l, stpl5, 1.0, gauge[nu], nu, stpl3[mu], sig);     // :202-203
+            }
+          }
+          mf_scale(stpl5, coef7);
+        }
+        if (coefL != 0.0) mf_axpy(stpl5, coefL, stpl3[rho]);                // :212
+        if (coefL != 0.0 || coef7 != 0.0)
+          sym_staple_deriv(l, deriv[rho], mid3, gauge[rho], rho, stpl5, sig, mid[sig]);   // :218-220
+        if (coefL != 0.0) mf_axpy(mid5[rho], coefL, mid3);                  // :224
+        mf_scale(mid3, coef7);                                              // :228
+        mf_axpy(mid3, coef5, mid[sig]);                                     // :230
+        for (int mu = 0; mu < 4; mu++) {
+          if (mu == sig || mu == rho) continue;
+          for (int nu = 0; nu < 4; nu++) {
+            if (nu == sig || nu == rho || nu == mu) continue;
+            sym_staple_deriv(l, deriv[mu], mid5[nu], gauge[mu], mu, stpl3[nu], sig, mid3);   // :239-241
+          }
+        }
+      }
+    }
+    if (have3) {
+      MF mid3(V, zero);
+      for (int mu = 0; mu < 4; mu++) {
+        if (mu == sig) continue;
+        MF stpl5(V);
+        for (int i = 0; i < V; i++) stpl5[i] = m3_scale(coef3, mid[sig][i]);
+        if (have5) mf_axpy(stpl5, 1.0, mid5[mu]);                           // :250-256
+        sym_staple_deriv(l, deriv[mu], mid3, gauge[mu], mu, gauge[sig], sig, stpl5);   // :259-261
+      }
+      mf_axpy(deriv[sig], 1.0, mid3);                                       // :265
+    }
+    if (coef1 != 0.0) mf_axpy(deriv[sig], coef1, mid[sig]);                 // :269
+  }
+  if (naik != 0.0) {                                                        // :300-326
+    for (int mu = 0; mu < 4; mu++) {
+      const MF& U = llgauge[mu];
+      const MF& M = llmid[mu];
+      const MF s1a = mf_shift(l, U, mu, +1);
+      MF tm1(V), tm2(V);
+      for (int i = 0; i < V; i++) { tm1[i] = m3_mul(m3_adj(U[i]), M[i]); tm2[i] = m3_mul(m3_adj(s1a[i]), m3_adj(U[i])); }
+      const MF sm1 = mf_shift(l, tm1, mu, -1);
+      const MF s1b = mf_shift(l, tm2, mu, +1);
+      for (int i = 0; i < V; i++) {
+        m3_axpy(llderiv[mu][i], naik, m3_mul(sm1[i], m3_adj(s1a[i])));
+        tm1[i] = m3_mul(m3_adj(U[i]), sm1[i]);
+      }
+      const MF sm2 = mf_shift(l, tm1, mu, -1);
+      for (int i = 0; i < V; i++) {
+        m3_axpy(llderiv[mu][i], naik, m3_mul(M[i], s1b[i]));
+        m3_axpy(llderiv[mu][i], naik, sm2[i]);
+      }
+    }
+  }
+}
+// fat7lDeriv(deriv, gauge, mid, coef, llderiv, llgauge, llmid, naik); ll* may be NULL when naik == 0.
+// deriv and llderiv are read, accumulated into and written back.
+void orc_fat7l_deriv(void* lat, double* deriv_, const double* gauge_, const double* mid_, const double* coef,
+                     double* llderiv_, const double* llgauge_, const double* llmid_, double naik) {
+  Lat* l = (Lat*)lat;
+  const size_t fs = (size_t)l->vol * 18;
+  MF d[4], g[4], m[4], ld[4], lg[4], lm[4];
+  for (int k = 0; k < 4; k++) {
+    d[k] = mf_load(l, deriv_ + k * fs); g[k] = mf_load(l, gauge_ + k * fs); m[k] = mf_load(l, mid_ + k * fs);
+    if (naik != 0.0) { ld[k] = mf_load(l, llderiv_ + k * fs); lg[k] = mf_load(l, llgauge_ + k * fs); lm[k] = mf_load(l, llmid_ + k * fs); }
+  }
+  fat7l_deriv(l, d, g, m, coef, ld, lg, lm, naik);
+  for (int k = 0; k < 4; k++) {
+    mf_store(l, deriv_ + k * fs, d[k]);
+    if (naik != 0.0) mf_store(l, llderiv_ + k * fs, ld[k]);
+  }
+}
+// HisqCoefs.smearGetForce -> smearedForce(dsdu, dsdsu, dsdsul), hisqsmear.nim:51-84; dsdu accumulates.
+void orc_hisq_force(void* lat, const double* u_, const double* c, const double* dsdsu_, const double* dsdsul_, double* dsdu_) {
+  Lat* l = (Lat*)lat;
+  const size_t fs = (size_t)l->vol * 18, n = fs * 4;
+  const int V = l->vol;
+  std::vector<double> v(n), w(n);
+  orc_makeImpLinks(lat, u_, c, v.data(), nullptr, 0.0, nullptr);
+  orc_projectU_field(lat, v.data(), w.data(), 4);
+  MF U[4], Vf[4], W[4], su[4], sul[4], f[4], fll[4], t[4], out[4];
+  const M3 zero = m3_scale(0.0, m3_load(u_));
+  for (int k = 0; k < 4; k++) {
+    U[k] = mf_load(l, u_ + k * fs); Vf[k] = mf_load(l, v.data() + k * fs); W[k] = mf_load(l, w.data() + k * fs);
+    su[k] = mf_load(l, dsdsu_ + k * fs); sul[k] = mf_load(l, dsdsul_ + k * fs);
+    f[k].assign(V, zero); fll[k].assign(V, zero); out[k] = mf_load(l, dsdu_ + k * fs);
+  }
+  fat7l_deriv(l, f, W, su, c + 5, fll, W, sul, c[10]);                       // asqtadDeriv :16-28
+  for (int k = 0; k < 4; k++) {
+    t[k].resize(V);
+#pragma omp parallel for
+    for (int i = 0; i < V; i++) t[k][i] = projectUderiv(W[k][i], Vf[k][i], m3_add(f[k][i], fll[k][i]));   // :77
+  }
+  fat7l_deriv(l, out, U, t, c, nullptr, nullptr, nullptr, 0.0);              // :78
+  for (int k = 0; k < 4; k++) mf_store(l, dsdu_ + k * fs, out[k]);
+}
+
+// ---------------------------------------------------------------------------
 // Fermion-force outer products (src/physics/stagD.nim:588-664; peqOuter/meqOuter
 // src/maths/matrixConcept.nim:717-724: r[i][j] +-= x[i] * conj(y[j])).
 // f = nd contiguous link-shaped fields [k][vol][18], hop of field k as in the operator.

@@ -50,6 +50,21 @@ class HisqCoefs(C.Structure):
     def smear(self, g, fl, ll):
         _ck(lib().qexb200_gauge_smear_hisq(fl.h, ll.h, g.h, C.byref(self)))
 
+    def smearGetForce(self, u, su, sul):
+        """smearGetForce(u, su, sul) (src/gauge/hisqsmear.nim:51-84): returns smearedForce(dsdu, dsdsu, dsdsul)
+        (dsdu accumulates); its .free() releases the kept fields."""
+        h = C.c_int()
+        _ck(lib().qexb200_hisq_smear_get_force(su.h, sul.h, u.h, C.byref(self), C.byref(h)))
+
+        def smearedForce(dsdu, dsdsu, dsdsul):
+            _ck(lib().qexb200_hisq_smeared_force(h.value, dsdu.h, dsdsu.h, dsdsul.h))
+
+        def free():
+            if is_initialized():
+                lib().qexb200_hisq_destroy(h.value)
+        smearedForce.free = free
+        return smearedForce
+
 
 class HypCoefs(C.Structure):
     """HypCoefs (src/gauge/hypsmear.nim:16-19,269-273): smear(g, fl)."""
@@ -106,6 +121,10 @@ def lib():
         L.qexb200_gauge_smear_hisq.argtypes = [C.c_int, C.c_int, C.c_int, C.POINTER(HisqCoefs)]
         L.qexb200_gauge_smear_hyp.argtypes = [C.c_int, C.c_int, C.POINTER(HypCoefs)]
         L.qexb200_gauge_projectU.argtypes = [C.c_int, C.c_int]
+        L.qexb200_gauge_fat7lDeriv.argtypes = [C.c_int, C.c_int, C.c_int, C.POINTER(Fat7lCoefs), C.c_int, C.c_int, C.c_int, C.c_double]
+        L.qexb200_hisq_smear_get_force.argtypes = [C.c_int, C.c_int, C.c_int, C.POINTER(HisqCoefs), ip]
+        L.qexb200_hisq_smeared_force.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int]
+        L.qexb200_hisq_destroy.argtypes = [C.c_int]
         L.qexb200_hyp_smear_get_force.argtypes = [C.c_int, C.c_int, C.POINTER(HypCoefs), ip]
         L.qexb200_hyp_smeared_force.argtypes = [C.c_int, C.c_int, C.c_int]
         L.qexb200_hyp_destroy.argtypes = [C.c_int]
@@ -573,6 +592,13 @@ def stagD2ee(s, r, x, m2):
 def stagD2oo(s, r, x, m2):
     """stagD2oo (stagD.nim:467-469)."""
     _ck(lib().qexb200_stagD2xx(s.h, ODD, _dp(r), _dp(x), m2))
+
+
+def fat7lDeriv(deriv, gauge, mid, coef, llderiv=None, llgauge=None, llmid=None, naik=0.0):
+    """fat7lDeriv (src/gauge/fat7lderiv.nim:122-335) on DeviceGauges; deriv / llderiv accumulate."""
+    _ck(lib().qexb200_gauge_fat7lDeriv(deriv.h, gauge.h, mid.h, C.byref(coef), llderiv.h if llderiv is not None else -1,
+                                       llgauge.h if llgauge is not None else -1, llmid.h if llmid is not None else -1,
+                                       float(naik)))
 
 
 def stagDeriv(s, f, x):

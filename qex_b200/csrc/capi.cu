@@ -55,6 +55,7 @@ int nccl_load() {
 static std::map<int, Gauge> g_gauges;
 static Gauge g_hf;   // staging link set of the host-field force calls
 static std::map<int, HypState> g_hyps;
+static std::map<int, HisqState> g_hisqs;
 static std::map<int, Field> g_fields;
 static int g_next_handle = 1;
 
@@ -463,6 +464,8 @@ int qexb200_finalize(void) {
   if (g_ht.ok) { cudaFree(g_ht.a.d); cudaFree(g_ht.b.d); g_ht = HostTmp(); }
   for (auto& kv : g_hyps) hyp_state_free(&kv.second);
   g_hyps.clear();
+  for (auto& kv : g_hisqs) hisq_state_free(&kv.second);
+  g_hisqs.clear();
   cg_free();
   smear_free();
   io_free();
@@ -638,6 +641,76 @@ int qexb200_gauge_smear_hyp(qexb200_gauge_t hfl, qexb200_gauge_t hg, const qexb2
   one_hop(fl, pfl); one_hop(g, pg);
   QB_CHECK(hyp_smear(pfl, pg, al));
   return links_written(fl);
+}
+// fat7lDeriv(deriv, gauge, mid, coef[, llderiv, llgauge, llmid, naik]) (fat7lderiv.nim:122-335); deriv, llderiv accumulate
+int qexb200_gauge_fat7lDeriv(qexb200_gauge_t hd, qexb200_gauge_t hg, qexb200_gauge_t hm, const qexb200_fat7l_coefs* coef,
+                             qexb200_gauge_t hld, qexb200_gauge_t hlg, qexb200_gauge_t hlm, double naik) {
+  QB_CHECK(need_ctx());
+  Gauge *d, *g, *m, *ld = nullptr, *lg = nullptr, *lm = nullptr;
+  QB_CHECK(get_gauge4(hd, &d, "fat7lDeriv(deriv)", true));
+  QB_CHECK(get_gauge4(hg, &g, "fat7lDeriv(gauge)", true));
+  QB_CHECK(get_gauge4(hm, &m, "fat7lDeriv(mid)", true));
+  if (d == g || d == m) return fail("fat7lDeriv: deriv must be its own link set");
+  const double c[5] = {coef->one_link, coef->three_staple, coef->five_staple, coef->seven_staple, coef->lepage};
+  double2 *pd[4], *pg[4], *pm[4], *pld[4], *plg[4], *plm[4];
+  one_hop(d, pd); one_hop(g, pg); one_hop(m, pm);
+  if (naik != 0.0) {
+    QB_CHECK(get_gauge4(hld, &ld, "fat7lDeriv(llderiv)", true));
+    QB_CHECK(get_gauge4(hlg, &lg, "fat7lDeriv(llgauge)", true));
+    QB_CHECK(get_gauge4(hlm, &lm, "fat7lDeriv(llmid)", true));
+    if (ld == lg || ld == lm) return fail("fat7lDeriv: llderiv must be its own link set");
+    one_hop(ld, pld); one_hop(lg, plg); one_hop(lm, plm);
+  }
+  return fat7_deriv(pd, pg, pm, c, ld ? pld : nullptr, lg ? plg : nullptr, lm ? plm : nullptr, naik);
+}
+// HisqCoefs.smearGetForce (hisqsmear.nim:51-84)
+int qexb200_hisq_smear_get_force(qexb200_gauge_t hfl, qexb200_gauge_t hll, qexb200_gauge_t hg,
+                                 const qexb200_hisq_coefs* coef, qexb200_hisq_t* out) {
+  QB_CHECK(need_ctx());
+  Gauge *fl, *ll, *g;
+  QB_CHECK(get_gauge4(hfl, &fl, "smearGetForce(su)", false));
+  QB_CHECK(get_gauge4(hll, &ll, "smearGetForce(sul)", false));
+  QB_CHECK(get_gauge4(hg, &g, "smearGetForce(u)", true));
+  if (fl == ll || fl == g || ll == g) return fail("smearGetForce: u, su and sul must be different link sets");
+  const qexb200_fat7l_coefs &a = coef->fat7first, &b = coef->fat7second;
+  const double c[11] = {a.one_link, a.three_staple, a.five_staple, a.seven_staple, a.lepage,
+                        b.one_link, b.three_staple, b.five_staple, b.seven_staple, b.lepage, coef->naik};
+  double2 *pfl[4], *pll[4], *pg[4];
+  one_hop(fl, pfl); one_hop(ll, pll); one_hop(g, pg);
+  HisqState st;
+  const int rc = hisq_smear(pfl, pll, pg, c, &st);
+  if (rc) { hisq_state_free(&st); return rc; }
+  st.gauge_handle = hg;
+  QB_CHECK(links_written(fl));
+  QB_CHECK(links_written(ll));
+  const int h = g_next_handle++;
+  g_hisqs[h] = st;
+  *out = h;
+  return 0;
+}
+int qexb200_hisq_smeared_force(qexb200_hisq_t hs, qexb200_gauge_t hdu, qexb200_gauge_t hdsu, qexb200_gauge_t hdsul) {
+  QB_CHECK(need_ctx());
+  auto it = g_hisqs.find(hs);
+  if (it == g_hisqs.end()) return fail("invalid smearing-state handle %d", hs);
+  Gauge *du, *dsu, *dsul, *g;
+  QB_CHECK(get_gauge4(hdu, &du, "smearedForce(dsdu)", true));
+  QB_CHECK(get_gauge4(hdsu, &dsu, "smearedForce(dsdsu)", true));
+  QB_CHECK(get_gauge4(hdsul, &dsul, "smearedForce(dsdsul)", true));
+  if (du == dsu || du == dsul) return fail("smearedForce: dsdu must be its own link set");
+  if (get_gauge(it->second.gauge_handle, &g) != 0 || link_field(g, 0) != it->second.u[0])
+    return fail("smearedForce: the thin links the state was built from are gone");
+  double2 *p0[4], *p1[4], *p2[4];
+  one_hop(du, p0); one_hop(dsu, p1); one_hop(dsul, p2);
+  return hisq_force(it->second, p0, p1, p2);
+}
+int qexb200_hisq_destroy(qexb200_hisq_t hs) {
+  QB_CHECK(need_ctx());
+  auto it = g_hisqs.find(hs);
+  if (it == g_hisqs.end()) return fail("invalid smearing-state handle %d", hs);
+  cudaStreamSynchronize(g_ctx.stream);
+  hisq_state_free(&it->second);
+  g_hisqs.erase(it);
+  return 0;
 }
 // smearGetForce (hypsmear.nim:49-162): smear AND keep what smearedForce needs
 int qexb200_hyp_smear_get_force(qexb200_gauge_t hfl, qexb200_gauge_t hg, const qexb200_hyp_coefs* coef, qexb200_hyp_t* out) {

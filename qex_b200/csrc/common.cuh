@@ -243,7 +243,19 @@ void free_compressed(Gauge& g);
 // ---- smear.cu (device link pipeline; matrix field = double2[2][9][Vh]) -------
 int make_imp_links(double2* const fl[4], const double2* const gf[4], const double coef[5], double2* const ll[4],
                    const double2* const gfl[4], double naik);
-int hisq_smear(double2* const fl[4], double2* const ll[4], const double2* const g[4], const double c[11]);
+// what HisqCoefs.smearGetForce keeps (hisqsmear.nim:60-71): v = first fat7, w = projectU(v); u by reference
+struct HisqState {
+  double2 *v[4] = {}, *w[4] = {};
+  const double2* u[4] = {};
+  double c[11] = {};
+  int gauge_handle = -1;
+  bool live = false;
+};
+int hisq_smear(double2* const fl[4], double2* const ll[4], const double2* const g[4], const double c[11], HisqState* st = nullptr);
+int hisq_force(const HisqState& st, double2* const dsdu[4], const double2* const dsdsu[4], const double2* const dsdsul[4]);
+void hisq_state_free(HisqState* st);
+int fat7_deriv(double2* const deriv[4], const double2* const gauge[4], const double2* const mid[4], const double coef[5],
+               double2* const llderiv[4], const double2* const llgauge[4], const double2* const llmid[4], double naik);
 // what smearGetForce keeps for smearedForce (hypsmear.nim:62-75): projected and unprojected fields of each level
 struct HypState {
   double2 *l1[4][4] = {}, *l2[4][4] = {}, *l1x[4][4] = {}, *l2x[4][4] = {}, *flx[4] = {};

@@ -342,6 +342,17 @@ QB_HD void staple_deriv_x(M3& f1, M3& f2, const double2* g1, int d1, const doubl
     m3_axpy(f2, 1.0, a);
   }
 }
+// Naik term of fat7lDeriv (src/gauge/fat7lderiv.nim:300-326), gathered in place; U = llgauge[mu], M = llmid[mu]:
+//   (U^+ M)(x-mu) U(x+mu)^+  +  M(x) (U(x+mu) U(x+2mu))^+  +  U(x-mu)^+ U(x-2mu)^+ M(x-2mu)
+template <bool MR>
+QB_HD M3 naik_deriv_x(const double2* U, const double2* M, int mu, const LSite& s, const int* X, int Vh, const Peers& pr) {
+  const LSite sp = lhop(s, mu, +1, X), spp = lhop(sp, mu, +1, X), sm = lhop(s, mu, -1, X), smm = lhop(sm, mu, -1, X);
+  const M3 Um = m3_ldx<MR>(U, sm, Vh, pr), Up = m3_ldx<MR>(U, sp, Vh, pr);
+  M3 r = m3_mul_na(m3_mul_an(Um, m3_ldx<MR>(M, sm, Vh, pr)), Up);
+  m3_axpy(r, 1.0, m3_mul_na(m3_ld(M, s, Vh), m3_mul(Up, m3_ldx<MR>(U, spp, Vh, pr))));
+  m3_axpy(r, 1.0, m3_mul_an(Um, m3_mul_an(m3_ldx<MR>(U, smm, Vh, pr), m3_ldx<MR>(M, smm, Vh, pr))));
+  return r;
+}
 // projectTAH, src/maths/matrixFunctions.nim:375-380: (x - x^+)/2 minus its trace / 3
 QB_HD M3 project_tah(const M3& x) {
   M3 r;

@@ -382,16 +382,29 @@ int make_imp_links(double2* const fl[4], const double2* const gf[4], const doubl
 
 // ---- HisqCoefs.smear, hisqLinks.nim:32-39 -------------------------------------------------------
 // c = {fat7first[5], fat7second[5], naik}
-int hisq_smear(double2* const fl[4], double2* const ll[4], const double2* const g[4], const double c[11]) {
+void hisq_state_free(HisqState* st) {
+  if (!st->live) return;
+  for (int d = 3; d >= 0; d--) { pool_put(st->w[d]); pool_put(st->v[d]); }
+  *st = HisqState();
+}
+// st != nullptr (smearGetForce, hisqsmear.nim:51-71): keeps v (first fat7) and w (its projection)
+int hisq_smear(double2* const fl[4], double2* const ll[4], const double2* const g[4], const double c[11], HisqState* st) {
   Tmp t1[4], t2[4];
-  double2* p1[4]; const double2* cp2[4];
-  for (int d = 0; d < 4; d++) { QB_CHECK(t1[d].get()); p1[d] = t1[d].p; }
+  double2 *p1[4], *p2[4]; const double2* cp2[4];
+  if (st) {
+    if (st->live) hisq_state_free(st);
+    for (int d = 0; d < 4; d++) { QB_CHECK(pool_get(&st->v[d])); QB_CHECK(pool_get(&st->w[d])); p1[d] = st->v[d]; p2[d] = st->w[d]; st->u[d] = g[d]; }
+    for (int k = 0; k < 11; k++) st->c[k] = c[k];
+    st->live = true;
+  } else {
+    for (int d = 0; d < 4; d++) { QB_CHECK(t1[d].get()); p1[d] = t1[d].p; }
+  }
   QB_CHECK(make_imp_links(p1, g, c, nullptr, nullptr, 0.0));
   for (int d = 0; d < 4; d++) {
-    QB_CHECK(t2[d].get());
-    QB_CHECK(project_fields(t2[d].p, t1[d].p, 1));
-    t1[d].drop();
-    cp2[d] = t2[d].p;
+    if (!st) { QB_CHECK(t2[d].get()); p2[d] = t2[d].p; }
+    QB_CHECK(project_fields(p2[d], p1[d], 1));
+    if (!st) t1[d].drop();
+    cp2[d] = p2[d];
   }
   return make_imp_links(fl, cp2, c + 5, ll, cp2, c[10]);
 }
@@ -499,10 +512,12 @@ __global__ void __launch_bounds__(SB) k_proj_deriv(const ProjDerivArgs a) {
   if (t >= 2 * a.Vh) return;
   LSite s; s.par = t / a.Vh; s.idx = t - s.par * a.Vh; s.nb = NB_HOME;
   const M3 r = project_u_deriv(m3_ld(a.x, s, a.Vh), m3_ld(a.chain, s, a.Vh));
-  M3 o = m3_zero();
-  if (a.acc) o = m3_ld(a.f, s, a.Vh);
-  m3_axpy(o, a.s_f, r);
-  m3_st(a.f, s, a.Vh, o);
+  if (a.f) {
+    M3 o = m3_zero();
+    if (a.acc) o = m3_ld(a.f, s, a.Vh);
+    m3_axpy(o, a.s_f, r);
+    m3_st(a.f, s, a.Vh, o);
+  }
   M3 k = m3_zero();
   m3_axpy(k, a.s_keep, r);
   m3_st(a.keep, s, a.Vh, k);
@@ -599,6 +614,130 @@ int hyp_force(const HypState& st, double2* const f[4], const double2* const chai
     QB_CHECK(launch_deriv(f[nu], f[mu], st.g[nu], nu, st.g[mu], mu, fl1[mu][nu].p));
   }
   return xbarrier();
+}
+
+// ---- fat7lDeriv, src/gauge/fat7lderiv.nim:122-335 -----------------------------------------------------------
+// Like the reference, built from symStaple (k_staple) and symStapleDeriv (k_staple_deriv); the two 7-staple
+// pairs and the Lepage term of one (sig, rho) go into stpl5 in ONE launch.  deriv / llderiv accumulate.
+template <bool MR>
+__global__ void __launch_bounds__(SB) k_naik_deriv(double2* out, const double2* U, const double2* M, int mu, double naik,
+                                                    int X0, int X1, int X2, int X3, int Vh, const Peers pr) {
+  const int par = blockIdx.x & 1, idx = (blockIdx.x >> 1) * SB + threadIdx.x;
+  if (idx >= Vh) return;
+  const int X[4] = {X0, X1, X2, X3};
+  const LSite s = lsite(idx, par, X);
+  M3 o = m3_ld(out, s, Vh);
+  m3_axpy(o, naik, naik_deriv_x<MR>(U, M, mu, s, X, Vh, pr));
+  m3_st(out, s, Vh, o);
+}
+// local whole-field updates between the launches; on a split lattice the peers may still be reading the
+// field from their previous launch, so the ranks are lined up first
+static int field_sync() { return multi() ? xbarrier() : 0; }
+static int field_zero(double2* f) {
+  QB_CHECK(field_sync());
+  QB_CUDA(cudaMemsetAsync(f, 0, sizeof(double2) * 18 * (size_t)ctx().g.Vh, ctx().stream));
+  return 0;
+}
+static int field_axpy(double2* y, double a, const double2* x) { QB_CHECK(field_sync()); return blas_axpy(y, a, x, (size_t)18 * ctx().g.Vh); }
+static int field_axpby(double2* y, double a, const double2* x, double b) { QB_CHECK(field_sync()); return blas_axpby(y, a, x, b, (size_t)18 * ctx().g.Vh); }
+
+int fat7_deriv(double2* const deriv[4], const double2* const gauge[4], const double2* const mid[4], const double coef[5],
+               double2* const llderiv[4], const double2* const llgauge[4], const double2* const llmid[4], double naik) {
+  Context& c = ctx();
+  QB_CHECK(mr_begin(&g_peers, {gauge[0], gauge[1], gauge[2], gauge[3], mid[0], mid[1], mid[2], mid[3],
+                               deriv[0], deriv[1], deriv[2], deriv[3]}));
+  for (int d = 0; d < 4; d++)
+    if (c.g.X[d] < 4) return fail("fat7lDeriv: local extent %d in direction %d is below 4", c.g.X[d], d);
+  const double coefL = coef[4], coef1 = coef[0] - 6 * coefL, coef3 = coef[1], coef5 = coef[2], coef7 = coef[3];
+  const bool have5 = coef5 != 0.0 || coef7 != 0.0 || coefL != 0.0;
+  const bool have3 = coef3 != 0.0 || have5;
+  Tmp stpl3[4], mid5[4], stpl5, mid3;
+  if (have3) { QB_CHECK(stpl5.get()); QB_CHECK(mid3.get()); }
+  for (int sig = 0; sig < 4; sig++) {
+    if (have5) {
+      for (int mu = 0; mu < 4; mu++) {
+        if (mu == sig) continue;
+        QB_CHECK(stpl3[mu].get()); QB_CHECK(mid5[mu].get());
+        StapleArgs a = staple_args(sig);                                    // :185-186
+        a.t[0] = {gauge[mu], gauge[sig], mu, 1.0};
+        a.out = stpl3[mu].p;
+        QB_CHECK(launch_staple(a, 1, false));
+        QB_CHECK(field_zero(mid5[mu].p));
+      }
+      for (int rho = 0; rho < 4; rho++) {
+        if (rho == sig) continue;
+        int m1 = -1, n1 = -1;                                               // the two directions besides sig, rho
+        for (int d = 0; d < 4; d++) if (d != sig && d != rho) { if (m1 < 0) m1 = d; else n1 = d; }
+        if (coef7 != 0.0) {                                                 // :195-212
+          StapleArgs a = staple_args(sig);
+          a.t[0] = {gauge[n1], stpl3[m1].p, n1, coef7};
+          a.t[1] = {gauge[m1], stpl3[n1].p, m1, coef7};
+          if (coefL != 0.0) { a.base = stpl3[rho].p; a.cbase = coefL; }
+          a.out = stpl5.p;
+          QB_CHECK(launch_staple(a, 2, false));
+        } else if (coefL != 0.0) {
+          QB_CHECK(field_sync());
+          QB_CHECK(scale_field(stpl5.p, stpl3[rho].p, coefL));
+        }
+        QB_CHECK(field_zero(mid3.p));
+        if (coefL != 0.0 || coef7 != 0.0)                                   // :218-220
+          QB_CHECK(launch_deriv(deriv[rho], mid3.p, gauge[rho], rho, stpl5.p, sig, mid[sig]));
+        if (coefL != 0.0) QB_CHECK(field_axpy(mid5[rho].p, coefL, mid3.p)); // :224
+        QB_CHECK(field_axpby(mid3.p, coef5, mid[sig], coef7));              // :228-230
+        QB_CHECK(launch_deriv(deriv[m1], mid5[n1].p, gauge[m1], m1, stpl3[n1].p, sig, mid3.p));   // :239-241
+        QB_CHECK(launch_deriv(deriv[n1], mid5[m1].p, gauge[n1], n1, stpl3[m1].p, sig, mid3.p));
+      }
+    }
+    if (have3) {
+      QB_CHECK(field_zero(mid3.p));
+      for (int mu = 0; mu < 4; mu++) {
+        if (mu == sig) continue;
+        QB_CHECK(field_sync());
+        QB_CHECK(scale_field(stpl5.p, mid[sig], coef3));                    // :250-256
+        if (have5) QB_CHECK(blas_axpy(stpl5.p, 1.0, mid5[mu].p, (size_t)18 * c.g.Vh));
+        QB_CHECK(launch_deriv(deriv[mu], mid3.p, gauge[mu], mu, gauge[sig], sig, stpl5.p));   // :259-261
+      }
+      QB_CHECK(field_axpy(deriv[sig], 1.0, mid3.p));                        // :265
+    }
+    if (coef1 != 0.0) QB_CHECK(field_axpy(deriv[sig], coef1, mid[sig]));    // :269
+  }
+  if (naik != 0.0) {                                                        // :300-326
+    if (!llderiv || !llgauge || !llmid) return fail("fat7lDeriv: naik != 0 needs the long-link fields");
+    const int grid = grid_par(c.g.Vh, SB);
+    for (int mu = 0; mu < 4; mu++) {
+      if (multi()) {
+        if (!in_arena(llgauge[mu]) || !in_arena(llmid[mu])) return fail("fat7lDeriv on a split lattice: a long-link field lives outside the peer arena");
+        QB_CHECK(xbarrier());
+        k_naik_deriv<true><<<grid, SB, 0, c.stream>>>(llderiv[mu], llgauge[mu], llmid[mu], mu, naik, c.g.X[0], c.g.X[1], c.g.X[2], c.g.X[3], c.g.Vh, g_peers);
+      } else {
+        k_naik_deriv<false><<<grid, SB, 0, c.stream>>>(llderiv[mu], llgauge[mu], llmid[mu], mu, naik, c.g.X[0], c.g.X[1], c.g.X[2], c.g.X[3], c.g.Vh, g_peers);
+      }
+      count_launch();
+    }
+    QB_CUDA(cudaGetLastError());
+  }
+  return xbarrier();
+}
+
+// smearedForce(dsdu, dsdsu, dsdsul), hisqsmear.nim:73-80: second fat7 (+ Naik) -> projectUderiv -> first fat7.
+// dsdu accumulates (fat7lDeriv's +=).
+int hisq_force(const HisqState& st, double2* const dsdu[4], const double2* const dsdsu[4], const double2* const dsdsul[4]) {
+  Context& c = ctx();
+  if (!st.live) return fail("HISQ smeared force: the smearing state is empty");
+  Tmp f[4], fll[4];
+  double2 *pf[4], *pl[4]; const double2 *cw[4], *ct[4];
+  for (int d = 0; d < 4; d++) {
+    QB_CHECK(f[d].get()); QB_CHECK(fll[d].get());
+    QB_CHECK(field_zero(f[d].p)); QB_CHECK(field_zero(fll[d].p));
+    pf[d] = f[d].p; pl[d] = fll[d].p; cw[d] = st.w[d];
+  }
+  QB_CHECK(fat7_deriv(pf, cw, dsdsu, st.c + 5, pl, cw, dsdsul, st.c[10]));   // asqtadDeriv :16-28
+  for (int d = 0; d < 4; d++) {
+    if (st.c[10] != 0.0) QB_CHECK(blas_axpy(pf[d], 1.0, pl[d], (size_t)18 * c.g.Vh));
+    QB_CHECK(launch_proj_deriv(st.v[d], pf[d], pf[d], 1.0, nullptr, 0.0, false));   // :77
+    ct[d] = pf[d];
+  }
+  return fat7_deriv(dsdu, st.u, ct, st.c, nullptr, nullptr, nullptr, 0.0);   // :78
 }
 
 // projTAH(f, g, adj) (src/stagg_pv_hmc/staghmc_spv_gforce.nim:256-291): f[mu] := projectTAH(f[mu] g[mu]^+), or of

@@ -48,6 +48,18 @@ void emu_staple_deriv_field(double* f1, double* f2, const double* g1, int d1, co
       m3_st((double2*)f2, s, Vh, b);
     }
 }
+// out += naik * naik-derivative(U, M) in direction mu
+void emu_naik_deriv_field(double* out, const double* U, const double* M, int mu, double naik, const int* X) {
+  const int Vh = X[0] * X[1] * X[2] * X[3] / 2;
+  Peers none; none.me = 0;
+  for (int par = 0; par < 2; par++)
+    for (int idx = 0; idx < Vh; idx++) {
+      const LSite s = lsite(idx, par, X);
+      M3 o = m3_ld((const double2*)out, s, Vh);
+      m3_axpy(o, naik, naik_deriv_x<false>((const double2*)U, (const double2*)M, mu, s, X, Vh, none));
+      m3_st((double2*)out, s, Vh, o);
+    }
+}
 void emu_project_tah_field(const double* in, const int* X, double* out) {
   const int Vh = X[0] * X[1] * X[2] * X[3] / 2;
   for (int par = 0; par < 2; par++)

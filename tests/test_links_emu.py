@@ -28,6 +28,7 @@ def emu():
     lib.emu_project_u_deriv_field.argtypes = [dp, dp, ip, dp]
     lib.emu_staple_deriv_field.argtypes = [dp, dp, dp, C.c_int, dp, C.c_int, dp, ip]
     lib.emu_project_tah_field.argtypes = [dp, ip, dp]
+    lib.emu_naik_deriv_field.argtypes = [dp, dp, dp, C.c_int, C.c_double, ip]
     return lib
 
 
@@ -151,3 +152,17 @@ def test_project_tah(emu):
     w = w - np.einsum("xaa->x", w)[:, None, None] / 3.0 * np.eye(3)
     got = from_dev(out)
     assert np.abs(got[..., 0] + 1j * got[..., 1] - w).max() < 1e-15
+
+
+def test_naik_deriv_matches_oracle(emu):
+    """Naik term of fat7lDeriv (fat7lderiv.nim:300-326): oracle with every fat coefficient zero."""
+    lat = oracle.Lattice(L)
+    g = lat.random_gauge(lat.new_rng(9))
+    mid = np.random.default_rng(5).standard_normal(g.shape)
+    d, ld = lat.gauge(4), lat.gauge(4)
+    lat.fat7lDeriv(d, g, mid, (0.0, 0.0, 0.0, 0.0, 0.0), ld, g, mid, 0.3)
+    X = (C.c_int * 4)(*L)
+    for mu in range(4):
+        out = np.zeros_like(to_dev(g[mu]))
+        emu.emu_naik_deriv_field(dp(out), dp(to_dev(g[mu])), dp(to_dev(mid[mu])), mu, 0.3, X)
+        assert np.linalg.norm(from_dev(out) - ld[mu]) / np.linalg.norm(ld[mu]) < 1e-14, mu

@@ -20,6 +20,11 @@ for _ in range(reps):
         qb.timer_start(); qb.HisqCoefs().init().smear(g, fl, ll); print("hisq ms", qb.timer_stop())
     if "nhyp" in which:
         qb.timer_start(); qb.HypCoefs(0.4, 0.5, 0.5).smear(g, fl); print("nhyp ms", qb.timer_stop())
+    if "hypforce" in which:
+        f = qb.DeviceGauge(nlinks=4); f.zero()
+        force = qb.HypCoefs(0.4, 0.5, 0.5).smearGetForce(g, fl)
+        qb.timer_start(); force(f, ll if "hisq" in which else fl); print("nhyp smearedForce ms", qb.timer_stop())
+        force.free(); f.free()
     if "force" in which:
         x, c = qb.DeviceField(gaussian_vector(vol, 1)), qb.DeviceField(gaussian_vector(vol, 2))
         s = qb.newStag(g)
