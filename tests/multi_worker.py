@@ -205,6 +205,26 @@ def links_case(L, G, inner, rank, world, local_rank, dist):
         w = mine(wfl[mu])
         site = np.linalg.norm((gfl[mu] - w).reshape(w.shape[0], -1), axis=1) / np.linalg.norm(w.reshape(w.shape[0], -1), axis=1)
         assert np.median(site) < 1e-14, (mu, float(np.median(site)))
+    if int(os.environ.get("QEXB200_ARENA_FIELDS", "64")) >= 100:
+        # fat7lDeriv and the HISQ smearedForce on the split lattice (fat7lderiv.nim:122-335, hisqsmear.nim:51-84), on
+        # links near the unit gauge so that the chain is well conditioned and the bar can be tight
+        gs = lat.projectU(lat.unit_gauge() + 0.15 * np.random.default_rng(8).standard_normal(g.shape))
+        lat.setBC(gs); lat.stagPhase(gs)
+        rr = np.random.default_rng(3)
+        ch, chl = rr.standard_normal(g.shape), rr.standard_normal(g.shape)
+        wantf = lat.hisq_force(gs, oracle.hisq_coefs(), ch, chl)
+        dgs = qb.DeviceGauge([mine(gs[k]) for k in range(4)])
+        su, sul, du = qb.DeviceGauge(nlinks=4), qb.DeviceGauge(nlinks=4), qb.DeviceGauge(nlinks=4)
+        dch, dchl = qb.DeviceGauge([mine(ch[k]) for k in range(4)]), qb.DeviceGauge([mine(chl[k]) for k in range(4)])
+        hforce = qb.HisqCoefs().init().smearGetForce(dgs, su, sul)
+        du.zero()
+        hforce(du, dch, dchl)
+        gotf = down(du)
+        res["hisq_force"] = max(rel_l2(gotf[mu], mine(wantf[mu])) for mu in range(4))
+        assert res["hisq_force"] <= 1e-12, res
+        hforce.free()
+        for d in (dgs, su, sul, du, dch, dchl):
+            d.free()
     # fat + Lepage only (all five coefficients), tight bar: no projection in between
     c5 = (1.0, -1 / 16., 1 / 64., -1 / 384., -1 / 8.)
     w5, w5l = lat.makeImpLinks(gp, c5, gfLong=gp, naik=-1 / 24.)
