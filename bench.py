@@ -351,7 +351,7 @@ def run_ours(args):
         # on several GPUs: link-shaped fields in the peer-mapped arena, neighbours read over NVLink (csrc/smear.cu)
         try:
             lp = link_pipeline_leg(qb, nsites, peak, rank, cpu=(world == 1 and not args.no_cpu))
-            for k in ("hisq", "nhyp", "nhyp_force"):
+            for k in ("hisq", "nhyp", "nhyp_force", "hisq_force"):
                 lp[k]["ms"] = maxreduce(lp[k]["ms"])
                 gbs = 1e-9 * nsites * lp[k]["algorithmic_bytes_per_site"] / (1e-3 * lp[k]["ms"])
                 lp[k]["achieved_gbs"], lp[k]["frac_of_hbm_peak"] = gbs, gbs / peak
@@ -375,6 +375,10 @@ def run_ours(args):
 # distinct field a launch reads counted once, every field it writes once.
 HYP_PASSES = 12 * 3 + 12 * 6 + 4 * 8
 HYP_FORCE_PASSES = 24 + 4 * 4 + 12 * 7 + 12 * 5 + 24 * 7 + 12 * 5 + 12 * 7     # smearedForce alone
+# fat7lDeriv, passes per direction sig: 3 staples (3) + 3 zeroings; per rho: stpl5 (6) + zero + deriv (7) + axpy (3) +
+# axpby (3) + 2 derivs (14); 3-staple part: zero + 3 x (scale 2 + axpy 3 + deriv 7) + 2 axpy (6)
+FAT7_DERIV_PASSES = 4 * (12 + 3 * 34 + 1 + 3 * 12 + 6)
+HISQ_FORCE_PASSES = 2 * FAT7_DERIV_PASSES - 4 * 3 * 3 + 16 + 8 + 4 * 3 + 4 * 3
 HISQ_PASSES = 4 * (3 * (5 + 10 + 6) - 1) + 4 * (3 * (5 + 10 + 8) - 1) + 4 * 2 + 4 * 2
 
 
@@ -409,6 +413,22 @@ def link_pipeline_leg(qb, nsites, peak, rank, cpu=True, reps=3):
     out["nhyp_force"] = {"ms": ms, "launches": qb.launch_count() // reps, "algorithmic_bytes_per_site": HYP_FORCE_PASSES * 144,
                          "achieved_gbs": gbs, "frac_of_hbm_peak": gbs / peak}
     force.free()
+    # HISQ: smearGetForce + smearedForce (hisqsmear.nim:51-84): second fat7 + Naik derivative, projectUderiv, first fat7
+    hforce = hc.smearGetForce(g, fl, ll)
+    du, c1, c2 = qb.DeviceGauge(nlinks=4), qb.DeviceGauge(nlinks=4), qb.DeviceGauge(nlinks=4)
+    du.zero(); c1.projectU(fl); c2.projectU(fl)          # any non-trivial chain fields will do for timing
+    for it in range(reps + 1):
+        if it == 1:
+            qb.sync(); qb.launch_count(reset=True); qb.timer_start()
+        hforce(du, c1, c2)
+    ms = qb.timer_stop() / reps
+    gbs = 1e-9 * nsites * HISQ_FORCE_PASSES * 144 / (1e-3 * ms)
+    out["hisq_force"] = {"ms": ms, "launches": qb.launch_count() // reps, "algorithmic_bytes_per_site": HISQ_FORCE_PASSES * 144,
+                         "achieved_gbs": gbs, "frac_of_hbm_peak": gbs / peak}
+    hforce.free()
+    for d in (du, c1, c2):
+        d.free()
+    yc.smear(g, fl)
     out["plaq_smeared"] = [float(t) for t in fl.plaq()]
     for d in (g, fl, ll):
         d.free()
