@@ -299,6 +299,11 @@ typedef struct {
 int qexb200_plan_halo(const int latsize[4], const int rankgeom[4], int myrank, int nlinks,
                       qexb200_halo_dir out[4], int* ndirs, long long* total_elems);
 
+/* Peer table of the multi-rank link pipeline (pure host arithmetic): peer_of[nb] = rank owning the sites that are
+ * disp_d in {-1, 0, +1} rank-grid steps away in direction d, nb = sum_d (disp_d + 1) 3^d (40 = this rank), periodic,
+ * ranks numbered as in qexb200_init.  A site whose neighbour lies there reads it from that rank's arena. */
+int qexb200_plan_peers(const int latsize[4], const int rankgeom[4], int myrank, unsigned char peer_of[81]);
+
 /* ---- measurement helpers (CUDA events on the library's compute stream) ---- */
 
 int qexb200_sync(void);

@@ -168,6 +168,7 @@ def lib():
         L.qexb200_dev_stagD2xx.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_double]
         L.qexb200_dev_solveXX.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, spp]
         L.qexb200_dev_solve.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, spp]
+        L.qexb200_plan_peers.argtypes = [ip, ip, C.c_int, C.POINTER(C.c_ubyte)]
         L.qexb200_plan_halo.argtypes = [ip, ip, C.c_int, C.c_int, C.POINTER(HaloDir), ip, C.POINTER(C.c_longlong)]
         L.qexb200_timer_stop.argtypes = [C.POINTER(C.c_float)]
         L.qexb200_launch_count.restype = C.c_longlong
@@ -248,6 +249,13 @@ def plan_halo(latsize, rankgeom, myrank, nlinks):
     n, tot = C.c_int(), C.c_longlong()
     _ck(lib().qexb200_plan_halo(_i4(latsize), _i4(rankgeom), int(myrank), int(nlinks), out, C.byref(n), C.byref(tot)))
     return [dict((f[0], getattr(out[i], f[0])) for f in HaloDir._fields_) for i in range(n.value)], tot.value
+
+
+def plan_peers(latsize, rankgeom, myrank):
+    """peer_of[81] of one rank (pure host arithmetic, works without a GPU)."""
+    out = (C.c_ubyte * 81)()
+    _ck(lib().qexb200_plan_peers(_i4(latsize), _i4(rankgeom), int(myrank), out))
+    return list(out)
 
 
 def finalize():

@@ -416,6 +416,15 @@ int qexb200_init(const int latsize[4], const int rankgeom[4], int myrank, int de
   return 0;
 }
 
+int qexb200_plan_peers(const int latsize[4], const int rankgeom[4], int myrank, unsigned char peer_of[81]) {
+  clear_error();
+  Geom g;
+  QB_CHECK(make_geom(latsize, rankgeom, myrank, &g));
+  if (g.nranks > XR_MAXR) return fail("plan_peers: at most %d ranks (one box)", XR_MAXR);
+  plan_peers(g, peer_of);
+  return 0;
+}
+
 int qexb200_plan_halo(const int latsize[4], const int rankgeom[4], int myrank, int nlinks,
                       qexb200_halo_dir out[4], int* ndirs, long long* total_elems) {
   clear_error();

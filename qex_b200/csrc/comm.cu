@@ -142,18 +142,22 @@ void links_free(double2* p, int nfields, bool arena) {
   const size_t i = (size_t)(reinterpret_cast<char*>(p) - (c.win + c.arena_off)) / c.arena_unit;
   for (int j = 0; j < nfields && i + j < c.arena_used.size(); j++) c.arena_used[i + j] = 0;
 }
+// rank that owns the sites displaced by nb = sum_d (disp_d + 1) 3^d rank-grid steps from this rank (periodic)
+void plan_peers(const Geom& g, unsigned char peer_of[81]) {
+  for (int nb = 0; nb < 81; nb++) {
+    int t = nb, r = 0, rc[4];
+    for (int d = 0; d < 4; d++) { const int disp = t % 3 - 1; t /= 3; rc[d] = ((g.rc[d] + disp) % g.G[d] + g.G[d]) % g.G[d]; }
+    for (int d = 0; d < 4; d++) r = r * g.G[d] + rc[d];   // dimension 0 slowest (qlayout.nim:94-113)
+    peer_of[nb] = (unsigned char)r;
+  }
+}
 int peers_fill(Peers* pr) {
   Context& c = ctx();
   if (!c.p2p) return fail("this operation on a lattice split over ranks needs the peer-memory transport (qexb200_p2p_attach)");
   memset(pr, 0, sizeof *pr);
   for (int r = 0; r < c.g.nranks; r++) pr->base[r] = c.peer_win[r] + c.arena_off;
   pr->me = c.g.rank;
-  for (int nb = 0; nb < 81; nb++) {
-    int t = nb, r = 0, rc[4];
-    for (int d = 0; d < 4; d++) { const int disp = t % 3 - 1; t /= 3; rc[d] = ((c.g.rc[d] + disp) % c.g.G[d] + c.g.G[d]) % c.g.G[d]; }
-    for (int d = 0; d < 4; d++) r = r * c.g.G[d] + rc[d];   // dimension 0 slowest (qlayout.nim:94-113)
-    pr->peer_of[nb] = (unsigned char)r;
-  }
+  plan_peers(c.g, pr->peer_of);
   return 0;
 }
 // Cross-rank barrier on the compute stream: one warp pushes a sequence word into every peer's LL slot and

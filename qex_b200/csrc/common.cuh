@@ -299,6 +299,7 @@ int p2p_free();
 int links_alloc(int nfields, double2** out, bool* in_arena);
 void links_free(double2* p, int nfields, bool in_arena);
 bool in_arena(const void* p);
+void plan_peers(const Geom& g, unsigned char peer_of[81]);
 int peers_fill(Peers* pr);          // kernel-side view of the arena (needs qexb200_p2p_attach)
 int xbarrier();                     // all ranks' earlier work on the compute stream is complete and visible
 int halo_begin(const Gauge& g);

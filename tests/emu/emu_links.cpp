@@ -25,6 +25,23 @@ void emu_project_field(const double* in, const int* X, double* out) {
       m3_st((double2*)out, s, Vh, project_u(m3_ld((const double2*)in, s, Vh)));
     }
 }
+// One rank of a split lattice: arenas = the nranks per-rank buffers (same layout on every rank), fields given as
+// byte offsets into the arena; a site's off-rank neighbours are read from the owner's arena (m3_ldx<true>).
+void emu_staple_field_mr(char* const* arenas, int nranks, int me, const unsigned char* peer_of, long long offG,
+                         long long offL, int dG, int dL, const int* X, double* out) {
+  const int Vh = X[0] * X[1] * X[2] * X[3] / 2;
+  Peers pr;
+  for (int r = 0; r < nranks; r++) pr.base[r] = arenas[r];
+  for (int k = 0; k < 81; k++) pr.peer_of[k] = peer_of[k];
+  pr.me = me;
+  const double2* G = (const double2*)(arenas[me] + offG);
+  const double2* L = (const double2*)(arenas[me] + offL);
+  for (int par = 0; par < 2; par++)
+    for (int idx = 0; idx < Vh; idx++) {
+      const LSite s = lsite(idx, par, X);
+      m3_st((double2*)out, s, Vh, staple_pair_x<true>(G, L, dG, dL, s, X, Vh, pr));
+    }
+}
 // out = projectUderiv(x, chain) site by site
 void emu_project_u_deriv_field(const double* x, const double* chain, const int* X, double* out) {
   const int Vh = X[0] * X[1] * X[2] * X[3] / 2;

@@ -28,6 +28,8 @@ def emu():
     lib.emu_project_u_deriv_field.argtypes = [dp, dp, ip, dp]
     lib.emu_staple_deriv_field.argtypes = [dp, dp, dp, C.c_int, dp, C.c_int, dp, ip]
     lib.emu_project_tah_field.argtypes = [dp, ip, dp]
+    lib.emu_staple_field_mr.argtypes = [C.POINTER(C.c_char_p), C.c_int, C.c_int, C.POINTER(C.c_ubyte), C.c_longlong,
+                                        C.c_longlong, C.c_int, C.c_int, ip, dp]
     lib.emu_naik_deriv_field.argtypes = [dp, dp, dp, C.c_int, C.c_double, ip]
     return lib
 
@@ -166,3 +168,39 @@ def test_naik_deriv_matches_oracle(emu):
         out = np.zeros_like(to_dev(g[mu]))
         emu.emu_naik_deriv_field(dp(out), dp(to_dev(g[mu])), dp(to_dev(mid[mu])), mu, 0.3, X)
         assert np.linalg.norm(from_dev(out) - ld[mu]) / np.linalg.norm(ld[mu]) < 1e-14, mu
+
+
+@pytest.mark.parametrize("G", [(1, 1, 1, 2), (1, 1, 2, 2), (2, 1, 1, 2)])
+def test_split_lattice_staple_reads_the_right_peer(emu, qb, G):
+    """The multi-rank path of the staple gather (m3_ldx<MR>, LSite.nb, qexb200_plan_peers) on the host: every rank's
+    arena is a host buffer, off-rank neighbours (incl. the corner x - nu + mu two ranks away) must come from the
+    owner's buffer.  Compared with the oracle's global 3-staple."""
+    Lg = (8, 4, 8, 8)
+    lat = oracle.Lattice(Lg)
+    g = lat.random_gauge(lat.new_rng(21))
+    want = lat.makeImpLinks(g, (0.0, 1.0, 0.0, 0.0, 0.0))
+    lo = oracle.QexLayout(Lg, G, (1, 1, 1, 1))
+    nr = int(np.prod(G))
+    X = [Lg[d] // G[d] for d in range(4)]
+    vloc = int(np.prod(X))
+    # per-rank arenas: 4 fields in the device layout, back to back
+    arenas = []
+    for r in range(nr):
+        fields = [to_dev(lo.scatter(g[mu])[r].reshape(vloc, 3, 3, 2)) for mu in range(4)]
+        arenas.append(np.ascontiguousarray(np.stack(fields)))
+    fbytes = arenas[0][0].nbytes
+    ptrs = (C.c_char_p * nr)(*[C.cast(a.ctypes.data, C.c_char_p) for a in arenas])
+    Xc = (C.c_int * 4)(*X)
+    for r in range(nr):
+        peer = (C.c_ubyte * 81)(*qb.plan_peers(Lg, G, r))
+        for mu in range(4):
+            acc = np.zeros_like(arenas[0][0])
+            for nu in range(4):
+                if nu == mu:
+                    continue
+                out = np.zeros_like(acc)
+                emu.emu_staple_field_mr(ptrs, nr, r, peer, nu * fbytes, mu * fbytes, nu, mu, Xc, dp(out))
+                acc += out
+            mine = lo.scatter(want[mu])[r].reshape(vloc, 3, 3, 2)
+            err = np.linalg.norm(from_dev(acc) - mine) / np.linalg.norm(mine)
+            assert err < 1e-14, (G, r, mu, err)
