@@ -12,7 +12,7 @@ import numpy as np
 EVEN, ODD, ALL = 0, 1, 2
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_LIBPATH = os.path.join(_HERE, "libqex_b200.so")
+_LIBPATH = os.environ.get("QEXB200_LIB") or os.path.join(_HERE, "libqex_b200.so")   # override: tuning builds only
 _lib = None
 
 

@@ -507,7 +507,10 @@ struct ProjDerivArgs {
   double2* f; double s_f; int acc;
   int Vh;
 };
-__global__ void __launch_bounds__(SB) k_proj_deriv(const ProjDerivArgs a) {
+#ifndef QB_PD_MINB
+#define QB_PD_MINB 1
+#endif
+__global__ void __launch_bounds__(SB, QB_PD_MINB) k_proj_deriv(const ProjDerivArgs a) {
   const int t = blockIdx.x * SB + threadIdx.x;
   if (t >= 2 * a.Vh) return;
   LSite s; s.par = t / a.Vh; s.idx = t - s.par * a.Vh; s.nb = NB_HOME;
@@ -541,8 +544,11 @@ struct DerivArgs {
   int Vh;
   Peers pr;
 };
+#ifndef QB_DERIV_MINB
+#define QB_DERIV_MINB 4
+#endif
 template <bool MR>
-__global__ void __launch_bounds__(SB, 4) k_staple_deriv(const DerivArgs a) {
+__global__ void __launch_bounds__(SB, QB_DERIV_MINB) k_staple_deriv(const DerivArgs a) {
   const int par = blockIdx.x & 1, idx = (blockIdx.x >> 1) * SB + threadIdx.x;
   if (idx >= a.Vh) return;
   const LSite s = lsite(idx, par, a.X);
