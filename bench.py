@@ -350,7 +350,7 @@ def run_ours(args):
     if world == 1 or args.transport == "p2p":
         # on several GPUs: link-shaped fields in the peer-mapped arena, neighbours read over NVLink (csrc/smear.cu)
         try:
-            lp = link_pipeline_leg(qb, nsites, peak, rank, cpu=(world == 1 and not args.no_cpu))
+            lp = link_pipeline_leg(qb, nsites, peak, rank, cpu=(world == 1 and not args.no_cpu), maxreduce_fn=maxreduce)
             for k in ("hisq", "nhyp", "nhyp_force", "hisq_force"):
                 lp[k]["ms"] = maxreduce(lp[k]["ms"])
                 gbs = 1e-9 * nsites * lp[k]["algorithmic_bytes_per_site"] / (1e-3 * lp[k]["ms"])
@@ -382,7 +382,7 @@ HISQ_FORCE_PASSES = 2 * FAT7_DERIV_PASSES - 4 * 3 * 3 + 16 + 8 + 4 * 3 + 4 * 3
 HISQ_PASSES = 4 * (3 * (5 + 10 + 6) - 1) + 4 * (3 * (5 + 10 + 8) - 1) + 4 * 2 + 4 * 2
 
 
-def link_pipeline_leg(qb, nsites, peak, rank, cpu=True, reps=3):
+def link_pipeline_leg(qb, nsites, peak, rank, cpu=True, reps=3, maxreduce_fn=lambda v: v):
     """HisqCoefs.smear and HypCoefs.smear on resident links (what an HMC force step does before
     its solves), timed with CUDA events on the library's stream; the oracle's CPU time per site beside."""
     from qex_b200.synth import random_su3_links
@@ -427,6 +427,34 @@ def link_pipeline_leg(qb, nsites, peak, rank, cpu=True, reps=3):
                          "achieved_gbs": gbs, "frac_of_hbm_peak": gbs / peak}
     hforce.free()
     for d in (du, c1, c2):
+        d.free()
+    # One massive-fermion force of staghmc_spv.nim on resident fields (the sequence BASELINE configs[3] repeats per
+    # force step): smearGetForce -> setBC/stagPhase -> solve D psi = phi (f_tol 1e-12, m = 0.1) -> psi (x) psi(+mu)^+ ->
+    # rephase -> smearedForce in place -> projTAH.  Stage times with CUDA events (each stage synchronised).
+    from qex_b200.synth import gaussian_vector
+    dphi, dpsi, frc = qb.DeviceField(gaussian_vector(nsites, 7 + rank)), qb.DeviceField(), qb.DeviceGauge(nlinks=4)
+    stages = {}
+
+    def timed(name, fn):
+        qb.timer_start()
+        r = fn()
+        stages[name] = stages.get(name, 0.0) + qb.timer_stop()
+        return r
+    for it in range(2):
+        stages.clear()
+        force = timed("smearGetForce", lambda: yc.smearGetForce(g, fl))
+        timed("rephase", fl.rephase)
+        sop = qb.newStag(fl)
+        sp = qb.SolverParams(r2req=1e-12, maxits=20000)
+        timed("solve", lambda: sop.dev_solve(dpsi, dphi, MASS, sp))
+        timed("outer_products", lambda: (frc.outer(dpsi, dpsi, -0.25, 0.25, accumulate=False), frc.rephase()))
+        timed("smearedForce", lambda: force(frc, frc))
+        timed("projTAH", lambda: frc.projTAH(g))
+        force.free()
+    stages = {k: maxreduce_fn(v) for k, v in stages.items()}
+    out["hmc_force_step"] = {"workload": "one massive-fermion force step of staghmc_spv on nHYP links, all on the device",
+                             "ms": sum(stages.values()), "stages_ms": stages, "cg_iterations": sp.iterations, "r2": sp.r2}
+    for d in (dphi, dpsi, frc):
         d.free()
     yc.smear(g, fl)
     out["plaq_smeared"] = [float(t) for t in fl.plaq()]

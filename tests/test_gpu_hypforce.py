@@ -124,3 +124,52 @@ def test_matter_force_tail(ctx_factory):
     force.free()
     for d in (dg, fl, f, dpsi):
         d.free()
+
+
+def test_fermion_force_step_of_staghmc_spv(ctx_factory):
+    """One massive-fermion force of src/stagg_pv_hmc/staghmc_spv.nim on the device, nothing but phi uploaded and the
+    force downloaded: smear (:367-386 smearGetForce, setBC, stagPhase) -> solve_fermion (:406-458, D psi = phi) ->
+    psi (x) psi(+mu)^+ with rescale (:697-711, :826-850) -> rephase, odd sites negated (:713-728) -> smeared force
+    in place (:745) -> projTAH against the thin links (:752).  Against the same chain on the oracle."""
+    L = (8, 8, 8, 8)
+    qb = ctx_factory(L)
+    lat, lo = oracle.Lattice(L), oracle.QexLayout(L)
+    g = lat.random_gauge(lat.new_rng(SEED), 4)
+    phi = lat.gaussian_vector(lat.new_rng(17))
+    mass, dt, r2req = 0.1, 0.05, 1e-20
+    scale = -0.5 * dt / mass
+    # oracle
+    sg = lat.hyp_smear(g, ALPHA)
+    lat.setBC(sg); lat.stagPhase(sg)
+    psi = lat.vector()
+    st = lat.solve(sg, psi, phi, mass, r2req)
+    want = lat.gauge(4)
+    lat.outer(want, psi, psi, scale, scale, accumulate=False)
+    lat.setBC(want); lat.stagPhase(want)
+    want[:, lat.half:] *= -1
+    want = lat.hyp_force(g, ALPHA, want)
+    m = (want[..., 0] + 1j * want[..., 1]) @ np.conj(g[..., 0] + 1j * g[..., 1]).transpose(0, 1, 3, 2)
+    t = 0.5 * (m - np.conj(m).transpose(0, 1, 3, 2))
+    t = t - np.einsum("kxaa->kx", t)[..., None, None] / 3.0 * np.eye(3)
+    want = np.stack([t.real, t.imag], axis=-1)
+    # device
+    dg, sgd, f = up(qb, lo, g), qb.DeviceGauge(nlinks=4), qb.DeviceGauge(nlinks=4)
+    force = qb.HypCoefs(*ALPHA).smearGetForce(dg, sgd)
+    sgd.rephase()
+    s = qb.newStag(sgd)
+    dphi, dpsi = qb.DeviceField(phi), qb.DeviceField()
+    sp = qb.SolverParams(r2req=r2req)
+    s.dev_solve(dpsi, dphi, mass, sp)
+    assert abs(sp.iterations - st.iterations) <= 2
+    f.outer(dpsi, dpsi, scale, -scale, accumulate=False)
+    f.rephase()
+    force(f, f)
+    f.projTAH(dg)
+    got = down(lat, lo, f)
+    assert rel_l2(got, want) <= 1e-8, rel_l2(got, want)      # two CG solutions at r2req = 1e-20
+    ah = got[..., 0] + 1j * got[..., 1]
+    assert np.abs(ah + np.conj(ah).transpose(0, 1, 3, 2)).max() < 1e-13     # anti-Hermitian
+    assert np.abs(np.einsum("kxaa->kx", ah)).max() < 1e-13                  # traceless
+    force.free()
+    for d in (s, dg, sgd, f, dphi, dpsi):
+        d.free()
