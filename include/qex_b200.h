@@ -182,6 +182,9 @@ int qexb200_gauge_projectU(qexb200_gauge_t dst, qexb200_gauge_t src);
 int qexb200_gauge_plaq(qexb200_gauge_t g, double pl[6]);
 /* newStag3(fl, ll) (stagD.nim:552-564): out (8 link fields) = {fl[0], ll[0], fl[1], ll[1], ...} */
 int qexb200_gauge_join3(qexb200_gauge_t out, qexb200_gauge_t fl, qexb200_gauge_t ll);
+/* the inverse: fl[mu] = in[2 mu], ll[mu] = in[2 mu + 1] -- e.g. the one-hop and three-hop outer products of
+ * examples/hisqhmc.nim:509-514 (f1, f3), formed in one pass by qexb200_dev_outer on an 8-field set */
+int qexb200_gauge_split3(qexb200_gauge_t fl, qexb200_gauge_t ll, qexb200_gauge_t in);
 /* device links -> native QEX host memory, links[k] as in qexb200_gauge_load */
 int qexb200_gauge_download(qexb200_gauge_t g, double* const* links);
 

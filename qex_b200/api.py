@@ -131,6 +131,7 @@ def lib():
         L.qexb200_gauge_projTAH.argtypes = [C.c_int, C.c_int, C.c_int]
         L.qexb200_gauge_plaq.argtypes = [C.c_int, dp]
         L.qexb200_gauge_join3.argtypes = [C.c_int, C.c_int, C.c_int]
+        L.qexb200_gauge_split3.argtypes = [C.c_int, C.c_int, C.c_int]
         L.qexb200_gauge_download.argtypes = [C.c_int, C.POINTER(dp)]
         L.qexb200_gauge_zero.argtypes = [C.c_int]
         L.qexb200_gauge_scale.argtypes = [C.c_int, C.c_double]
@@ -423,6 +424,10 @@ class DeviceGauge:
     def projTAH(self, g, adj="no_adj"):
         """projTAH(f, g, adj) (src/stagg_pv_hmc/staghmc_spv_gforce.nim:256-291)."""
         _ck(lib().qexb200_gauge_projTAH(self.h, g.h, int(adj == "adj")))
+
+    def split3(self, fl, ll):
+        """fl[mu] = self[2 mu], ll[mu] = self[2 mu + 1] (the inverse of newStag3's interleaving)."""
+        _ck(lib().qexb200_gauge_split3(fl.h, ll.h, self.h))
 
     def zero(self):
         _ck(lib().qexb200_gauge_zero(self.h))

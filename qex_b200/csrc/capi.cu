@@ -810,6 +810,24 @@ int qexb200_scidac_lattice(const char* filename, int dims[4]) {
   return scidac_lattice(filename, dims);
 }
 
+// the inverse of join3: fl[mu] = in[2 mu], ll[mu] = in[2 mu + 1]
+int qexb200_gauge_split3(qexb200_gauge_t hfl, qexb200_gauge_t hll, qexb200_gauge_t hin) {
+  QB_CHECK(need_ctx());
+  Gauge *in, *fl, *ll;
+  QB_CHECK(get_gauge(hin, &in));
+  if (in->nlinks != 8 || !in->loaded) return fail("gauge_split3: the input must hold 8 loaded link fields");
+  QB_CHECK(get_gauge4(hfl, &fl, "gauge_split3(fl)", false));
+  QB_CHECK(get_gauge4(hll, &ll, "gauge_split3(ll)", false));
+  if (fl == ll) return fail("gauge_split3: fl and ll must be different link sets");
+  const size_t n = (size_t)18 * g_ctx.g.Vh;
+  for (int mu = 0; mu < 4; mu++) {
+    QB_CUDA(cudaMemcpyAsync(link_field(fl, mu), link_field(in, 2 * mu), sizeof(double2) * n, cudaMemcpyDeviceToDevice, g_ctx.stream));
+    QB_CUDA(cudaMemcpyAsync(link_field(ll, mu), link_field(in, 2 * mu + 1), sizeof(double2) * n, cudaMemcpyDeviceToDevice, g_ctx.stream));
+  }
+  QB_CHECK(links_written(fl));
+  return links_written(ll);
+}
+
 // ---- device fields -----------------------------------------------------------
 int qexb200_field_create(qexb200_field_t* out) {
   QB_CHECK(need_ctx());

@@ -148,3 +148,52 @@ def test_device_hisq_force_is_the_gradient(ctx_factory):
     force.free()
     for d in (a, su, sul, du, dch, dchl):
         d.free()
+
+
+def test_fermion_force_step_of_hisqhmc(ctx_factory):
+    """fermionForce of src/examples/hisqhmc.nim:496-545 on the device: smearRephase (:405-414) -> solve -> one-hop and
+    three-hop outer products p (x) p(+mu)^+, p (x) p(+3mu)^+ (one pass), odd sites negated -> HISQ smearedForce on the
+    phased thin links -> projectTAH(ff g^+).  Near-unit links (well conditioned chain, see above)."""
+    L = (8, 8, 8, 8)
+    qb = ctx_factory(L)
+    lat, lo = oracle.Lattice(L), oracle.QexLayout(L)
+    u = lat.projectU(lat.unit_gauge() + 0.15 * np.random.default_rng(8).standard_normal(lat.unit_gauge().shape))
+    phi = lat.gaussian_vector(lat.new_rng(17))
+    mass, r2req = 0.1, 1e-20
+    hc = oracle.hisq_coefs()
+    # oracle
+    up_ = u.copy()
+    lat.setBC(up_); lat.stagPhase(up_)                     # g.rephase
+    su, sul = lat.hisq_smear(up_, hc)
+    gg = np.zeros((8,) + su.shape[1:])
+    gg[0::2], gg[1::2] = su, sul
+    psi = lat.vector()
+    st = lat.solve(gg, psi, phi, mass, r2req)
+    f13 = lat.gauge(8)
+    lat.outer(f13, psi, psi, 1.0, -1.0, accumulate=False)
+    ff = lat.hisq_force(up_, hc, np.ascontiguousarray(f13[0::2]), np.ascontiguousarray(f13[1::2]))
+    m = (ff[..., 0] + 1j * ff[..., 1]) @ np.conj(up_[..., 0] + 1j * up_[..., 1]).transpose(0, 1, 3, 2)
+    t = 0.5 * (m - np.conj(m).transpose(0, 1, 3, 2))
+    t = t - np.einsum("kxaa->kx", t)[..., None, None] / 3.0 * np.eye(3)
+    want = np.stack([t.real, t.imag], axis=-1)
+    # device
+    du = up(qb, lo, u)
+    du.rephase()
+    dsu, dsul = qb.DeviceGauge(nlinks=4), qb.DeviceGauge(nlinks=4)
+    force = qb.HisqCoefs().init().smearGetForce(du, dsu, dsul)
+    s = qb.newStag3(dsu, dsul)
+    dphi, dpsi = qb.DeviceField(phi), qb.DeviceField()
+    sp = qb.SolverParams(r2req=r2req)
+    s.dev_solve(dpsi, dphi, mass, sp)
+    assert abs(sp.iterations - st.iterations) <= 2
+    f8, f1, f3, dff = qb.DeviceGauge(nlinks=8), qb.DeviceGauge(nlinks=4), qb.DeviceGauge(nlinks=4), qb.DeviceGauge(nlinks=4)
+    f8.outer(dpsi, dpsi, 1.0, -1.0, accumulate=False)
+    f8.split3(f1, f3)
+    dff.zero()
+    force(dff, f1, f3)
+    dff.projTAH(du)
+    got = down(lat, lo, dff)
+    assert rel_l2(got, want) <= 1e-8, rel_l2(got, want)
+    force.free()
+    for d in (s, du, dsu, dsul, dphi, dpsi, f8, f1, f3, dff):
+        d.free()
