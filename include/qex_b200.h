@@ -198,6 +198,13 @@ int qexb200_stagD(qexb200_gauge_t g, int parity, double* r, const double* x, dou
 /* D / Ddag (stagD.nim:566-571), both parities */
 int qexb200_D(qexb200_gauge_t g, double* r, const double* x, double m);
 int qexb200_Ddag(qexb200_gauge_t g, double* r, const double* x, double m);
+/* peqDdag (stagD.nim:572-574): r += Ddag x;  eoReduce (:575-580): r.even = (Ddag b).even */
+int qexb200_peqDdag(qexb200_gauge_t g, double* r, const double* x, double m);
+int qexb200_eoReduce(qexb200_gauge_t g, double* r, const double* b, double m);
+/* stagDb (stagD.nim:425-427): stagD2 with b = m/(0.5 sc), i.e. (m x + sc D x)/(0.5 sc) without the rescaling pass */
+int qexb200_stagDb(qexb200_gauge_t g, int parity, double* r, const double* x, double m, double sc);
+/* stagD1 (minus = 0) / stagD1x (minus != 0) (stagD.nim:414-422): r[p] = +- sum_k [U_k x(+h_k) - U_k^+ x(-h_k)] */
+int qexb200_stagD1(qexb200_gauge_t g, int parity, double* r, const double* x, int minus);
 /* stagD2ee / stagD2oo (stagD.nim:433-469): r[p] = 4 m2 x - (2D)(2D) x */
 int qexb200_stagD2xx(qexb200_gauge_t g, int parity, double* r, const double* x, double m2);
 /* eoReconstruct (stagD.nim:582-586): r.odd = (b.odd - D_oe r.even)/m */
@@ -247,6 +254,8 @@ int qexb200_dev_D(qexb200_gauge_t g, qexb200_field_t r, qexb200_field_t x, doubl
 int qexb200_dev_Ddag(qexb200_gauge_t g, qexb200_field_t r, qexb200_field_t x, double m);
 int qexb200_dev_stagD2xx(qexb200_gauge_t g, int parity, qexb200_field_t r, qexb200_field_t x,
                          double m2);
+int qexb200_dev_peqDdag(qexb200_gauge_t g, qexb200_field_t r, qexb200_field_t x, double m);
+int qexb200_dev_eoReduce(qexb200_gauge_t g, qexb200_field_t r, qexb200_field_t b, double m);
 int qexb200_dev_solveXX(qexb200_gauge_t g, int parity, qexb200_field_t r, qexb200_field_t x,
                         double m, qexb200_solver_params* sp);
 int qexb200_dev_solve(qexb200_gauge_t g, qexb200_field_t x, qexb200_field_t b, double m,

@@ -148,6 +148,12 @@ def lib():
         L.qexb200_D.argtypes = [C.c_int, dp, dp, C.c_double]
         L.qexb200_Ddag.argtypes = [C.c_int, dp, dp, C.c_double]
         L.qexb200_stagD2xx.argtypes = [C.c_int, C.c_int, dp, dp, C.c_double]
+        L.qexb200_peqDdag.argtypes = [C.c_int, dp, dp, C.c_double]
+        L.qexb200_eoReduce.argtypes = [C.c_int, dp, dp, C.c_double]
+        L.qexb200_stagDb.argtypes = [C.c_int, C.c_int, dp, dp, C.c_double, C.c_double]
+        L.qexb200_stagD1.argtypes = [C.c_int, C.c_int, dp, dp, C.c_int]
+        L.qexb200_dev_peqDdag.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double]
+        L.qexb200_dev_eoReduce.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double]
         L.qexb200_eoReconstruct.argtypes = [C.c_int, dp, dp, C.c_double]
         L.qexb200_solveXX.argtypes = [C.c_int, C.c_int, dp, dp, C.c_double, spp]
         L.qexb200_solve.argtypes = [C.c_int, dp, dp, C.c_double, spp]
@@ -479,6 +485,20 @@ class Staggered(DeviceGauge):
     def eoReconstruct(self, r, b, m):
         _ck(lib().qexb200_eoReconstruct(self.h, _dp(r), _dp(b), m))
 
+    def peqDdag(self, r, x, m):
+        """peqDdag (stagD.nim:572-574): r += Ddag x (host arrays, or DeviceFields)."""
+        if isinstance(r, DeviceField):
+            _ck(lib().qexb200_dev_peqDdag(self.h, r.h, x.h, m))
+        else:
+            _ck(lib().qexb200_peqDdag(self.h, _dp(r), _dp(x), m))
+
+    def eoReduce(self, r, b, m):
+        """eoReduce (stagD.nim:575-580): r.even = (Ddag b).even."""
+        if isinstance(r, DeviceField):
+            _ck(lib().qexb200_dev_eoReduce(self.h, r.h, b.h, m))
+        else:
+            _ck(lib().qexb200_eoReduce(self.h, _dp(r), _dp(b), m))
+
     def solveXX(self, r, x, m, sp, parEven=True):
         c = sp._c()
         _ck(lib().qexb200_solveXX(self.h, EVEN if parEven else ODD, _dp(r), _dp(x), m, C.byref(c)))
@@ -630,3 +650,18 @@ def stagD2deriv(s, g, c, x):
     else:
         arr = (C.POINTER(C.c_double) * len(g))(*[_dp(t) for t in g])
         _ck(lib().qexb200_stagD2deriv(s.h, arr, _dp(c), _dp(x)))
+
+
+def stagDb(s, parity, r, x, m, sc=1.0):
+    """stagDb(sd, r, g, x, m, sc) (stagD.nim:425-427)."""
+    _ck(lib().qexb200_stagDb(s.h, parity, _dp(r), _dp(x), m, sc))
+
+
+def stagD1(s, parity, r, x):
+    """stagD1 (stagD.nim:414-417)."""
+    _ck(lib().qexb200_stagD1(s.h, parity, _dp(r), _dp(x), 0))
+
+
+def stagD1x(s, parity, r, x):
+    """stagD1x (stagD.nim:419-422)."""
+    _ck(lib().qexb200_stagD1(s.h, parity, _dp(r), _dp(x), 1))

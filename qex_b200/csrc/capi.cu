@@ -1026,6 +1026,51 @@ int qexb200_Ddag(qexb200_gauge_t hg, double* r, const double* x, double m) {
   QB_CHECK(op_Ddag(*g, R, X, m));
   return download_vector(R, r);
 }
+// The remaining flavours of stagD.nim:405-427,572-580, each a parameter choice of the same sweep:
+// peqDdag: r += Ddag x; eoReduce: r.even = (Ddag b).even; stagDb: r = m x + sc D x without the final rescaling pass
+// (i.e. stagD2 with b = m/(0.5 sc)); stagD1 / stagD1x: + / - the bare hop sum.
+int qexb200_peqDdag(qexb200_gauge_t hg, double* r, const double* x, double m) {
+  HOST_PROLOGUE(hg);
+  QB_CHECK(upload_vector(R, r));
+  QB_CHECK(upload_vector(X, x));
+  QB_CHECK(op_stagD(*g, 0, R, X, m, -1.0, 1.0));
+  QB_CHECK(op_stagD(*g, 1, R, X, m, -1.0, 1.0));
+  return download_vector(R, r);
+}
+int qexb200_eoReduce(qexb200_gauge_t hg, double* r, const double* b, double m) {
+  HOST_PROLOGUE(hg);
+  QB_CHECK(upload_vector(R, r));
+  QB_CHECK(upload_vector(X, b));
+  QB_CHECK(op_stagD(*g, 0, R, X, m, -1.0, 0.0));
+  return download_vector(R, r);
+}
+int qexb200_stagDb(qexb200_gauge_t hg, int parity, double* r, const double* x, double m, double sc) {
+  HOST_PROLOGUE(hg);
+  if (parity != 0 && parity != 1) return fail("stagDb: parity must be 0 or 1");
+  if (sc == 0.0) return fail("stagDb: sc must not be 0");
+  QB_CHECK(upload_vector(R, r));
+  QB_CHECK(upload_vector(X, x));
+  QB_CHECK(op_stagD2(*g, parity, R, X, 0.0, m / (0.5 * sc)));
+  return download_vector(R, r);
+}
+int qexb200_stagD1(qexb200_gauge_t hg, int parity, double* r, const double* x, int minus) {
+  HOST_PROLOGUE(hg);
+  if (parity != 0 && parity != 1) return fail("stagD1: parity must be 0 or 1");
+  QB_CHECK(upload_vector(R, r));
+  QB_CHECK(upload_vector(X, x));
+  QB_CHECK(op_stagD2(*g, parity, R, X, 0.0, 0.0));
+  if (minus) QB_CHECK(blas_scale(hf(R, parity), -1.0, nhalf()));
+  return download_vector(R, r);
+}
+int qexb200_dev_peqDdag(qexb200_gauge_t hg, qexb200_field_t r, qexb200_field_t x, double m) {
+  GET_G_F2(hg, r, x);
+  QB_CHECK(op_stagD(*g, 0, *f1, *f2, m, -1.0, 1.0));
+  return op_stagD(*g, 1, *f1, *f2, m, -1.0, 1.0);
+}
+int qexb200_dev_eoReduce(qexb200_gauge_t hg, qexb200_field_t r, qexb200_field_t b, double m) {
+  GET_G_F2(hg, r, b);
+  return op_stagD(*g, 0, *f1, *f2, m, -1.0, 0.0);
+}
 int qexb200_stagD2xx(qexb200_gauge_t hg, int parity, double* r, const double* x, double m2) {
   HOST_PROLOGUE(hg);
   if (parity != 0 && parity != 1) return fail("stagD2xx: parity must be 0 or 1");

@@ -446,3 +446,40 @@ def test_large_lattice_properties(qb, ctx_factory):
     for f in (fx, fy, fa, fb):
         f.free()
     s.free()
+
+
+def test_remaining_stagD_flavours(orc, ctx_factory):
+    """peqDdag, eoReduce, stagDb, stagD1, stagD1x (stagD.nim:414-427,572-580) -- parameter choices of the sweep."""
+    L = (8, 8, 8, 8)
+    qb = ctx_factory(L)
+    lat, g, (x, r0) = make_inputs(L, 8)
+    s = qb.Staggered([g[k] for k in range(8)])
+    m = 0.13
+    dd = lat.vector()
+    lat.Ddag(g, dd, x, m)
+    got = r0.copy()
+    s.peqDdag(got, x, m)
+    assert rel_l2(got, r0 + dd) <= DSLASH_TOL
+    got = r0.copy()
+    s.eoReduce(got, x, m)
+    assert rel_l2(got[:lat.half], dd[:lat.half]) <= DSLASH_TOL and np.array_equal(got[lat.half:], r0[lat.half:])
+    fr, fx = qb.DeviceField(r0), qb.DeviceField(x)
+    s.peqDdag(fr, fx, m)
+    assert rel_l2(fr.download(lat.vector()), r0 + dd) <= DSLASH_TOL
+    fr.free(); fx.free()
+    for parity in (0, 1):
+        sl = slice(0, lat.half) if parity == 0 else slice(lat.half, lat.vol)
+        hop = lat.vector()
+        lat.stagD2(g, hop, x, 0.0, 0.0, parity)
+        got = r0.copy()
+        qb.stagD1(s, parity, got, x)
+        assert rel_l2(got[sl], hop[sl]) <= DSLASH_TOL
+        got = r0.copy()
+        qb.stagD1x(s, parity, got, x)
+        assert rel_l2(got[sl], -hop[sl]) <= DSLASH_TOL
+        want = lat.vector()
+        lat.stagD2(g, want, x, 0.0, m / (0.5 * 0.7), parity)
+        got = r0.copy()
+        qb.stagDb(s, parity, got, x, m, 0.7)
+        assert rel_l2(got[sl], want[sl]) <= DSLASH_TOL
+    s.free()
