@@ -49,12 +49,18 @@ QB_HD LSite lsite(int idx, int par, const int* X) {
   return s;
 }
 // one hop of d = +-1 (or +-k) in direction mu with local wrap-around (single rank: periodic)
+// (selects instead of s.x[mu]: a run-time index would put the coordinates in local memory)
 QB_HD LSite lhop(LSite s, int mu, int d, const int* X) {
-  int c = s.x[mu] + d;
+  const int xm = mu == 0 ? s.x[0] : (mu == 1 ? s.x[1] : (mu == 2 ? s.x[2] : s.x[3]));
+  const int Xm = mu == 0 ? X[0] : (mu == 1 ? X[1] : (mu == 2 ? X[2] : X[3]));
+  int c = xm + d;
   const int p3 = mu == 0 ? 1 : (mu == 1 ? 3 : (mu == 2 ? 9 : 27));
-  if (c >= X[mu]) { c -= X[mu]; s.nb += p3; }
-  if (c < 0) { c += X[mu]; s.nb -= p3; }
-  s.x[mu] = c;
+  if (c >= Xm) { c -= Xm; s.nb += p3; }
+  if (c < 0) { c += Xm; s.nb -= p3; }
+  s.x[0] = mu == 0 ? c : s.x[0];
+  s.x[1] = mu == 1 ? c : s.x[1];
+  s.x[2] = mu == 2 ? c : s.x[2];
+  s.x[3] = mu == 3 ? c : s.x[3];
   if (d & 1) s.par ^= 1;
   s.idx = (((s.x[3] * X[2] + s.x[2]) * X[1] + s.x[1]) * X[0] + s.x[0]) >> 1;
   return s;

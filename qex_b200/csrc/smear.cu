@@ -121,6 +121,164 @@ __global__ void __launch_bounds__(SB, QB_STAPLE_MINB) k_staple(const StapleArgs 
 
 static inline int grid_par(int Vh, int block) { return 2 * ((Vh + block - 1) / block); }
 
+// ---- the same staple sum with the gathers staged through shared memory (single rank) --------------------
+// k_staple above is bound by latency: six 144-byte matrices per pair pass through registers, at 168 registers
+// a thread has at most three of them in flight and an SM holds 12 warps (ncu: 18 % of the warp slots, DRAM at
+// 35-47 %, FP64 pipe at 46-56 %).  Measured (32^4, profiles/r01_staple_pipe_ab.log): HISQ 16.0 -> 15.1 ms,
+// nHYP 5.6-5.8 -> 5.4-5.5 ms; bit-identical results (tests/test_gpu_links.py).  Here a thread streams its sites through a private shared-memory ring with
+// cp.async (LDGSTS): the ring has one slot for the upper bracket's three matrices and one for the lower's, and
+// each slot is refilled for the NEXT (site, pair) as soon as it has been read, so a full pair of matrix products
+// (and the projection, when fused) runs between the request and the use of every matrix.  No block barrier:
+// a thread only ever reads what it staged itself.  Blocks are persistent and keep the parity interleave
+// (the grid is even, block b stays on parity b & 1).  The arithmetic is that of staple_pair_x, in the same order.
+#ifndef QB_PB
+#define QB_PB 64
+#endif
+#ifndef QB_CPASYNC
+#define QB_CPASYNC "cp.async.cg.shared.global"   // .cg: past L1 -- with the ring taking the carve-out .ca thrashes what little L1 is left (measured 21.8 vs 15.1 ms)
+#endif
+constexpr int PB = QB_PB;                   // threads per block
+constexpr int PIPE_SMEM = 54 * PB * 16;     // 6 matrices * 9 elements * 16 B per thread = 55296 B per block
+#ifndef QB_PIPE_MINB
+#define QB_PIPE_MINB 4
+#endif
+
+__device__ __forceinline__ void cp16(double2* smem, const double2* g) {
+  const unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile(QB_CPASYNC " [%0], [%1], 16;" ::"r"(sa), "l"(g) : "memory");
+}
+__device__ __forceinline__ void cp_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_wait1() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+__device__ __forceinline__ void cp_wait0() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+// request matrix `f` at site s into ring position m (0..5)
+__device__ __forceinline__ void stage_m3(double2* my, int m, const double2* f, const LSite& s, int Vh) {
+  const double2* p = f + (size_t)s.par * 9 * Vh + s.idx;
+#pragma unroll
+  for (int e = 0; e < 9; e++) cp16(my + (m * 9 + e) * PB, p + (size_t)e * Vh);
+}
+__device__ __forceinline__ M3 ring_m3(const double2* my, int m) {
+  M3 r;
+#pragma unroll
+  for (int e = 0; e < 9; e++) r.e[e] = my[(m * 9 + e) * PB];
+  return r;
+}
+// upper bracket of pair t at site s: G(s), L(s+dG), G(s+dL); lower: G(s-dG), L(s-dG), G(s-dG+dL)
+__device__ __forceinline__ void stage_up(double2* my, const StapleTerm& t, int dL, const LSite& s, const int* X, int Vh) {
+  stage_m3(my, 0, t.G, s, Vh);
+  stage_m3(my, 1, t.L, lhop(s, t.dG, +1, X), Vh);
+  stage_m3(my, 2, t.G, lhop(s, dL, +1, X), Vh);
+}
+__device__ __forceinline__ void stage_down(double2* my, const StapleTerm& t, int dL, const LSite& s, const int* X, int Vh) {
+  const LSite sb = lhop(s, t.dG, -1, X);
+  stage_m3(my, 3, t.G, sb, Vh);
+  stage_m3(my, 4, t.L, sb, Vh);
+  stage_m3(my, 5, t.G, lhop(sb, dL, +1, X), Vh);
+}
+
+template <int NS, bool PROJ>
+__global__ void __launch_bounds__(PB, QB_PIPE_MINB) k_staple_pipe(const StapleArgs a, int ntiles) {
+  extern __shared__ double2 ring[];
+  double2* my = ring + threadIdx.x;
+  const int par = blockIdx.x & 1;           // gridDim.x is even: the parity of a block never changes
+  int tile = blockIdx.x;
+  int idx = (tile >> 1) * PB + threadIdx.x;
+  bool live = tile < ntiles && idx < a.Vh;
+  LSite s = lsite(live ? idx : 0, par, a.X);
+  if (live) stage_up(my, a.t[0], a.dL, s, a.X, a.Vh);
+  cp_commit();
+  if (live) stage_down(my, a.t[0], a.dL, s, a.X, a.Vh);
+  cp_commit();
+  while (tile < ntiles) {                   // uniform over the block
+    const int ntile = tile + gridDim.x;
+    const int nidx = (ntile >> 1) * PB + threadIdx.x;
+    const bool nlive = ntile < ntiles && nidx < a.Vh;
+    const LSite ns = lsite(nlive ? nidx : 0, par, a.X);
+    // cbase*base or acc (the launcher never passes both here): requested now, first used after the first pair
+    const double2* isrc = a.base ? a.base : a.acc;
+    const double c0 = a.base ? a.cbase : 1.0;
+    M3 ini = m3_zero();
+    if (live && isrc) ini = m3_ld(isrc, s, a.Vh);
+    M3 r = m3_zero();
+#pragma unroll
+    for (int k = 0; k < NS; k++) {
+      const bool last = k + 1 == NS;
+      cp_wait1();                           // the upper bracket of (site, k) has landed; only the lower one may be in flight
+      M3 st;
+      {
+        const M3 A = ring_m3(my, 0), B = ring_m3(my, 1), C = ring_m3(my, 2);
+        if (!last) { if (live) stage_up(my, a.t[(k + 1) % NS], a.dL, s, a.X, a.Vh); }
+        else if (nlive) stage_up(my, a.t[0], a.dL, ns, a.X, a.Vh);
+        cp_commit();
+        st = m3_mul_na(m3_mul(A, B), C);
+      }
+      cp_wait1();                           // the lower bracket has landed; the refill just issued may be in flight
+      {
+        const M3 A = ring_m3(my, 3), B = ring_m3(my, 4), C = ring_m3(my, 5);
+        if (!last) { if (live) stage_down(my, a.t[(k + 1) % NS], a.dL, s, a.X, a.Vh); }
+        else if (nlive) stage_down(my, a.t[0], a.dL, ns, a.X, a.Vh);
+        cp_commit();
+        const M3 lo = m3_mul(m3_mul_an(A, B), C);
+        m3_axpy(st, 1.0, lo);
+      }
+      if (live) {
+        if (NS == 1 && a.save) m3_st(a.save, s, a.Vh, st);
+        if (k == 0 && isrc) m3_axpy(r, c0, ini);
+        m3_axpy(r, a.t[k].coef, st);
+      }
+    }
+    if (live) {
+      if (PROJ) {
+        if (a.raw) m3_st(a.raw, s, a.Vh, r);
+        r = project_u(r);
+      }
+      m3_st(a.out, s, a.Vh, r);
+    }
+    tile = ntile; idx = nidx; live = nlive; s = ns;
+  }
+  cp_wait0();
+}
+
+// QEXB200_STAPLE_PIPE=0 selects the register-gather kernel on a single rank as well (A/B runs).
+static bool staple_pipe_enabled() {
+  const char* e = getenv("QEXB200_STAPLE_PIPE");   // read per launch: the A/B test flips it inside one process
+  return !(e && e[0] == '0');
+}
+// Persistent grid = what is resident at once (the ring needs the full shared-memory carve-out to fit
+// QB_PIPE_MINB blocks per SM; a grid larger than one wave would serialise whole blocks).
+template <int NS, bool PROJ>
+static int launch_pipe_t(const StapleArgs& a, int ntiles, cudaStream_t st) {
+  static int resident = 0;
+  if (!resident) {
+    QB_CUDA(cudaFuncSetAttribute(k_staple_pipe<NS, PROJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, PIPE_SMEM));
+    QB_CUDA(cudaFuncSetAttribute(k_staple_pipe<NS, PROJ>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    int dev = 0, sms = 0, occ = 0;
+    QB_CUDA(cudaGetDevice(&dev));
+    QB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    QB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_staple_pipe<NS, PROJ>, PB, PIPE_SMEM));
+    if (occ < 1) return fail("k_staple_pipe does not fit on an SM");
+    resident = sms * occ;
+    if (getenv("QEXB200_PIPE_VERBOSE")) fprintf(stderr, "k_staple_pipe<%d,%d>: %d blocks/SM, %d resident\n", NS, (int)PROJ, occ, resident);
+  }
+  int grid = resident;
+  if (const char* e = getenv("QEXB200_PIPE_GRID")) grid = atoi(e) > 1 ? atoi(e) : 2;   // tests: few blocks, many tiles each
+  grid -= grid & 1;
+  if (grid > ntiles) grid = ntiles;
+  k_staple_pipe<NS, PROJ><<<grid, PB, PIPE_SMEM, st>>>(a, ntiles);
+  return 0;
+}
+static int launch_staple_pipe(const StapleArgs& a, int ns, bool proj) {
+  Context& c = ctx();
+  const int ntiles = grid_par(c.g.Vh, PB);
+  if (proj) {
+    if (ns == 1) return launch_pipe_t<1, true>(a, ntiles, c.stream);
+    if (ns == 2) return launch_pipe_t<2, true>(a, ntiles, c.stream);
+    return launch_pipe_t<3, true>(a, ntiles, c.stream);
+  }
+  if (ns == 1) return launch_pipe_t<1, false>(a, ntiles, c.stream);
+  if (ns == 2) return launch_pipe_t<2, false>(a, ntiles, c.stream);
+  return launch_pipe_t<3, false>(a, ntiles, c.stream);
+}
 template <bool MR>
 static void launch_staple_t(const StapleArgs& a, int ns, bool proj, int grid, cudaStream_t st) {
   if (proj) {
@@ -141,6 +299,8 @@ static int launch_staple(const StapleArgs& a, int ns, bool proj) {
       if (!in_arena(a.t[k].G) || !in_arena(a.t[k].L)) return fail("link pipeline on a split lattice: a field lives outside the peer arena");
     QB_CHECK(xbarrier());
     launch_staple_t<true>(a, ns, proj, grid, c.stream);
+  } else if (staple_pipe_enabled() && !(a.base && a.acc)) {
+    QB_CHECK(launch_staple_pipe(a, ns, proj));
   } else {
     launch_staple_t<false>(a, ns, proj, grid, c.stream);
   }

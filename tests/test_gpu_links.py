@@ -201,6 +201,36 @@ def test_hyp_smear_parity_and_solve(ctx_factory, L, inner):
         d.free()
 
 
+@pytest.mark.parametrize("L,grid", [((8, 8, 8, 8), "6"), ((4, 6, 8, 10), "2"), ((16, 16, 16, 16), None)])
+def test_staged_staple_kernel_is_bit_identical(ctx_factory, monkeypatch, L, grid):
+    """The shared-memory-staged staple kernel (k_staple_pipe, the single-rank default) does the arithmetic of the
+    register-gather kernel in the same order: HISQ and nHYP links must agree bit for bit, also when a block
+    walks many tiles (QEXB200_PIPE_GRID) and when the last tile is ragged."""
+    qb = ctx_factory(L)
+    vol = int(np.prod(L))
+    from qex_b200.synth import random_su3_links
+    g = qb.DeviceGauge(random_su3_links(vol, 4, seed=5))
+    out = {}
+    for mode in ("1", "0"):
+        monkeypatch.setenv("QEXB200_STAPLE_PIPE", mode)
+        if grid and mode == "1":
+            monkeypatch.setenv("QEXB200_PIPE_GRID", grid)
+        fl, ll, hl = qb.DeviceGauge(nlinks=4), qb.DeviceGauge(nlinks=4), qb.DeviceGauge(nlinks=4)
+        qb.HisqCoefs().init().smear(g, fl, ll)
+        qb.HypCoefs(0.4, 0.5, 0.5).smear(g, hl)
+        res = []
+        for dg in (fl, ll, hl):
+            parts = [np.zeros((vol, 3, 3, 2)) for _ in range(4)]
+            dg.download(parts)
+            res.append(np.stack(parts))
+            dg.free()
+        out[mode] = res
+    monkeypatch.delenv("QEXB200_PIPE_GRID", raising=False)
+    for a, b in zip(out["1"], out["0"]):
+        assert np.isfinite(a).all() and np.array_equal(a, b)
+    g.free()
+
+
 def test_hyp_unit_gauge_is_fixed_point(ctx_factory):
     L = (4, 4, 4, 4)
     qb = ctx_factory(L)
