@@ -440,6 +440,9 @@ def link_pipeline_leg(qb, nsites, peak, rank, cpu=True, reps=3, maxreduce_fn=lam
         r = fn()
         stages[name] = stages.get(name, 0.0) + qb.timer_stop()
         return r
+    # nHYP links are U(3): rows 0,1 + the determinant factor (14 reals) instead of 18 for the solve's sweeps;
+    # sticky, re-derived (and re-verified on the device) inside smearGetForce and rephase below
+    fl.recon(14)
     for it in range(2):
         stages.clear()
         force = timed("smearGetForce", lambda: yc.smearGetForce(g, fl))
@@ -452,8 +455,11 @@ def link_pipeline_leg(qb, nsites, peak, rank, cpu=True, reps=3, maxreduce_fn=lam
         timed("projTAH", lambda: frc.projTAH(g))
         force.free()
     stages = {k: maxreduce_fn(v) for k, v in stages.items()}
+    storage = fl.recon(14)[0][0]      # what the solve above read (18 on a split lattice: not enabled there yet)
     out["hmc_force_step"] = {"workload": "one massive-fermion force step of staghmc_spv on nHYP links, all on the device",
-                             "ms": sum(stages.values()), "stages_ms": stages, "cg_iterations": sp.iterations, "r2": sp.r2}
+                             "ms": sum(stages.values()), "stages_ms": stages, "cg_iterations": sp.iterations, "r2": sp.r2,
+                             "link_storage": "%d-real" % storage}
+    fl.recon(18)
     for d in (dphi, dpsi, frc):
         d.free()
     yc.smear(g, fl)

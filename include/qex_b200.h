@@ -109,8 +109,12 @@ int qexb200_gauge_destroy(qexb200_gauge_t g);
  * verifies the form on the device (rebuilt matrix within 2e-14 |s|) and reports per class what it
  * uses in got[2] (12 or 18) and the measured deviation in dev[2].  want = 1812 / 1218 restricts
  * the request to the three-hop / one-hop class (1812: fat links 18, Naik links 12 -- what a real
- * HISQ or asqtad link set allows).  The request is sticky: it is
- * re-applied after every qexb200_gauge_load / qexb200_gauge_rephase. */
+ * HISQ or asqtad link set allows).  want = 14 (or 1814, 1418, 1214 ...): rows 0,1 plus ONE complex
+ * factor phi per link, third row = phi conj(row0 x row1) (112 bytes per link) -- for links that are
+ * c*U(3) with a determinant phase that changes from site to site: projectU'd smeared links (nHYP,
+ * src/gauge/hypsmear.nim:49-162) and the Naik products of the HISQ W links (src/gauge/fat7l.nim:156-167).
+ * Same on-device verification.  The request is sticky: it is re-applied after every
+ * qexb200_gauge_load / qexb200_gauge_rephase and after every device smear that writes the set. */
 int qexb200_gauge_recon(qexb200_gauge_t g, int want, int got[2], double dev[2]);
 /* Staggered.rephase on the device copy: setBC then stagPhase with phases {8,9,11,0}
  * (stagD.nim:72-80,509-522; gauge/gaugeUtils.nim:124-131).  One-hop links only. */

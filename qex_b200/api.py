@@ -446,8 +446,10 @@ class DeviceGauge:
         _ck(lib().qexb200_dev_outer(self.h, a.h, b.h, float(scale_even), float(scale_odd), int(accumulate)))
 
     def recon(self, want=12):
-        """Ask for 12-real (rows 0,1 + rebuilt third row) or 18-real link storage; returns
-        ([recon of one-hop class, recon of three-hop class], [measured deviation per class])."""
+        """Ask for 12-real (rows 0,1 + rebuilt third row; +-s*SU(3) links), 14-real (rows 0,1 + one complex factor
+        per link; c*U(3) links: projected smeared links, HISQ Naik links) or 18-real link storage; four digits
+        address the one-hop and three-hop class separately (1814 = fat links 18, Naik links 14).  Returns
+        ([storage of the one-hop class, of the three-hop class], [measured deviation per class])."""
         got, dev = (C.c_int * 2)(), (C.c_double * 2)()
         _ck(lib().qexb200_gauge_recon(self.h, int(want), got, dev))
         return [got[0], got[1]], [dev[0], dev[1]]

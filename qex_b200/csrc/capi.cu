@@ -540,8 +540,12 @@ int qexb200_gauge_destroy(qexb200_gauge_t h) {
 int qexb200_gauge_recon(qexb200_gauge_t h, int want, int got[2], double dev[2]) {
   QB_CHECK(need_ctx());
   Gauge* g; QB_CHECK(get_gauge(h, &g));
-  if (want != 12 && want != 18 && want != 1812 && want != 1218) return fail("gauge_recon: want must be 12, 18, 1812 or 1218");
-  g->want12 = (want == 12) ? 3 : (want == 1812) ? 2 : (want == 1218) ? 1 : 0;
+  // two digits: both link classes; four digits: one-hop class, then three-hop class (1814 = fat 18, long 14)
+  const int w0 = want >= 100 ? want / 100 : want, w1 = want >= 100 ? want % 100 : want;
+  if ((w0 != 12 && w0 != 14 && w0 != 18) || (w1 != 12 && w1 != 14 && w1 != 18) || want < 0)
+    return fail("gauge_recon: want must be 12, 14, 18 or a pair of them (1812, 1814, 1418 ...)");
+  g->want12 = (w0 == 12 ? 1 : 0) | (w1 == 12 ? 2 : 0);
+  g->want14 = (w0 == 14 ? 1 : 0) | (w1 == 14 ? 2 : 0);
   QB_CHECK(compress_links(*g));
   if (got) { got[0] = g->recon[0]; got[1] = g->recon[1]; }
   if (dev) { dev[0] = g->dev[0]; dev[1] = g->dev[1]; }

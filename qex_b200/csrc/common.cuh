@@ -32,7 +32,7 @@ struct Geom {
 // sgn[par][idx] bit (2 mu + j) for U_{mu,j}(s), bit 8 + (2 mu + j) for U_{mu,j}(s - h_j mu).
 struct Links {
   const double2* u;          // [nlinks][2][9][Vh]
-  const double2* u12[2];     // per class: [4 mu][2][6][Vh] or nullptr
+  const double2* u12[2];     // per class: [4 mu][2][6][Vh] (12-real) / [4 mu][2][7][Vh] (14-real) or nullptr
   const unsigned short* sgn; // [2][Vh]
   double inv[2];             // 1/|s| per class
 };
@@ -187,7 +187,10 @@ struct Gauge {
   unsigned short* sgn = nullptr;
   double inv[2] = {1.0, 1.0};
   double dev[2] = {0.0, 0.0};     // measured max |U - rebuilt U| / |s| per class (diagnostic)
-  int rc() const { return (recon[0] == 12 ? 1 : 0) | (recon[1] == 12 ? 2 : 0); }
+  int want14 = 0;                 // same, 14-real storage (rows 0, 1 + one complex factor per link)
+  int rc() const {
+    return (recon[0] == 12 ? 1 : 0) | (recon[1] == 12 ? 2 : 0) | (recon[0] == 14 ? 4 : 0) | (recon[1] == 14 ? 8 : 0);
+  }
   Links links() const {
     Links L;
     L.u = d; L.u12[0] = d12[0]; L.u12[1] = d12[1]; L.sgn = sgn; L.inv[0] = inv[0]; L.inv[1] = inv[1];

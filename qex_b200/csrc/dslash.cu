@@ -18,20 +18,21 @@ namespace qb {
 constexpr int SWEEP_BLOCK = 128;
 
 // Expands LAUNCH once with the compile-time constants NL (link classes), RC (bit j: class j is
-// read as 12 reals) and DOT that match the link set and the request.
+// read as 12 reals, bit 2+j: as 14 reals) and DOT that match the link set and the request.
 #define QB_CASE(KEY, NLV, RCV, DOTV, ...) \
   case KEY: { constexpr int NL = NLV; constexpr int RC = RCV; constexpr bool DOT = DOTV; (void)DOT; __VA_ARGS__; } break;
+#define QB_CASE2(NLV, RCV, ...) \
+  QB_CASE(((NLV) == 2 ? 32 : 0) | ((RCV) << 1), NLV, RCV, false, __VA_ARGS__) \
+  QB_CASE(((NLV) == 2 ? 32 : 0) | ((RCV) << 1) | 1, NLV, RCV, true, __VA_ARGS__)
 #define QB_DISPATCH(g, dot, ...)                                                           \
   do {                                                                                     \
     const int nl_ = (g).nlinks / 4;                                                        \
-    const int rc_ = (nl_ == 2) ? (g).rc() : ((g).rc() & 1);                                \
-    switch ((nl_ == 2 ? 8 : 0) | (rc_ << 1) | ((dot) ? 1 : 0)) {                           \
-      QB_CASE(0, 1, 0, false, __VA_ARGS__) QB_CASE(1, 1, 0, true, __VA_ARGS__)                       \
-      QB_CASE(2, 1, 1, false, __VA_ARGS__) QB_CASE(3, 1, 1, true, __VA_ARGS__)                       \
-      QB_CASE(8, 2, 0, false, __VA_ARGS__) QB_CASE(9, 2, 0, true, __VA_ARGS__)                       \
-      QB_CASE(10, 2, 1, false, __VA_ARGS__) QB_CASE(11, 2, 1, true, __VA_ARGS__)                     \
-      QB_CASE(12, 2, 2, false, __VA_ARGS__) QB_CASE(13, 2, 2, true, __VA_ARGS__)                     \
-      QB_CASE(14, 2, 3, false, __VA_ARGS__) QB_CASE(15, 2, 3, true, __VA_ARGS__)                     \
+    const int rc_ = (nl_ == 2) ? (g).rc() : ((g).rc() & 5);                                \
+    switch ((nl_ == 2 ? 32 : 0) | (rc_ << 1) | ((dot) ? 1 : 0)) {                          \
+      QB_CASE2(1, 0, __VA_ARGS__) QB_CASE2(1, 1, __VA_ARGS__) QB_CASE2(1, 4, __VA_ARGS__)  \
+      QB_CASE2(2, 0, __VA_ARGS__) QB_CASE2(2, 1, __VA_ARGS__) QB_CASE2(2, 4, __VA_ARGS__)  \
+      QB_CASE2(2, 2, __VA_ARGS__) QB_CASE2(2, 3, __VA_ARGS__) QB_CASE2(2, 6, __VA_ARGS__)  \
+      QB_CASE2(2, 8, __VA_ARGS__) QB_CASE2(2, 9, __VA_ARGS__) QB_CASE2(2, 12, __VA_ARGS__) \
       default: return fail("sweep: no kernel for this link set");                          \
     }                                                                                      \
   } while (0)
@@ -62,7 +63,7 @@ __device__ __forceinline__ double site_epilogue(const SweepArgs& A, int idx, con
 template <int NL, int RC>
 __device__ __forceinline__ void stencil_local(const SweepArgs& A, const Site& s, int idx, double2 (&acc)[3]) {
   const int Vh = A.Vh, p = A.parity, q = 1 - A.parity;
-  const unsigned int sg = RC ? A.L.sgn[(size_t)p * Vh + idx] : 0u;
+  const unsigned int sg = (RC & 3) ? A.L.sgn[(size_t)p * Vh + idx] : 0u;
 #pragma unroll
   for (int mu = 0; mu < 4; mu++) {
     const int st = stride_of(mu, A.X);
@@ -220,7 +221,7 @@ __global__ void __launch_bounds__(SWEEP_BLOCK) k_exterior(const ExtArgs A) {
   const int lex = ((x[3] * A.X[2] + x[2]) * A.X[1] + x[1]) * A.X[0] + x[0];
   const int idx = lex >> 1, Vh = A.Vh;
   double2 acc[3] = {{0, 0}, {0, 0}, {0, 0}};
-  const unsigned int sg = RC ? A.L.sgn[(size_t)A.parity * Vh + idx] : 0u;
+  const unsigned int sg = (RC & 3) ? A.L.sgn[(size_t)A.parity * Vh + idx] : 0u;
   for (int di = 0; di < A.ndir; di++) {
     const ExtDir& D = A.d[di];
     const int mu = D.mu, Xm = A.X[mu], xmu = x[mu], d = D.depth;
@@ -303,7 +304,7 @@ __device__ __forceinline__ void pack_item(const PackArgs& A, int t) {
     const Site s = site_from_face(fidx, mu, Xm - h + jl, A.q, A.X);
     const int idx = s.lex >> 1;
     double2 U[9], v[3], acc[3] = {{0, 0}, {0, 0}, {0, 0}};
-    const unsigned int sg = RC ? A.L.sgn[(size_t)A.q * Vh + idx] : 0u;
+    const unsigned int sg = (RC & 3) ? A.L.sgn[(size_t)A.q * Vh + idx] : 0u;
     if (NL == 2 && j == 1) load_link_k<NL, RC>(U, A.L, mu, 1, A.q, idx, Vh, (sg >> (2 * mu + 1)) & 1u);
     else load_link_k<NL, RC>(U, A.L, mu, 0, A.q, idx, Vh, (sg >> (2 * mu)) & 1u);
     load_vec(v, A.x + idx, Vh);
@@ -399,7 +400,7 @@ __global__ void __launch_bounds__(SWEEP_BLOCK, MINB) k_sweep_fused(const FusedAr
     if (active) {
       const int idx = s.lex >> 1;
       double2 acc[3] = {{0, 0}, {0, 0}, {0, 0}};
-      const unsigned int sg = RC ? A.L.sgn[(size_t)p * Vh + idx] : 0u;
+      const unsigned int sg = (RC & 3) ? A.L.sgn[(size_t)p * Vh + idx] : 0u;
       int di = 0;   // index into E.d of the current split direction (tail only)
 #pragma unroll
       for (int mu = 0; mu < 4; mu++) {

@@ -245,10 +245,13 @@ __device__ __forceinline__ double warp_min(double v) {
   return v;
 }
 
+// mode0 / mode1: storage tried for class 0 / 1: 12, 14 or 0 (class left alone).
+// 14-real form: row2 = phi conj(row0 x row1) with phi = <c, row2> / <c, c> stored as the 7th element; the
+// evidence is the deviation of the rebuilt third row alone (no common scale, no sign bit).
 template <int NL>
 __global__ void __launch_bounds__(LB) k_compress(const double2* __restrict__ u, double2* __restrict__ u12_0,
                                                   double2* __restrict__ u12_1, unsigned short* __restrict__ sgn,
-                                                  unsigned long long* stats, int Vh) {
+                                                  unsigned long long* stats, int Vh, int mode0, int mode1) {
   const int ds = blockIdx.x * LB + threadIdx.x;
   const bool live = ds < 2 * Vh;
   const int par = live ? ds / Vh : 0, idx = live ? ds - par * Vh : 0;
@@ -259,11 +262,14 @@ __global__ void __launch_bounds__(LB) k_compress(const double2* __restrict__ u, 
     for (int mu = 0; mu < 4; mu++) {
 #pragma unroll
       for (int j = 0; j < NL; j++) {
+        const int mode = j == 0 ? mode0 : mode1;
+        if (mode == 0) continue;
+        const int ne = mode == 14 ? 7 : 6;
         const double2* p = u + ((size_t)((mu * NL + j) * 2 + par) * 9) * Vh + idx;
         double2 U[9];
 #pragma unroll
         for (int e = 0; e < 9; e++) U[e] = p[(size_t)e * Vh];
-        double2* o = (j == 0 ? u12_0 : u12_1) + ((size_t)(mu * 2 + par) * 6) * Vh + idx;
+        double2* o = (j == 0 ? u12_0 : u12_1) + ((size_t)(mu * 2 + par) * ne) * Vh + idx;
 #pragma unroll
         for (int e = 0; e < 6; e++) o[(size_t)e * Vh] = U[e];
         const double s2 = U[0].x * U[0].x + U[0].y * U[0].y + U[1].x * U[1].x + U[1].y * U[1].y +
@@ -283,24 +289,46 @@ __global__ void __launch_bounds__(LB) k_compress(const double2* __restrict__ u, 
         c[1].y = -(U[2].x * U[3].y + U[2].y * U[3].x - (U[0].x * U[5].y + U[0].y * U[5].x));
         c[2].x = U[0].x * U[4].x - U[0].y * U[4].y - (U[1].x * U[3].x - U[1].y * U[3].y);
         c[2].y = -(U[0].x * U[4].y + U[0].y * U[4].x - (U[1].x * U[3].y + U[1].y * U[3].x));
-        double re = 0.0;       // Re <c, row2> = sigma |c|^2 / |s|
-#pragma unroll
-        for (int e = 0; e < 3; e++) re += c[e].x * U[6 + e].x + c[e].y * U[6 + e].y;
-        const bool neg = re < 0.0;
-        if (neg) bits |= 1u << (2 * mu + j);
         const double inv = s2 > 0.0 ? rsqrt(s2) : 0.0;
-        const double f = neg ? -inv : inv;
-        double d = fmax(fabs(t2 - s2), sqrt(ov.x * ov.x + ov.y * ov.y)) * inv * inv;
+        double d;
+        if (mode == 14) {
+          double2 num = {0, 0};   // <c, row2> = sum conj(c_e) row2_e
+          double cc = 0.0;
 #pragma unroll
-        for (int e = 0; e < 3; e++)
-          d = fmax(d, fmax(fabs(U[6 + e].x - f * c[e].x), fabs(U[6 + e].y - f * c[e].y)) * inv);
-        if (!(s2 > 0.0)) d = 1.0;
+          for (int e = 0; e < 3; e++) {
+            num.x += c[e].x * U[6 + e].x + c[e].y * U[6 + e].y;
+            num.y += c[e].x * U[6 + e].y - c[e].y * U[6 + e].x;
+            cc += c[e].x * c[e].x + c[e].y * c[e].y;
+          }
+          const double icc = cc > 0.0 ? 1.0 / cc : 0.0;
+          const double2 phi = {num.x * icc, num.y * icc};
+          o[(size_t)6 * Vh] = phi;
+          d = 0.0;
+#pragma unroll
+          for (int e = 0; e < 3; e++) {   // exactly what the sweeps rebuild
+            const double rx = phi.x * c[e].x - phi.y * c[e].y, ry = phi.x * c[e].y + phi.y * c[e].x;
+            d = fmax(d, fmax(fabs(U[6 + e].x - rx), fabs(U[6 + e].y - ry)) * inv);
+          }
+          if (!(s2 > 0.0) || !(cc > 0.0)) d = 1.0;
+        } else {
+          double re = 0.0;       // Re <c, row2> = sigma |c|^2 / |s|
+#pragma unroll
+          for (int e = 0; e < 3; e++) re += c[e].x * U[6 + e].x + c[e].y * U[6 + e].y;
+          const bool neg = re < 0.0;
+          if (neg) bits |= 1u << (2 * mu + j);
+          const double f = neg ? -inv : inv;
+          d = fmax(fabs(t2 - s2), sqrt(ov.x * ov.x + ov.y * ov.y)) * inv * inv;
+#pragma unroll
+          for (int e = 0; e < 3; e++)
+            d = fmax(d, fmax(fabs(U[6 + e].x - f * c[e].x), fabs(U[6 + e].y - f * c[e].y)) * inv);
+          if (!(s2 > 0.0)) d = 1.0;
+        }
         dev[j] = fmax(dev[j], d);
         smin[j] = fmin(smin[j], s2);
         smax[j] = fmax(smax[j], s2);
       }
     }
-    sgn[ds] = (unsigned short)bits;
+    if (sgn) sgn[ds] = (unsigned short)bits;
   }
 #pragma unroll
   for (int j = 0; j < NL; j++) {
@@ -347,7 +375,7 @@ void free_compressed(Gauge& g) {
 }
 
 // Tolerances of the 12-real form: rebuilt matrix within 2e-14 |s| of the stored one, |s|^2 equal
-// over the field to 1e-13 relative (the Dslash parity bar is 1e-13).
+// over the field to 1e-13 relative (the Dslash parity bar is 1e-13).  14-real form: the deviation bar alone.
 constexpr double RECON_DEV_TOL = 2e-14;
 constexpr double RECON_SCALE_TOL = 1e-13;
 
@@ -355,38 +383,51 @@ int compress_links(Gauge& g) {
   Context& c = ctx();
   QB_CUDA(cudaStreamSynchronize(c.stream));
   free_compressed(g);
-  if (!g.want12 || !g.loaded) return 0;
+  if ((!g.want12 && !g.want14) || !g.loaded) return 0;
   const int nl = g.nlinks / 4;
-  const size_t n12 = (size_t)4 * 2 * 6 * c.g.Vh;
-  for (int j = 0; j < nl; j++) QB_CUDA(cudaMalloc(&g.d12[j], sizeof(double2) * n12));
-  QB_CUDA(cudaMalloc(&g.sgn, sizeof(unsigned short) * 2 * (size_t)c.g.Vh));
+  int mode[2] = {0, 0};
+  bool any12 = false, anym = false;
+  for (int j = 0; j < nl; j++) {
+    // 14-real sets on a split lattice: not enabled yet (face-pack / exterior kernels untested in that form) -> 18
+    const bool w14 = ((g.want14 >> j) & 1) && c.g.nranks == 1;
+    mode[j] = w14 ? 14 : (((g.want12 >> j) & 1) ? 12 : 0);
+    if (!mode[j]) continue;
+    anym = true; any12 = any12 || mode[j] == 12;
+    const size_t n = (size_t)4 * 2 * (mode[j] == 14 ? 7 : 6) * c.g.Vh;
+    QB_CUDA(cudaMalloc(&g.d12[j], sizeof(double2) * n));
+  }
+  if (!anym) return 0;
+  if (any12) QB_CUDA(cudaMalloc(&g.sgn, sizeof(unsigned short) * 2 * (size_t)c.g.Vh));
   unsigned long long* stats = reinterpret_cast<unsigned long long*>(c.d_scal + 56);
   unsigned long long init[6] = {0, 0, 0x7ff0000000000000ull, 0x7ff0000000000000ull, 0, 0};
   QB_CUDA(cudaMemcpyAsync(stats, init, sizeof init, cudaMemcpyHostToDevice, c.stream));
   const int grid = (2 * c.g.Vh + LB - 1) / LB;
-  if (nl == 2) k_compress<2><<<grid, LB, 0, c.stream>>>(g.d, g.d12[0], g.d12[1], g.sgn, stats, c.g.Vh);
-  else k_compress<1><<<grid, LB, 0, c.stream>>>(g.d, g.d12[0], nullptr, g.sgn, stats, c.g.Vh);
+  if (nl == 2) k_compress<2><<<grid, LB, 0, c.stream>>>(g.d, g.d12[0], g.d12[1], g.sgn, stats, c.g.Vh, mode[0], mode[1]);
+  else k_compress<1><<<grid, LB, 0, c.stream>>>(g.d, g.d12[0], nullptr, g.sgn, stats, c.g.Vh, mode[0], 0);
   count_launch();
-  if (nl == 2) k_sign_bwd<2><<<grid, LB, 0, c.stream>>>(g.sgn, c.g.Vh, c.g.X[0], c.g.X[1], c.g.X[2], c.g.X[3]);
-  else k_sign_bwd<1><<<grid, LB, 0, c.stream>>>(g.sgn, c.g.Vh, c.g.X[0], c.g.X[1], c.g.X[2], c.g.X[3]);
-  count_launch();
+  if (any12) {
+    if (nl == 2) k_sign_bwd<2><<<grid, LB, 0, c.stream>>>(g.sgn, c.g.Vh, c.g.X[0], c.g.X[1], c.g.X[2], c.g.X[3]);
+    else k_sign_bwd<1><<<grid, LB, 0, c.stream>>>(g.sgn, c.g.Vh, c.g.X[0], c.g.X[1], c.g.X[2], c.g.X[3]);
+    count_launch();
+  }
   QB_CUDA(cudaGetLastError());
   double hs[6];
   QB_CHECK(fetch_scalars(c.d_scal + 56, hs, 6));
-  bool any = false;
+  bool keep_sgn = false;
   for (int j = 0; j < nl; j++) {
+    if (!mode[j]) continue;
     const double dev = hs[j], smin = hs[2 + j], smax = hs[4 + j];
     g.dev[j] = dev;
-    const bool ok = ((g.want12 >> j) & 1) && dev <= RECON_DEV_TOL && smin > 0.0 && (smax - smin) <= RECON_SCALE_TOL * smax;
+    bool ok = dev <= RECON_DEV_TOL && smin > 0.0;
+    if (mode[j] == 12) ok = ok && (smax - smin) <= RECON_SCALE_TOL * smax;
     if (ok) {
-      g.recon[j] = 12;
-      g.inv[j] = 1.0 / sqrt(0.5 * (smin + smax));
-      any = true;
+      g.recon[j] = mode[j];
+      if (mode[j] == 12) { g.inv[j] = 1.0 / sqrt(0.5 * (smin + smax)); keep_sgn = true; }
     } else {
       cudaFree(g.d12[j]); g.d12[j] = nullptr; g.recon[j] = 18;
     }
   }
-  if (!any) { cudaFree(g.sgn); g.sgn = nullptr; }
+  if (!keep_sgn && g.sgn) { cudaFree(g.sgn); g.sgn = nullptr; }
   return 0;
 }
 

@@ -59,12 +59,33 @@ __device__ __forceinline__ void load_link(double2 (&U)[9], const double2* __rest
 #pragma unroll
   for (int e = 0; e < 9; e++) U[e] = __ldcs(p + (size_t)e * Vh);
 }
-// Link U_{mu,j}(par, idx) of a set with NL classes; RC bit j set: class j is read as 12 reals and
-// the third row rebuilt (neg = its sign bit).  j is a compile-time constant after unrolling.
+// conj(row0 x row1) of the two stored rows
+__device__ __forceinline__ void cross_conj(double2 (&c)[3], const double2 (&U)[9]) {
+  c[0].x = U[1].x * U[5].x - U[1].y * U[5].y - (U[2].x * U[4].x - U[2].y * U[4].y);
+  c[0].y = -(U[1].x * U[5].y + U[1].y * U[5].x - (U[2].x * U[4].y + U[2].y * U[4].x));
+  c[1].x = U[2].x * U[3].x - U[2].y * U[3].y - (U[0].x * U[5].x - U[0].y * U[5].y);
+  c[1].y = -(U[2].x * U[3].y + U[2].y * U[3].x - (U[0].x * U[5].y + U[0].y * U[5].x));
+  c[2].x = U[0].x * U[4].x - U[0].y * U[4].y - (U[1].x * U[3].x - U[1].y * U[3].y);
+  c[2].y = -(U[0].x * U[4].y + U[0].y * U[4].x - (U[1].x * U[3].y + U[1].y * U[3].x));
+}
+// Link U_{mu,j}(par, idx) of a set with NL classes.  RC bit j set: class j is read as 12 reals and
+// the third row rebuilt (neg = its sign bit).  RC bit 2+j set: class j is read as 14 reals -- rows 0, 1 and
+// one complex factor phi per link, row2 = phi conj(row0 x row1): links that are c * U(3) (projected smeared
+// links, Naik products of them), whose determinant phase differs from site to site.
+// j is a compile-time constant after unrolling.
 template <int NL, int RC>
 __device__ __forceinline__ void load_link_k(double2 (&U)[9], const Links& L, int mu, int j, int par,
                                             int idx, int Vh, unsigned int neg) {
-  if ((RC >> j) & 1) {
+  if ((RC >> (2 + j)) & 1) {
+    const double2* __restrict__ p = L.u12[j] + ((size_t)(mu * 2 + par) * 7) * Vh + idx;
+#pragma unroll
+    for (int e = 0; e < 6; e++) U[e] = __ldcs(p + (size_t)e * Vh);
+    const double2 phi = __ldcs(p + (size_t)6 * Vh);
+    double2 c[3];
+    cross_conj(c, U);
+#pragma unroll
+    for (int e = 0; e < 3; e++) U[6 + e] = make_double2(phi.x * c[e].x - phi.y * c[e].y, phi.x * c[e].y + phi.y * c[e].x);
+  } else if ((RC >> j) & 1) {
     const double2* __restrict__ p = L.u12[j] + ((size_t)(mu * 2 + par) * 6) * Vh + idx;
 #pragma unroll
     for (int e = 0; e < 6; e++) U[e] = __ldcs(p + (size_t)e * Vh);

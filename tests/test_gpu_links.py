@@ -231,6 +231,102 @@ def test_staged_staple_kernel_is_bit_identical(ctx_factory, monkeypatch, L, grid
     g.free()
 
 
+def test_recon14_on_projected_links(ctx_factory):
+    """14-real link storage (rows 0,1 + one complex factor per link, include/qex_b200.h qexb200_gauge_recon) for
+    links that are U(3) rather than SU(3): nHYP links smeared on the device.  The 12-real form must refuse them,
+    the 14-real form must take them, the Dslash stays within the 1e-13 bar of the 18-real oracle, the solve
+    within +-1 iteration, and the request survives a fresh smear + rephase."""
+    L = (8, 8, 8, 8)
+    qb = ctx_factory(L)
+    lat, g = thin_links(L, phases=False)
+    lo = oracle.QexLayout(L)
+    alpha = (0.4, 0.5, 0.5)
+    want = lat.hyp_smear(g, alpha)
+    lat.setBC(want)
+    lat.stagPhase(want)
+    dg, fl = up(qb, lo, g), qb.DeviceGauge(nlinks=4)
+    hyp = qb.HypCoefs(*alpha)
+    hyp.smear(dg, fl)
+    fl.rephase()
+    s = qb.newStag(fl)
+    x = lat.gaussian_vector(lat.new_rng(3))
+    ref, r18, r14 = lat.vector(), lat.vector(), lat.vector()
+    lat.D(want, ref, x, 0.1)
+    s.D(r18, x, 0.1)
+    got_rc, dev = s.recon(12)
+    assert got_rc[0] == 18 and dev[0] > 1e-3          # det phase != +-1: not s*SU(3)
+    got_rc, dev = s.recon(14)
+    assert got_rc[0] == 14 and dev[0] <= 2e-14, (got_rc, dev)
+    s.D(r14, x, 0.1)
+    assert rel_l2(r14, ref) <= TOL and rel_l2(r14, r18) <= 1e-14
+    for parity in (0, 1):                               # a, b terms and both parities through stagD2
+        a, b = lat.vector(), lat.vector()
+        a[:] = x; b[:] = x
+        lat.stagD2(want, a, x, 0.7, -0.3, parity)
+        qb.stagD2(s, parity, b, x, 0.7, -0.3)
+        sl = slice(0, lat.half) if parity == 0 else slice(lat.half, lat.vol)
+        assert rel_l2(b[sl], a[sl]) <= TOL
+    sol, solref = lat.vector(), lat.vector()
+    sp = qb.SolverParams(r2req=1e-12)
+    s.solve(sol, x, 0.1, sp)
+    st = lat.solve(want, solref, x, 0.1, 1e-12)
+    assert abs(sp.iterations - st.iterations) <= 1
+    assert rel_l2(sol, solref) < 1e-5
+    # sticky: smear again into the same set, phases on the device, still 14 reals and still right
+    hyp.smear(dg, fl)
+    fl.rephase()
+    assert s.recon(14)[0][0] == 14
+    s.D(r14, x, 0.1)
+    assert rel_l2(r14, ref) <= TOL
+    assert s.recon(18)[0] == [18, 18]
+    s.D(r14, x, 0.1)
+    assert np.array_equal(r14, r18)
+    for d in (s, dg, fl):
+        d.free()
+
+
+def test_recon14_on_hisq_long_links(ctx_factory):
+    """HISQ: the fat links are sums of staples (stay at 18 reals), the Naik links are naik * W W W with W in U(3)
+    (src/gauge/fat7l.nim:156-167 on the projected links of src/physics/hisqLinks.nim:32-39): 14 reals."""
+    L = (8, 8, 8, 8)
+    qb = ctx_factory(L)
+    # Links near the unit gauge, like a thermalised configuration.  On a hot start the closed-form projectU of the
+    # reference leaves a few per cent of the W links unitary to 1e-11 only (nearly singular fat links); the Naik
+    # products then miss the 2e-14 bar and the library keeps them at 18 reals, as it must.
+    lat, lo = oracle.Lattice(L), oracle.QexLayout(L)
+    g = lat.projectU(lat.unit_gauge() + 0.15 * np.random.default_rng(8).standard_normal(lat.unit_gauge().shape))
+    lat.setBC(g)
+    lat.stagPhase(g)
+    dg, fl, ll = up(qb, lo, g), qb.DeviceGauge(nlinks=4), qb.DeviceGauge(nlinks=4)
+    qb.HisqCoefs().init().smear(dg, fl, ll)
+    s = qb.newStag3(fl, ll)
+    x = lat.gaussian_vector(lat.new_rng(4))
+    r18, r14 = lat.vector(), lat.vector()
+    s.D(r18, x, 0.05)
+    got_rc, dev = s.recon(12)
+    assert got_rc == [18, 18]
+    got_rc, dev = s.recon(14)
+    assert got_rc == [18, 14] and dev[1] <= 2e-14 and dev[0] > 1e-3, (got_rc, dev)
+    s.D(r14, x, 0.05)
+    assert rel_l2(r14, r18) <= 1e-14
+    assert s.recon(1814)[0] == [18, 14] and s.recon(1418)[0] == [18, 18]
+    fat, lng, efat, elng = hisq_reference(lat, g, oracle.hisq_coefs())
+    links = np.empty((8,) + fat.shape[1:])
+    links[0::2], links[1::2] = fat, lng
+    ref = lat.vector()
+    lat.D(links, ref, x, 0.05)
+    assert rel_l2(r14, ref) <= max(hisq_bar(fat, efat), hisq_bar(lng, elng), TOL)   # device links vs oracle links
+    sp, sp18 = qb.SolverParams(r2req=1e-10), qb.SolverParams(r2req=1e-10)
+    a, b = lat.vector(), lat.vector()
+    s.recon(1814)
+    s.solve(a, x, 0.05, sp)
+    s.recon(18)
+    s.solve(b, x, 0.05, sp18)
+    assert abs(sp.iterations - sp18.iterations) <= 1 and rel_l2(a, b) < 1e-6
+    for d in (s, dg, fl, ll):
+        d.free()
+
+
 def test_hyp_unit_gauge_is_fixed_point(ctx_factory):
     L = (4, 4, 4, 4)
     qb = ctx_factory(L)
