@@ -348,6 +348,104 @@ QB_HD void staple_deriv_x(M3& f1, M3& f2, const double2* g1, int d1, const doubl
     m3_axpy(f2, 1.0, a);
   }
 }
+// ---- the same derivative with the 14 gathers streamed through a two-slot ring ---------------------------
+// (smear.cu k_staple_deriv_pipe; experimental, QEXB200_DERIV_PIPE=1).  The 14 matrices of a site are consumed in
+// five half-steps of <= 3 matrices; half-step n is read from slot n & 1, which is refilled at once with the
+// matrices of half-step n + 2 (of this site or of the thread's next site), so every request has two half-steps
+// of products between issue and use.  G1(x+d2), C(x+d1) and G1(x-d2) stay in registers across half-steps.
+// R is the ring policy: put(slot, m, field, site, Vh) requests a matrix into position m of a slot, get(slot, m)
+// reads it, commit() closes a group of requests, wait1() returns once all groups but the newest have landed,
+// wait0() once all have.  Device: cp.async into shared memory.  tests/emu: a host ring that delivers either at
+// once or as late as the waits allow, which checks the slot reuse order and the wait counts without a GPU.
+// Arithmetic and summation order are those of staple_deriv_x.
+template <class R>
+QB_HD void deriv_ring_fill(R& ring, int slot, int k, const double2* g1, int d1, const double2* g2, int d2,
+                           const double2* c, const LSite& s, const int* X, int Vh) {
+  if (k == 0) {
+    ring.put(slot, 0, g2, s, Vh); ring.put(slot, 1, g1, lhop(s, d2, +1, X), Vh); ring.put(slot, 2, c, lhop(s, d1, +1, X), Vh);
+  } else if (k == 1) {
+    ring.put(slot, 0, c, s, Vh); ring.put(slot, 1, g2, lhop(s, d1, +1, X), Vh); ring.put(slot, 2, g1, s, Vh);
+  } else if (k == 2) {
+    const LSite y = lhop(s, d2, -1, X);
+    ring.put(slot, 0, g2, y, Vh); ring.put(slot, 1, g1, y, Vh); ring.put(slot, 2, c, lhop(y, d1, +1, X), Vh);
+  } else if (k == 3) {
+    const LSite y = lhop(s, d2, -1, X);
+    ring.put(slot, 0, c, y, Vh); ring.put(slot, 1, g2, lhop(y, d1, +1, X), Vh);
+  } else {
+    const LSite z = lhop(s, d1, -1, X);
+    ring.put(slot, 0, g1, z, Vh); ring.put(slot, 1, c, z, Vh); ring.put(slot, 2, g1, lhop(z, d2, +1, X), Vh);
+  }
+}
+// One thread of a persistent block: tiles block, block + nblocks, ... (nblocks even: the parity never changes),
+// site (tile >> 1) * pb + tid of each.  F1, F2 accumulate (read-modify-write of the thread's own site only).
+template <class R>
+QB_HD void staple_deriv_pipe_thread(R& ring, double2* F1, double2* F2, const double2* g1, int d1, const double2* g2,
+                                    int d2, const double2* c, const int* X, int Vh, int ntiles, int block,
+                                    int nblocks, int tid, int pb) {
+  const int par = block & 1;
+  int tile = block;
+  int idx = (tile >> 1) * pb + tid;
+  bool live = tile < ntiles && idx < Vh;
+  LSite s = lsite(live ? idx : 0, par, X);
+  if (live) deriv_ring_fill(ring, 0, 0, g1, d1, g2, d2, c, s, X, Vh);
+  ring.commit();
+  if (live) deriv_ring_fill(ring, 1, 1, g1, d1, g2, d2, c, s, X, Vh);
+  ring.commit();
+  int p = 0;   // slot of this site's half-step 0 (five half-steps per site: it alternates)
+  while (tile < ntiles) {
+    const int ntile = tile + nblocks;
+    const int nidx = (ntile >> 1) * pb + tid;
+    const bool nlive = ntile < ntiles && nidx < Vh;
+    const LSite ns = lsite(nlive ? nidx : 0, par, X);
+    const int q = p ^ 1;
+    M3 f1 = m3_zero(), f2 = m3_zero();
+    if (live) { f1 = m3_ld(F1, s, Vh); f2 = m3_ld(F2, s, Vh); }
+    M3 G1x2, Cx1, G1y;
+    ring.wait1();   // half-step 0: g2(x), g1(x+d2), c(x+d1)
+    {
+      const M3 A = ring.get(p, 0);
+      G1x2 = ring.get(p, 1); Cx1 = ring.get(p, 2);
+      if (live) deriv_ring_fill(ring, p, 2, g1, d1, g2, d2, c, s, X, Vh);
+      ring.commit();
+      m3_axpy(f1, 1.0, m3_mul_na(m3_mul(A, G1x2), Cx1));
+    }
+    ring.wait1();   // half-step 1: c(x), g2(x+d1), g1(x)
+    {
+      const M3 A = ring.get(q, 0), B = ring.get(q, 1), G1s = ring.get(q, 2);
+      if (live) deriv_ring_fill(ring, q, 3, g1, d1, g2, d2, c, s, X, Vh);
+      ring.commit();
+      m3_axpy(f1, 1.0, m3_mul_na(m3_mul(A, G1x2), B));
+      m3_axpy(f2, 1.0, m3_mul_na(m3_mul(G1s, Cx1), G1x2));
+    }
+    ring.wait1();   // half-step 2: g2(y), g1(y), c(y+d1), y = x-d2
+    {
+      const M3 A = ring.get(p, 0);
+      G1y = ring.get(p, 1);
+      const M3 B = ring.get(p, 2);
+      if (live) deriv_ring_fill(ring, p, 4, g1, d1, g2, d2, c, s, X, Vh);
+      ring.commit();
+      m3_axpy(f1, 1.0, m3_mul(m3_mul_an(A, G1y), B));
+    }
+    ring.wait1();   // half-step 3: c(y), g2(y+d1)
+    {
+      const M3 A = ring.get(q, 0), B = ring.get(q, 1);
+      if (nlive) deriv_ring_fill(ring, q, 0, g1, d1, g2, d2, c, ns, X, Vh);
+      ring.commit();
+      m3_axpy(f1, 1.0, m3_mul(m3_mul_an(A, G1y), B));
+    }
+    ring.wait1();   // half-step 4: g1(z), c(z), g1(z+d2), z = x-d1
+    {
+      const M3 A = ring.get(p, 0), B = ring.get(p, 1), C = ring.get(p, 2);
+      if (nlive) deriv_ring_fill(ring, p, 1, g1, d1, g2, d2, c, ns, X, Vh);
+      ring.commit();
+      m3_axpy(f2, 1.0, m3_mul(m3_mul_an(A, B), C));
+    }
+    if (live) { m3_st(F1, s, Vh, f1); m3_st(F2, s, Vh, f2); }
+    tile = ntile; idx = nidx; live = nlive; s = ns; p = q;
+  }
+  ring.wait0();
+}
+
 // Naik term of fat7lDeriv (src/gauge/fat7lderiv.nim:300-326), gathered in place; U = llgauge[mu], M = llmid[mu]:
 //   (U^+ M)(x-mu) U(x+mu)^+  +  M(x) (U(x+mu) U(x+2mu))^+  +  U(x-mu)^+ U(x-2mu)^+ M(x-2mu)
 template <bool MR>

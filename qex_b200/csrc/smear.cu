@@ -717,6 +717,71 @@ __global__ void __launch_bounds__(SB, QB_DERIV_MINB) k_staple_deriv(const DerivA
   m3_st(a.f1, s, a.Vh, f1);
   m3_st(a.f2, s, a.Vh, f2);
 }
+// The same through the two-slot shared-memory ring of linkops.cuh staple_deriv_pipe_thread (single rank).
+// EXPERIMENTAL, off unless QEXB200_DERIV_PIPE=1: the pipeline logic is checked on the host (tests/test_links_emu.py
+// runs this very body on a host ring), but the kernel has not been timed on a B200 yet (tools/ab_deriv_pipe.py).
+struct SmemRing {
+  double2* my;   // this thread's column of the block's ring: element (slot, m, e) at my[((slot * 3 + m) * 9 + e) * PB]
+  QB_HD void put(int slot, int m, const double2* f, const LSite& s, int Vh) {
+#if defined(__CUDA_ARCH__)
+    const double2* p = f + (size_t)s.par * 9 * Vh + s.idx;
+#pragma unroll
+    for (int e = 0; e < 9; e++) cp16(my + ((slot * 3 + m) * 9 + e) * PB, p + (size_t)e * Vh);
+#endif
+  }
+  QB_HD M3 get(int slot, int m) const {
+    M3 r;
+#pragma unroll
+    for (int e = 0; e < 9; e++) r.e[e] = my[((slot * 3 + m) * 9 + e) * PB];
+    return r;
+  }
+  QB_HD void commit() {
+#if defined(__CUDA_ARCH__)
+    cp_commit();
+#endif
+  }
+  QB_HD void wait1() {
+#if defined(__CUDA_ARCH__)
+    cp_wait1();
+#endif
+  }
+  QB_HD void wait0() {
+#if defined(__CUDA_ARCH__)
+    cp_wait0();
+#endif
+  }
+};
+__global__ void __launch_bounds__(PB, QB_PIPE_MINB) k_staple_deriv_pipe(const DerivArgs a, int ntiles) {
+  extern __shared__ double2 ring[];
+  SmemRing r = {ring + threadIdx.x};
+  staple_deriv_pipe_thread(r, a.f1, a.f2, a.g1, a.d1, a.g2, a.d2, a.c, a.X, a.Vh, ntiles, (int)blockIdx.x, (int)gridDim.x,
+                           (int)threadIdx.x, PB);
+}
+static bool deriv_pipe_enabled() {
+  const char* e = getenv("QEXB200_DERIV_PIPE");
+  return e && e[0] == '1';
+}
+static int launch_deriv_pipe(const DerivArgs& a) {
+  Context& c = ctx();
+  static int resident = 0;
+  if (!resident) {
+    QB_CUDA(cudaFuncSetAttribute(k_staple_deriv_pipe, cudaFuncAttributeMaxDynamicSharedMemorySize, PIPE_SMEM));
+    QB_CUDA(cudaFuncSetAttribute(k_staple_deriv_pipe, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    int dev = 0, sms = 0, occ = 0;
+    QB_CUDA(cudaGetDevice(&dev));
+    QB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    QB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_staple_deriv_pipe, PB, PIPE_SMEM));
+    if (occ < 1) return fail("k_staple_deriv_pipe does not fit on an SM");
+    resident = sms * occ;
+  }
+  const int ntiles = grid_par(c.g.Vh, PB);
+  int grid = resident;
+  if (const char* e = getenv("QEXB200_PIPE_GRID")) grid = atoi(e) > 1 ? atoi(e) : 2;
+  grid -= grid & 1;
+  if (grid > ntiles) grid = ntiles;
+  k_staple_deriv_pipe<<<grid, PB, PIPE_SMEM, c.stream>>>(a, ntiles);
+  return 0;
+}
 static int launch_deriv(double2* f1, double2* f2, const double2* g1, int d1, const double2* g2, int d2, const double2* ch) {
   Context& c = ctx();
   DerivArgs a;
@@ -727,6 +792,8 @@ static int launch_deriv(double2* f1, double2* f2, const double2* g1, int d1, con
     if (!in_arena(g1) || !in_arena(g2) || !in_arena(ch)) return fail("smeared force on a split lattice: a field lives outside the peer arena");
     QB_CHECK(xbarrier());
     k_staple_deriv<true><<<grid, SB, 0, c.stream>>>(a);
+  } else if (deriv_pipe_enabled()) {
+    QB_CHECK(launch_deriv_pipe(a));
   } else {
     k_staple_deriv<false><<<grid, SB, 0, c.stream>>>(a);
   }

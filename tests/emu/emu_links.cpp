@@ -6,6 +6,7 @@
 
 using namespace qb;
 
+#include <vector>
 extern "C" {
 // fields in the DEVICE layout double2[2][9][Vh]
 void emu_staple_field(const double* G, const double* L, int dG, int dL, const int* X, double* out) {
@@ -63,6 +64,46 @@ void emu_staple_deriv_field(double* f1, double* f2, const double* g1, int d1, co
       staple_deriv_x<false>(a, b, (const double2*)g1, d1, (const double2*)g2, d2, (const double2*)c, s, X, Vh, none);
       m3_st((double2*)f1, s, Vh, a);
       m3_st((double2*)f2, s, Vh, b);
+    }
+}
+// Host ring for staple_deriv_pipe_thread.  late = 0: a request is delivered when it is made (the earliest a
+// cp.async can land: a slot refilled before its last read would show).  late = 1: requests are queued per
+// commit group and delivered only when a wait demands it (the latest they may land: a read ahead of its wait,
+// or a wrong wait count, would return stale data).
+struct HostRing {
+  struct Req { double2* dst; const double2* src; int stride; };
+  double2 buf[2 * 27];
+  std::vector<std::vector<Req>> groups;
+  std::vector<Req> open;
+  int late;
+  explicit HostRing(int l) : late(l) { for (auto& b : buf) b = make_double2(1e300, -1e300); }
+  static void deliver(const Req& r) { for (int e = 0; e < 9; e++) r.dst[e] = r.src[(size_t)e * r.stride]; }
+  void put(int slot, int m, const double2* f, const LSite& s, int Vh) {
+    Req r = {buf + (slot * 3 + m) * 9, f + (size_t)s.par * 9 * Vh + s.idx, Vh};
+    if (late) open.push_back(r); else deliver(r);
+  }
+  M3 get(int slot, int m) const {
+    M3 r;
+    for (int e = 0; e < 9; e++) r.e[e] = buf[(slot * 3 + m) * 9 + e];
+    return r;
+  }
+  void commit() { groups.push_back(open); open.clear(); }
+  void drain(size_t keep) {
+    while (groups.size() > keep) { for (const Req& r : groups.front()) deliver(r); groups.erase(groups.begin()); }
+  }
+  void wait1() { drain(1); }
+  void wait0() { drain(0); }
+};
+// f1, f2 += symStapleDeriv through the ring pipeline: nblocks persistent blocks of pb threads, run one thread after another
+void emu_staple_deriv_pipe_field(double* f1, double* f2, const double* g1, int d1, const double* g2, int d2, const double* c,
+                                 const int* X, int nblocks, int pb, int late) {
+  const int Vh = X[0] * X[1] * X[2] * X[3] / 2;
+  const int ntiles = 2 * ((Vh + pb - 1) / pb);
+  for (int b = 0; b < nblocks; b++)
+    for (int t = 0; t < pb; t++) {
+      HostRing ring(late);
+      staple_deriv_pipe_thread(ring, (double2*)f1, (double2*)f2, (const double2*)g1, d1, (const double2*)g2, d2,
+                               (const double2*)c, X, Vh, ntiles, b, nblocks, t, pb);
     }
 }
 // out += naik * naik-derivative(U, M) in direction mu

@@ -31,6 +31,7 @@ def emu():
     lib.emu_staple_field_mr.argtypes = [C.POINTER(C.c_char_p), C.c_int, C.c_int, C.POINTER(C.c_ubyte), C.c_longlong,
                                         C.c_longlong, C.c_int, C.c_int, ip, dp]
     lib.emu_naik_deriv_field.argtypes = [dp, dp, dp, C.c_int, C.c_double, ip]
+    lib.emu_staple_deriv_pipe_field.argtypes = [dp, dp, dp, C.c_int, dp, C.c_int, dp, ip, C.c_int, C.c_int, C.c_int]
     return lib
 
 
@@ -141,6 +142,27 @@ def test_staple_deriv_matches_oracle(emu):
             emu.emu_staple_deriv_field(dp(e1), dp(e2), dp(to_dev(g[d1])), d1, dp(to_dev(g[d2])), d2, dp(to_dev(c)), X)
             assert np.linalg.norm(from_dev(e1) - w1) / np.linalg.norm(w1) < 1e-14, (d1, d2)
             assert np.linalg.norm(from_dev(e2) - w2) / np.linalg.norm(w2) < 1e-14, (d1, d2)
+
+
+@pytest.mark.parametrize("late", [0, 1])
+@pytest.mark.parametrize("nblocks,pb", [(2, 64), (6, 32), (64, 8)])
+def test_staple_deriv_ring_pipeline_is_bit_identical(emu, nblocks, pb, late):
+    """staple_deriv_pipe_thread (the body of k_staple_deriv_pipe) on a host ring, with requests delivered at once
+    (late=0) and as late as its waits allow (late=1): slot reuse order, wait counts, the hand-over from a site to
+    the thread's next site and the ragged last tile -- bit for bit the plain gather's result."""
+    lat = oracle.Lattice(L)
+    g = lat.random_gauge(lat.new_rng(9))
+    rng = np.random.default_rng(2)
+    c = rng.standard_normal(g[0].shape)
+    X = (C.c_int * 4)(*L)
+    for d1, d2 in ((0, 1), (1, 0), (2, 3), (3, 0), (1, 2)):
+        f1, f2 = rng.standard_normal(c.shape), rng.standard_normal(c.shape)
+        e1, e2, p1, p2 = to_dev(f1), to_dev(f2), to_dev(f1), to_dev(f2)
+        G1, G2, Cc = to_dev(g[d1]), to_dev(g[d2]), to_dev(c)
+        emu.emu_staple_deriv_field(dp(e1), dp(e2), dp(G1), d1, dp(G2), d2, dp(Cc), X)
+        emu.emu_staple_deriv_pipe_field(dp(p1), dp(p2), dp(G1), d1, dp(G2), d2, dp(Cc), X, nblocks, pb, late)
+        assert np.array_equal(p1, e1) and np.array_equal(p2, e2), (d1, d2)
+        assert not np.array_equal(e1, to_dev(f1))
 
 
 def test_project_tah(emu):
