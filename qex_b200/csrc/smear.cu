@@ -129,7 +129,10 @@ static inline int grid_par(int Vh, int block) { return 2 * ((Vh + block - 1) / b
 // cp.async (LDGSTS): the ring has one slot for the upper bracket's three matrices and one for the lower's, and
 // each slot is refilled for the NEXT (site, pair) as soon as it has been read, so a full pair of matrix products
 // (and the projection, when fused) runs between the request and the use of every matrix.  No block barrier:
-// a thread only ever reads what it staged itself.  Blocks are persistent and keep the parity interleave
+// a thread only ever reads what it staged itself.  Slot reuse: the ld.shared of a slot are issued before the
+// cp.async that refill it (program order, "memory" clobbers), and a refill cannot land before its global read
+// returns (>= an L2 round trip, hundreds of cycles after the 16-byte shared loads have been served in order by the
+// same LSU); the bit-for-bit A/B test against the register kernel runs this reuse millions of times per launch.  Blocks are persistent and keep the parity interleave
 // (the grid is even, block b stays on parity b & 1).  The arithmetic is that of staple_pair_x, in the same order.
 #ifndef QB_PB
 #define QB_PB 64
