@@ -42,6 +42,7 @@ extern "C" {
 
 typedef int qexb200_gauge_t; /* handle of a device-resident link set */
 typedef int qexb200_field_t; /* handle of a device-resident colour-vector field */
+typedef int qexb200_rng_t;   /* handle of a device-resident per-site random number field */
 
 /* SolverParams, src/solvers/solverBase.nim:10-28 (inputs first, outputs after). */
 typedef struct {
@@ -300,6 +301,22 @@ int qexb200_stagD2deriv(qexb200_gauge_t s, double* const* g, const double* c, co
  * f[k](x) (+)= (x even ? scale_even : scale_odd) * a(x) (x) b(x+h_k)^+; accumulate == 0 overwrites. */
 int qexb200_dev_outer(qexb200_gauge_t f, qexb200_field_t a, qexb200_field_t b, double scale_even,
                       double scale_odd, int accumulate);
+
+/* ---- per-site random number field: the input generator of the reference's tests and benchmarks ---------- */
+
+/* newRNGField(RngMilc6, lo, seed) (src/rng/distributionUtils.nim:306-331): one RngMilc6 (src/rng/milcrng.nim:92-154)
+ * per site, seeded with the GLOBAL lexicographic site index, so the fields do not depend on the rank geometry.  The
+ * integer streams are bit-identical with QEX's; a deviate (milcrng.nim:158-188) is float32, as in QEX. */
+int qexb200_rng_create(unsigned long long seed, qexb200_rng_t* r);
+int qexb200_rng_destroy(qexb200_rng_t r);
+/* g.random r (src/gauge/gaugeUtils.nim:1348-1355,1424-1429): field by field, 18 deviates per site, projectSU. */
+int qexb200_gauge_random(qexb200_gauge_t g, qexb200_rng_t r);
+/* p.randomTAH r (gaugeUtils.nim:1353-1383,1452-1454): 8 deviates per site and field. */
+int qexb200_gauge_randomTAH(qexb200_gauge_t g, qexb200_rng_t r);
+/* g.unit (gaugeUtils.nim:1448-1450). */
+int qexb200_gauge_unit(qexb200_gauge_t g);
+/* v.gaussian r (src/rng/distributionUtils.nim:65-97): 6 deviates per site. */
+int qexb200_field_gaussian(qexb200_field_t f, qexb200_rng_t r);
 
 /* ---- halo plan (pure host arithmetic, usable without a GPU) ---------------- */
 

@@ -61,6 +61,7 @@ def lib():
         L.orc_rng_next_site.argtypes = [vp, C.c_int]
         L.orc_gaussian.argtypes = [vp, vp, dp, C.c_int]
         L.orc_random_gauge.argtypes = [vp, vp, dp, C.c_int]
+        L.orc_random_tah.argtypes = [vp, vp, dp]
         L.orc_plaq.argtypes = [vp, dp, dp]
         L.orc_setbc.argtypes = [vp, dp]
         L.orc_stagphase.argtypes = [vp, dp]
@@ -158,6 +159,13 @@ class Lattice:
         g = self.gauge(n)
         lib().orc_random_gauge(self.h, rng.h, _dp(g), n)
         return g
+
+    def random_tah(self, rng, n=4):
+        """randomTAH(g, r) (gaugeUtils.nim:1353-1383,1452-1454): field by field, 8 deviates per site each."""
+        p = self.gauge(n)
+        for mu in range(n):
+            lib().orc_random_tah(self.h, rng.h, _dp(p[mu]))
+        return p
 
     def unit_gauge(self, n=4):
         g = self.gauge(n)

@@ -291,6 +291,28 @@ void orc_gaussian(void* lat, void* rng, double* f, int nreal) {
     for (int k = 0; k < nreal; k++) f[(size_t)i * nreal + k] = rng_gaussian(&r[i]);
 }
 
+// randomTAH(Field, RNGField) for nc = 3: randTah3, gauge/gaugeUtils.nim:1353-1383 -- eight deviates per
+// site in the order r3, r8, r01, r02, r12, i01, i02, i12 (each the float32 result of gaussian widened to
+// float64, times sqrt(1/2)); the matrix is traceless anti-Hermitian with an imaginary diagonal.
+void orc_random_tah(void* lat, void* rng, double* f) {
+  Lat* l = (Lat*)lat; Rng* r = (Rng*)rng;
+  const double s2 = 0.70710678118654752440, s3 = 0.57735026918962576450;
+  for (int i = 0; i < l->vol; i++) {
+    double* m = f + (size_t)i * 18;
+    Rng* s = &r[i];
+    double r3 = s2 * rng_gaussian(s);
+    double r8 = s2 * s3 * rng_gaussian(s);
+    double r01 = s2 * rng_gaussian(s), r02 = s2 * rng_gaussian(s), r12 = s2 * rng_gaussian(s);
+    double i01 = s2 * rng_gaussian(s), i02 = s2 * rng_gaussian(s), i12 = s2 * rng_gaussian(s);
+#define TAH_SET(a, b, re, im) do { m[((a) * 3 + (b)) * 2] = (re); m[((a) * 3 + (b)) * 2 + 1] = (im); } while (0)
+    TAH_SET(0, 0, 0.0, r8 + r3); TAH_SET(1, 1, 0.0, r8 - r3); TAH_SET(2, 2, 0.0, -2 * r8);
+    TAH_SET(0, 1, r01, i01); TAH_SET(1, 0, -r01, i01);
+    TAH_SET(0, 2, r02, i02); TAH_SET(2, 0, -r02, i02);
+    TAH_SET(1, 2, r12, i12); TAH_SET(2, 1, -r12, i12);
+#undef TAH_SET
+  }
+}
+
 // ---------------------------------------------------------------------------
 // 3x3 complex algebra
 // ---------------------------------------------------------------------------

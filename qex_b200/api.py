@@ -161,6 +161,12 @@ def lib():
         L.qexb200_solve_multi.argtypes = [C.c_int, C.POINTER(dp), dp, dp, C.c_int, spp]
         L.qexb200_dev_solveXX_multi.argtypes = [C.c_int, C.c_int, ip, C.c_int, dp, C.c_int, spp]
         L.qexb200_dev_solve_multi.argtypes = [C.c_int, ip, C.c_int, dp, C.c_int, spp]
+        L.qexb200_rng_create.argtypes = [C.c_ulonglong, ip]
+        L.qexb200_rng_destroy.argtypes = [C.c_int]
+        L.qexb200_gauge_random.argtypes = [C.c_int, C.c_int]
+        L.qexb200_gauge_randomTAH.argtypes = [C.c_int, C.c_int]
+        L.qexb200_gauge_unit.argtypes = [C.c_int]
+        L.qexb200_field_gaussian.argtypes = [C.c_int, C.c_int]
         L.qexb200_field_create.argtypes = [ip]
         L.qexb200_field_destroy.argtypes = [C.c_int]
         L.qexb200_field_upload.argtypes = [C.c_int, dp]
@@ -345,6 +351,25 @@ class SolverParams:
                                             1e-9 * self.flops / s, self.r2)
 
 
+# ---- per-site random number field (newRNGField, src/rng/distributionUtils.nim:306-331) ------------
+class RngField:
+    """newRNGField(RngMilc6, lo, seed) on the device; g.random(r), p.randomTAH(r) and v.gaussian(r) draw from it."""
+
+    def __init__(self, seed=17 ** 7):
+        h = C.c_int()
+        _ck(lib().qexb200_rng_create(C.c_ulonglong(int(seed)), C.byref(h)))
+        self.h = h.value
+
+    def free(self):
+        if self.h is not None and is_initialized():
+            lib().qexb200_rng_destroy(self.h)
+        self.h = None
+
+
+def newRNGField(seed=17 ** 7):
+    return RngField(seed)
+
+
 # ---- device-resident field -------------------------------------------------------
 class DeviceField:
     def __init__(self, host=None):
@@ -363,6 +388,10 @@ class DeviceField:
 
     def zero(self):
         _ck(lib().qexb200_field_zero(self.h))
+
+    def gaussian(self, rng):
+        """v.gaussian r (src/rng/distributionUtils.nim:65-97)."""
+        _ck(lib().qexb200_field_gaussian(self.h, rng.h))
 
     def norm2(self, subset=ALL):
         o = C.c_double()
@@ -405,6 +434,18 @@ class DeviceGauge:
 
     def rephase(self):
         _ck(lib().qexb200_gauge_rephase(self.h))
+
+    def random(self, rng):
+        """g.random r (src/gauge/gaugeUtils.nim:1424-1429)."""
+        _ck(lib().qexb200_gauge_random(self.h, rng.h))
+
+    def randomTAH(self, rng):
+        """p.randomTAH r (gaugeUtils.nim:1353-1383,1452-1454)."""
+        _ck(lib().qexb200_gauge_randomTAH(self.h, rng.h))
+
+    def unit(self):
+        """g.unit (gaugeUtils.nim:1448-1450)."""
+        _ck(lib().qexb200_gauge_unit(self.h))
 
     def loadGauge(self, fn):
         """loadGauge(g, fn) (src/gauge/gaugeUtils.nim:87-106): first lattice record of a SciDAC/ILDG file.

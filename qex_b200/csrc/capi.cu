@@ -57,6 +57,7 @@ static Gauge g_hf;   // staging link set of the host-field force calls
 static std::map<int, HypState> g_hyps;
 static std::map<int, HisqState> g_hisqs;
 static std::map<int, Field> g_fields;
+static std::map<int, RngField> g_rngs;
 static int g_next_handle = 1;
 
 static int need_ctx() {
@@ -465,6 +466,8 @@ int qexb200_finalize(void) {
   for (auto& kv : g_gauges) { links_free(kv.second.d, kv.second.nlinks, kv.second.arena); free_compressed(kv.second); }
   for (auto& kv : g_fields) cudaFree(kv.second.d);
   g_gauges.clear(); g_fields.clear();
+  for (auto& kv : g_rngs) rng_destroy(&kv.second);
+  g_rngs.clear();
   if (g_sw.ok) { cudaFree(g_sw.r.d); cudaFree(g_sw.y.d); cudaFree(g_sw.d.d); g_sw = SolveWork(); }
   for (auto& f : g_mw.ys) cudaFree(f.d);
   for (auto& f : g_mw.hx) cudaFree(f.d);
@@ -515,6 +518,14 @@ int qexb200_local_sites(int* nsites, int* neven) {
 int qexb200_gauge_create(int nlinks, qexb200_gauge_t* out) {
   QB_CHECK(need_ctx());
   if (nlinks != 4 && nlinks != 8) return fail("gauge_create: nlinks must be 4 (naive) or 8 (fat+Naik), got %d", nlinks);
+  // the three-hop neighbour index wraps once (dslash.cu hop_site, layout.cu k_sign_bwd): x +- 3 must stay within
+  // one period, i.e. every local extent >= 4 (extents are even).  QEX's own limit is len <= outerGeom
+  // (layout/shiftX.nim:96-97).
+  if (nlinks == 8)
+    for (int d = 0; d < 4; d++)
+      if (g_ctx.g.X[d] < 4)
+        return fail("gauge_create: fat+Naik link sets (nlinks=8) need every local extent >= 4 (three-hop shifts); "
+                    "direction %d has %d", d, g_ctx.g.X[d]);
   Gauge g;
   g.nlinks = nlinks;
   QB_CHECK(links_alloc(nlinks, &g.d, &g.arena));
@@ -832,6 +843,55 @@ int qexb200_gauge_split3(qexb200_gauge_t hfl, qexb200_gauge_t hll, qexb200_gauge
   return links_written(ll);
 }
 
+// ---- per-site random number field on the device (rng.cu) -----------------------
+int qexb200_rng_create(unsigned long long seed, qexb200_rng_t* out) {
+  QB_CHECK(need_ctx());
+  RngField r;
+  QB_CHECK(rng_create((unsigned int)seed, &r));
+  const int h = g_next_handle++;
+  g_rngs[h] = r;
+  *out = h;
+  return 0;
+}
+int qexb200_rng_destroy(qexb200_rng_t h) {
+  QB_CHECK(need_ctx());
+  auto it = g_rngs.find(h);
+  if (it == g_rngs.end()) return fail("invalid rng handle %d", h);
+  cudaStreamSynchronize(g_ctx.stream);
+  rng_destroy(&it->second);
+  g_rngs.erase(it);
+  return 0;
+}
+static int get_rng(int h, RngField** r) {
+  auto it = g_rngs.find(h);
+  if (it == g_rngs.end()) return fail("invalid rng handle %d", h);
+  *r = &it->second;
+  return 0;
+}
+int qexb200_gauge_random(qexb200_gauge_t hg, qexb200_rng_t hr) {
+  QB_CHECK(need_ctx());
+  Gauge* g; QB_CHECK(get_gauge(hg, &g));
+  RngField* r; QB_CHECK(get_rng(hr, &r));
+  return rng_matrix_fields(*r, *g, 0);
+}
+int qexb200_gauge_randomTAH(qexb200_gauge_t hg, qexb200_rng_t hr) {
+  QB_CHECK(need_ctx());
+  Gauge* g; QB_CHECK(get_gauge(hg, &g));
+  RngField* r; QB_CHECK(get_rng(hr, &r));
+  return rng_matrix_fields(*r, *g, 1);
+}
+int qexb200_gauge_unit(qexb200_gauge_t hg) {
+  QB_CHECK(need_ctx());
+  Gauge* g; QB_CHECK(get_gauge(hg, &g));
+  return unit_links(*g);
+}
+int qexb200_field_gaussian(qexb200_field_t hf_, qexb200_rng_t hr) {
+  QB_CHECK(need_ctx());
+  Field* f; QB_CHECK(get_field(hf_, &f));
+  RngField* r; QB_CHECK(get_rng(hr, &r));
+  return rng_gaussian_vector(*r, *f);
+}
+
 // ---- device fields -----------------------------------------------------------
 int qexb200_field_create(qexb200_field_t* out) {
   QB_CHECK(need_ctx());
@@ -927,7 +987,8 @@ static int op_outer(Gauge& f, const Field& a, const Field& b, double ce, double 
   const OuterPair p = {a.d, b.d, ce, co};
   QB_CHECK(outer_products(f, &p, 1, acc));
   f.loaded = true;
-  return 0;
+  // the links changed in place: refresh a 12/14-real copy if one was asked for (none: no sync, nothing to do)
+  return (f.want12 || f.want14) ? compress_links(f) : 0;
 }
 // stagDeriv(s, f, x), stagD.nim:635-664: f[mu] += x (x) x(+mu)^+ on even sites, -= on odd sites, then s.rephase f
 static int op_stagDeriv(Gauge& f, const Field& x) {
@@ -940,7 +1001,7 @@ static int op_stagD2deriv(Gauge& g, const Field& c, const Field& x) {
   const OuterPair p[2] = {{c.d, x.d, 1.0, 1.0}, {x.d, c.d, -1.0, -1.0}};
   QB_CHECK(outer_products(g, p, 2, true));
   g.loaded = true;
-  return 0;
+  return (g.want12 || g.want14) ? compress_links(g) : 0;
 }
 static int same_links(const Gauge* s, const Gauge* f, const char* who) {
   if (s->nlinks != f->nlinks) return fail("%s: operator has %d link fields, force field %d", who, s->nlinks, f->nlinks);

@@ -289,6 +289,16 @@ int read_scidac(Gauge& g, const char* fn, unsigned sums[4]);
 int scidac_lattice(const char* fn, int dims[4]);
 int io_free();
 
+// ---- rng.cu (per-site RngMilc6 field on the device: the reference's input generator) ----
+struct RngField {
+  unsigned int* st = nullptr;   // [9][V]: r0..r6, ic, mult of RngMilc6; site = parity * Vh + idx
+};
+int rng_create(unsigned int seed, RngField* r);
+void rng_destroy(RngField* r);
+int rng_gaussian_vector(RngField& r, Field& f);
+int rng_matrix_fields(RngField& r, Gauge& g, int mode);   // 0: g.random r, 1: g.randomTAH r
+int unit_links(Gauge& g);
+
 // ---- comm.cu ----------------------------------------------------------------
 int halo_setup();
 int plan_halo(const Geom& g, int nl, std::vector<HaloDir>& dirs, size_t* total);

@@ -12,6 +12,7 @@
 // File format restated from the public SciDAC/LIME conventions (c-lime, QIO): see scidac_* below.
 // The reference tree holds no SciDAC file, so this row is pinned only by an independent writer in
 // tests/ (format round trip) -- "parity unpinned" against a QEX-written file.
+#include <algorithm>
 #include <fcntl.h>
 #include <sys/stat.h>
 #include <unistd.h>
@@ -214,7 +215,14 @@ int read_scidac(Gauge& g, const char* fn, unsigned sums[4]) {
   const size_t row = (size_t)X[0] * site_bytes;
   bool ok = true;
   if (c.g.nranks == 1) {
-    ok = pread(fd, buf.data(), buf.size(), info.data_off) == (ssize_t)buf.size();
+    // one pread moves at most ~2 GiB on Linux: loop until the record is in (48^3 x 96 fp64 is 6.1 GB)
+    size_t done = 0;
+    while (done < buf.size()) {
+      const size_t want = std::min(buf.size() - done, (size_t)1 << 30);
+      const ssize_t n = pread(fd, buf.data() + done, want, info.data_off + (long long)done);
+      if (n <= 0) { ok = false; break; }
+      done += (size_t)n;
+    }
   } else {
     for (int x3 = 0; x3 < X[3] && ok; x3++) for (int x2 = 0; x2 < X[2] && ok; x2++) for (int x1 = 0; x1 < X[1] && ok; x1++) {
       const long long gl = (((long long)(c.g.rc[3] * X[3] + x3) * Lg[2] + (c.g.rc[2] * X[2] + x2)) * Lg[1] + (c.g.rc[1] * X[1] + x1)) * Lg[0] + (long long)c.g.rc[0] * X[0];

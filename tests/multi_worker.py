@@ -110,6 +110,23 @@ def gpu_case(L, G, nlinks, inner, rank, world, local_rank, dist, transport="nccl
     n2 = fx.norm2()
     assert abs(n2 - lat.norm2(x)) <= 1e-12 * n2
     fx.free()
+    # device RNG field: seeded with the GLOBAL lexicographic site index, so every rank draws its block of the same
+    # global fields (distributionUtils.nim:319-324)
+    if inner == (1, 1, 1, 1):
+        ro = lat.new_rng(12345)
+        go, vo = lat.random_gauge(ro, 4), lat.gaussian_vector(ro)
+        rd = qb.newRNGField(12345)
+        dg, dv = qb.DeviceGauge(nlinks=4), qb.DeviceField()
+        dg.random(rd)
+        dv.gaussian(rd)
+        gd = [np.zeros_like(mine(go[0])) for _ in range(4)]
+        dg.download(gd)
+        vd = dv.download(np.zeros_like(mine(vo)))
+        assert np.count_nonzero(vd != mine(vo)) <= 1, "device gaussian field differs from the oracle's block"
+        res["rng_links"] = max(rel_l2(gd[k], mine(go[k])) for k in range(4))
+        assert res["rng_links"] <= 1e-9, res
+        for d in (dg, dv, rd):
+            d.free()
     # CG and the full solve
     m, r2req = 0.1, 1e-10
     want = lat.vector()

@@ -1,0 +1,132 @@
+"""The per-site random number field on the device (csrc/rng.cu) against the oracle's restatement of RngMilc6 /
+gaussian / g.random / randomTAH, and against the reference's own golden numbers."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from util import rel_l2
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+@pytest.fixture()
+def ctx(qb):
+    def make(L):
+        if qb.is_initialized():
+            qb.finalize()
+        qb.init(L)
+        return qb
+    yield make
+    if qb.is_initialized():
+        qb.finalize()
+
+
+def _down(qb, lat, dg):
+    parts = [lat.gauge(1)[0] for _ in range(dg.nlinks)]
+    dg.download(parts)
+    return np.stack(parts)
+
+
+@pytest.mark.parametrize("L,seed", [((8, 8, 8, 8), 17 ** 7), ((4, 6, 8, 10), 987654321), ((16, 16, 16, 16), 987654321)])
+def test_device_rng_streams_match_the_oracle(orc, ctx, L, seed):
+    """g.random r, then v.gaussian r twice from the continued streams, then p.randomTAH r: the deviates are float32
+    values and must be bit-identical with the oracle's except where the device's log/cos differ from glibc's in the
+    last bit of the double AND that survives the float32 rounding (rare: counted, bounded, at most one float32 ulp)."""
+    qb = ctx(L)
+    lat = orc.Lattice(L)
+    ro = lat.new_rng(seed)
+    g_o = lat.random_gauge(ro, 4)
+    v_o = [lat.gaussian_vector(ro) for _ in range(2)]
+    p_o = lat.random_tah(ro)
+    rd = qb.newRNGField(seed)
+    dg, dp, dv = qb.DeviceGauge(nlinks=4), qb.DeviceGauge(nlinks=4), qb.DeviceField()
+    dg.random(rd)
+    g_d = _down(qb, lat, dg)
+    v_d = []
+    for _ in range(2):
+        dv.gaussian(rd)
+        v_d.append(dv.download(lat.vector()))
+    dp.randomTAH(rd)
+    p_d = _down(qb, lat, dp)
+    ndraw = nbad = 0
+    for a, b in zip(v_d, v_o):
+        bad = a != b
+        ndraw += a.size
+        nbad += int(bad.sum())
+        if bad.any():
+            assert np.abs(a - b)[bad].max() <= 2.0 ** -22 * np.abs(b)[bad].max()
+    assert nbad <= max(1, ndraw // 100000), (nbad, ndraw)
+    # the streams stayed in step through 72 + 12 draws per site: the TAH momenta agree too
+    bad = np.abs(p_d - p_o) > 1e-6 * np.abs(p_o).max()
+    assert bad.sum() == 0
+    assert rel_l2(p_d, p_o) <= 1e-7
+    # links: same gaussians through the same closed-form projectSU; site by site the typical deviation is rounding
+    # level, the L2 figure carries the ill-conditioned tail of eigs3 (matrixFunctions.nim:79-111)
+    site = np.linalg.norm((g_d - g_o).reshape(4, lat.vol, -1), axis=2)
+    assert np.median(site) < 1e-14
+    assert rel_l2(g_d, g_o) <= 1e-9
+    assert np.abs(lat.plaq(g_d) - lat.plaq(g_o)).max() <= 1e-13
+    for d in (dg, dp, dv, rd):
+        d.free()
+
+
+def test_device_random_gauge_reproduces_the_reference_plaquettes(orc, ctx):
+    """tests/reprod/trandgauge.nim:14-29: g.random on 8^4, seed 17^7 -- generated AND measured on the device."""
+    P = np.array(json.load(open(os.path.join(GOLD, "trandgauge.json")))["P"])
+    qb = ctx((8, 8, 8, 8))
+    rd = qb.newRNGField(17 ** 7)
+    dg = qb.DeviceGauge(nlinks=4)
+    dg.random(rd)
+    pl = dg.plaq()
+    assert float(((pl - P) ** 2).sum()) <= 1e-26, pl - P
+    dg.free(); rd.free()
+
+
+def test_begin_H_with_inputs_generated_on_the_device(orc, ctx):
+    """The golden `Begin H` of tests/extra/staghmc_sh/ref.0 with NOTHING from the host: RNG field, randomTAH, unit
+    gauge, nHYP, rephase, gaussian pseudofermions, D, solve, norm2 all on the device (device-field entry points)."""
+    fx = json.load(open(os.path.join(GOLD, "staghmc_sh.json")))
+    run = fx["runs"]["0"]
+    qb = ctx(fx["lattice"])
+    vol = int(np.prod(fx["lattice"]))
+    r = qb.newRNGField(fx["seed"])
+    p = qb.DeviceGauge(nlinks=4)
+    p.randomTAH(r)
+    lat = orc.Lattice(fx["lattice"])
+    ph = _down(qb, lat, p)
+    T = 0.5 * float(np.square(ph).sum()) - 16.0 * vol
+    assert abs(T - run["T"]) <= fx["rel_tol"] * abs(run["T"])
+    g, sg = qb.DeviceGauge(nlinks=4), qb.DeviceGauge(nlinks=4)
+    g.unit()
+    qb.HypCoefs(0.4, 0.5, 0.5).smear(g, sg)
+    sg.rephase()
+    s = qb.newStag(sg)
+    mass, hm = run["mass"][0], run["hmasses"][0]
+    psi = [qb.DeviceField() for _ in range(3)]
+    phi = [qb.DeviceField() for _ in range(3)]
+    ftmp = qb.DeviceField()
+    for f in psi:
+        f.gaussian(r)
+    sp = lambda: qb.SolverParams(r2req=fx["arsq"], maxits=1000000)
+    zero_odd = np.zeros((vol, 3, 2))
+    for i in range(3):
+        if i != 2:
+            s.dev_D(ftmp, psi[i], -mass if i == 0 else -hm[i - 1])
+            s.dev_solve(phi[i], ftmp, -hm[i], sp())
+        else:
+            s.dev_D(phi[i], psi[i], -hm[i - 1])
+        h = phi[i].download(zero_odd.copy())      # phi.odd := 0 (staghmc_sh.nim:757)
+        h[vol // 2:] = 0.0
+        phi[i].upload(h)
+    for i in range(2):
+        s.dev_D(ftmp, phi[i], hm[i])
+        s.dev_solve(psi[i], ftmp, mass if i == 0 else hm[i - 1], sp())
+    s.dev_solve(psi[2], phi[2], hm[1], sp())
+    Sf = [0.5 * f.norm2() for f in psi]
+    for a, b in zip(Sf, run["Sf"][0]):
+        assert abs(a - b) <= fx["rel_tol"] * abs(b), (Sf, run["Sf"])
+    for d in psi + phi + [ftmp, p, g, sg, r]:
+        d.free()

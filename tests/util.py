@@ -79,3 +79,111 @@ def hisq_bar(want, exact, base=1e-13, factor=10.0):
     over the whole lattice and all four directions (the error sits in a handful of nearly singular sites, so the
     statistic of a single direction or of one rank's block fluctuates by several x), never below `base`."""
     return max(base, factor * rel_l2(want, exact))
+
+
+# ---- the reference-held pin for D / Ddag conventions / solve: the first "Begin H" of staghmc_sh --------------------
+class OracleOps:
+    """The operations `staghmc_begin_H` needs, on the oracle."""
+
+    def __init__(self, lat):
+        self.lat = lat
+
+    def smear_rephase(self, g, alpha):
+        sg = self.lat.hyp_smear(g, alpha)
+        self.lat.setBC(sg)
+        self.lat.stagPhase(sg)
+        return sg
+
+    def D(self, sg, r, x, m):
+        self.lat.D(sg, r, x, m)
+
+    def solve(self, sg, x, b, m, r2req, maxits):
+        st = self.lat.solve(sg, x, b, m, r2req, maxits)
+        return st.iterations, st.r2
+
+    def norm2(self, x):
+        return self.lat.norm2(x)
+
+
+def staghmc_begin_H(lat, ops, mass, hmasses, arsq=1e-24, seed=SEED, maxits=1000000, alpha=(0.4, 0.5, 0.5)):
+    """Everything src/examples/staghmc_sh.nim does up to its first `Begin H` line (:716-762), which happens before
+    any molecular-dynamics step: per-site RngMilc6 field (:178) -> p.randomTAH r (:722) -> unit gauge (:707),
+    nHYP smear + setBC + stagPhase (:728, :309-319) -> psi[k][i].gaussian r in the interleaved order of :735-745
+    -> phi = D(m2)^-1 D(m1) psi with the `-m` convention and phi.odd := 0 (:747-757) -> faction (:344-370)
+    -> fa = 0.5 |psi|^2, T = 0.5 p^2 - 16 vol (:334-342).
+    Inputs (RNG streams) come from the oracle; `ops` supplies smear_rephase / D / solve / norm2, so the same
+    sequence runs on the oracle and through the C ABI on the GPU.
+    Returns (Sf[k][i], T, log) with log = [(what, mass, iterations, r2)] of every solve in call order."""
+    r = lat.new_rng(seed)
+    p = lat.random_tah(r)
+    p2 = 0.0
+    for mu in range(4):
+        p2 += float(np.square(p[mu]).sum())
+    T = 0.5 * p2 - float(16 * lat.vol)
+    sg = ops.smear_rephase(lat.unit_gauge(), alpha)
+    nk = len(mass)
+    psi = [[None] * (len(hmasses[k]) + 1) for k in range(nk)]
+    phi = [[None] * (len(hmasses[k]) + 1) for k in range(nk)]
+    i, running = 0, True
+    while running:
+        running = False
+        for k in range(nk):
+            if i >= len(psi[k]):
+                continue
+            psi[k][i] = lat.gaussian_vector(r)
+            running = True
+        i += 1
+    log = []
+    for k in range(nk):
+        hm, n = hmasses[k], len(hmasses[k]) + 1
+        for i in range(n):
+            phi[k][i] = lat.vector()
+            if i != n - 1:
+                ftmp = lat.vector()
+                ops.D(sg, ftmp, psi[k][i], -mass[k] if i == 0 else -hm[i - 1])
+                it, r2 = ops.solve(sg, phi[k][i], ftmp, -hm[i], arsq, maxits)
+                log.append(("init", k, hm[i], it, r2))
+            else:
+                ops.D(sg, phi[k][i], psi[k][i], -hm[i - 1] if len(hm) > 0 else -mass[k])
+            phi[k][i][lat.half:] = 0.0
+    Sf = []
+    for k in range(nk):
+        hm, n = hmasses[k], len(hmasses[k]) + 1
+        for i in range(n - 1):
+            ftmp = lat.vector()
+            ops.D(sg, ftmp, phi[k][i], hm[i])
+            m = mass[k] if i == 0 else hm[i - 1]
+            it, r2 = ops.solve(sg, psi[k][i], ftmp, m, arsq, maxits)
+            log.append(("action", k, m, it, r2))
+        m = hm[-1] if len(hm) > 0 else mass[k]
+        it, r2 = ops.solve(sg, psi[k][n - 1], phi[k][n - 1], m, arsq, maxits)
+        log.append(("action", k, m, it, r2))
+        Sf.append([0.5 * ops.norm2(psi[k][i]) for i in range(n)])
+    return Sf, T, log
+
+
+def check_begin_H(run, Sf, T, log, rel_tol):
+    """Holds (Sf, T, log) of staghmc_begin_H to one run record of tests/golden/staghmc_sh.json: Sf and T at the
+    reference's own relative bar (tests/extra/staghmc_sh/run:43, diffnum 2e-11), and the CG iteration counts to the
+    `calls: (iterations div calls):max` statistics the log prints for trajectory 1 (solverBase.nim:84-112): with c
+    calls of which c-1 happen before `Begin H`... the last call (at `End H`) is the maximum, so
+    its_div_calls == (sum(begin iterations) + its_max) div calls must hold for the begin iterations within +-1."""
+    worst = abs(T - run["T"]) / abs(run["T"])
+    for k, row in enumerate(run["Sf"]):
+        for i, want in enumerate(row):
+            worst = max(worst, abs(Sf[k][i] - want) / abs(want))
+    assert worst <= rel_tol, (worst, Sf, T)
+    # solver statistics: spa[k] serves the action solve at mass[k]; spah[k][i] serves the init solve AND the action solve
+    stats = list(run["action_stats"])
+    pos = 0
+    for k in range(len(run["mass"])):
+        ms = [run["mass"][k]] + list(run["hmasses"][k])
+        for j, m in enumerate(ms):
+            st = stats[pos]
+            pos += 1
+            assert abs(st["m"] - m) < 1e-12
+            mine = [e[3] for e in log if e[1] == k and abs(e[2] - m) < 1e-12]
+            assert len(mine) == st["calls"] - 1, (mine, st)
+            ok = any((sum(mine) + d + st["its_max"]) // st["calls"] == st["its_div_calls"] for d in (-1, 0, 1))
+            assert ok, (mine, st)
+    return worst
