@@ -302,6 +302,26 @@ int qexb200_stagD2deriv(qexb200_gauge_t s, double* const* g, const double* c, co
 int qexb200_dev_outer(qexb200_gauge_t f, qexb200_field_t a, qexb200_field_t b, double scale_even,
                       double scale_odd, int accumulate);
 
+/* ---- CgState as an object and solveEO (src/solvers/cg.nim:13-53,256-283; src/physics/stagSolve.nim:17-38) ----- */
+
+typedef int qexb200_cg_t;    /* handle of a restartable CG state (CgState[T]: r, p and the recurrence scalars) */
+/* solveEO(s, r, x, m, sp): cgSolve(r, x, stagD2ee(m^2)) on the even subset.  Unlike solveXX, r is NOT zeroed: its
+ * even part on entry is the initial guess (r0 = x - A r is formed by the first call of CgState.solve, cg.nim:146-149).
+ * sp.r2 = final recursive r2/b2. */
+int qexb200_solveEO(qexb200_gauge_t g, double* r, const double* x, double m, qexb200_solver_params* sp);
+int qexb200_dev_solveEO(qexb200_gauge_t g, qexb200_field_t r, qexb200_field_t x, double m, qexb200_solver_params* sp);
+/* newCgState(x, b) bound to A = stagD2ee / stagD2oo of gauge g (parity QEXB200_EVEN / QEXB200_ODD).  The fields are
+ * referenced, not copied; x holds the initial guess. */
+int qexb200_cg_create(qexb200_gauge_t g, int parity, qexb200_field_t x, qexb200_field_t b, qexb200_cg_t* cg);
+/* CgState.reset (cg.nim:21-27): the next solve starts over from the current x. */
+int qexb200_cg_reset(qexb200_cg_t cg);
+/* CgState.solve(op, sp) (cg.nim:55-254).  First call after create/reset: b2, r = b - A x.  Later calls CONTINUE the
+ * same Krylov sequence (r, p, r2old, iteration counter carry over): raising sp.maxits or tightening sp.r2req and
+ * calling again gives exactly the iterates of one uninterrupted solve.  sp.maxits and sp.iterations are cumulative,
+ * as in the reference (while itn < maxits; sp.finalIterations = state.iterations). */
+int qexb200_cg_solve(qexb200_cg_t cg, double mass, qexb200_solver_params* sp);
+int qexb200_cg_destroy(qexb200_cg_t cg);
+
 /* ---- per-site random number field: the input generator of the reference's tests and benchmarks ---------- */
 
 /* newRNGField(RngMilc6, lo, seed) (src/rng/distributionUtils.nim:306-331): one RngMilc6 (src/rng/milcrng.nim:92-154)
@@ -315,6 +335,11 @@ int qexb200_gauge_random(qexb200_gauge_t g, qexb200_rng_t r);
 int qexb200_gauge_randomTAH(qexb200_gauge_t g, qexb200_rng_t r);
 /* g.unit (gaugeUtils.nim:1448-1450). */
 int qexb200_gauge_unit(qexb200_gauge_t g);
+/* reunit(g) of the HMC drivers (src/examples/staghmc_sh.nim:247-257): checkSU, projectSU on every link
+ * (src/maths/matrixFunctions.nim:359-370), checkSU again.  dev[4] = {avg, max} deviation before and {avg, max} after,
+ * normalised like checkSU (src/gauge/gaugeUtils.nim:1407-1422).  g.random leaves links unitary to ~1e-11 (closed-form
+ * eigs3 on a gaussian matrix); after reunit they are unitary to ~1e-15 and qualify for the 12-real storage. */
+int qexb200_gauge_reunit(qexb200_gauge_t g, double dev[4]);
 /* v.gaussian r (src/rng/distributionUtils.nim:65-97): 6 deviates per site. */
 int qexb200_field_gaussian(qexb200_field_t f, qexb200_rng_t r);
 
@@ -336,6 +361,18 @@ int qexb200_plan_halo(const int latsize[4], const int rankgeom[4], int myrank, i
  * disp_d in {-1, 0, +1} rank-grid steps away in direction d, nb = sum_d (disp_d + 1) 3^d (40 = this rank), periodic,
  * ranks numbered as in qexb200_init.  A site whose neighbour lies there reads it from that rank's arena. */
 int qexb200_plan_peers(const int latsize[4], const int rankgeom[4], int myrank, unsigned char peer_of[81]);
+/* Host arithmetic of the multi-rank sweep's block -> tile table (no CUDA): tiles of 128 consecutive checkerboard
+ * sites of parity `parity`, those without an off-rank hop first, the face tiles last; entry = tile | need << 24,
+ * need bit 2 mu: the tile reads the + neighbour's x layers in mu, bit 2 mu + 1: the - neighbour's U^+ x products
+ * (the remote part of startSB / boundarySB2, src/layout/shifts.nim:67-94,254-285).  out holds ceil(Vh/128) words. */
+int qexb200_plan_tiles(const int latsize[4], const int rankgeom[4], int myrank, int nlinks, int parity,
+                       unsigned int* out, int* ntiles);
+/* Diagnostic of the peer-memory transport: on = 1 arms a ring of per-launch role timestamps (%globaltimer, ns) inside
+ * the multi-rank sweep -- 1024 launches x 8 words {first block start, last pack block end, last interior tile end,
+ * first face tile past its flag wait, last face tile end, longest flag wait, sum of flag waits, face tiles that
+ * waited} -- followed by 8 words for the cross-rank sums {ns inside, calls, longest}.  on = 0 copies up to nwords
+ * words out and disarms.  The counterpart of the reference's per-phase timers tic/toc in stagD.nim:355-393. */
+int qexb200_debug_role_times(int on, unsigned long long* out, int nwords);
 
 /* ---- measurement helpers (CUDA events on the library's compute stream) ---- */
 

@@ -166,6 +166,7 @@ def lib():
         L.qexb200_gauge_random.argtypes = [C.c_int, C.c_int]
         L.qexb200_gauge_randomTAH.argtypes = [C.c_int, C.c_int]
         L.qexb200_gauge_unit.argtypes = [C.c_int]
+        L.qexb200_gauge_reunit.argtypes = [C.c_int, dp]
         L.qexb200_field_gaussian.argtypes = [C.c_int, C.c_int]
         L.qexb200_field_create.argtypes = [ip]
         L.qexb200_field_destroy.argtypes = [C.c_int]
@@ -182,6 +183,14 @@ def lib():
         L.qexb200_dev_solveXX.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, spp]
         L.qexb200_dev_solve.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, spp]
         L.qexb200_plan_peers.argtypes = [ip, ip, C.c_int, C.POINTER(C.c_ubyte)]
+        L.qexb200_solveEO.argtypes = [C.c_int, dp, dp, C.c_double, spp]
+        L.qexb200_dev_solveEO.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, spp]
+        L.qexb200_cg_create.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, ip]
+        L.qexb200_cg_reset.argtypes = [C.c_int]
+        L.qexb200_cg_solve.argtypes = [C.c_int, C.c_double, spp]
+        L.qexb200_cg_destroy.argtypes = [C.c_int]
+        L.qexb200_plan_tiles.argtypes = [ip, ip, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_uint), ip]
+        L.qexb200_debug_role_times.argtypes = [C.c_int, C.POINTER(C.c_ulonglong), C.c_int]
         L.qexb200_plan_halo.argtypes = [ip, ip, C.c_int, C.c_int, C.POINTER(HaloDir), ip, C.POINTER(C.c_longlong)]
         L.qexb200_timer_stop.argtypes = [C.POINTER(C.c_float)]
         L.qexb200_launch_count.restype = C.c_longlong
@@ -262,6 +271,29 @@ def plan_halo(latsize, rankgeom, myrank, nlinks):
     n, tot = C.c_int(), C.c_longlong()
     _ck(lib().qexb200_plan_halo(_i4(latsize), _i4(rankgeom), int(myrank), int(nlinks), out, C.byref(n), C.byref(tot)))
     return [dict((f[0], getattr(out[i], f[0])) for f in HaloDir._fields_) for i in range(n.value)], tot.value
+
+
+def plan_tiles(latsize, rankgeom, myrank, nlinks, parity):
+    """Block -> tile table of the multi-rank sweep (host arithmetic): list of (tile, need bits)."""
+    n = C.c_int(0)
+    _ck(lib().qexb200_plan_tiles(_i4(latsize), _i4(rankgeom), int(myrank), int(nlinks), int(parity), None, C.byref(n)))
+    out = (C.c_uint * n.value)()
+    _ck(lib().qexb200_plan_tiles(_i4(latsize), _i4(rankgeom), int(myrank), int(nlinks), int(parity), out, C.byref(n)))
+    return [(int(e) & 0xffffff, int(e) >> 24) for e in out]
+
+
+def role_times(on):
+    """Arms (on=True) or reads and disarms the per-launch role timestamps of the multi-rank sweep; returns
+    (ring[1024][8], xrank[8]) as numpy uint64 when reading."""
+    import numpy as np
+    if on:
+        _ck(lib().qexb200_debug_role_times(1, None, 0))
+        return None
+    n = 1024 * 8 + 8
+    buf = (C.c_ulonglong * n)()
+    _ck(lib().qexb200_debug_role_times(0, buf, n))
+    a = np.frombuffer(buf, dtype=np.uint64).copy()
+    return a[:1024 * 8].reshape(1024, 8), a[1024 * 8:]
 
 
 def plan_peers(latsize, rankgeom, myrank):
@@ -447,6 +479,13 @@ class DeviceGauge:
         """g.unit (gaugeUtils.nim:1448-1450)."""
         _ck(lib().qexb200_gauge_unit(self.h))
 
+    def reunit(self):
+        """reunit(g) (src/examples/staghmc_sh.nim:247-257): projectSU on every link; returns
+        ((avg, max) before, (avg, max) after) of checkSU."""
+        d = np.zeros(4)
+        _ck(lib().qexb200_gauge_reunit(self.h, _dp(d)))
+        return (float(d[0]), float(d[1])), (float(d[2]), float(d[3]))
+
     def loadGauge(self, fn):
         """loadGauge(g, fn) (src/gauge/gaugeUtils.nim:87-106): first lattice record of a SciDAC/ILDG file.
         Returns (file suma, file sumb, this rank's suma, this rank's sumb)."""
@@ -550,6 +589,16 @@ class Staggered(DeviceGauge):
     def solveEE(self, r, x, m, sp):
         self.solveXX(r, x, m, sp, True)
 
+    def solveEO(self, r, x, m, sp):
+        """solveEO (stagSolve.nim:17-38): CG on the even subset starting from the content of r (host arrays or
+        DeviceFields)."""
+        c = sp._c()
+        if isinstance(r, DeviceField):
+            _ck(lib().qexb200_dev_solveEO(self.h, r.h, x.h, m, C.byref(c)))
+        else:
+            _ck(lib().qexb200_solveEO(self.h, _dp(r), _dp(x), m, C.byref(c)))
+        sp._addStats(c)
+
     def solveOO(self, r, x, m, sp):
         self.solveXX(r, x, m, sp, False)
 
@@ -618,6 +667,29 @@ class Staggered(DeviceGauge):
         c = sp._c()
         _ck(lib().qexb200_dev_solve(self.h, x.h, b.h, m, C.byref(c)))
         sp._addStats(c)
+
+
+class CgState:
+    """CgState[T] (src/solvers/cg.nim:13-53): newCgState(x, b) bound to A = stagD2ee/oo(m^2) of `stag`; solve() can
+    be called again to continue the same Krylov sequence, reset() starts over from the current x."""
+
+    def __init__(self, stag, x, b, parEven=True):
+        h = C.c_int()
+        _ck(lib().qexb200_cg_create(stag.h, EVEN if parEven else ODD, x.h, b.h, C.byref(h)))
+        self.h = h.value
+
+    def reset(self):
+        _ck(lib().qexb200_cg_reset(self.h))
+
+    def solve(self, m, sp):
+        c = sp._c()
+        _ck(lib().qexb200_cg_solve(self.h, m, C.byref(c)))
+        sp._addStats(c)
+
+    def free(self):
+        if self.h is not None and _lib is not None and _lib.qexb200_is_initialized():
+            _lib.qexb200_cg_destroy(self.h)
+        self.h = None
 
 
 def newStag(g):

@@ -58,6 +58,8 @@ static std::map<int, HypState> g_hyps;
 static std::map<int, HisqState> g_hisqs;
 static std::map<int, Field> g_fields;
 static std::map<int, RngField> g_rngs;
+struct CgObj { CgKeep k; int gauge, parity, x, b; };   // a CgState bound to its operator and fields
+static std::map<int, CgObj> g_cgs;
 static int g_next_handle = 1;
 
 static int need_ctx() {
@@ -446,6 +448,24 @@ int qexb200_plan_halo(const int latsize[4], const int rankgeom[4], int myrank, i
   return 0;
 }
 
+int qexb200_plan_tiles(const int latsize[4], const int rankgeom[4], int myrank, int nlinks, int parity,
+                       unsigned int* out, int* ntiles) {
+  clear_error();
+  if (nlinks != 4 && nlinks != 8) return fail("plan_tiles: nlinks must be 4 or 8");
+  if (parity != 0 && parity != 1) return fail("plan_tiles: parity must be 0 or 1");
+  Geom g;
+  QB_CHECK(make_geom(latsize, rankgeom, myrank, &g));
+  std::vector<unsigned int> t;
+  plan_tiles(g, nlinks / 4, parity, t);
+  if (out) memcpy(out, t.data(), sizeof(unsigned int) * t.size());
+  if (ntiles) *ntiles = (int)t.size();
+  return 0;
+}
+int qexb200_debug_role_times(int on, unsigned long long* out, int nwords) {
+  QB_CHECK(need_ctx());
+  return role_times(on, out, nwords);
+}
+
 struct HostTmp { Field a, b; bool ok = false; int Vh = 0; };
 static HostTmp g_ht;
 
@@ -468,6 +488,8 @@ int qexb200_finalize(void) {
   g_gauges.clear(); g_fields.clear();
   for (auto& kv : g_rngs) rng_destroy(&kv.second);
   g_rngs.clear();
+  for (auto& kv : g_cgs) { cudaFree(kv.second.k.r); cudaFree(kv.second.k.p); }
+  g_cgs.clear();
   if (g_sw.ok) { cudaFree(g_sw.r.d); cudaFree(g_sw.y.d); cudaFree(g_sw.d.d); g_sw = SolveWork(); }
   for (auto& f : g_mw.ys) cudaFree(f.d);
   for (auto& f : g_mw.hx) cudaFree(f.d);
@@ -885,6 +907,11 @@ int qexb200_gauge_unit(qexb200_gauge_t hg) {
   Gauge* g; QB_CHECK(get_gauge(hg, &g));
   return unit_links(*g);
 }
+int qexb200_gauge_reunit(qexb200_gauge_t hg, double dev[4]) {
+  QB_CHECK(need_ctx());
+  Gauge* g; QB_CHECK(get_gauge(hg, &g));
+  return reunit_links(*g, dev);
+}
 int qexb200_field_gaussian(qexb200_field_t hf_, qexb200_rng_t hr) {
   QB_CHECK(need_ctx());
   Field* f; QB_CHECK(get_field(hf_, &f));
@@ -980,6 +1007,78 @@ int qexb200_dev_solveXX(qexb200_gauge_t hg, int parity, qexb200_field_t r, qexb2
 int qexb200_dev_solve(qexb200_gauge_t hg, qexb200_field_t x, qexb200_field_t b, double m, qexb200_solver_params* sp) {
   GET_G_F2(hg, x, b);
   return op_solve(*g, *f1, *f2, m, sp);
+}
+
+// solveEO, stagSolve.nim:17-38: cgSolve(r, x, stagD2ee(m^2)) on the even subset -- r is NOT zeroed, its content is
+// the initial guess (CgState.solve forms r0 = b - A x on its first call, cg.nim:146-149)
+static int op_solveEO(const Gauge& g, Field& r, const Field& x, double m, qexb200_solver_params* sp) {
+  const double t0 = now_s();
+  CgResult res;
+  QB_CHECK(cg_xx(g, 0, hf(r, 0), hf(x, 0), m * m, sp->r2req, sp->maxits, false, &res));
+  sp->calls = 1;
+  sp->iterations = res.iterations;
+  sp->iterations_max = res.iterations;
+  sp->seconds = now_s() - t0;
+  sp->flops = (double)(g.nlinks * 4 * 72 + 60) * (double)g_ctx.g.Vh * g_ctx.g.nranks * res.iterations;   // :31
+  sp->r2 = res.b2 > 0 ? res.r2 / res.b2 : 0.0;
+  return 0;
+}
+int qexb200_dev_solveEO(qexb200_gauge_t hg, qexb200_field_t r, qexb200_field_t x, double m, qexb200_solver_params* sp) {
+  GET_G_F2(hg, r, x);
+  return op_solveEO(*g, *f1, *f2, m, sp);
+}
+
+// ---- CgState as an object (cg.nim:13-53, 256-283): newCgState / reset / solve (restartable) -------------------
+int qexb200_cg_create(qexb200_gauge_t hg, int parity, qexb200_field_t x, qexb200_field_t b, qexb200_cg_t* out) {
+  GET_G_F2(hg, x, b);
+  (void)g; (void)f1; (void)f2;
+  if (parity != 0 && parity != 1) return fail("cg_create: parity must be 0 or 1");
+  CgObj o;
+  o.gauge = hg; o.parity = parity; o.x = x; o.b = b;
+  QB_CUDA(cudaMalloc(&o.k.r, sizeof(double2) * nhalf()));
+  QB_CUDA(cudaMalloc(&o.k.p, sizeof(double2) * nhalf()));
+  QB_CUDA(cudaMemsetAsync(o.k.p, 0, sizeof(double2) * nhalf(), g_ctx.stream));
+  const int h = g_next_handle++;
+  g_cgs[h] = o;
+  *out = h;
+  return 0;
+}
+static int get_cg(int h, CgObj** o) {
+  auto it = g_cgs.find(h);
+  if (it == g_cgs.end()) return fail("invalid CG state handle %d", h);
+  *o = &it->second;
+  return 0;
+}
+int qexb200_cg_reset(qexb200_cg_t h) {     // CgState.reset, cg.nim:21-27
+  QB_CHECK(need_ctx());
+  CgObj* o; QB_CHECK(get_cg(h, &o));
+  o->k.b2 = -1.0; o->k.iterations = 0; o->k.r2 = 1.0; o->k.r2old = 1.0;
+  return 0;
+}
+int qexb200_cg_solve(qexb200_cg_t h, double m, qexb200_solver_params* sp) {   // CgState.solve(op, sp), cg.nim:55-254
+  QB_CHECK(need_ctx());
+  CgObj* o; QB_CHECK(get_cg(h, &o));
+  Gauge* g; QB_CHECK(get_gauge(o->gauge, &g));
+  Field *x, *b; QB_CHECK(get_field(o->x, &x)); QB_CHECK(get_field(o->b, &b));
+  const double t0 = now_s();
+  const int before = o->k.b2 >= 0.0 ? o->k.iterations : 0;
+  CgResult res;
+  QB_CHECK(cg_xx(*g, o->parity, hf(*x, o->parity), hf(*b, o->parity), m * m, sp->r2req, sp->maxits, false, &res, &o->k));
+  sp->calls = 1;
+  sp->iterations = res.iterations;          // sp.finalIterations = state.iterations: cumulative (cg.nim:252)
+  sp->iterations_max = res.iterations;
+  sp->seconds = now_s() - t0;
+  sp->flops = (double)(g->nlinks * 4 * 72 + 60) * (double)g_ctx.g.Vh * g_ctx.g.nranks * (res.iterations - before);
+  sp->r2 = res.b2 > 0 ? res.r2 / res.b2 : 0.0;
+  return 0;
+}
+int qexb200_cg_destroy(qexb200_cg_t h) {
+  QB_CHECK(need_ctx());
+  CgObj* o; QB_CHECK(get_cg(h, &o));
+  cudaStreamSynchronize(g_ctx.stream);
+  cudaFree(o->k.r); cudaFree(o->k.p);
+  g_cgs.erase(h);
+  return 0;
 }
 
 // ---- fermion-force outer products (force.cu) ----------------------
@@ -1182,6 +1281,16 @@ int qexb200_solveXX(qexb200_gauge_t hg, int parity, double* r, const double* x, 
   const double t0 = now_s();
   QB_CHECK(upload_vector(X, x));
   QB_CHECK(op_solveXX(*g, parity, R, X, m, sp));
+  QB_CHECK(download_vector(R, r));
+  sp->seconds = now_s() - t0;
+  return 0;
+}
+int qexb200_solveEO(qexb200_gauge_t hg, double* r, const double* x, double m, qexb200_solver_params* sp) {
+  HOST_PROLOGUE(hg);
+  const double t0 = now_s();
+  QB_CHECK(upload_vector(R, r));     // the initial guess
+  QB_CHECK(upload_vector(X, x));
+  QB_CHECK(op_solveEO(*g, R, X, m, sp));
   QB_CHECK(download_vector(R, r));
   sp->seconds = now_s() - t0;
   return 0;

@@ -77,6 +77,36 @@ int halo_free() {
   c.halo.clear();
   c.halo_elems = 0;
   halo_nl = 0;
+  for (int i = 0; i < 2; i++)
+    for (int p = 0; p < 2; p++) { if (c.d_order[i][p]) cudaFree(c.d_order[i][p]); c.d_order[i][p] = nullptr; }
+  return 0;
+}
+
+// Diagnostic (qexb200_debug_role_times): on = 1 arms the timestamp ring of the multi-rank sweep and of the cross-rank
+// sums; on = 0 copies it out (STAMP_RING launches x 8 words, then 8 words of xrank_sum) and disarms.
+int role_times(int on, unsigned long long* out, int nwords) {
+  Context& c = ctx();
+  if (!c.p2p) return fail("role_times: needs the peer-memory transport");
+  const size_t n = (size_t)STAMP_RING * 8 + 8;
+  QB_CUDA(cudaStreamSynchronize(c.stream));
+  if (on) {
+    if (!c.d_stamps) QB_CUDA(cudaMalloc(&c.d_stamps, n * sizeof(unsigned long long)));
+    std::vector<unsigned long long> h(n, 0ull);
+    for (int i = 0; i < STAMP_RING; i++) h[(size_t)i * 8 + 0] = h[(size_t)i * 8 + 3] = ~0ull;
+    QB_CUDA(cudaMemcpy(c.d_stamps, h.data(), n * sizeof(unsigned long long), cudaMemcpyHostToDevice));
+    unsigned long long* xs = c.d_stamps + (size_t)STAMP_RING * 8;
+    QB_CUDA(cudaMemcpy(&c.d_xr->stamps, &xs, sizeof xs, cudaMemcpyHostToDevice));
+    return 0;
+  }
+  if (!c.d_stamps) return fail("role_times: not armed");
+  if (out) {
+    const size_t m = (size_t)nwords < n ? (size_t)nwords : n;
+    QB_CUDA(cudaMemcpy(out, c.d_stamps, m * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+  }
+  unsigned long long* none = nullptr;
+  QB_CUDA(cudaMemcpy(&c.d_xr->stamps, &none, sizeof none, cudaMemcpyHostToDevice));
+  cudaFree(c.d_stamps);
+  c.d_stamps = nullptr;
   return 0;
 }
 
@@ -231,6 +261,8 @@ int p2p_free() {
   }
   if (c.win) cudaFree(c.win);
   if (c.d_xr) cudaFree(c.d_xr);
+  if (c.d_stamps) cudaFree(c.d_stamps);
+  c.d_stamps = nullptr;
   c.win = nullptr; c.d_xr = nullptr; c.p2p = false; c.win_bytes = 0; c.halo_cap = 0;
   c.arena_units = 0; c.arena_used.clear(); c.arena_off = 0;
   return 0;

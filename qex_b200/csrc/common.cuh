@@ -86,6 +86,7 @@ struct XRank {
   unsigned int seq;        // reductions done so far (device side counter)
   int* err;                // mapped host word: != 0 after a wait timed out
   unsigned long long timeout_ns;
+  unsigned long long* stamps;   // diagnostic: [0] ns spent inside xrank_sum, [1] calls, [2] longest (or nullptr)
 };
 
 struct Context {
@@ -128,7 +129,12 @@ struct Context {
   int arena_units = 0;
   std::vector<char> arena_used;     // one flag per unit
   unsigned long long p2p_timeout_ns = 120ull * 1000000000ull;  // QEXB200_P2P_TIMEOUT_S
+  // multi-rank sweep: block -> tile tables [link classes - 1][output parity] (dslash.cu tile_order)
+  unsigned int* d_order[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};
+  // role timestamps of the multi-rank sweep (qexb200_debug_role_times): STAMP_RING launches x 8 words + 8 for xrank_sum
+  unsigned long long* d_stamps = nullptr;
 };
+constexpr int STAMP_RING = 1024;
 
 // NCCL is bound at run time (dlopen of libnccl.so.2) the first time a multi-rank
 // context is created: a process that also hosts another NCCL user (e.g. torch) must
@@ -226,8 +232,14 @@ int check_device_error();
 
 // ---- solver.cu --------------------------------------------------------------
 struct CgResult { int iterations; double r2, b2; };
+// what a CgState keeps between calls of solve (cg.nim:13-27): r, p and the scalars; b2 < 0 = after reset
+struct CgKeep {
+  double2 *r = nullptr, *p = nullptr;   // half fields
+  double b2 = -1.0, r2 = 1.0, r2old = 1.0;
+  int iterations = 0;
+};
 int cg_xx(const Gauge& g, int parity, double2* x, const double2* b, double m2, double r2req,
-          int maxits, bool x_is_zero, CgResult* res);
+          int maxits, bool x_is_zero, CgResult* res, CgKeep* keep = nullptr);
 int cgm_xx(const Gauge& g, int parity, double2* const* xs, const double2* b, double m2, const double* sigmas,
            int nmass, double r2req, int maxits, CgResult* res);
 int apply_xx_public(const Gauge& g, int parity, double2* out, const double2* x, double m2);
@@ -298,6 +310,7 @@ void rng_destroy(RngField* r);
 int rng_gaussian_vector(RngField& r, Field& f);
 int rng_matrix_fields(RngField& r, Gauge& g, int mode);   // 0: g.random r, 1: g.randomTAH r
 int unit_links(Gauge& g);
+int reunit_links(Gauge& g, double out[4]);   // checkSU, projectSU, checkSU (staghmc_sh.nim:247-257)
 
 // ---- comm.cu ----------------------------------------------------------------
 int halo_setup();
@@ -316,6 +329,8 @@ void plan_peers(const Geom& g, unsigned char peer_of[81]);
 int peers_fill(Peers* pr);          // kernel-side view of the arena (needs qexb200_p2p_attach)
 int xbarrier();                     // all ranks' earlier work on the compute stream is complete and visible
 int halo_begin(const Gauge& g);
+void plan_tiles(const Geom& g, int nl, int parity, std::vector<unsigned int>& out);   // dslash.cu
+int role_times(int on, unsigned long long* out, int nwords);                          // comm.cu
 // Start the exchange for a sweep that outputs `parity`: pack, then send/recv on comm_stream.
 int halo_start(const Gauge& g, int parity, const double2* x);
 // Make the compute stream wait for the exchange.

@@ -128,6 +128,7 @@ __global__ void __launch_bounds__(SWEEP_BLOCK, SWEEP_MINB) k_sweep(const SweepAr
   if (DOT) grid_reduce<SWEEP_BLOCK>(dot, A.partials, A.ticket, A.result);
 }
 
+#ifdef QEXB200_TUNE
 // launch-shape experiments (QEXB200_SWEEP_TUNE): same body, other block size / residency
 template <int NL, int BLOCK, int MINB>
 __global__ void __launch_bounds__(BLOCK, MINB) k_sweep_t(const SweepArgs A) {
@@ -139,6 +140,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_sweep_t(const SweepArgs A) {
     site_epilogue<false>(A, idx, acc);
   }
 }
+#endif
 
 // ---- exterior: one launch for all split directions -----------------------------------------
 // Adds the terms whose neighbour lives on another rank (boundarySB2 of stagD.nim:381-393).
@@ -342,122 +344,148 @@ __global__ void __launch_bounds__(SWEEP_BLOCK) k_pack(const PackArgs A) {
 }
 
 // ---- the whole multi-rank sweep as ONE kernel (peer-memory path) -----------------------------
-// Blocks take one of three roles by index, in the order the hardware dispatches them:
-//   [0, npack)          pack the faces straight into the neighbours' windows over NVLink and,
-//                       when the last of them is done, raise the neighbours' flags;
-//   [npack, +nint)      all sites WITHOUT an off-rank hop: the plain stencil (the transfer is in
-//                       flight meanwhile);
-//   [.., +next)         the boundary sites: wait for the neighbours' flags, then the full stencil
-//                       with ghost data substituted for off-rank hops.
-// Pack blocks never wait, boundary blocks wait only on REMOTE pack blocks: no cycle.  The
-// Re<bx, r> reduction (and its sum over ranks) closes the same kernel, so a CG iteration on
-// N GPUs launches exactly the kernels it launches on one.
-struct FusedArgs {
+// Blocks take a role by index, in the order the hardware dispatches them:
+//   [0, npack)       pack the faces straight into the neighbours' windows over NVLink and, when the
+//                    last of them is done, raise the neighbours' flags;
+//   [npack, +ntiles) one TILE of 128 consecutive checkerboard sites each, in the order of a table
+//                    built once per geometry: tiles without an off-rank hop first (the transfer is in
+//                    flight meanwhile), tiles that touch a face last.  A face tile waits for exactly
+//                    the flags its sites need (bits of the table entry), then runs the same stencil
+//                    with ghost data substituted for its off-rank hops.
+// Every site is visited by exactly one thread and every thread has a site: the grid is the single-
+// rank grid plus the pack blocks (the round-1 kernel ran all Vh threads with the boundary ones idle
+// and then a third group of blocks for the boundary: +36 % blocks at 1.2.2.2, 0.109 vs 0.070 ms).
+// Pack blocks never wait, face tiles wait only on REMOTE pack blocks: no cycle.  The Re<bx, r>
+// reduction (and its sum over ranks) closes the same kernel, so a CG iteration on N GPUs launches
+// exactly the kernels it launches on one.
+struct GhostDir {                        // indexed by mu; entries of unsplit directions stay null
+  const double2 *gf, *gb0, *gb1;         // + neighbour's first layers of x ; - neighbour's U_k^+ x per link class
+  const unsigned int *flag_f, *flag_b;   // raised by the + / - neighbour's pack blocks
+  int faceh;
+};
+struct MRArgs {
   SweepArgs A;
   PackArgs P;
-  ExtArgs E;
-  int npack, nint;
+  GhostDir gd[4];
+  const unsigned int* order;   // block -> tile (low 24 bits) | flags it waits for (bit 24 + 2 mu + side)
+  int npack, ntiles;
+  unsigned int seq;
+  int* err;
+  unsigned long long timeout_ns;
+  XRank* xr;
+  unsigned long long* stamps;  // role timestamps of this launch (qexb200_debug_role_times) or nullptr
 };
+// stamps[0] first block start, [1] last pack block end, [2] last interior tile end, [3] first face tile past its
+// wait, [4] last face tile end, [5] longest flag wait, [6] sum of flag waits, [7] face tiles that had to wait
+enum { ST_START = 0, ST_PACK_END, ST_INT_END, ST_FACE_START, ST_FACE_END, ST_WAIT_MAX, ST_WAIT_SUM, ST_WAIT_N, ST_N };
 
-template <int NL, int RC, bool DOT, int MINB>
-__global__ void __launch_bounds__(SWEEP_BLOCK, MINB) k_sweep_fused(const FusedArgs F) {
+template <int NL, int RC>
+__device__ __forceinline__ void stencil_ghost(const MRArgs& F, const Site& s, int idx, double2 (&acc)[3]) {
+  const SweepArgs& A = F.A;
+  const int Vh = A.Vh, p = A.parity, q = 1 - A.parity;
+  constexpr int dep = (NL == 2) ? 3 : 1;
+  const unsigned int sg = (RC & 3) ? A.L.sgn[(size_t)p * Vh + idx] : 0u;
+#pragma unroll
+  for (int mu = 0; mu < 4; mu++) {
+    const int st = stride_of(mu, A.X);
+    const int Xm = A.X[mu], xm = s.x[mu];
+    const bool split = (A.comm_mask >> mu) & 1;
+    const GhostDir& D = F.gd[mu];
+    int fidx = 0;
+    if (split && (xm < dep || xm >= Xm - dep)) fidx = face_lex(s.x, mu, A.X) >> 1;
+#pragma unroll
+    for (int j = 0; j < NL; j++) {
+      const int h = (j == 0) ? 1 : 3;
+      {  // forward hop: U_k(s) x(s + h mu), x from the + neighbour's first layers when s + h mu left the rank
+        const int y = xm + h;
+        int ln = s.lex + h * st;
+        const bool off = y >= Xm;
+        if (off) ln -= Xm * st;
+        double2 U[9], v[3];
+        load_link_k<NL, RC>(U, A.L, mu, j, p, idx, Vh, (sg >> (2 * mu + j)) & 1u);
+        if (off && split) {
+#pragma unroll
+          for (int c = 0; c < 3; c++)
+            v[c] = __ldcg(D.gf + (size_t)c * dep * D.faceh + (size_t)(y - Xm) * D.faceh + fidx);
+        } else {
+          load_vec(v, A.x + (ln >> 1), Vh);
+        }
+        mv_add(acc, U, v);
+      }
+      {  // backward hop: the product U_k^+ x was formed at the source when s - h mu left the rank
+        const int y = xm - h;
+        int ln = s.lex - h * st;
+        const bool off = y < 0;
+        if (off) ln += Xm * st;
+        if (off && split) {
+          const double2* gb = (j == 0) ? D.gb0 : D.gb1;
+#pragma unroll
+          for (int c = 0; c < 3; c++) {
+            const double2 w = __ldcg(gb + (size_t)c * h * D.faceh + (size_t)xm * D.faceh + fidx);
+            acc[c].x -= w.x; acc[c].y -= w.y;
+          }
+        } else {
+          double2 U[9], v[3];
+          const int ib = ln >> 1;
+          load_link_k<NL, RC>(U, A.L, mu, j, q, ib, Vh, (sg >> (8 + 2 * mu + j)) & 1u);
+          load_vec(v, A.x + ib, Vh);
+          mv_adj_sub(acc, U, v);
+        }
+      }
+    }
+  }
+}
+
+template <int NL, int RC, bool DOT>
+__global__ void __launch_bounds__(SWEEP_BLOCK, SWEEP_MINB) k_sweep_mr(const MRArgs F) {
   const SweepArgs& A = F.A;
   const int bid = blockIdx.x;
+  const bool stamp = F.stamps != nullptr && threadIdx.x == 0;
+  if (stamp) atomicMin(F.stamps + ST_START, globaltimer_ns());
   double dot = 0.0;
   if (bid < F.npack) {
     const int t = bid * SWEEP_BLOCK + threadIdx.x;
     if (t < F.P.d[F.P.ndir - 1].end) pack_item<NL, RC>(F.P, t);
     pack_signal(F.P, F.npack);
+    if (stamp) atomicMax(F.stamps + ST_PACK_END, globaltimer_ns());
   } else {
-    const ExtArgs& E = F.E;
-    const bool tail = bid >= F.npack + F.nint;
-    const int Vh = A.Vh, p = A.parity, q = 1 - A.parity;
-    constexpr int dep = (NL == 2) ? 3 : 1;
-    bool active;
-    Site s;
-    if (!tail) {
-      const int idx0 = (bid - F.npack) * SWEEP_BLOCK + threadIdx.x;
-      active = idx0 < Vh;
-      if (active) {
-        s = site_from_idx(idx0, p, A.X);
+    const unsigned int e = F.order[bid - F.npack];
+    const int tile = (int)(e & 0xffffffu);
+    const unsigned int need = e >> 24;
+    if (need) {
+      if (threadIdx.x < 8 && ((need >> threadIdx.x) & 1u)) {
+        const unsigned int* fl = nullptr;
 #pragma unroll
-        for (int mu = 0; mu < 4; mu++)
-          if ((A.comm_mask >> mu) & 1) active = active && s.x[mu] >= dep && s.x[mu] < A.X[mu] - dep;
-      }
-    } else {
-      if ((int)threadIdx.x < 2 * E.ndir) {
-        const ExtDir& D = E.d[threadIdx.x >> 1];
-        wait_flag((threadIdx.x & 1) ? D.flag_b : D.flag_f, E.seq, E.err, E.timeout_ns);
+        for (int k = 0; k < 8; k++)
+          if ((int)threadIdx.x == k) fl = (k & 1) ? F.gd[k >> 1].flag_b : F.gd[k >> 1].flag_f;
+        if (F.stamps) {
+          const unsigned long long w0 = globaltimer_ns();
+          const bool ready = ld_acquire_sys(fl) == F.seq;
+          wait_flag(fl, F.seq, F.err, F.timeout_ns);
+          if (!ready) {
+            const unsigned long long dt = globaltimer_ns() - w0;
+            atomicMax(F.stamps + ST_WAIT_MAX, dt);
+            atomicAdd(F.stamps + ST_WAIT_SUM, dt);
+            atomicAdd(F.stamps + ST_WAIT_N, 1ull);
+          }
+        } else {
+          wait_flag(fl, F.seq, F.err, F.timeout_ns);
+        }
       }
       __syncthreads();
-      const int t = (bid - F.npack - F.nint) * SWEEP_BLOCK + threadIdx.x;
-      active = t < E.reg[E.nreg - 1].end;
-      if (active) {
-        region_site(E, t, s.x);
-        s.lex = ((s.x[3] * A.X[2] + s.x[2]) * A.X[1] + s.x[1]) * A.X[0] + s.x[0];
-      }
+      if (stamp) atomicMin(F.stamps + ST_FACE_START, globaltimer_ns());
     }
-    if (active) {
-      const int idx = s.lex >> 1;
+    const int idx = tile * SWEEP_BLOCK + threadIdx.x;
+    if (idx < A.Vh) {
+      const Site s = site_from_idx(idx, A.parity, A.X);
       double2 acc[3] = {{0, 0}, {0, 0}, {0, 0}};
-      const unsigned int sg = (RC & 3) ? A.L.sgn[(size_t)p * Vh + idx] : 0u;
-      int di = 0;   // index into E.d of the current split direction (tail only)
-#pragma unroll
-      for (int mu = 0; mu < 4; mu++) {
-        const int st = stride_of(mu, A.X);
-        const int Xm = A.X[mu];
-        const bool split = (A.comm_mask >> mu) & 1;
-        const bool ghost = tail && split && (s.x[mu] < dep || s.x[mu] >= Xm - dep);
-        int fidx = 0;
-        if (ghost) fidx = face_lex(s.x, mu, A.X) >> 1;
-#pragma unroll
-        for (int j = 0; j < NL; j++) {
-          const int h = (j == 0) ? 1 : 3;
-              {  // forward hop
-            const int y = s.x[mu] + h;
-            int ln = s.lex + h * st;
-            const bool off = y >= Xm;
-            if (off) ln -= Xm * st;
-            double2 U[9], v[3];
-            load_link_k<NL, RC>(U, A.L, mu, j, p, idx, Vh, (sg >> (2 * mu + j)) & 1u);
-            if (off && split) {
-              const ExtDir& D = E.d[di];
-#pragma unroll
-              for (int c = 0; c < 3; c++)
-                v[c] = __ldcg(D.ghost_f + (size_t)c * dep * D.faceh + (size_t)(y - Xm) * D.faceh + fidx);
-            } else {
-              load_vec(v, A.x + (ln >> 1), Vh);
-            }
-            mv_add(acc, U, v);
-          }
-          {  // backward hop
-            const int y = s.x[mu] - h;
-            int ln = s.lex - h * st;
-            const bool off = y < 0;
-            if (off) ln += Xm * st;
-            if (off && split) {
-              const ExtDir& D = E.d[di];
-              const double2* gb = (j == 0) ? D.ghost_b0 : D.ghost_b1;
-#pragma unroll
-              for (int c = 0; c < 3; c++) {
-                const double2 w = __ldcg(gb + (size_t)c * h * D.faceh + (size_t)s.x[mu] * D.faceh + fidx);
-                acc[c].x -= w.x; acc[c].y -= w.y;
-              }
-            } else {
-              double2 U[9], v[3];
-              const int ib = ln >> 1;
-              load_link_k<NL, RC>(U, A.L, mu, j, q, ib, Vh, (sg >> (8 + 2 * mu + j)) & 1u);
-              load_vec(v, A.x + ib, Vh);
-              mv_adj_sub(acc, U, v);
-            }
-          }
-        }
-        if (split) di++;
-      }
+      if (need) stencil_ghost<NL, RC>(F, s, idx, acc);
+      else stencil_local<NL, RC>(A, s, idx, acc);
       dot = site_epilogue<DOT>(A, idx, acc);
     }
+    if (stamp) atomicMax(F.stamps + (need ? ST_FACE_END : ST_INT_END), globaltimer_ns());
   }
-  if (DOT) grid_reduce<SWEEP_BLOCK>(dot, A.partials, A.ticket, A.result, F.E.xr);
+  if (DOT) grid_reduce<SWEEP_BLOCK>(dot, A.partials, A.ticket, A.result, F.xr);
 }
 
 static inline unsigned int* win_flag(char* win, int buf, int mu, int side) {
@@ -570,6 +598,53 @@ static int exterior(const Gauge& g, int parity, double2* r, double scale, const 
   return 0;
 }
 
+// Block -> tile table of the multi-rank sweep for output parity `parity` and hop depth of `nl` link classes:
+// tiles whose sites all stay on the rank first, then the tiles with a face site, each tagged with the flags
+// (bit 2 mu: + neighbour's x layers, bit 2 mu + 1: - neighbour's products) its sites read.  Built once per geometry.
+void plan_tiles(const Geom& g, int nl, int parity, std::vector<unsigned int>& out) {
+  const int dep = (nl == 2) ? 3 : 1;
+  const int ntiles = (g.Vh + SWEEP_BLOCK - 1) / SWEEP_BLOCK;
+  std::vector<unsigned int> face;
+  out.clear();
+  out.reserve((size_t)ntiles);
+  const int xh = g.X[0] >> 1;
+  for (int t = 0; t < ntiles; t++) {
+    unsigned int need = 0;
+    const int i1 = (t + 1) * SWEEP_BLOCK < g.Vh ? (t + 1) * SWEEP_BLOCK : g.Vh;
+    for (int idx = t * SWEEP_BLOCK; idx < i1; idx++) {
+      int r = idx, x[4];
+      const int x0h = r % xh; r /= xh;
+      x[1] = r % g.X[1]; r /= g.X[1];
+      x[2] = r % g.X[2];
+      x[3] = r / g.X[2];
+      x[0] = 2 * x0h + ((parity + x[1] + x[2] + x[3]) & 1);
+      for (int mu = 0; mu < 4; mu++) {
+        if (!((g.comm_mask >> mu) & 1)) continue;
+        if (x[mu] + dep >= g.X[mu]) need |= 1u << (2 * mu);
+        if (x[mu] - dep < 0) need |= 1u << (2 * mu + 1);
+      }
+    }
+    if (need) face.push_back((unsigned int)t | (need << 24));
+    else out.push_back((unsigned int)t);
+  }
+  out.insert(out.end(), face.begin(), face.end());
+}
+
+static int tile_order(int nl, int parity, const unsigned int** order, int* ntiles) {
+  Context& c = ctx();
+  unsigned int*& d = c.d_order[nl - 1][parity];
+  const int n = (c.g.Vh + SWEEP_BLOCK - 1) / SWEEP_BLOCK;
+  if (!d) {
+    if (n >= (1 << 24)) return fail("sweep: %d tiles exceed the 24-bit tile index", n);
+    std::vector<unsigned int> h;
+    plan_tiles(c.g, nl, parity, h);
+    QB_CUDA(cudaMalloc(&d, sizeof(unsigned int) * h.size()));
+    QB_CUDA(cudaMemcpy(d, h.data(), sizeof(unsigned int) * h.size(), cudaMemcpyHostToDevice));
+  }
+  *order = d; *ntiles = n;
+  return 0;
+}
+
 int sweep(const Gauge& g, int parity, double2* r, const double2* x, const double2* bx, double a,
           double b, double sgn, double post, double* dot_out) {
   Context& c = ctx();
@@ -586,23 +661,38 @@ int sweep(const Gauge& g, int parity, double2* r, const double2* x, const double
   const bool fused_dot = dot_out != nullptr;
 
   if (multi && c.p2p) {
-    // peer-memory path: pack + interior + boundary (+ dot over ranks) in one launch
+    // peer-memory path: pack + all tiles (+ dot over ranks) in one launch
     QB_CHECK(halo_begin(g));
-    FusedArgs F;
+    MRArgs F;
     F.A = A;
     const int npk = fill_pack(g, 1 - parity, x, c.halo_seq, F.P);
-    const int nbd = fill_ext(g, parity, r, post * sgn, bx, dot_out, nullptr, F.E);
+    const int nl = g.nlinks / 4;
+    QB_CHECK(tile_order(nl, parity, &F.order, &F.ntiles));
+    const int buf = c.halo_seq & 1;
+    const double2* rb = win_recv(c.win, buf, c.halo_cap);
+    for (int mu = 0; mu < 4; mu++) F.gd[mu] = GhostDir{nullptr, nullptr, nullptr, nullptr, nullptr, 0};
+    for (const HaloDir& hd : c.halo) {
+      GhostDir& D = F.gd[hd.mu];
+      D.gf = rb + hd.off_f;
+      D.gb0 = rb + hd.off_b;
+      D.gb1 = rb + hd.off_b + (size_t)3 * hd.faceh;
+      D.flag_f = win_flag(c.win, buf, hd.mu, 0);
+      D.flag_b = win_flag(c.win, buf, hd.mu, 1);
+      D.faceh = hd.faceh;
+    }
     F.npack = (npk + SWEEP_BLOCK - 1) / SWEEP_BLOCK;
-    F.nint = grid;
-    const int total = F.npack + F.nint + (nbd + SWEEP_BLOCK - 1) / SWEEP_BLOCK;
+    F.seq = c.halo_seq; F.err = c.d_err; F.timeout_ns = c.p2p_timeout_ns; F.xr = xrank();
+    F.stamps = c.d_stamps ? c.d_stamps + (size_t)ST_N * (c.halo_seq % STAMP_RING) : nullptr;
+    const int total = F.npack + F.ntiles;
     if ((size_t)total > c.npart) return fail("sweep: %d blocks exceed the %zu reduction slots", total, c.npart);
     // residency 6 blocks/SM measured best for every variant (tools/tune_fused.py: 5, 4, 3 are 1-20 % slower)
-    QB_DISPATCH(g, fused_dot, k_sweep_fused<NL, RC, DOT, SWEEP_MINB><<<total, SWEEP_BLOCK, 0, c.stream>>>(F));
+    QB_DISPATCH(g, fused_dot, k_sweep_mr<NL, RC, DOT><<<total, SWEEP_BLOCK, 0, c.stream>>>(F));
     count_launch();
     QB_CUDA(cudaGetLastError());
     return 0;
   }
 
+#ifdef QEXB200_TUNE   // launch-shape experiments (tools/tune_sweep.py), not part of the product binary
   const int tune = getenv("QEXB200_SWEEP_TUNE") ? atoi(getenv("QEXB200_SWEEP_TUNE")) : 0;
   if (!multi && !fused_dot && tune > 0) {
 #define QB_T(ID, BLOCK, MINB)                                                               \
@@ -618,6 +708,7 @@ int sweep(const Gauge& g, int parity, double2* r, const double2* x, const double
     QB_CUDA(cudaGetLastError());
     return 0;
   }
+#endif
   if (multi) QB_CHECK(halo_start(g, parity, x));
   // NCCL path: the interior part of the dot goes to a scratch scalar, k_exterior finishes it
   double* dot_interior = c.d_scal + 48;

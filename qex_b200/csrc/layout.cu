@@ -388,8 +388,8 @@ int compress_links(Gauge& g) {
   int mode[2] = {0, 0};
   bool any12 = false, anym = false;
   for (int j = 0; j < nl; j++) {
-    // 14-real sets on a split lattice: not enabled yet (face-pack / exterior kernels untested in that form) -> 18
-    const bool w14 = ((g.want14 >> j) & 1) && c.g.nranks == 1;
+    // each rank decides for its own block of the lattice: the halo layout does not depend on the storage form
+    const bool w14 = ((g.want14 >> j) & 1) != 0;
     mode[j] = w14 ? 14 : (((g.want12 >> j) & 1) ? 12 : 0);
     if (!mode[j]) continue;
     anym = true; any12 = any12 || mode[j] == 12;

@@ -13,7 +13,7 @@
 // double and rounded to float32 (the one reading of milcrng.nim:183-188 that reproduces the reference's golden
 // plaquettes, tests/reprod/trandgauge.nim:17); the device's log/cos differ from glibc's in the last bit of the DOUBLE now and
 // then, which survives the float32 rounding about once in 1e8 draws (tests/test_gpu_rng.py counts them).
-#include "common.cuh"
+#include "stencil.cuh"
 
 namespace qb {
 
@@ -187,6 +187,105 @@ int rng_matrix_fields(RngField& r, Gauge& g, int mode) {
   g.loaded = true;
   return compress_links(g);
 }
+// ---- reunit (src/examples/staghmc_sh.nim:247-257): checkSU, projectSU on every link, checkSU again --------------
+// checkSU of one matrix = |x^+ x - 1|^2 + |det x - 1|^2 (maths/matrixFunctions.nim:392-396)
+__device__ __forceinline__ double2 m3_det(const M3& m) {
+  const double2 a = c_mul(m.e[0], m.e[4]), b = c_mul(m.e[1], m.e[3]);
+  const double2 c = c_mul(m.e[2], m.e[3]), d = c_mul(m.e[0], m.e[5]);
+  const double2 g = c_mul(m.e[1], m.e[5]), h = c_mul(m.e[2], m.e[4]);
+  const double2 t0 = c_mul(make_double2(a.x - b.x, a.y - b.y), m.e[8]);
+  const double2 t1 = c_mul(make_double2(c.x - d.x, c.y - d.y), m.e[7]);
+  const double2 t2 = c_mul(make_double2(g.x - h.x, g.y - h.y), m.e[6]);
+  return make_double2(t0.x + t1.x + t2.x, t0.y + t1.y + t2.y);
+}
+__device__ __forceinline__ double check_su(const M3& m) {
+  double d = 0.0;
+#pragma unroll
+  for (int i = 0; i < 3; i++)
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+      double2 s = make_double2(i == j ? -1.0 : 0.0, 0.0);   // (x^+ x)_ij = sum_k conj(x_ki) x_kj
+#pragma unroll
+      for (int k = 0; k < 3; k++) {
+        const double2 a = m.e[k * 3 + i], b = m.e[k * 3 + j];
+        s.x += a.x * b.x + a.y * b.y;
+        s.y += a.x * b.y - a.y * b.x;
+      }
+      d += s.x * s.x + s.y * s.y;
+    }
+  const double2 det = m3_det(m);
+  return d + (det.x - 1.0) * (det.x - 1.0) + det.y * det.y;
+}
+// acc[0] sum before, [1] sum after (atomic adds: a diagnostic, like the echo of the reference), [2],[3] maxima as bits
+__global__ void __launch_bounds__(RNG_BLOCK) k_reunit(double2* f, int Vh, int nfields, double* acc) {
+  const size_t t = (size_t)blockIdx.x * RNG_BLOCK + threadIdx.x;
+  const size_t n = (size_t)nfields * 2 * Vh;
+  double db = 0.0, da = 0.0;
+  if (t < n) {
+    const size_t fp = t / Vh;            // field * 2 + parity
+    const int idx = (int)(t - fp * Vh);
+    double2* o = f + fp * 9 * Vh + idx;
+    M3 m;
+#pragma unroll
+    for (int e = 0; e < 9; e++) m.e[e] = o[(size_t)e * Vh];
+    db = check_su(m);
+    m = project_u(m);                    // projectSU = projectU, then det^(-1/3) (matrixFunctions.nim:359-370)
+    const double2 det = m3_det(m);
+    const double ph = (1.0 / -3.0) * atan2(det.y, det.x);
+    const double2 w = make_double2(cos(ph), sin(ph));
+#pragma unroll
+    for (int e = 0; e < 9; e++) m.e[e] = c_mul(w, m.e[e]);
+    da = check_su(m);
+#pragma unroll
+    for (int e = 0; e < 9; e++) o[(size_t)e * Vh] = m.e[e];
+  }
+  double sb = db, sa = da, mb = db, ma = da;
+#pragma unroll
+  for (int o2 = 16; o2 > 0; o2 >>= 1) {
+    sb += __shfl_down_sync(0xffffffffu, sb, o2); sa += __shfl_down_sync(0xffffffffu, sa, o2);
+    mb = fmax(mb, __shfl_down_sync(0xffffffffu, mb, o2)); ma = fmax(ma, __shfl_down_sync(0xffffffffu, ma, o2));
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicAdd(acc + 0, sb); atomicAdd(acc + 1, sa);
+    atomicMax(reinterpret_cast<unsigned long long*>(acc + 2), (unsigned long long)__double_as_longlong(mb));
+    atomicMax(reinterpret_cast<unsigned long long*>(acc + 3), (unsigned long long)__double_as_longlong(ma));
+  }
+}
+__global__ void k_xsum4(XRank* xr, double* acc) {   // sums [0],[1] and maxima [2],[3] over the ranks of the box
+  const double a = xrank_sum(xr, acc[0]), b = xrank_sum(xr, acc[1]);
+  const double c = xrank_sum<true>(xr, acc[2]), d = xrank_sum<true>(xr, acc[3]);
+  if ((threadIdx.x & 31) == 0) { acc[0] = a; acc[1] = b; acc[2] = c; acc[3] = d; }
+}
+// out[0..3] = avg, max before; avg, max after -- normalised like checkSU (gauge/gaugeUtils.nim:1407-1422)
+int reunit_links(Gauge& g, double out[4]) {
+  Context& c = ctx();
+  if (!g.loaded) return fail("gauge_reunit: gauge not loaded");
+  double* acc = c.d_scal + 40;
+  QB_CUDA(cudaMemsetAsync(acc, 0, sizeof(double) * 4, c.stream));
+  const size_t n = (size_t)g.nlinks * 2 * c.g.Vh;
+  k_reunit<<<(unsigned)((n + RNG_BLOCK - 1) / RNG_BLOCK), RNG_BLOCK, 0, c.stream>>>(g.d, c.g.Vh, g.nlinks, acc);
+  count_launch();
+  if (c.g.nranks > 1) {
+    if (c.p2p) {
+      k_xsum4<<<1, 32, 0, c.stream>>>(c.d_xr, acc);
+      count_launch();
+    } else if (c.nccl) {
+      QB_NCCL(nccl().AllReduce(acc, acc, 2, ncclDouble, ncclSum, c.nccl, c.stream));
+      QB_NCCL(nccl().AllReduce(acc + 2, acc + 2, 2, ncclDouble, ncclMax, c.nccl, c.stream));
+    }
+  }
+  QB_CUDA(cudaGetLastError());
+  double h[4];
+  QB_CHECK(fetch_scalars(acc, h, 4));
+  const double cn = 2.0 * (3 * 3 + 1);
+  const double vol = (double)c.g.V * c.g.nranks;
+  if (out) {
+    out[0] = sqrt(h[0] / (cn * g.nlinks * vol)); out[1] = sqrt(h[2] / cn);
+    out[2] = sqrt(h[1] / (cn * g.nlinks * vol)); out[3] = sqrt(h[3] / cn);
+  }
+  return compress_links(g);
+}
+
 int unit_links(Gauge& g) {
   Context& c = ctx();
   const size_t n = (size_t)g.nlinks * 18 * c.g.Vh;

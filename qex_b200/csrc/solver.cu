@@ -120,15 +120,16 @@ __global__ void k_cg_step(double* S, CgStatus* st) {
 }
 
 // after the initial residual: r2stop = r2req*b2 (cg.nim:155), loop entry test (:163)
-__global__ void k_cg_init(double* S, CgStatus* st, double r2req, double maxits) {
+// itn0 > 0: a restarted CgState (cg.nim:158-161 picks up iterations, r2old from the state)
+__global__ void k_cg_init(double* S, CgStatus* st, double r2req, double maxits, double itn0, double r2old0) {
   S[S_R2] = S[S_R2NEW];
-  S[S_R2OLD] = 1.0;
+  S[S_R2OLD] = r2old0;
   S[S_R2STOP] = r2req * S[S_B2];
-  S[S_ITN] = 0.0;
+  S[S_ITN] = itn0;
   S[S_MAXITS] = maxits;
-  S[S_DONE] = (!(S[S_R2] > S[S_R2STOP]) || maxits <= 0.0) ? 1.0 : 0.0;
+  S[S_DONE] = (!(S[S_R2] > S[S_R2STOP]) || maxits <= itn0) ? 1.0 : 0.0;
   S[S_SEQ] = 0.0;
-  st->itn = 0; st->done = (long long)S[S_DONE]; st->r2 = S[S_R2];
+  st->itn = (long long)itn0; st->done = (long long)S[S_DONE]; st->r2 = S[S_R2];
   __threadfence_system();
   st->seq = 0;
 }
@@ -177,34 +178,47 @@ static inline int cg_grid(size_t n) {
 }
 
 int cg_xx(const Gauge& g, int parity, double2* x, const double2* b, double m2, double r2req,
-          int maxits, bool x_is_zero, CgResult* res) {
+          int maxits, bool x_is_zero, CgResult* res, CgKeep* keep) {
   Context& c = ctx();
   QB_CHECK(cg_workspace());
   const size_t n = (size_t)3 * c.g.Vh;
   double* S = c.d_scal;
   const int grid = cg_grid(n);
+  // a CgState object keeps r and p between calls (cg.nim:13-19); one-shot solves use the shared work vectors
+  double2* const w_r = keep ? keep->r : qb::w_r;
+  double2* const w_p = keep ? keep->p : qb::w_p;
+  const bool restart = keep && keep->b2 >= 0.0;
+  const int itn0 = restart ? keep->iterations : 0;
 
   QB_CUDA(cudaStreamSynchronize(c.stream));
   for (int i = 0; i < RING; i++) h_status[i].seq = -1;
 
-  // first call of CgState.solve, cg.nim:132-153
-  QB_CHECK(blas_norm2(b, n, S + S_B2));
-  if (x_is_zero) {
-    QB_CHECK(blas_copy(w_r, b, n));
+  if (!restart) {
+    // first call of CgState.solve, cg.nim:132-153
+    QB_CHECK(blas_norm2(b, n, S + S_B2));
+    if (x_is_zero) {
+      QB_CHECK(blas_copy(w_r, b, n));
+    } else {
+      QB_CHECK(apply_xx(g, parity, w_Ap, x, m2, nullptr));
+      QB_CHECK(blas_xmy(w_r, b, w_Ap, n));
+    }
+    QB_CHECK(blas_norm2(w_r, n, S + S_R2NEW));
+    QB_CHECK(allreduce_scalars(S + S_B2, 1));
+    QB_CHECK(allreduce_scalars(S + S_R2NEW, 1));
   } else {
-    QB_CHECK(apply_xx(g, parity, w_Ap, x, m2, nullptr));
-    QB_CHECK(blas_xmy(w_r, b, w_Ap, n));
+    // later call on the same state (cg.nim:155-161): b2, r2, r2old, iterations and the vectors r, p carry over
+    c.h_scal[0] = keep->b2; c.h_scal[1] = keep->r2;
+    QB_CUDA(cudaMemcpyAsync(S + S_B2, c.h_scal, sizeof(double), cudaMemcpyHostToDevice, c.stream));
+    QB_CUDA(cudaMemcpyAsync(S + S_R2NEW, c.h_scal + 1, sizeof(double), cudaMemcpyHostToDevice, c.stream));
   }
-  QB_CHECK(blas_norm2(w_r, n, S + S_R2NEW));
-  QB_CHECK(allreduce_scalars(S + S_B2, 1));
-  QB_CHECK(allreduce_scalars(S + S_R2NEW, 1));
-  k_cg_init<<<1, 1, 0, c.stream>>>(S, d_status, r2req, (double)maxits);
+  k_cg_init<<<1, 1, 0, c.stream>>>(S, d_status, r2req, (double)maxits, (double)itn0, restart ? keep->r2old : 1.0);
   count_launch();
   double hs[2];
   QB_CHECK(fetch_scalars(S + S_B2, hs, 1));
   const double b2 = hs[0];
   if (b2 == 0.0) {  // cg.nim:139-144
     QB_CHECK(blas_zero(x, n));
+    if (keep) { QB_CHECK(blas_zero(w_r, n)); keep->b2 = 0.0; keep->r2 = 0.0; keep->r2old = 1.0; keep->iterations = 0; }
     res->iterations = 0; res->r2 = 0.0; res->b2 = 0.0;
     return 0;
   }
@@ -212,7 +226,7 @@ int cg_xx(const Gauge& g, int parity, double2* x, const double2* b, double m2, d
   const int LAG = 3;  // iterations the host may run ahead of the device
   int launched = 0;
   bool done = h_status[0].done != 0;  // slot 0 = state after k_cg_init (fetch_scalars synchronised)
-  while (!done && launched < maxits) {
+  while (!done && launched < maxits - itn0) {
     k_cg_p<<<grid, CB, 0, c.stream>>>(w_p, w_r, S, n);
     count_launch();
     QB_CHECK(apply_xx(g, parity, w_Ap, w_p, m2, S + S_PAP));
@@ -249,6 +263,7 @@ int cg_xx(const Gauge& g, int parity, double2* x, const double2* b, double m2, d
   res->iterations = (int)fin[S_ITN];
   res->r2 = fin[S_R2];
   res->b2 = b2;
+  if (keep) { keep->b2 = b2; keep->r2 = fin[S_R2]; keep->r2old = fin[S_R2OLD]; keep->iterations = (int)fin[S_ITN]; }
   return 0;
 }
 

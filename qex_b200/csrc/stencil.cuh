@@ -194,12 +194,15 @@ __device__ __forceinline__ void wait_flag(const unsigned int* flag, unsigned int
 // seq matches carries valid data: no fence, one fabric traversal), then collects rank j's value
 // from the local slot.  Every rank adds the same values in rank order: the result is
 // bit-identical everywhere and run-to-run.
+template <bool MAXOP = false>
 __device__ __forceinline__ double xrank_sum(XRank* xr, double v) {
   const int lane = threadIdx.x & 31;
   const int n = xr->nranks, me = xr->rank;
   const unsigned int seq = xr->seq + 1u;
   const int b = seq % XR_NB;
   double got = 0.0;
+  unsigned long long* const stamps = xr->stamps;
+  const unsigned long long t_in = stamps ? globaltimer_ns() : 0ull;
   if (lane < n) {
     const unsigned long long bits = (unsigned long long)__double_as_longlong(v);
     const unsigned long long hi = (unsigned long long)seq << 32;
@@ -218,10 +221,20 @@ __device__ __forceinline__ double xrank_sum(XRank* xr, double v) {
     }
     got = __longlong_as_double((long long)((w0 & 0xffffffffull) | (w1 << 32)));
   }
-  double s = 0.0;
-  for (int j = 0; j < n; j++) s += __shfl_sync(0xffffffffu, got, j);
+  double s = MAXOP ? -1.797693134862315e308 : 0.0;
+  for (int j = 0; j < n; j++) {
+    const double gj = __shfl_sync(0xffffffffu, got, j);
+    s = MAXOP ? fmax(s, gj) : s + gj;
+  }
   __syncwarp();
-  if (lane == 0) xr->seq = seq;
+  if (lane == 0) {
+    xr->seq = seq;
+    if (stamps) {
+      const unsigned long long dt = globaltimer_ns() - t_in;
+      stamps[0] += dt; stamps[1] += 1ull;
+      if (dt > stamps[2]) stamps[2] = dt;
+    }
+  }
   return s;
 }
 

@@ -42,6 +42,33 @@ def cpu_plan_check(L, G, nlinks, rank, world, dist):
         assert h["faceh"] == int(np.prod(X)) // X[mu] // 2
         assert h["depth"] == (3 if nlinks == 8 else 1)
         assert h["n_f"] == 3 * h["depth"] * h["faceh"] and h["n_b"] == 3 * (4 if nlinks == 8 else 1) * h["faceh"]
+    # block -> tile table of the one-kernel multi-rank sweep (csrc/dslash.cu plan_tiles): every tile once, interior tiles
+    # first, and a face tile waits exactly for the neighbours its sites hop to
+    X = [L[d] // G[d] for d in range(4)]
+    Vh = int(np.prod(X)) // 2
+    dep = 3 if nlinks == 8 else 1
+    for parity in (0, 1):
+        tiles = qb.plan_tiles(L, G, rank, nlinks, parity)
+        ntiles = (Vh + 127) // 128
+        assert sorted(t for t, _ in tiles) == list(range(ntiles))
+        needs = [n for _, n in tiles]
+        first_face = next((i for i, n in enumerate(needs) if n), len(needs))
+        assert all(n == 0 for n in needs[:first_face]) and all(n != 0 for n in needs[first_face:])
+        idx = np.arange(Vh)
+        xh = X[0] // 2
+        x1 = (idx // xh) % X[1]; x2 = (idx // (xh * X[1])) % X[2]; x3 = idx // (xh * X[1] * X[2])
+        x0 = 2 * (idx % xh) + ((parity + x1 + x2 + x3) & 1)
+        xs = [x0, x1, x2, x3]
+        want = np.zeros(ntiles, dtype=np.int64)
+        for mu in range(4):
+            if G[mu] == 1:
+                continue
+            np.bitwise_or.at(want, idx // 128, np.where(xs[mu] + dep >= X[mu], 1 << (2 * mu), 0))
+            np.bitwise_or.at(want, idx // 128, np.where(xs[mu] - dep < 0, 1 << (2 * mu + 1), 0))
+        for t, n in tiles:
+            assert n == want[t], (parity, t, n, want[t])
+        split = {h["mu"] for h in plan}
+        assert all(((n >> (2 * mu)) & 3) == 0 for n in needs for mu in range(4) if mu not in split)
     # emulate one sweep's exchange with gloo: same order as csrc/comm.cu halo_start
     send = torch.arange(2 * total, dtype=torch.float64) + 1e6 * rank
     recv = torch.zeros(2 * total, dtype=torch.float64)
@@ -76,14 +103,20 @@ def gpu_case(L, G, nlinks, inner, rank, world, local_rank, dist, transport="nccl
         qb.p2p_attach_torch(dist)
         assert qb.p2p_active()
     qb.set_host_layout(inner)
-    lat, g, (x, b) = (make_exact_inputs if recon == 12 else make_inputs)(L, nlinks)
+    lat, g, (x, b) = (make_exact_inputs if recon in (12, 14) else make_inputs)(L, nlinks)
+    if recon == 14:
+        # U(3) links whose determinant phase changes from site to site (what projectU leaves: nHYP links, the Naik
+        # products of the HISQ W links): exact SU(3) times a per-link phase
+        th = np.random.default_rng(99).uniform(0, 2 * np.pi, g.shape[:2])
+        gc = (g[..., 0] + 1j * g[..., 1]) * np.exp(1j * th)[:, :, None, None]
+        g = np.ascontiguousarray(np.stack([gc.real, gc.imag], axis=-1))
     lo = oracle.QexLayout(L, G, inner)
     mine = lambda f: lo.scatter(f)[rank]
     s = qb.Staggered([mine(g[k]) for k in range(nlinks)])
     res = {}
-    if recon == 12:
-        got_rc, dev = s.recon(12)
-        assert got_rc == ([12, 12] if nlinks == 8 else [12, 18]), (got_rc, dev)
+    if recon in (12, 14):
+        got_rc, dev = s.recon(recon)
+        assert got_rc == ([recon, recon] if nlinks == 8 else [recon, 18]), (got_rc, dev)
     # Dslash, all flavours
     for parity in (0, 1):
         want = b.copy()
@@ -287,7 +320,7 @@ def main():
     ap.add_argument("--inner", default="1,1,1,1")
     ap.add_argument("--nlinks", type=int, default=4)
     ap.add_argument("--transport", default="nccl", choices=["nccl", "p2p"])
-    ap.add_argument("--recon", type=int, default=18, choices=[12, 18])
+    ap.add_argument("--recon", type=int, default=18, choices=[12, 14, 18])
     ap.add_argument("--links", action="store_true", help="link pipeline / force case instead of the Dslash + CG case")
     a = ap.parse_args()
     import torch.distributed as dist

@@ -47,6 +47,28 @@ def test_multi_gpu_parity_recon12(nproc, lat, rg, nlinks, transport):
     run_case(nproc, lat, rg, "1,1,1,1", nlinks, transport, recon=12)
 
 
+@pytest.mark.parametrize("nproc,lat,rg,nlinks", [
+    (2, "8,8,8,16", "1,1,1,2", 4),
+    (2, "8,8,12,8", "1,1,2,1", 8),
+    (4, "8,8,16,16", "1,1,2,2", 8),
+    (8, "8,16,16,16", "1,2,2,2", 4),
+])
+def test_multi_gpu_parity_recon14(nproc, lat, rg, nlinks):
+    """14-real storage (rows 0,1 + one complex factor per link) on a split lattice: U(3) links with a site-dependent
+    determinant phase -- what the nHYP solves of BASELINE configs[3] read."""
+    run_case(nproc, lat, rg, "1,1,1,1", nlinks, "p2p", recon=14)
+
+
+@pytest.mark.parametrize("nproc,lat,rg,nlinks,transport", [
+    (4, "8,16,16,8", "1,2,2,1", 4, "p2p"),          # x1 split: every fourth tile touches a face
+    (4, "8,16,16,8", "1,2,2,1", 8, "p2p"),
+    (8, "8,8,16,32", "1,1,2,4", 8, "p2p"),          # the rank geometry SURVEY 8e recommends for 8 GPUs
+    (8, "8,8,16,32", "1,1,2,4", 4, "nccl"),
+])
+def test_multi_gpu_parity_more_geometries(nproc, lat, rg, nlinks, transport):
+    run_case(nproc, lat, rg, "1,1,1,1", nlinks, transport)
+
+
 @pytest.mark.parametrize("nproc,lat,rg,inner", [
     (2, "8,8,8,16", "1,1,1,2", "1,1,1,1"),
     (2, "8,8,8,8", "1,1,1,2", "1,2,2,1"),        # local extent 4: the 3-hop and the staples leave the rank both ways

@@ -483,3 +483,114 @@ def test_remaining_stagD_flavours(orc, ctx_factory):
         qb.stagDb(s, parity, got, x, m, 0.7)
         assert rel_l2(got[sl], want[sl]) <= DSLASH_TOL
     s.free()
+
+
+def test_solveEO_starts_from_the_callers_guess(orc, ctx_factory):
+    """solveEO (stagSolve.nim:17-38): cgSolve(r, x, stagD2ee) with r's content as the initial guess -- against the
+    oracle's CG from the same guess; a good guess must cost fewer iterations than the zero start."""
+    L, m, r2req = (8, 8, 8, 16), 0.1, 1e-12
+    qb = ctx_factory(L)
+    lat, g, (b, g0) = make_inputs(L, 4)
+    s = qb.Staggered([g[k] for k in range(4)])
+    for guess in (0.01 * g0, None):
+        if guess is None:       # the solution of a looser solve as the guess
+            guess = lat.vector()
+            lat.cg_xx(g, guess, b, m * m, 0, 1e-6, 10000)
+        want = guess.copy()
+        it_o, r2_o, b2_o = lat.cg_xx(g, want, b, m * m, 0, r2req, 10000)
+        got = guess.copy()
+        sp = qb.SolverParams(r2req=r2req, maxits=10000)
+        s.solveEO(got, b, m, sp)
+        assert abs(sp.iterations - it_o) <= 1, (sp.iterations, it_o)
+        assert rel_l2(got[:lat.half], want[:lat.half]) <= 10 * np.sqrt(r2req)
+        assert np.array_equal(got[lat.half:], guess[lat.half:])       # the odd part is not touched
+        assert sp.r2 <= r2req
+        assert sp.flops == (4 * 4 * 72 + 60) * lat.half * sp.iterations
+    zero = lat.vector()
+    it_zero, _, _ = lat.cg_xx(g, zero, b, m * m, 0, r2req, 10000)
+    assert sp.iterations < it_zero
+    # device-resident flavour, bit-identical with the host-buffer call
+    dr, dx = qb.DeviceField(guess), qb.DeviceField(b)
+    sp2 = qb.SolverParams(r2req=r2req, maxits=10000)
+    s.solveEO(dr, dx, m, sp2)
+    assert sp2.iterations == sp.iterations
+    assert np.array_equal(dr.download(lat.vector())[:lat.half], got[:lat.half])
+    dr.free(); dx.free(); s.free()
+
+
+def test_cgstate_restart_continues_the_same_krylov_sequence(orc, ctx_factory):
+    """CgState (cg.nim:13-53,256-283): solve() called again without reset continues where it stopped -- capped at
+    20 iterations and then released it must give the iterates of one uninterrupted solve bit for bit; after
+    reset() it starts over from the current x (fewer iterations than from zero)."""
+    L, m, r2req = (8, 8, 8, 8), 0.1, 1e-12
+    qb = ctx_factory(L)
+    lat, g, (b, _) = make_inputs(L, 8)
+    s = qb.Staggered([g[k] for k in range(8)])
+    db = qb.DeviceField(b)
+    x1, x2 = qb.DeviceField(), qb.DeviceField()
+    one = qb.SolverParams(r2req=r2req, maxits=10000)
+    s.dev_solveXX(x1, db, m, one, parEven=True)
+    x2.zero()
+    cg = qb.CgState(s, x2, db, parEven=True)
+    sp = qb.SolverParams(r2req=r2req, maxits=20)
+    cg.solve(m, sp)
+    assert sp.iterations == 20 and sp.r2 > r2req
+    mid = x2.download(lat.vector()).copy()
+    sp = qb.SolverParams(r2req=r2req, maxits=10000)
+    cg.solve(m, sp)
+    assert sp.iterations == one.iterations                   # cumulative, like sp.finalIterations = state.iterations
+    assert sp.r2 == one.r2
+    a, c = x1.download(lat.vector()), x2.download(lat.vector())
+    assert np.array_equal(a[:lat.half], c[:lat.half])
+    assert not np.array_equal(mid[:lat.half], c[:lat.half])
+    # a converged state does nothing more
+    sp3 = qb.SolverParams(r2req=r2req, maxits=10000)
+    cg.solve(m, sp3)
+    assert sp3.iterations == one.iterations
+    # reset: b2 and r are recomputed from the current x; tightening the request now takes a few iterations only
+    cg.reset()
+    sp = qb.SolverParams(r2req=1e-16, maxits=10000)
+    cg.solve(m, sp)
+    assert 0 < sp.iterations < one.iterations // 2
+    want = lat.vector()
+    lat.cg_xx(g, want, b, m * m, 0, 1e-16, 10000)
+    assert rel_l2(x2.download(lat.vector())[:lat.half], want[:lat.half]) <= 1e-7
+    cg.free()
+    for d in (db, x1, x2, s):
+        d.free()
+
+
+def test_reunit_makes_qex_links_exact_and_12_real_storage_applies(orc, ctx_factory):
+    """reunit (staghmc_sh.nim:247-257 = checkSU, projectSU, checkSU): g.random leaves links unitary to ~1e-11 (the
+    12-real form refuses them); after reunit they are unitary to ~1e-15, the 12-real form is accepted, and the
+    Dslash on them matches the oracle's 18-real Dslash on the SAME (downloaded) links to 1e-13."""
+    L = (8, 8, 8, 16)
+    qb = ctx_factory(L)
+    lat = orc.Lattice(L)
+    r = qb.newRNGField(987654321)
+    g = qb.DeviceGauge(nlinks=4)
+    g.random(r)
+    got_rc, dev = g.recon(12)
+    assert got_rc[0] == 18 and dev[0] > 2e-14               # as generated: refused
+    before, after = g.reunit()
+    assert 1e-13 < before[1] < 1e-9 and before[0] <= before[1]
+    assert after[1] < 5e-15 and after[0] <= after[1]
+    links = [lat.gauge(1)[0] for _ in range(4)]
+    g.download(links)
+    go = lat.random_gauge(lat.new_rng(987654321), 4)
+    assert 0 < np.abs(np.stack(links) - go).max() < 1e-9     # moved, by the size of the old deviation only
+    g.rephase()
+    got_rc, dev = g.recon(12)
+    assert got_rc[0] == 12 and dev[0] <= 2e-14, (got_rc, dev)
+    gl = np.ascontiguousarray(np.stack(links))
+    lat.setBC(gl); lat.stagPhase(gl)
+    x = lat.gaussian_vector(lat.new_rng(3))
+    s = qb.newStag(g)
+    for parity in (0, 1):
+        want = lat.vector()
+        lat.stagD2(gl, want, x, 0.0, 0.0, parity)
+        got = lat.vector()
+        qb.stagD2(s, parity, got, x, 0.0, 0.0)
+        sl = slice(0, lat.half) if parity == 0 else slice(lat.half, lat.vol)
+        assert rel_l2(got[sl], want[sl]) <= DSLASH_TOL
+    r.free(); g.free()
