@@ -250,6 +250,9 @@ int qexb200_field_zero(qexb200_field_t f);
 /* norm2 / redot on a subset (src/field/fieldET.nim:605-625,704-724), summed over ranks */
 int qexb200_field_norm2(qexb200_field_t f, int subset, double* out);
 int qexb200_field_redot(qexb200_field_t f, qexb200_field_t g, int subset, double* out);
+/* y = a x + b y on a subset: the assignments `y := x`, `y += a*x`, `y := a*x + b*y` of the field expression
+ * templates (src/field/fieldET.nim:547-599) for callers that keep their vectors on the GPU. */
+int qexb200_field_axpby(qexb200_field_t y, double a, qexb200_field_t x, double b, int subset);
 
 int qexb200_dev_stagD2(qexb200_gauge_t g, int parity, qexb200_field_t r, qexb200_field_t x,
                        double a, double b);

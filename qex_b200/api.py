@@ -183,6 +183,7 @@ def lib():
         L.qexb200_dev_solveXX.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, spp]
         L.qexb200_dev_solve.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, spp]
         L.qexb200_plan_peers.argtypes = [ip, ip, C.c_int, C.POINTER(C.c_ubyte)]
+        L.qexb200_field_axpby.argtypes = [C.c_int, C.c_double, C.c_int, C.c_double, C.c_int]
         L.qexb200_solveEO.argtypes = [C.c_int, dp, dp, C.c_double, spp]
         L.qexb200_dev_solveEO.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, spp]
         L.qexb200_cg_create.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, ip]
@@ -429,6 +430,13 @@ class DeviceField:
         o = C.c_double()
         _ck(lib().qexb200_field_norm2(self.h, subset, C.byref(o)))
         return o.value
+
+    def axpby(self, a, x, b, subset=ALL):
+        """self = a x + b self on a subset (`:=`, `+=` of src/field/fieldET.nim:547-599)."""
+        _ck(lib().qexb200_field_axpby(self.h, float(a), x.h, float(b), subset))
+
+    def assign(self, x, subset=ALL):
+        self.axpby(1.0, x, 0.0, subset)
 
     def redot(self, other, subset=ALL):
         o = C.c_double()

@@ -976,6 +976,15 @@ int qexb200_field_redot(qexb200_field_t hf, qexb200_field_t hg, int subset, doub
   Gauge* g; QB_CHECK(get_gauge(hg, &g));           \
   Field *f1, *f2; QB_CHECK(get_field(h1, &f1)); QB_CHECK(get_field(h2, &f2));
 
+int qexb200_field_axpby(qexb200_field_t hy, double a, qexb200_field_t hx, double b, int subset) {
+  QB_CHECK(need_ctx());
+  Field *y, *x; QB_CHECK(get_field(hy, &y)); QB_CHECK(get_field(hx, &x));
+  if (subset < QEXB200_EVEN || subset > QEXB200_ALL) return fail("field_axpby: subset must be EVEN, ODD or ALL");
+  const size_t off = (subset == QEXB200_ODD) ? nhalf() : 0;
+  const size_t n = (subset == QEXB200_ALL) ? 2 * nhalf() : nhalf();
+  if (b == 0.0 && a == 1.0) return y == x ? 0 : blas_copy(y->d + off, x->d + off, n);
+  return blas_axpby(y->d + off, a, x->d + off, b, n);
+}
 int qexb200_dev_stagD2(qexb200_gauge_t hg, int parity, qexb200_field_t r, qexb200_field_t x, double a, double b) {
   GET_G_F2(hg, r, x);
   if (parity != 0 && parity != 1) return fail("stagD2: parity must be 0 or 1");

@@ -244,6 +244,7 @@ int p2p_attach(const void* handles) {
     if (sec > 0) c.p2p_timeout_ns = (unsigned long long)(sec * 1e9);
   }
   xr.timeout_ns = c.p2p_timeout_ns;
+  if (const char* ev = getenv("QEXB200_PACK_BLOCKS")) { if (atoi(ev) > 0) c.pack_blocks = atoi(ev); }
   if (!c.d_xr) QB_CUDA(cudaMalloc(&c.d_xr, sizeof(XRank)));
   QB_CUDA(cudaMemcpy(c.d_xr, &xr, sizeof xr, cudaMemcpyHostToDevice));
   // buffers laid out for the NCCL path are no longer needed

@@ -131,6 +131,7 @@ struct Context {
   unsigned long long p2p_timeout_ns = 120ull * 1000000000ull;  // QEXB200_P2P_TIMEOUT_S
   // multi-rank sweep: block -> tile tables [link classes - 1][output parity] (dslash.cu tile_order)
   unsigned int* d_order[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};
+  int pack_blocks = 2 * 148;   // cap on the pack blocks of the multi-rank sweep (QEXB200_PACK_BLOCKS)
   // role timestamps of the multi-rank sweep (qexb200_debug_role_times): STAMP_RING launches x 8 words + 8 for xrank_sum
   unsigned long long* d_stamps = nullptr;
 };

@@ -11,6 +11,7 @@
 // coalesced along the site index.  Links are streamed with ld.global.cs, vectors
 // go through the read-only path so the 8/16 neighbour re-reads hit L1/L2.
 #include "stencil.cuh"
+#include <algorithm>
 #include <cstdlib>
 
 namespace qb {
@@ -444,8 +445,13 @@ __global__ void __launch_bounds__(SWEEP_BLOCK, SWEEP_MINB) k_sweep_mr(const MRAr
   if (stamp) atomicMin(F.stamps + ST_START, globaltimer_ns());
   double dot = 0.0;
   if (bid < F.npack) {
-    const int t = bid * SWEEP_BLOCK + threadIdx.x;
-    if (t < F.P.d[F.P.ndir - 1].end) pack_item<NL, RC>(F.P, t);
+    // few, persistent pack blocks: a pack item is one link + one vector in flight, so a block per 128 items holds a
+    // residency slot for a full load -> NVLink store -> system fence round trip while moving almost nothing (896
+    // such blocks = the whole first wave of the fat+Naik sweep on 2 ranks, 22 us of 193).  Here every pack thread
+    // strides over the items (stores are fire-and-forget) and the block pays ONE fence at the end.
+    const int end = F.P.d[F.P.ndir - 1].end;
+#pragma unroll 1
+    for (int t = bid * SWEEP_BLOCK + threadIdx.x; t < end; t += F.npack * SWEEP_BLOCK) pack_item<NL, RC>(F.P, t);
     pack_signal(F.P, F.npack);
     if (stamp) atomicMax(F.stamps + ST_PACK_END, globaltimer_ns());
   } else {
@@ -630,6 +636,11 @@ void plan_tiles(const Geom& g, int nl, int parity, std::vector<unsigned int>& ou
   out.insert(out.end(), face.begin(), face.end());
 }
 
+static bool overlap_on() {
+  const char* ev = getenv("QEXB200_OVERLAP");
+  return !(ev && ev[0] == '0');
+}
+
 static int tile_order(int nl, int parity, const unsigned int** order, int* ntiles) {
   Context& c = ctx();
   unsigned int*& d = c.d_order[nl - 1][parity];
@@ -638,6 +649,11 @@ static int tile_order(int nl, int parity, const unsigned int** order, int* ntile
     if (n >= (1 << 24)) return fail("sweep: %d tiles exceed the 24-bit tile index", n);
     std::vector<unsigned int> h;
     plan_tiles(c.g, nl, parity, h);
+    if (!overlap_on()) {
+      // measurement switch (QEXB200_OVERLAP=0): face tiles FIRST, so the whole grid queues up behind the halo wait and
+      // nothing hides the transfer -- the "overlap off" arm of the reference's 3-phase protocol (stagD.nim:355-393)
+      std::stable_partition(h.begin(), h.end(), [](unsigned int e) { return (e >> 24) != 0; });
+    }
     QB_CUDA(cudaMalloc(&d, sizeof(unsigned int) * h.size()));
     QB_CUDA(cudaMemcpy(d, h.data(), sizeof(unsigned int) * h.size(), cudaMemcpyHostToDevice));
   }
@@ -680,7 +696,7 @@ int sweep(const Gauge& g, int parity, double2* r, const double2* x, const double
       D.flag_b = win_flag(c.win, buf, hd.mu, 1);
       D.faceh = hd.faceh;
     }
-    F.npack = (npk + SWEEP_BLOCK - 1) / SWEEP_BLOCK;
+    F.npack = std::min((npk + SWEEP_BLOCK - 1) / SWEEP_BLOCK, c.pack_blocks);
     F.seq = c.halo_seq; F.err = c.d_err; F.timeout_ns = c.p2p_timeout_ns; F.xr = xrank();
     F.stamps = c.d_stamps ? c.d_stamps + (size_t)ST_N * (c.halo_seq % STAMP_RING) : nullptr;
     const int total = F.npack + F.ntiles;
@@ -713,6 +729,7 @@ int sweep(const Gauge& g, int parity, double2* r, const double2* x, const double
   // NCCL path: the interior part of the dot goes to a scratch scalar, k_exterior finishes it
   double* dot_interior = c.d_scal + 48;
   if (multi) A.result = dot_interior;
+  if (multi && !overlap_on()) QB_CHECK(halo_wait());   // measurement switch: exchange first, then the interior
   QB_DISPATCH(g, fused_dot, k_sweep<NL, RC, DOT><<<grid, SWEEP_BLOCK, 0, c.stream>>>(A));
   count_launch();
   QB_CUDA(cudaGetLastError());
