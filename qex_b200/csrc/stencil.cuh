@@ -198,7 +198,10 @@ template <bool MAXOP = false>
 __device__ __forceinline__ double xrank_sum(XRank* xr, double v) {
   const int lane = threadIdx.x & 31;
   const int n = xr->nranks, me = xr->rank;
-  const unsigned int seq = xr->seq + 1u;
+  // lane 0 owns the counter; the others take its value (several sums may follow each other inside one kernel)
+  unsigned int seq = 0;
+  if (lane == 0) seq = *(volatile unsigned int*)&xr->seq + 1u;
+  seq = __shfl_sync(0xffffffffu, seq, 0);
   const int b = seq % XR_NB;
   double got = 0.0;
   unsigned long long* const stamps = xr->stamps;
@@ -228,7 +231,7 @@ __device__ __forceinline__ double xrank_sum(XRank* xr, double v) {
   }
   __syncwarp();
   if (lane == 0) {
-    xr->seq = seq;
+    *(volatile unsigned int*)&xr->seq = seq;
     if (stamps) {
       const unsigned long long dt = globaltimer_ns() - t_in;
       stamps[0] += dt; stamps[1] += 1ull;

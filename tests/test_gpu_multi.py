@@ -7,7 +7,16 @@ from test_dist_cpu import launch
 pytestmark = pytest.mark.gpu
 
 
+def only_nproc(nproc):
+    """QEXB200_TEST_NPROC=8 runs just the 8-rank cases (GPU time on an N-GPU box is charged N-fold)."""
+    import os
+    want = os.environ.get("QEXB200_TEST_NPROC")
+    if want and int(want) != nproc:
+        pytest.skip("QEXB200_TEST_NPROC=%s" % want)
+
+
 def run_case(nproc, lat, rg, inner, nlinks, transport, recon=18):
+    only_nproc(nproc)
     if ngpus() < nproc:
         pytest.skip("needs %d GPUs" % nproc)
     r = launch(nproc, ["--lat", lat, "--rankgeom", rg, "--inner", inner, "--nlinks", str(nlinks),
@@ -80,6 +89,7 @@ def test_multi_gpu_parity_more_geometries(nproc, lat, rg, nlinks, transport):
 def test_multi_gpu_links_and_force(nproc, lat, rg, inner):
     """nHYP / HISQ / fat7+Naik smearing, plaq, stagDeriv / stagD2deriv on a lattice split over ranks: link-shaped
     fields live in the IPC-mapped arena and off-rank neighbours are read over NVLink (csrc/smear.cu, force.cu)."""
+    only_nproc(nproc)
     if ngpus() < nproc:
         pytest.skip("needs %d GPUs" % nproc)
     # the nHYP force keeps 52 fields and works in 28 more: a larger arena than the default 64
