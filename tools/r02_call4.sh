@@ -22,8 +22,8 @@ PY
 run_roles naive_1124 32,32,64,128 1,1,2,4 4
 run_roles naive_1222 32,64,64,64 1,2,2,2 4
 run_roles hisq_1124 32,32,64,128 1,1,2,4 8
-timeout 400 $TR --nproc-per-node 8 --master-port 29512 bench.py --gpus 8 --steps 3 --no-links --no-cold \
+timeout 400 $TR --nproc-per-node 8 --master-port 29512 bench.py --gpus 8 --steps 3 --no-links --no-cold --recon 18 \
   2> gpurun_out/r02_bench_n8.err | grep '^{' > gpurun_out/r02_bench_n8.json
 tail -c 300 gpurun_out/r02_bench_n8.json; tail -2 gpurun_out/r02_bench_n8.err
-QEXB200_TEST_NPROC=8 timeout 600 python -m pytest tests/test_gpu_multi.py -q -m gpu -rA 2>&1 | grep -v "^$" | tail -30 > gpurun_out/r02_multi_tests_n8.log
+QEXB200_P2P_TIMEOUT_S=20 QEXB200_TEST_NPROC=8 timeout 600 python -m pytest tests/test_gpu_multi.py -q -m gpu -rA 2>&1 | grep -v "^$" | tail -30 > gpurun_out/r02_multi_tests_n8.log
 tail -12 gpurun_out/r02_multi_tests_n8.log
