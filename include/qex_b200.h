@@ -102,6 +102,16 @@ int qexb200_local_sites(int* nsites, int* neven);
 int qexb200_gauge_create(int nlinks, qexb200_gauge_t* g);
 int qexb200_gauge_load(qexb200_gauge_t g, const double* const* links);
 int qexb200_gauge_destroy(qexb200_gauge_t g);
+/* Resident handle for a caller that owns HOST link fields (the Nim glue of INTEGRATION.md section 2): the device copy
+ * is cached against (links[0..nlinks) pointers, version).  Same pointers and same version: the handle made earlier is
+ * returned and nothing is uploaded (*cached = 1).  Same pointers, new version: the links are uploaded again INTO the
+ * same handle (*cached = 0).  New pointers: create + load; at most 8 sets are kept, the least recently used one is
+ * destroyed.  `version` is the caller's update counter of these links -- QEX rewrites fermion links only through
+ * smear -> setBC -> stagPhase (src/stagg_pv_hmc/staghmc_spv.nim:367-386, src/physics/stagD.nim:72-80), the glue bumps
+ * its counter there.  What qudaSolveXX re-does on every call (src/quda/qudaWrapperImpl.nim:198-261) is paid once per
+ * link update.  Handles obtained here are owned by the cache: do not pass them to qexb200_gauge_destroy. */
+int qexb200_gauge_cached(const double* const* links, int nlinks, unsigned long long version,
+                         qexb200_gauge_t* g, int* cached);
 /* Link storage the sweeps read.  want = 18: all 18 reals of every link (default).  want = 12: each
  * link class (one-hop, three-hop) whose matrices are s*SU(3) with a single |s| -- naive links with
  * staggered phases and BC (+-SU(3)), Naik links -- is additionally held as rows 0,1 and the third

@@ -183,6 +183,7 @@ def lib():
         L.qexb200_dev_solveXX.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, spp]
         L.qexb200_dev_solve.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, spp]
         L.qexb200_plan_peers.argtypes = [ip, ip, C.c_int, C.POINTER(C.c_ubyte)]
+        L.qexb200_gauge_cached.argtypes = [C.POINTER(C.POINTER(C.c_double)), C.c_int, C.c_ulonglong, ip, ip]
         L.qexb200_field_axpby.argtypes = [C.c_int, C.c_double, C.c_int, C.c_double, C.c_int]
         L.qexb200_solveEO.argtypes = [C.c_int, dp, dp, C.c_double, spp]
         L.qexb200_dev_solveEO.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, spp]
@@ -698,6 +699,18 @@ class CgState:
         if self.h is not None and _lib is not None and _lib.qexb200_is_initialized():
             _lib.qexb200_cg_destroy(self.h)
         self.h = None
+
+
+def cachedStag(links, version):
+    """The glue's handle cache (qexb200_gauge_cached): a Staggered for HOST link fields, uploaded only when the
+    (pointers, version) pair is new.  Returns (Staggered that does not own its handle, was_cached)."""
+    n = len(links)
+    arr = (C.POINTER(C.c_double) * n)(*[_dp(l) for l in links])
+    h, hit = C.c_int(), C.c_int()
+    _ck(lib().qexb200_gauge_cached(arr, n, C.c_ulonglong(int(version)), C.byref(h), C.byref(hit)))
+    g = DeviceGauge.__new__(DeviceGauge)
+    g.nlinks, g.h, g._owner = n, h.value, False
+    return Staggered(g), bool(hit.value)
 
 
 def newStag(g):

@@ -61,6 +61,11 @@ static std::map<int, RngField> g_rngs;
 struct CgObj { CgKeep k; int gauge, parity, x, b; };   // a CgState bound to its operator and fields
 static std::map<int, CgObj> g_cgs;
 static int g_next_handle = 1;
+// device copies cached against the caller's host link pointers (qexb200_gauge_cached)
+struct CacheEntry { std::vector<const double*> ptrs; unsigned long long version; int handle; unsigned long long used; };
+static std::vector<CacheEntry> g_cache;
+static unsigned long long g_cache_clock = 0;
+constexpr size_t CACHE_MAX = 8;
 
 static int need_ctx() {
   if (!g_ctx.live) return fail("qexb200 is not initialised (call qexb200_init; a CUDA device is required, there is no CPU fallback)");
@@ -486,6 +491,7 @@ int qexb200_finalize(void) {
   for (auto& kv : g_gauges) { links_free(kv.second.d, kv.second.nlinks, kv.second.arena); free_compressed(kv.second); }
   for (auto& kv : g_fields) cudaFree(kv.second.d);
   g_gauges.clear(); g_fields.clear();
+  g_cache.clear();
   for (auto& kv : g_rngs) rng_destroy(&kv.second);
   g_rngs.clear();
   for (auto& kv : g_cgs) { cudaFree(kv.second.k.r); cudaFree(kv.second.k.p); }
@@ -561,6 +567,44 @@ int qexb200_gauge_load(qexb200_gauge_t h, const double* const* links) {
   Gauge* g; QB_CHECK(get_gauge(h, &g));
   return upload_links(*g, links);
 }
+// ---- handle cache for callers that own host links ------------------------------------
+static void cache_forget(int h) {
+  for (size_t i = 0; i < g_cache.size(); i++)
+    if (g_cache[i].handle == h) { g_cache.erase(g_cache.begin() + (long)i); return; }
+}
+int qexb200_gauge_cached(const double* const* links, int nlinks, unsigned long long version,
+                         qexb200_gauge_t* out, int* cached) {
+  QB_CHECK(need_ctx());
+  if (!links || !out) return fail("gauge_cached: null argument");
+  if (nlinks != 4 && nlinks != 8) return fail("gauge_cached: nlinks must be 4 or 8, got %d", nlinks);
+  std::vector<const double*> key(links, links + nlinks);
+  for (CacheEntry& e : g_cache) {
+    if (e.ptrs != key) continue;
+    e.used = ++g_cache_clock;
+    *out = e.handle;
+    if (e.version == version) { if (cached) *cached = 1; return 0; }
+    Gauge* g; QB_CHECK(get_gauge(e.handle, &g));
+    QB_CHECK(upload_links(*g, links));          // same storage, new content (sticky recon request re-applied)
+    e.version = version;
+    if (cached) *cached = 0;
+    return 0;
+  }
+  if (g_cache.size() >= CACHE_MAX) {            // evict the least recently used set
+    size_t lru = 0;
+    for (size_t i = 1; i < g_cache.size(); i++) if (g_cache[i].used < g_cache[lru].used) lru = i;
+    const int victim = g_cache[lru].handle;
+    g_cache.erase(g_cache.begin() + (long)lru);
+    QB_CHECK(qexb200_gauge_destroy(victim));
+  }
+  int h = 0;
+  QB_CHECK(qexb200_gauge_create(nlinks, &h));
+  if (qexb200_gauge_load(h, links) != 0) { const std::string keep = g_err; qexb200_gauge_destroy(h); g_err = keep; return 1; }
+  g_cache.push_back(CacheEntry{key, version, h, ++g_cache_clock});
+  *out = h;
+  if (cached) *cached = 0;
+  return 0;
+}
+
 int qexb200_gauge_destroy(qexb200_gauge_t h) {
   QB_CHECK(need_ctx());
   Gauge* g; QB_CHECK(get_gauge(h, &g));
@@ -568,6 +612,7 @@ int qexb200_gauge_destroy(qexb200_gauge_t h) {
   links_free(g->d, g->nlinks, g->arena);
   free_compressed(*g);
   g_gauges.erase(h);
+  cache_forget(h);
   return 0;
 }
 int qexb200_gauge_recon(qexb200_gauge_t h, int want, int got[2], double dev[2]) {

@@ -594,3 +594,39 @@ def test_reunit_makes_qex_links_exact_and_12_real_storage_applies(orc, ctx_facto
         sl = slice(0, lat.half) if parity == 0 else slice(lat.half, lat.vol)
         assert rel_l2(got[sl], want[sl]) <= DSLASH_TOL
     r.free(); g.free()
+
+
+def test_gauge_handle_cache_of_the_glue(orc, ctx_factory):
+    """qexb200_gauge_cached: the device copy is keyed on the host link pointers and the
+    caller's update counter -- second call: no upload, same handle; bumped counter: re-upload into the same handle
+    (new results); other pointers: another handle; the ninth set evicts the least recently used one."""
+    L = (8, 8, 8, 8)
+    qb = ctx_factory(L)
+    lat, g, (x, _) = make_inputs(L, 4)
+    links = [np.ascontiguousarray(g[k]) for k in range(4)]
+    s1, hit = qb.cachedStag(links, 1)
+    assert not hit
+    want, got = lat.vector(), lat.vector()
+    lat.D(g, want, x, 0.1)
+    s1.D(got, x, 0.1)
+    assert rel_l2(got, want) <= DSLASH_TOL
+    n0 = qb.launch_count()
+    s2, hit = qb.cachedStag(links, 1)
+    assert hit and s2.h == s1.h and qb.launch_count() == n0          # nothing ran: no re-layout kernel
+    for l in links:                                                   # the caller rewrites its links in place ...
+        l *= -1.0
+    s3, hit = qb.cachedStag(links, 1)
+    s3.D(got, x, 0.1)
+    assert hit and rel_l2(got, want) <= DSLASH_TOL                    # ... same counter: the stale copy is used (by contract)
+    s4, hit = qb.cachedStag(links, 2)                                 # ... bumped counter: uploaded again, same handle
+    assert not hit and s4.h == s1.h
+    lat.D(-g, want, x, 0.1)
+    s4.D(got, x, 0.1)
+    assert rel_l2(got, want) <= DSLASH_TOL
+    others = [[np.ascontiguousarray(g[k]) for k in range(4)] for _ in range(8)]
+    hs = [qb.cachedStag(o, 1)[0].h for o in others]
+    assert len(set(hs)) == 8 and s1.h not in hs
+    _, hit = qb.cachedStag(links, 2)                                  # evicted by the eight newer sets
+    assert not hit
+    _, hit = qb.cachedStag(others[-1], 1)
+    assert hit
