@@ -52,6 +52,10 @@ struct SweepArgs {
   double* partials;
   unsigned int* ticket;
   double* result;
+  // != nullptr: the whole launch is a no-op once *skip != 0 -- the CG's "done" scalar: the host runs a few
+  // iterations ahead of the device, and the sweeps it queued past convergence must cost nothing (all ranks hold the
+  // same value, so on a split lattice every rank skips the same launches)
+  const double* skip;
 };
 
 // Halo geometry of one split direction.
@@ -210,7 +214,7 @@ inline double2* hf(const Field& f, int parity) { return f.d + (size_t)parity * 3
 // r[p] = post*(a*r + b*bx + sgn*sum_k[U x(+h) - U^+ x(-h)]); dot != nullptr also returns
 // sum Re<bx, r_new> over ranks' local sites into *dot (device pointer, not yet all-reduced).
 int sweep(const Gauge& g, int parity, double2* r, const double2* x, const double2* bx, double a,
-          double b, double sgn, double post, double* dot_out);
+          double b, double sgn, double post, double* dot_out, const double* skip = nullptr);
 
 // ---- blas.cu ----------------------------------------------------------------
 // All vectors are half fields (3*Vh double2) unless n is given.

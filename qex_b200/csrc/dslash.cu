@@ -109,6 +109,7 @@ constexpr int SWEEP_MINB = 6;
 
 template <int NL, int RC, bool DOT>
 __global__ void __launch_bounds__(SWEEP_BLOCK, SWEEP_MINB) k_sweep(const SweepArgs A) {
+  if (A.skip != nullptr && *A.skip != 0.0) return;
   const int idx = blockIdx.x * SWEEP_BLOCK + threadIdx.x;
   double dot = 0.0;
   if (idx < A.Vh) {
@@ -179,6 +180,7 @@ struct ExtArgs {
   double* result;
   const double* interior;
   XRank* xr;
+  const double* skip;   // as SweepArgs::skip
 };
 
 // thread t of the boundary enumeration -> local coordinates of its site (parity A.parity)
@@ -209,6 +211,7 @@ __device__ __forceinline__ void region_site(const ExtArgs& A, int t, int (&x)[4]
 
 template <int NL, int RC, bool DOT>
 __global__ void __launch_bounds__(SWEEP_BLOCK) k_exterior(const ExtArgs A) {
+  if (A.skip != nullptr && *A.skip != 0.0) return;
   if (A.wait) {
     if ((int)threadIdx.x < 2 * A.ndir) {
       const ExtDir& D = A.d[threadIdx.x >> 1];
@@ -440,6 +443,7 @@ __device__ __forceinline__ void stencil_ghost(const MRArgs& F, const Site& s, in
 template <int NL, int RC, bool DOT>
 __global__ void __launch_bounds__(SWEEP_BLOCK, SWEEP_MINB) k_sweep_mr(const MRArgs F) {
   const SweepArgs& A = F.A;
+  if (A.skip != nullptr && *A.skip != 0.0) return;   // past convergence: no pack, no flags, no sum -- on every rank alike
   const int bid = blockIdx.x;
   const bool stamp = F.stamps != nullptr && threadIdx.x == 0;
   if (stamp) atomicMin(F.stamps + ST_START, globaltimer_ns());
@@ -592,10 +596,11 @@ static int fill_ext(const Gauge& g, int parity, double2* r, double scale, const 
 
 // NCCL path.  dot_out != nullptr: also completes Re<bx, r> (interior part already in *dot_interior).
 static int exterior(const Gauge& g, int parity, double2* r, double scale, const double2* bx,
-                    double* dot_out, const double* dot_interior) {
+                    double* dot_out, const double* dot_interior, const double* skip) {
   Context& c = ctx();
   ExtArgs E;
   const int end = fill_ext(g, parity, r, scale, bx, dot_out, dot_interior, E);
+  E.skip = skip;
   if (end == 0) return 0;
   const int grid = (end + SWEEP_BLOCK - 1) / SWEEP_BLOCK;
   QB_DISPATCH(g, dot_out != nullptr, k_exterior<NL, RC, DOT><<<grid, SWEEP_BLOCK, 0, c.stream>>>(E));
@@ -662,7 +667,7 @@ static int tile_order(int nl, int parity, const unsigned int** order, int* ntile
 }
 
 int sweep(const Gauge& g, int parity, double2* r, const double2* x, const double2* bx, double a,
-          double b, double sgn, double post, double* dot_out) {
+          double b, double sgn, double post, double* dot_out, const double* skip) {
   Context& c = ctx();
   if (!g.loaded) return fail("sweep: gauge not loaded");
   const bool multi = c.g.comm_mask != 0;
@@ -673,6 +678,7 @@ int sweep(const Gauge& g, int parity, double2* r, const double2* x, const double
   for (int i = 0; i < 4; i++) A.X[i] = c.g.X[i];
   A.Vh = c.g.Vh; A.parity = parity; A.comm_mask = c.g.comm_mask;
   A.partials = c.d_partials; A.ticket = c.d_ticket; A.result = dot_out;
+  A.skip = skip;
   const int grid = (c.g.Vh + SWEEP_BLOCK - 1) / SWEEP_BLOCK;
   const bool fused_dot = dot_out != nullptr;
 
@@ -735,7 +741,7 @@ int sweep(const Gauge& g, int parity, double2* r, const double2* x, const double
   QB_CUDA(cudaGetLastError());
   if (multi) {
     QB_CHECK(halo_wait());
-    QB_CHECK(exterior(g, parity, r, post * sgn, bx, dot_out, dot_interior));
+    QB_CHECK(exterior(g, parity, r, post * sgn, bx, dot_out, dot_interior, skip));
   }
   return 0;
 }

@@ -242,21 +242,25 @@ __global__ void __launch_bounds__(PB, QB_PIPE_MINB) k_staple_pipe(const StapleAr
   cp_wait0();
 }
 
-// QEXB200_STAPLE_PIPE=0 selects the register-gather kernel on a single rank as well (A/B runs).
+// QEXB200_STAPLE_PIPE=1 selects the shared-memory-staged kernel on a single rank (A/B runs; bit-identical results,
+// HISQ 16.0 -> 15.1 ms at 32^4).  OPT-IN: the refill of a ring slot right after its ld.shared is ordered by a latency
+// argument, not by a cp.async.wait; the register-gather kernel is the default until racecheck has run on it.
 static bool staple_pipe_enabled() {
   const char* e = getenv("QEXB200_STAPLE_PIPE");   // read per launch: the A/B test flips it inside one process
-  return !(e && e[0] == '0');
+  return e && e[0] == '1';
 }
 // Persistent grid = what is resident at once (the ring needs the full shared-memory carve-out to fit
 // QB_PIPE_MINB blocks per SM; a grid larger than one wave would serialise whole blocks).
 template <int NS, bool PROJ>
 static int launch_pipe_t(const StapleArgs& a, int ntiles, cudaStream_t st) {
-  static int resident = 0;
-  if (!resident) {
+  static int resident = 0, resident_dev = -1;   // function attributes are per device: redo them after init on another one
+  int dev = 0;
+  QB_CUDA(cudaGetDevice(&dev));
+  if (!resident || resident_dev != dev) {
     QB_CUDA(cudaFuncSetAttribute(k_staple_pipe<NS, PROJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, PIPE_SMEM));
     QB_CUDA(cudaFuncSetAttribute(k_staple_pipe<NS, PROJ>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    int dev = 0, sms = 0, occ = 0;
-    QB_CUDA(cudaGetDevice(&dev));
+    int sms = 0, occ = 0;
+    resident_dev = dev;
     QB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     QB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_staple_pipe<NS, PROJ>, PB, PIPE_SMEM));
     if (occ < 1) return fail("k_staple_pipe does not fit on an SM");

@@ -160,9 +160,11 @@ int cg_free() {
 }
 
 // A = stagD2xx (stagD.nim:433-469): t[q] = (2D) x ; out[p] = 4 m2 x - (2D) t ; optional <x, out>
-static int apply_xx(const Gauge& g, int parity, double2* out, const double2* x, double m2, double* dot) {
-  QB_CHECK(sweep(g, 1 - parity, w_t, x, nullptr, 0.0, 0.0, 1.0, 1.0, nullptr));
-  QB_CHECK(sweep(g, parity, out, w_t, x, 0.0, 4.0 * m2, -1.0, 1.0, dot));
+// skip: device scalar that turns both sweeps into no-ops when non-zero (the CG's done flag, see SweepArgs::skip)
+static int apply_xx(const Gauge& g, int parity, double2* out, const double2* x, double m2, double* dot,
+                    const double* skip = nullptr) {
+  QB_CHECK(sweep(g, 1 - parity, w_t, x, nullptr, 0.0, 0.0, 1.0, 1.0, nullptr, skip));
+  QB_CHECK(sweep(g, parity, out, w_t, x, 0.0, 4.0 * m2, -1.0, 1.0, dot, skip));
   return 0;
 }
 
@@ -229,7 +231,7 @@ int cg_xx(const Gauge& g, int parity, double2* x, const double2* b, double m2, d
   while (!done && launched < maxits - itn0) {
     k_cg_p<<<grid, CB, 0, c.stream>>>(w_p, w_r, S, n);
     count_launch();
-    QB_CHECK(apply_xx(g, parity, w_Ap, w_p, m2, S + S_PAP));
+    QB_CHECK(apply_xx(g, parity, w_Ap, w_p, m2, S + S_PAP, S + S_DONE));
     QB_CHECK(allreduce_scalars(S + S_PAP, 1));
     if (c.g.nranks > 1 && !c.p2p) {
       // NCCL path: the sum over ranks sits between the update and the loop control
@@ -432,7 +434,7 @@ int cgm_xx(const Gauge& g, int parity, double2* const* xs, const double2* b, dou
   int launched = 0;
   bool done = h_status[0].done != 0;
   while (!done && launched < maxits) {
-    QB_CHECK(apply_xx(g, parity, w_Ap, p0, m2, S + S_PAP));
+    QB_CHECK(apply_xx(g, parity, w_Ap, p0, m2, S + S_PAP, S + S_DONE));
     QB_CHECK(allreduce_scalars(S + S_PAP, 1));
     k_cgm_xr<<<grid, CB, 0, c.stream>>>(xs[0], w_r, p0, w_Ap, S, n, c.d_partials, c.d_ticket, xrank(), d_status, d_cgm);
     launched++;

@@ -203,7 +203,7 @@ def test_hyp_smear_parity_and_solve(ctx_factory, L, inner):
 
 @pytest.mark.parametrize("L,grid", [((8, 8, 8, 8), "6"), ((4, 6, 8, 10), "2"), ((16, 16, 16, 16), None)])
 def test_staged_staple_kernel_is_bit_identical(ctx_factory, monkeypatch, L, grid):
-    """The shared-memory-staged staple kernel (k_staple_pipe, the single-rank default) does the arithmetic of the
+    """The shared-memory-staged staple kernel (k_staple_pipe, opt-in with QEXB200_STAPLE_PIPE=1) does the arithmetic of the
     register-gather kernel in the same order: HISQ and nHYP links must agree bit for bit, also when a block
     walks many tiles (QEXB200_PIPE_GRID) and when the last tile is ragged."""
     qb = ctx_factory(L)
