@@ -28,7 +28,7 @@ def build(force=False, verbose=False):
     if not force and not stale():
         return LIB
     objs = []
-    flags = [f for f in FLAGS if not f.startswith("--use_fast_math")]
+    flags = [f for f in FLAGS if not f.startswith("--use_fast_math")] + os.environ.get("QEXB200_EXTRA_FLAGS", "").split()
     procs = []
     os.makedirs(os.path.join(HERE, "build"), exist_ok=True)
     for src in sources():

@@ -707,7 +707,7 @@ int sweep(const Gauge& g, int parity, double2* r, const double2* x, const double
     F.stamps = c.d_stamps ? c.d_stamps + (size_t)ST_N * (c.halo_seq % STAMP_RING) : nullptr;
     const int total = F.npack + F.ntiles;
     if ((size_t)total > c.npart) return fail("sweep: %d blocks exceed the %zu reduction slots", total, c.npart);
-    // residency 6 blocks/SM measured best for every variant (tools/tune_fused.py: 5, 4, 3 are 1-20 % slower)
+    // residency 6 blocks/SM measured best for every variant in round 1 (5, 4, 3 were 1-20 % slower)
     QB_DISPATCH(g, fused_dot, k_sweep_mr<NL, RC, DOT><<<total, SWEEP_BLOCK, 0, c.stream>>>(F));
     count_launch();
     QB_CUDA(cudaGetLastError());

@@ -1,4 +1,5 @@
-"""Launch-shape sweep of the parity-sweep kernel on one GPU (QEXB200_SWEEP_TUNE variants in csrc/dslash.cu)."""
+"""Launch-shape sweep of the parity-sweep kernel on one GPU (QEXB200_SWEEP_TUNE variants in csrc/dslash.cu).
+The variants are compiled only with -DQEXB200_TUNE: build with `QEXB200_EXTRA_FLAGS=-DQEXB200_TUNE python -m qex_b200.build --force`."""
 import os
 import sys
 
