@@ -468,7 +468,7 @@ def run_ours(args):
             }
             # ---- cold e2e (first variant only): what a caller without a cached handle pays, like qudaSolveXX
             # (qudaWrapperImpl.nim:198-261): create + upload + re-layout of the links, then the host-buffer solve
-            if vi == 0 and not args.no_cold and not big:
+            if vi == 0 and not args.no_cold and not big and world == 1:
                 host_links = [np.zeros((nsites, 3, 3, 2)) for _ in range(nlinks)]
                 s.download(host_links)
                 barrier()
