@@ -603,7 +603,7 @@ def test_gauge_handle_cache_of_the_glue(orc, ctx_factory):
     L = (8, 8, 8, 8)
     qb = ctx_factory(L)
     lat, g, (x, _) = make_inputs(L, 4)
-    links = [np.ascontiguousarray(g[k]) for k in range(4)]
+    links = [g[k].copy() for k in range(4)]
     s1, hit = qb.cachedStag(links, 1)
     assert not hit
     want, got = lat.vector(), lat.vector()
@@ -623,7 +623,7 @@ def test_gauge_handle_cache_of_the_glue(orc, ctx_factory):
     lat.D(-g, want, x, 0.1)
     s4.D(got, x, 0.1)
     assert rel_l2(got, want) <= DSLASH_TOL
-    others = [[np.ascontiguousarray(g[k]) for k in range(4)] for _ in range(8)]
+    others = [[g[k].copy() for k in range(4)] for _ in range(8)]
     hs = [qb.cachedStag(o, 1)[0].h for o in others]
     assert len(set(hs)) == 8 and s1.h not in hs
     _, hit = qb.cachedStag(links, 2)                                  # evicted by the eight newer sets
