@@ -7,7 +7,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <nccl.h>
-#include "linkops.cuh"
+#include "sweep_site.cuh"   // Links, SweepArgs, the per-site functions (includes linkops.cuh)
 #include <cstdint>
 #include <cstdio>
 #include <string>
@@ -23,39 +23,6 @@ struct Geom {
   int V, Vh;
   int comm_mask; // bit mu set: direction mu is split over ranks
   int nranks, rank;
-};
-
-// A link set as the kernels see it.  Every link class j (0: one-hop, 1: three-hop) is held with
-// all 18 reals; a class whose links are s * SU(3) with one |s| for the whole field (naive links
-// with staggered phases, Naik links) can ALSO be held as 12 reals: rows 0 and 1, the third row is
-// rebuilt in registers as (sigma/|s|) conj(row0 x row1).  sigma = sign of det, one bit per link:
-// sgn[par][idx] bit (2 mu + j) for U_{mu,j}(s), bit 8 + (2 mu + j) for U_{mu,j}(s - h_j mu).
-struct Links {
-  const double2* u;          // [nlinks][2][9][Vh]
-  const double2* u12[2];     // per class: [4 mu][2][6][Vh] (12-real) / [4 mu][2][7][Vh] (14-real) or nullptr
-  const unsigned short* sgn; // [2][Vh]
-  double inv[2];             // 1/|s| per class
-};
-
-// Arguments of one parity sweep (kernel parameter block, passed by value).
-struct SweepArgs {
-  Links L;            // link set
-  const double2* x;   // input half field (parity 1-p): x[c*Vh + idx]
-  double2* r;         // output half field (parity p)
-  const double2* bx;  // half field (parity p) scaled by b, may alias r's parity of the source
-  double a, b, sgn, post;   // r = post*(a*r + b*bx + sgn*sum)
-  int X[4];
-  int Vh;
-  int parity;         // output parity p
-  int comm_mask;
-  // reduction epilogue (DOT): sum over sites of Re<bx, r_new>
-  double* partials;
-  unsigned int* ticket;
-  double* result;
-  // != nullptr: the whole launch is a no-op once *skip != 0 -- the CG's "done" scalar: the host runs a few
-  // iterations ahead of the device, and the sweeps it queued past convergence must cost nothing (all ranks hold the
-  // same value, so on a split lattice every rank skips the same launches)
-  const double* skip;
 };
 
 // Halo geometry of one split direction.

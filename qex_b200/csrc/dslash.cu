@@ -16,7 +16,6 @@
 
 namespace qb {
 
-constexpr int SWEEP_BLOCK = 128;
 
 // Expands LAUNCH once with the compile-time constants NL (link classes), RC (bit j: class j is
 // read as 12 reals, bit 2+j: as 14 reals) and DOT that match the link set and the request.
@@ -37,70 +36,6 @@ constexpr int SWEEP_BLOCK = 128;
       default: return fail("sweep: no kernel for this link set");                          \
     }                                                                                      \
   } while (0)
-
-// r = post*(a*r + b*bx + sgn*acc) for one site; returns Re<bx, r_new> when DOT
-template <bool DOT>
-__device__ __forceinline__ double site_epilogue(const SweepArgs& A, int idx, const double2 (&acc)[3]) {
-  const int Vh = A.Vh;
-  double dot = 0.0;
-#pragma unroll
-  for (int c = 0; c < 3; c++) {
-    double2 o = {A.sgn * acc[c].x, A.sgn * acc[c].y};
-    double2 bxv = {0, 0};
-    if (A.b != 0.0 || DOT) bxv = A.bx[(size_t)c * Vh + idx];
-    if (A.b != 0.0) { o.x = fma(A.b, bxv.x, o.x); o.y = fma(A.b, bxv.y, o.y); }
-    if (A.a != 0.0) {
-      const double2 ro = A.r[(size_t)c * Vh + idx];
-      o.x = fma(A.a, ro.x, o.x); o.y = fma(A.a, ro.y, o.y);
-    }
-    o.x *= A.post; o.y *= A.post;
-    A.r[(size_t)c * Vh + idx] = o;
-    if (DOT) dot += bxv.x * o.x + bxv.y * o.y;
-  }
-  return dot;
-}
-
-// sum_k [U_k(s) x(s+h_k) - U_k(s-h_k)^+ x(s-h_k)] over the hops that stay on this rank
-template <int NL, int RC>
-__device__ __forceinline__ void stencil_local(const SweepArgs& A, const Site& s, int idx, double2 (&acc)[3]) {
-  const int Vh = A.Vh, p = A.parity, q = 1 - A.parity;
-  const unsigned int sg = (RC & 3) ? A.L.sgn[(size_t)p * Vh + idx] : 0u;
-#pragma unroll
-  for (int mu = 0; mu < 4; mu++) {
-    const int st = stride_of(mu, A.X);
-    const int Xm = A.X[mu];
-    const bool split = (A.comm_mask >> mu) & 1;
-#pragma unroll
-    for (int j = 0; j < NL; j++) {
-      const int h = (j == 0) ? 1 : 3;
-      {  // forward hop: U_k(s) x(s + h mu)
-        int y = s.x[mu] + h;
-        int ln = s.lex + h * st;
-        bool off = y >= Xm;
-        if (off) ln -= Xm * st;
-        if (!(off && split)) {
-          double2 U[9], v[3];
-          load_link_k<NL, RC>(U, A.L, mu, j, p, idx, Vh, (sg >> (2 * mu + j)) & 1u);
-          load_vec(v, A.x + (ln >> 1), Vh);
-          mv_add(acc, U, v);
-        }
-      }
-      {  // backward hop: U_k(s - h mu)^+ x(s - h mu)
-        int y = s.x[mu] - h;
-        int ln = s.lex - h * st;
-        bool off = y < 0;
-        if (off) ln += Xm * st;
-        if (!(off && split)) {
-          double2 U[9], v[3];
-          const int ib = ln >> 1;
-          load_link_k<NL, RC>(U, A.L, mu, j, q, ib, Vh, (sg >> (8 + 2 * mu + j)) & 1u);
-          load_vec(v, A.x + ib, Vh);
-          mv_adj_sub(acc, U, v);
-        }
-      }
-    }
-  }
-}
 
 // Residency: 6 blocks of 128 threads per SM (<= 85 registers) measured fastest on B200 -- the
 // compiler keeps more 16-byte loads in flight per thread than at the default 9 blocks/SM
@@ -270,58 +205,6 @@ __global__ void __launch_bounds__(SWEEP_BLOCK) k_exterior(const ExtArgs A) {
 // my last h_j layers for the + neighbour.  On the peer-memory path the destinations are the
 // neighbours' receive buffers (NVLink stores) and the last block to finish raises the
 // neighbours' flags; on the NCCL path they are the local send buffer.
-struct PackDir {
-  int mu, depth, faceh, end;
-  double2 *out_f, *out_b0, *out_b1;
-  unsigned int *flag_f, *flag_b;   // flag at the - neighbour (its side 0) / + neighbour (its side 1)
-};
-struct PackArgs {
-  Links L;
-  const double2* x;   // half field of parity q (the sweep's input parity)
-  int X[4];
-  int Vh, q, ndir;
-  PackDir d[4];
-  unsigned int seq;
-  unsigned int* ticket;   // nullptr: no signalling
-};
-
-// one work item of the packing (t < A.d[ndir-1].end)
-template <int NL, int RC>
-__device__ __forceinline__ void pack_item(const PackArgs& A, int t) {
-  int di = 0, base = 0;
-#pragma unroll
-  for (int i = 0; i < 3; i++)
-    if (i + 1 < A.ndir && t >= A.d[i].end) { di = i + 1; base = A.d[i].end; }
-  const PackDir& P = A.d[di];
-  const int tt = t - base;
-  const int nf = P.depth * P.faceh;        // forward-psi items
-  const int mu = P.mu, Xm = A.X[mu], Vh = A.Vh;
-  if (tt < nf) {
-    const int l = tt / P.faceh, fidx = tt - l * P.faceh;
-    const Site s = site_from_face(fidx, mu, l, A.q, A.X);
-    const int idx = s.lex >> 1;
-#pragma unroll
-    for (int c = 0; c < 3; c++) P.out_f[(size_t)c * nf + tt] = A.x[(size_t)c * Vh + idx];
-  } else {
-    int tb = tt - nf;
-    int j = 0, h = 1;
-    if (NL == 2 && tb >= P.faceh) { j = 1; h = 3; tb -= P.faceh; }
-    const int jl = tb / P.faceh, fidx = tb - jl * P.faceh;
-    const Site s = site_from_face(fidx, mu, Xm - h + jl, A.q, A.X);
-    const int idx = s.lex >> 1;
-    double2 U[9], v[3], acc[3] = {{0, 0}, {0, 0}, {0, 0}};
-    const unsigned int sg = (RC & 3) ? A.L.sgn[(size_t)A.q * Vh + idx] : 0u;
-    if (NL == 2 && j == 1) load_link_k<NL, RC>(U, A.L, mu, 1, A.q, idx, Vh, (sg >> (2 * mu + 1)) & 1u);
-    else load_link_k<NL, RC>(U, A.L, mu, 0, A.q, idx, Vh, (sg >> (2 * mu)) & 1u);
-    load_vec(v, A.x + idx, Vh);
-    mv_adj_sub(acc, U, v);
-    double2* ob = (j == 0) ? P.out_b0 : P.out_b1;
-#pragma unroll
-    for (int c = 0; c < 3; c++)
-      ob[(size_t)c * h * P.faceh + tb] = make_double2(-acc[c].x, -acc[c].y);
-  }
-}
-
 // Called by every thread of every packing block after its stores: the last block to arrive
 // raises the neighbours' flags (release at system scope, after the data of all blocks).
 __device__ __forceinline__ void pack_signal(const PackArgs& A, unsigned int nblocks) {
@@ -362,84 +245,6 @@ __global__ void __launch_bounds__(SWEEP_BLOCK) k_pack(const PackArgs A) {
 // Pack blocks never wait, face tiles wait only on REMOTE pack blocks: no cycle.  The Re<bx, r>
 // reduction (and its sum over ranks) closes the same kernel, so a CG iteration on N GPUs launches
 // exactly the kernels it launches on one.
-struct GhostDir {                        // indexed by mu; entries of unsplit directions stay null
-  const double2 *gf, *gb0, *gb1;         // + neighbour's first layers of x ; - neighbour's U_k^+ x per link class
-  const unsigned int *flag_f, *flag_b;   // raised by the + / - neighbour's pack blocks
-  int faceh;
-};
-struct MRArgs {
-  SweepArgs A;
-  PackArgs P;
-  GhostDir gd[4];
-  const unsigned int* order;   // block -> tile (low 24 bits) | flags it waits for (bit 24 + 2 mu + side)
-  int npack, ntiles;
-  unsigned int seq;
-  int* err;
-  unsigned long long timeout_ns;
-  XRank* xr;
-  unsigned long long* stamps;  // role timestamps of this launch (qexb200_debug_role_times) or nullptr
-};
-// stamps[0] first block start, [1] last pack block end, [2] last interior tile end, [3] first face tile past its
-// wait, [4] last face tile end, [5] longest flag wait, [6] sum of flag waits, [7] face tiles that had to wait
-enum { ST_START = 0, ST_PACK_END, ST_INT_END, ST_FACE_START, ST_FACE_END, ST_WAIT_MAX, ST_WAIT_SUM, ST_WAIT_N, ST_N };
-
-template <int NL, int RC>
-__device__ __forceinline__ void stencil_ghost(const MRArgs& F, const Site& s, int idx, double2 (&acc)[3]) {
-  const SweepArgs& A = F.A;
-  const int Vh = A.Vh, p = A.parity, q = 1 - A.parity;
-  constexpr int dep = (NL == 2) ? 3 : 1;
-  const unsigned int sg = (RC & 3) ? A.L.sgn[(size_t)p * Vh + idx] : 0u;
-#pragma unroll
-  for (int mu = 0; mu < 4; mu++) {
-    const int st = stride_of(mu, A.X);
-    const int Xm = A.X[mu], xm = s.x[mu];
-    const bool split = (A.comm_mask >> mu) & 1;
-    const GhostDir& D = F.gd[mu];
-    int fidx = 0;
-    if (split && (xm < dep || xm >= Xm - dep)) fidx = face_lex(s.x, mu, A.X) >> 1;
-#pragma unroll
-    for (int j = 0; j < NL; j++) {
-      const int h = (j == 0) ? 1 : 3;
-      {  // forward hop: U_k(s) x(s + h mu), x from the + neighbour's first layers when s + h mu left the rank
-        const int y = xm + h;
-        int ln = s.lex + h * st;
-        const bool off = y >= Xm;
-        if (off) ln -= Xm * st;
-        double2 U[9], v[3];
-        load_link_k<NL, RC>(U, A.L, mu, j, p, idx, Vh, (sg >> (2 * mu + j)) & 1u);
-        if (off && split) {
-#pragma unroll
-          for (int c = 0; c < 3; c++)
-            v[c] = __ldcg(D.gf + (size_t)c * dep * D.faceh + (size_t)(y - Xm) * D.faceh + fidx);
-        } else {
-          load_vec(v, A.x + (ln >> 1), Vh);
-        }
-        mv_add(acc, U, v);
-      }
-      {  // backward hop: the product U_k^+ x was formed at the source when s - h mu left the rank
-        const int y = xm - h;
-        int ln = s.lex - h * st;
-        const bool off = y < 0;
-        if (off) ln += Xm * st;
-        if (off && split) {
-          const double2* gb = (j == 0) ? D.gb0 : D.gb1;
-#pragma unroll
-          for (int c = 0; c < 3; c++) {
-            const double2 w = __ldcg(gb + (size_t)c * h * D.faceh + (size_t)xm * D.faceh + fidx);
-            acc[c].x -= w.x; acc[c].y -= w.y;
-          }
-        } else {
-          double2 U[9], v[3];
-          const int ib = ln >> 1;
-          load_link_k<NL, RC>(U, A.L, mu, j, q, ib, Vh, (sg >> (8 + 2 * mu + j)) & 1u);
-          load_vec(v, A.x + ib, Vh);
-          mv_adj_sub(acc, U, v);
-        }
-      }
-    }
-  }
-}
-
 template <int NL, int RC, bool DOT>
 __global__ void __launch_bounds__(SWEEP_BLOCK, SWEEP_MINB) k_sweep_mr(const MRArgs F) {
   const SweepArgs& A = F.A;

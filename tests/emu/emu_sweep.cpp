@@ -1,0 +1,98 @@
+// TEST HARNESS ONLY: one parity sweep of the staggered Dslash on a lattice split over several ranks, with every rank
+// emulated in this process and the per-site functions of qex_b200/csrc/sweep_site.cuh -- the very code the kernels
+// k_pack / k_sweep_mr of dslash.cu wrap -- executed on the host: pack_item writes the psi layers and the U^+ psi
+// products into the neighbours' receive buffers, then every tile of the block -> tile table runs stencil_local or
+// stencil_ghost and the epilogue.  What the GPU adds on top (flags, fences, the grid) is ordering only.  Compiled by
+// tests/test_sweep_emu.py with g++; never part of libqex_b200.so.
+#include "../../qex_b200/csrc/sweep_site.cuh"
+
+using namespace qb;
+
+struct EmuHalo {   // one split direction of one rank: the fields of qexb200_halo_dir the sweep uses
+  int mu, depth, faceh, rank_plus, rank_minus;
+  long long off_f, off_b;
+};
+
+template <int NL>
+static void sweep_all(int nranks, const int* X, int comm_mask, int parity, const double* const* links,
+                      const double* const* x, double* const* r, double a, double b, double sgn, double post,
+                      const EmuHalo* halo, int ndir, double* const* recv, const unsigned int* const* tiles, int ntiles) {
+  const int Vh = X[0] * X[1] * X[2] * X[3] / 2;
+  const int q = 1 - parity;
+  // phase 1 -- what the pack blocks do (fill_pack of dslash.cu, peer-memory destinations)
+  for (int me = 0; me < nranks; me++) {
+    PackArgs P;
+    P.L.u = (const double2*)links[me]; P.L.u12[0] = P.L.u12[1] = nullptr; P.L.sgn = nullptr; P.L.inv[0] = P.L.inv[1] = 1.0;
+    P.x = (const double2*)x[me] + (size_t)q * 3 * Vh;
+    for (int d = 0; d < 4; d++) P.X[d] = X[d];
+    P.Vh = Vh; P.q = q; P.ndir = ndir; P.seq = 1; P.ticket = nullptr;
+    int end = 0;
+    for (int i = 0; i < ndir; i++) {
+      const EmuHalo& h = halo[me * 4 + i];
+      PackDir& D = P.d[i];
+      D.mu = h.mu; D.depth = h.depth; D.faceh = h.faceh;
+      end += (h.depth + (NL == 2 ? 4 : 1)) * h.faceh;
+      D.end = end;
+      D.out_f = (double2*)recv[h.rank_minus] + h.off_f;
+      D.out_b0 = (double2*)recv[h.rank_plus] + h.off_b;
+      D.out_b1 = D.out_b0 + (size_t)3 * h.faceh;
+      D.flag_f = D.flag_b = nullptr;
+    }
+    for (int t = 0; t < end; t++) pack_item<NL, 0>(P, t);
+  }
+  // phase 2 -- what the tile blocks do, in table order (interior tiles first, face tiles last)
+  for (int me = 0; me < nranks; me++) {
+    MRArgs F;
+    SweepArgs& A = F.A;
+    A.L.u = (const double2*)links[me]; A.L.u12[0] = A.L.u12[1] = nullptr; A.L.sgn = nullptr; A.L.inv[0] = A.L.inv[1] = 1.0;
+    A.x = (const double2*)x[me] + (size_t)q * 3 * Vh;
+    A.r = (double2*)r[me] + (size_t)parity * 3 * Vh;
+    A.bx = (const double2*)x[me] + (size_t)parity * 3 * Vh;
+    A.a = a; A.b = b; A.sgn = sgn; A.post = post;
+    for (int d = 0; d < 4; d++) A.X[d] = X[d];
+    A.Vh = Vh; A.parity = parity; A.comm_mask = comm_mask;
+    A.partials = nullptr; A.ticket = nullptr; A.result = nullptr; A.skip = nullptr;
+    for (int mu = 0; mu < 4; mu++) F.gd[mu] = GhostDir{nullptr, nullptr, nullptr, nullptr, nullptr, 0};
+    for (int i = 0; i < ndir; i++) {
+      const EmuHalo& h = halo[me * 4 + i];
+      GhostDir& D = F.gd[h.mu];
+      D.gf = (const double2*)recv[me] + h.off_f;
+      D.gb0 = (const double2*)recv[me] + h.off_b;
+      D.gb1 = D.gb0 + (size_t)3 * h.faceh;
+      D.faceh = h.faceh;
+    }
+    for (int bi = 0; bi < ntiles; bi++) {
+      const unsigned int e = tiles[me][bi];
+      const int tile = (int)(e & 0xffffffu);
+      const unsigned int need = e >> 24;
+      for (int tid = 0; tid < SWEEP_BLOCK; tid++) {
+        const int idx = tile * SWEEP_BLOCK + tid;
+        if (idx >= Vh) continue;
+        const Site s = site_from_idx(idx, parity, A.X);
+        double2 acc[3] = {{0, 0}, {0, 0}, {0, 0}};
+        if (need) stencil_ghost<NL, 0>(F, s, idx, acc);
+        else stencil_local<NL, 0>(A, s, idx, acc);
+        site_epilogue<false>(A, idx, acc);
+      }
+    }
+  }
+}
+
+extern "C" {
+// fields in the DEVICE layout: links[r] = double2[nlinks][2][9][Vh], x[r] / r[r] = double2[2][3][Vh];
+// recv[r] = the receive buffer of rank r; halo[r * 4 + i], i < ndir; tiles[r] = qexb200_plan_tiles of rank r
+int emu_sweep_mr(int nranks, int nl, const int* X, int comm_mask, int parity, const double* const* links,
+                 const double* const* x, double* const* r, double a, double b, double sgn, double post,
+                 const EmuHalo* halo, int ndir, double* const* recv, const unsigned int* const* tiles, int ntiles) {
+  if (nl == 1) sweep_all<1>(nranks, X, comm_mask, parity, links, x, r, a, b, sgn, post, halo, ndir, recv, tiles, ntiles);
+  else if (nl == 2) sweep_all<2>(nranks, X, comm_mask, parity, links, x, r, a, b, sgn, post, halo, ndir, recv, tiles, ntiles);
+  else return 1;
+  return 0;
+}
+// idx of parity par -> local coordinates (site_from_idx): the map the tests check against the oracle's site order
+void emu_site(int idx, int par, const int* X, int* out5) {
+  const Site s = site_from_idx(idx, par, X);
+  for (int d = 0; d < 4; d++) out5[d] = s.x[d];
+  out5[4] = s.lex;
+}
+}

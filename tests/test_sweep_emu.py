@@ -1,0 +1,161 @@
+"""The multi-rank Dslash sweep on the CPU: the per-site functions of qex_b200/csrc/sweep_site.cuh -- the code the CUDA
+kernels k_pack / k_sweep_mr wrap (pack_item, stencil_local, stencil_ghost, site_epilogue) -- compiled with g++ and run
+over a lattice split into 2, 4 or 8 emulated ranks, with the library's own halo plan (qexb200_plan_halo) and block ->
+tile table (qexb200_plan_tiles), against the oracle's global stagD2.  No GPU: this is the N > 1 path's index
+arithmetic, buffer layout and ghost substitution under the driver's CPU suite (the multi-GPU pytest cases need 2-8
+GPUs and are skipped on a 1-GPU box)."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import oracle
+from util import make_inputs, rel_l2
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+SO = os.path.join(HERE, "emu", "_emu_sweep.so")
+
+
+class EmuHalo(C.Structure):
+    _fields_ = [("mu", C.c_int), ("depth", C.c_int), ("faceh", C.c_int), ("rank_plus", C.c_int), ("rank_minus", C.c_int),
+                ("off_f", C.c_longlong), ("off_b", C.c_longlong)]
+
+
+@pytest.fixture(scope="module")
+def emu():
+    src = os.path.join(HERE, "emu", "emu_sweep.cpp")
+    hdrs = [os.path.join(HERE, "..", "qex_b200", "csrc", h) for h in ("sweep_site.cuh", "linkops.cuh")]
+    if not os.path.exists(SO) or os.path.getmtime(SO) < max(os.path.getmtime(p) for p in [src] + hdrs):
+        subprocess.check_call(["/usr/bin/g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-x", "c++", "-w",
+                               "-I/usr/local/cuda/include", src, "-o", SO])
+    lib = C.CDLL(SO)
+    dpp, ip = C.POINTER(C.POINTER(C.c_double)), C.POINTER(C.c_int)
+    lib.emu_sweep_mr.argtypes = [C.c_int, C.c_int, ip, C.c_int, C.c_int, dpp, dpp, dpp, C.c_double, C.c_double, C.c_double,
+                                 C.c_double, C.POINTER(EmuHalo), C.c_int, dpp, C.POINTER(C.POINTER(C.c_uint)), C.c_int]
+    lib.emu_site.argtypes = [C.c_int, C.c_int, ip, ip]
+    return lib
+
+
+def rank_coords(rank, G):
+    rc = [0] * 4
+    for d in (3, 2, 1, 0):          # dimension 0 slowest (qlayout.nim:94-113)
+        rc[d] = rank % G[d]
+        rank //= G[d]
+    return rc
+
+
+def block_index(L, G, rank):
+    """Global oracle index of every local site of `rank`, in the device order (parity, idx)."""
+    X = [L[d] // G[d] for d in range(4)]
+    rc = rank_coords(rank, G)
+    Vh = int(np.prod(X)) // 2
+    idx = np.arange(Vh)
+    xh = X[0] // 2
+    out = []
+    for par in (0, 1):
+        x1 = (idx // xh) % X[1]; x2 = (idx // (xh * X[1])) % X[2]; x3 = idx // (xh * X[1] * X[2])
+        x0 = 2 * (idx % xh) + ((par + x1 + x2 + x3) & 1)
+        g = [x0 + rc[0] * X[0], x1 + rc[1] * X[1], x2 + rc[2] * X[2], x3 + rc[3] * X[3]]
+        lex = ((g[3] * L[2] + g[2]) * L[1] + g[1]) * L[0] + g[0]
+        out.append(((g[0] + g[1] + g[2] + g[3]) & 1) * (int(np.prod(L)) // 2) + lex // 2)
+    return np.concatenate(out)
+
+
+def vec_to_dev(v):      # [2 Vh, 3, 2] in (parity, idx) order -> double2[2][3][Vh]
+    n = v.shape[0] // 2
+    return np.ascontiguousarray(v.reshape(2, n, 3, 2).transpose(0, 2, 1, 3))
+
+
+def vec_from_dev(d):
+    n = d.shape[2]
+    return np.ascontiguousarray(d.transpose(0, 2, 1, 3)).reshape(2 * n, 3, 2)
+
+
+def links_to_dev(g):    # [nlinks, 2 Vh, 3, 3, 2] -> double2[nlinks][2][9][Vh]
+    nl, n = g.shape[0], g.shape[1] // 2
+    return np.ascontiguousarray(g.reshape(nl, 2, n, 9, 2).transpose(0, 1, 3, 2, 4))
+
+
+def test_device_site_order_is_the_oracles(emu):
+    """idx -> coordinates of the kernels (site_from_idx) = the oracle's site order, on a ragged lattice."""
+    L = (4, 6, 8, 10)
+    lat = oracle.Lattice(L)
+    co = lat.coords
+    X = (C.c_int * 4)(*L)
+    out = (C.c_int * 5)()
+    for i in np.random.default_rng(0).integers(0, lat.vol, 400):
+        par, idx = divmod(int(i), lat.half)
+        emu.emu_site(idx, par, X, out)
+        assert tuple(out[:4]) == tuple(int(co[k][i]) for k in range(4))
+    assert np.array_equal(block_index(L, (1, 1, 1, 1), 0), np.arange(lat.vol))
+
+
+CASES = [
+    ((8, 8, 8, 16), (1, 1, 1, 2), 4),
+    ((8, 8, 8, 16), (1, 1, 1, 2), 8),
+    ((8, 8, 12, 8), (1, 1, 2, 1), 8),       # local extent 6 in the split direction: three-hop both ways
+    ((8, 8, 8, 8), (1, 1, 1, 2), 8),        # local extent 4 < 2 * depth: a site hops off-rank both ways
+    ((8, 8, 16, 16), (1, 1, 2, 2), 8),      # corners
+    ((16, 8, 8, 8), (4, 1, 1, 1), 4),       # x0 split (the checkerboarded direction); neighbours are distinct ranks
+    ((16, 8, 8, 8), (2, 1, 1, 1), 8),
+    ((8, 16, 16, 8), (1, 2, 2, 1), 4),      # x1 split: every fourth tile touches a face
+    ((8, 8, 16, 32), (1, 1, 2, 4), 8),      # the 8-GPU rank grid of SURVEY 8e
+    ((8, 16, 16, 16), (1, 2, 2, 2), 4),     # the other 8-GPU rank grid
+    ((4, 6, 8, 20), (1, 1, 1, 2), 4),       # ragged local lattice 4.6.8.10: partial last tile
+]
+
+
+@pytest.mark.parametrize("L,G,nlinks", CASES)
+def test_multi_rank_sweep_on_the_host_matches_the_oracle(emu, L, G, nlinks):
+    import qex_b200 as qb
+    world = int(np.prod(G))
+    lat, g, (x, r0) = make_inputs(L, nlinks)
+    X = [L[d] // G[d] for d in range(4)]
+    Vh = int(np.prod(X)) // 2
+    blocks = [block_index(L, G, r) for r in range(world)]
+    plans = [qb.plan_halo(L, G, r, nlinks) for r in range(world)]
+    ndir = len(plans[0][0])
+    cap = max(p[1] for p in plans)
+    halo = (EmuHalo * (4 * world))()
+    for r, (plan, _) in enumerate(plans):
+        assert len(plan) == ndir
+        for i, h in enumerate(plan):
+            halo[4 * r + i] = EmuHalo(h["mu"], h["depth"], h["faceh"], h["rank_plus"], h["rank_minus"], h["off_f"], h["off_b"])
+    comm_mask = sum(1 << d for d in range(4) if G[d] > 1)
+    dl = [links_to_dev(g[:, b]) for b in blocks]
+    dx = [vec_to_dev(x[b]) for b in blocks]
+    dp = lambda a: a.ctypes.data_as(C.POINTER(C.c_double))
+    arr = lambda xs: (C.POINTER(C.c_double) * world)(*[dp(a) for a in xs])
+    Xc = (C.c_int * 4)(*X)
+    ntiles = (Vh + 127) // 128
+    for parity in (0, 1):
+        tiles = []
+        for r in range(world):
+            t = qb.plan_tiles(L, G, r, nlinks, parity)
+            tiles.append(np.array([ti | (need << 24) for ti, need in t], dtype=np.uint32))
+            assert len(t) == ntiles
+        tarr = (C.POINTER(C.c_uint) * world)(*[t.ctypes.data_as(C.POINTER(C.c_uint)) for t in tiles])
+        for a, b, sgn, post in ((0.0, 0.0, 1.0, 1.0), (0.7, -0.3, 1.0, 1.0), (0.0, 0.04, -1.0, 1.0)):
+            dr = [vec_to_dev(r0[bk]) for bk in blocks]
+            recv = [np.full(2 * cap, np.nan) for _ in range(world)]      # anything read but never packed shows as NaN
+            rc = emu.emu_sweep_mr(world, nlinks // 4, Xc, comm_mask, parity, arr(dl), arr(dx), arr(dr), a, b, sgn, post,
+                                  halo, ndir, arr(recv), tarr, ntiles)
+            assert rc == 0
+            want = r0.copy()
+            if sgn > 0:
+                lat.stagD2(g, want, x, a, b, parity)
+            else:       # the second sweep of stagD2ee: r = b x - hops(x) (stagD.nim:433-469 with 4 m^2 -> b)
+                hop = np.zeros_like(r0)
+                lat.stagD2(g, hop, x, 0.0, 0.0, parity)
+                sl = slice(0, lat.half) if parity == 0 else slice(lat.half, lat.vol)
+                want[sl] = b * x[sl] - hop[sl]
+            for r in range(world):
+                got = vec_from_dev(dr[r])
+                w = want[blocks[r]]
+                sl = slice(0, Vh) if parity == 0 else slice(Vh, 2 * Vh)
+                osl = slice(Vh, 2 * Vh) if parity == 0 else slice(0, Vh)
+                assert np.isfinite(got).all()
+                assert rel_l2(got[sl], w[sl]) <= 1e-13, (r, parity, a, b)
+                assert np.array_equal(got[osl], r0[blocks[r]][osl])       # the other parity is untouched
