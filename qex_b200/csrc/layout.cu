@@ -258,76 +258,7 @@ __global__ void __launch_bounds__(LB) k_compress(const double2* __restrict__ u, 
   double dev[2] = {0.0, 0.0}, smin[2] = {1e300, 1e300}, smax[2] = {0.0, 0.0};
   unsigned int bits = 0;
   if (live) {
-#pragma unroll
-    for (int mu = 0; mu < 4; mu++) {
-#pragma unroll
-      for (int j = 0; j < NL; j++) {
-        const int mode = j == 0 ? mode0 : mode1;
-        if (mode == 0) continue;
-        const int ne = mode == 14 ? 7 : 6;
-        const double2* p = u + ((size_t)((mu * NL + j) * 2 + par) * 9) * Vh + idx;
-        double2 U[9];
-#pragma unroll
-        for (int e = 0; e < 9; e++) U[e] = p[(size_t)e * Vh];
-        double2* o = (j == 0 ? u12_0 : u12_1) + ((size_t)(mu * 2 + par) * ne) * Vh + idx;
-#pragma unroll
-        for (int e = 0; e < 6; e++) o[(size_t)e * Vh] = U[e];
-        const double s2 = U[0].x * U[0].x + U[0].y * U[0].y + U[1].x * U[1].x + U[1].y * U[1].y +
-                          U[2].x * U[2].x + U[2].y * U[2].y;
-        const double t2 = U[3].x * U[3].x + U[3].y * U[3].y + U[4].x * U[4].x + U[4].y * U[4].y +
-                          U[5].x * U[5].x + U[5].y * U[5].y;
-        double2 ov = {0, 0};   // <row0, row1>
-#pragma unroll
-        for (int e = 0; e < 3; e++) {
-          ov.x += U[e].x * U[3 + e].x + U[e].y * U[3 + e].y;
-          ov.y += U[e].x * U[3 + e].y - U[e].y * U[3 + e].x;
-        }
-        double2 c[3];          // conj(row0 x row1)
-        c[0].x = U[1].x * U[5].x - U[1].y * U[5].y - (U[2].x * U[4].x - U[2].y * U[4].y);
-        c[0].y = -(U[1].x * U[5].y + U[1].y * U[5].x - (U[2].x * U[4].y + U[2].y * U[4].x));
-        c[1].x = U[2].x * U[3].x - U[2].y * U[3].y - (U[0].x * U[5].x - U[0].y * U[5].y);
-        c[1].y = -(U[2].x * U[3].y + U[2].y * U[3].x - (U[0].x * U[5].y + U[0].y * U[5].x));
-        c[2].x = U[0].x * U[4].x - U[0].y * U[4].y - (U[1].x * U[3].x - U[1].y * U[3].y);
-        c[2].y = -(U[0].x * U[4].y + U[0].y * U[4].x - (U[1].x * U[3].y + U[1].y * U[3].x));
-        const double inv = s2 > 0.0 ? rsqrt(s2) : 0.0;
-        double d;
-        if (mode == 14) {
-          double2 num = {0, 0};   // <c, row2> = sum conj(c_e) row2_e
-          double cc = 0.0;
-#pragma unroll
-          for (int e = 0; e < 3; e++) {
-            num.x += c[e].x * U[6 + e].x + c[e].y * U[6 + e].y;
-            num.y += c[e].x * U[6 + e].y - c[e].y * U[6 + e].x;
-            cc += c[e].x * c[e].x + c[e].y * c[e].y;
-          }
-          const double icc = cc > 0.0 ? 1.0 / cc : 0.0;
-          const double2 phi = {num.x * icc, num.y * icc};
-          o[(size_t)6 * Vh] = phi;
-          d = 0.0;
-#pragma unroll
-          for (int e = 0; e < 3; e++) {   // exactly what the sweeps rebuild
-            const double rx = phi.x * c[e].x - phi.y * c[e].y, ry = phi.x * c[e].y + phi.y * c[e].x;
-            d = fmax(d, fmax(fabs(U[6 + e].x - rx), fabs(U[6 + e].y - ry)) * inv);
-          }
-          if (!(s2 > 0.0) || !(cc > 0.0)) d = 1.0;
-        } else {
-          double re = 0.0;       // Re <c, row2> = sigma |c|^2 / |s|
-#pragma unroll
-          for (int e = 0; e < 3; e++) re += c[e].x * U[6 + e].x + c[e].y * U[6 + e].y;
-          const bool neg = re < 0.0;
-          if (neg) bits |= 1u << (2 * mu + j);
-          const double f = neg ? -inv : inv;
-          d = fmax(fabs(t2 - s2), sqrt(ov.x * ov.x + ov.y * ov.y)) * inv * inv;
-#pragma unroll
-          for (int e = 0; e < 3; e++)
-            d = fmax(d, fmax(fabs(U[6 + e].x - f * c[e].x), fabs(U[6 + e].y - f * c[e].y)) * inv);
-          if (!(s2 > 0.0)) d = 1.0;
-        }
-        dev[j] = fmax(dev[j], d);
-        smin[j] = fmin(smin[j], s2);
-        smax[j] = fmax(smax[j], s2);
-      }
-    }
+    bits = compress_site<NL>(u, u12_0, u12_1, Vh, par, idx, mode0, mode1, dev, smin, smax);
     if (sgn) sgn[ds] = (unsigned short)bits;
   }
 #pragma unroll
@@ -348,20 +279,8 @@ __global__ void __launch_bounds__(LB) k_sign_bwd(unsigned short* sgn, int Vh, in
   if (ds >= 2 * Vh) return;
   const int par = ds / Vh, idx = ds - par * Vh;
   const int X[4] = {X0, X1, X2, X3};
-  const Site s = site_from_idx(idx, par, X);
   unsigned int bits = sgn[ds] & 0xffu;
-#pragma unroll
-  for (int mu = 0; mu < 4; mu++) {
-    const int st = stride_of(mu, X);
-#pragma unroll
-    for (int j = 0; j < NL; j++) {
-      const int h = (j == 0) ? 1 : 3;
-      int ln = s.lex - h * st;
-      if (s.x[mu] - h < 0) ln += X[mu] * st;   // local wrap; off-rank hops never read this bit
-      const unsigned int nb = sgn[(size_t)(1 - par) * Vh + (ln >> 1)];
-      bits |= ((nb >> (2 * mu + j)) & 1u) << (8 + 2 * mu + j);
-    }
-  }
+  bits = sign_bwd_site<NL>(sgn, Vh, par, idx, X, bits);
   sgn[ds] = (unsigned short)bits;
 }
 

@@ -9,6 +9,10 @@
 
 namespace qb {
 
+#if !defined(__CUDACC__)
+inline double rsqrt(double x) { return 1.0 / sqrt(x); }   // host harness only (g++ has no rsqrt)
+#endif
+
 constexpr int SWEEP_BLOCK = 128;   // threads per block = sites per tile
 
 // loads with the cache hints the sweep relies on (plain loads on the host)
@@ -275,6 +279,107 @@ QB_HD void stencil_local(const SweepArgs& A, const Site& s, int idx, double2 (&a
   }
 }
 
+
+// ---- 12- / 14-real link storage: what k_compress does for one site (layout.cu) --------------------------------
+// Writes rows 0, 1 (and the factor phi of the 14-real form) of every link of site (par, idx) for the classes whose
+// mode is 12 or 14, folds the evidence the host decides on into dev / smin / smax (max deviation of the rebuilt third
+// row, range of |s|^2) and returns the sign bits of the 12-real form (bit 2 mu + j).
+template <int NL>
+QB_HD unsigned int compress_site(const double2* __restrict__ u, double2* __restrict__ u12_0, double2* __restrict__ u12_1,
+                                 int Vh, int par, int idx, int mode0, int mode1, double (&dev)[2], double (&smin)[2],
+                                 double (&smax)[2]) {
+  unsigned int bits = 0;
+#pragma unroll
+  for (int mu = 0; mu < 4; mu++) {
+#pragma unroll
+    for (int j = 0; j < NL; j++) {
+      const int mode = j == 0 ? mode0 : mode1;
+      if (mode == 0) continue;
+      const int ne = mode == 14 ? 7 : 6;
+      const double2* p = u + ((size_t)((mu * NL + j) * 2 + par) * 9) * Vh + idx;
+      double2 U[9];
+#pragma unroll
+      for (int e = 0; e < 9; e++) U[e] = p[(size_t)e * Vh];
+      double2* o = (j == 0 ? u12_0 : u12_1) + ((size_t)(mu * 2 + par) * ne) * Vh + idx;
+#pragma unroll
+      for (int e = 0; e < 6; e++) o[(size_t)e * Vh] = U[e];
+      const double s2 = U[0].x * U[0].x + U[0].y * U[0].y + U[1].x * U[1].x + U[1].y * U[1].y +
+                        U[2].x * U[2].x + U[2].y * U[2].y;
+      const double t2 = U[3].x * U[3].x + U[3].y * U[3].y + U[4].x * U[4].x + U[4].y * U[4].y +
+                        U[5].x * U[5].x + U[5].y * U[5].y;
+      double2 ov = {0, 0};   // <row0, row1>
+#pragma unroll
+      for (int e = 0; e < 3; e++) {
+        ov.x += U[e].x * U[3 + e].x + U[e].y * U[3 + e].y;
+        ov.y += U[e].x * U[3 + e].y - U[e].y * U[3 + e].x;
+      }
+      double2 c[3];          // conj(row0 x row1)
+      c[0].x = U[1].x * U[5].x - U[1].y * U[5].y - (U[2].x * U[4].x - U[2].y * U[4].y);
+      c[0].y = -(U[1].x * U[5].y + U[1].y * U[5].x - (U[2].x * U[4].y + U[2].y * U[4].x));
+      c[1].x = U[2].x * U[3].x - U[2].y * U[3].y - (U[0].x * U[5].x - U[0].y * U[5].y);
+      c[1].y = -(U[2].x * U[3].y + U[2].y * U[3].x - (U[0].x * U[5].y + U[0].y * U[5].x));
+      c[2].x = U[0].x * U[4].x - U[0].y * U[4].y - (U[1].x * U[3].x - U[1].y * U[3].y);
+      c[2].y = -(U[0].x * U[4].y + U[0].y * U[4].x - (U[1].x * U[3].y + U[1].y * U[3].x));
+      const double inv = s2 > 0.0 ? rsqrt(s2) : 0.0;
+      double d;
+      if (mode == 14) {
+        double2 num = {0, 0};   // <c, row2> = sum conj(c_e) row2_e
+        double cc = 0.0;
+#pragma unroll
+        for (int e = 0; e < 3; e++) {
+          num.x += c[e].x * U[6 + e].x + c[e].y * U[6 + e].y;
+          num.y += c[e].x * U[6 + e].y - c[e].y * U[6 + e].x;
+          cc += c[e].x * c[e].x + c[e].y * c[e].y;
+        }
+        const double icc = cc > 0.0 ? 1.0 / cc : 0.0;
+        const double2 phi = {num.x * icc, num.y * icc};
+        o[(size_t)6 * Vh] = phi;
+        d = 0.0;
+#pragma unroll
+        for (int e = 0; e < 3; e++) {   // exactly what the sweeps rebuild
+          const double rx = phi.x * c[e].x - phi.y * c[e].y, ry = phi.x * c[e].y + phi.y * c[e].x;
+          d = fmax(d, fmax(fabs(U[6 + e].x - rx), fabs(U[6 + e].y - ry)) * inv);
+        }
+        if (!(s2 > 0.0) || !(cc > 0.0)) d = 1.0;
+      } else {
+        double re = 0.0;       // Re <c, row2> = sigma |c|^2 / |s|
+#pragma unroll
+        for (int e = 0; e < 3; e++) re += c[e].x * U[6 + e].x + c[e].y * U[6 + e].y;
+        const bool neg = re < 0.0;
+        if (neg) bits |= 1u << (2 * mu + j);
+        const double f = neg ? -inv : inv;
+        d = fmax(fabs(t2 - s2), sqrt(ov.x * ov.x + ov.y * ov.y)) * inv * inv;
+#pragma unroll
+        for (int e = 0; e < 3; e++)
+          d = fmax(d, fmax(fabs(U[6 + e].x - f * c[e].x), fabs(U[6 + e].y - f * c[e].y)) * inv);
+        if (!(s2 > 0.0)) d = 1.0;
+      }
+      dev[j] = fmax(dev[j], d);
+      smin[j] = fmin(smin[j], s2);
+      smax[j] = fmax(smax[j], s2);
+    }
+  }
+  return bits;
+}
+
+// high byte of the sign word: the sign bits of the links the BACKWARD hops of site (par, idx) read, U_{mu,j}(s - h_j mu)
+template <int NL>
+QB_HD unsigned int sign_bwd_site(const unsigned short* sgn, int Vh, int par, int idx, const int* X, unsigned int bits) {
+  const Site s = site_from_idx(idx, par, X);   // bits on entry: the site's own low byte
+#pragma unroll
+  for (int mu = 0; mu < 4; mu++) {
+    const int st = stride_of(mu, X);
+#pragma unroll
+    for (int j = 0; j < NL; j++) {
+      const int h = (j == 0) ? 1 : 3;
+      int ln = s.lex - h * st;
+      if (s.x[mu] - h < 0) ln += X[mu] * st;   // local wrap; off-rank hops never read this bit
+      const unsigned int nb = sgn[(size_t)(1 - par) * Vh + (ln >> 1)];
+      bits |= ((nb >> (2 * mu + j)) & 1u) << (8 + 2 * mu + j);
+    }
+  }
+  return bits;
+}
 
 // ---- face packing: one work item (see k_pack / k_sweep_mr in dslash.cu) ----------------------
 struct PackDir {

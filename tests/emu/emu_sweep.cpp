@@ -13,8 +13,14 @@ struct EmuHalo {   // one split direction of one rank: the fields of qexb200_hal
   long long off_f, off_b;
 };
 
-template <int NL>
-static void sweep_all(int nranks, const int* X, int comm_mask, int parity, const double* const* links,
+struct EmuRecon {   // per rank: the compressed copies k_compress / k_sign_bwd leave (layout.cu compress_links)
+  const double* u12[2];
+  const unsigned short* sgn;
+  double inv[2];
+};
+
+template <int NL, int RC>
+static void sweep_all(int nranks, const int* X, int comm_mask, int parity, const double* const* links, const EmuRecon* rec,
                       const double* const* x, double* const* r, double a, double b, double sgn, double post,
                       const EmuHalo* halo, int ndir, double* const* recv, const unsigned int* const* tiles, int ntiles) {
   const int Vh = X[0] * X[1] * X[2] * X[3] / 2;
@@ -22,7 +28,9 @@ static void sweep_all(int nranks, const int* X, int comm_mask, int parity, const
   // phase 1 -- what the pack blocks do (fill_pack of dslash.cu, peer-memory destinations)
   for (int me = 0; me < nranks; me++) {
     PackArgs P;
-    P.L.u = (const double2*)links[me]; P.L.u12[0] = P.L.u12[1] = nullptr; P.L.sgn = nullptr; P.L.inv[0] = P.L.inv[1] = 1.0;
+    P.L.u = (const double2*)links[me];
+    for (int j = 0; j < 2; j++) { P.L.u12[j] = rec ? (const double2*)rec[me].u12[j] : nullptr; P.L.inv[j] = rec ? rec[me].inv[j] : 1.0; }
+    P.L.sgn = rec ? rec[me].sgn : nullptr;
     P.x = (const double2*)x[me] + (size_t)q * 3 * Vh;
     for (int d = 0; d < 4; d++) P.X[d] = X[d];
     P.Vh = Vh; P.q = q; P.ndir = ndir; P.seq = 1; P.ticket = nullptr;
@@ -38,13 +46,16 @@ static void sweep_all(int nranks, const int* X, int comm_mask, int parity, const
       D.out_b1 = D.out_b0 + (size_t)3 * h.faceh;
       D.flag_f = D.flag_b = nullptr;
     }
-    for (int t = 0; t < end; t++) pack_item<NL, 0>(P, t);
+    for (int t = 0; t < end; t++) pack_item<NL, RC>(P, t);
   }
   // phase 2 -- what the tile blocks do, in table order (interior tiles first, face tiles last)
   for (int me = 0; me < nranks; me++) {
     MRArgs F;
     SweepArgs& A = F.A;
-    A.L.u = (const double2*)links[me]; A.L.u12[0] = A.L.u12[1] = nullptr; A.L.sgn = nullptr; A.L.inv[0] = A.L.inv[1] = 1.0;
+    A.L = Links();
+    A.L.u = (const double2*)links[me];
+    for (int j = 0; j < 2; j++) { A.L.u12[j] = rec ? (const double2*)rec[me].u12[j] : nullptr; A.L.inv[j] = rec ? rec[me].inv[j] : 1.0; }
+    A.L.sgn = rec ? rec[me].sgn : nullptr;
     A.x = (const double2*)x[me] + (size_t)q * 3 * Vh;
     A.r = (double2*)r[me] + (size_t)parity * 3 * Vh;
     A.bx = (const double2*)x[me] + (size_t)parity * 3 * Vh;
@@ -70,8 +81,8 @@ static void sweep_all(int nranks, const int* X, int comm_mask, int parity, const
         if (idx >= Vh) continue;
         const Site s = site_from_idx(idx, parity, A.X);
         double2 acc[3] = {{0, 0}, {0, 0}, {0, 0}};
-        if (need) stencil_ghost<NL, 0>(F, s, idx, acc);
-        else stencil_local<NL, 0>(A, s, idx, acc);
+        if (need) stencil_ghost<NL, RC>(F, s, idx, acc);
+        else stencil_local<NL, RC>(A, s, idx, acc);
         site_epilogue<false>(A, idx, acc);
       }
     }
@@ -80,13 +91,44 @@ static void sweep_all(int nranks, const int* X, int comm_mask, int parity, const
 
 extern "C" {
 // fields in the DEVICE layout: links[r] = double2[nlinks][2][9][Vh], x[r] / r[r] = double2[2][3][Vh];
-// recv[r] = the receive buffer of rank r; halo[r * 4 + i], i < ndir; tiles[r] = qexb200_plan_tiles of rank r
-int emu_sweep_mr(int nranks, int nl, const int* X, int comm_mask, int parity, const double* const* links,
-                 const double* const* x, double* const* r, double a, double b, double sgn, double post,
+// recv[r] = the receive buffer of rank r; halo[r * 4 + i], i < ndir; tiles[r] = qexb200_plan_tiles of rank r;
+// rc = the storage bits of Gauge::rc() (bit j: class j as 12 reals, bit 2 + j: as 14 reals), rec = the compressed copies
+int emu_sweep_mr(int nranks, int nl, int rc, const int* X, int comm_mask, int parity, const double* const* links,
+                 const EmuRecon* rec, const double* const* x, double* const* r, double a, double b, double sgn, double post,
                  const EmuHalo* halo, int ndir, double* const* recv, const unsigned int* const* tiles, int ntiles) {
-  if (nl == 1) sweep_all<1>(nranks, X, comm_mask, parity, links, x, r, a, b, sgn, post, halo, ndir, recv, tiles, ntiles);
-  else if (nl == 2) sweep_all<2>(nranks, X, comm_mask, parity, links, x, r, a, b, sgn, post, halo, ndir, recv, tiles, ntiles);
-  else return 1;
+#define EMU_CASE(NLV, RCV)                                                                                              \
+  if (nl == NLV && rc == RCV) {                                                                                         \
+    sweep_all<NLV, RCV>(nranks, X, comm_mask, parity, links, RCV ? rec : nullptr, x, r, a, b, sgn, post, halo, ndir, recv, \
+                        tiles, ntiles);                                                                                 \
+    return 0;                                                                                                           \
+  }
+  EMU_CASE(1, 0) EMU_CASE(1, 1) EMU_CASE(1, 4)
+  EMU_CASE(2, 0) EMU_CASE(2, 2) EMU_CASE(2, 3) EMU_CASE(2, 8) EMU_CASE(2, 12) EMU_CASE(2, 9) EMU_CASE(2, 6)
+#undef EMU_CASE
+  return 1;
+}
+// compress_links of layout.cu on the host: k_compress + k_sign_bwd site by site.  stats[6] = max deviation per class,
+// min |s|^2, max |s|^2 (what the host decides on); u12_j sized [4][2][6 or 7][Vh] double2, sgn [2][Vh].
+int emu_compress(int nl, const int* X, const double* links, double* u12_0, double* u12_1, unsigned short* sgn,
+                 int mode0, int mode1, double* stats) {
+  const int Vh = X[0] * X[1] * X[2] * X[3] / 2;
+  double dev[2] = {0.0, 0.0}, smin[2] = {1e300, 1e300}, smax[2] = {0.0, 0.0};
+  for (int par = 0; par < 2; par++)
+    for (int idx = 0; idx < Vh; idx++) {
+      unsigned int bits;
+      if (nl == 2) bits = compress_site<2>((const double2*)links, (double2*)u12_0, (double2*)u12_1, Vh, par, idx, mode0, mode1, dev, smin, smax);
+      else bits = compress_site<1>((const double2*)links, (double2*)u12_0, (double2*)u12_1, Vh, par, idx, mode0, 0, dev, smin, smax);
+      if (sgn) sgn[(size_t)par * Vh + idx] = (unsigned short)bits;
+    }
+  if (sgn)
+    for (int par = 0; par < 2; par++)      // all low bytes are final before any high byte is built (two launches on the GPU)
+      for (int idx = 0; idx < Vh; idx++) {
+        const size_t ds = (size_t)par * Vh + idx;
+        unsigned int bits = sgn[ds] & 0xffu;
+        bits = (nl == 2) ? sign_bwd_site<2>(sgn, Vh, par, idx, X, bits) : sign_bwd_site<1>(sgn, Vh, par, idx, X, bits);
+        sgn[ds] = (unsigned short)bits;
+      }
+  for (int j = 0; j < 2; j++) { stats[j] = dev[j]; stats[2 + j] = smin[j]; stats[4 + j] = smax[j]; }
   return 0;
 }
 // idx of parity par -> local coordinates (site_from_idx): the map the tests check against the oracle's site order

@@ -23,6 +23,10 @@ class EmuHalo(C.Structure):
                 ("off_f", C.c_longlong), ("off_b", C.c_longlong)]
 
 
+class EmuRecon(C.Structure):
+    _fields_ = [("u12", C.POINTER(C.c_double) * 2), ("sgn", C.POINTER(C.c_ushort)), ("inv", C.c_double * 2)]
+
+
 @pytest.fixture(scope="module")
 def emu():
     src = os.path.join(HERE, "emu", "emu_sweep.cpp")
@@ -32,8 +36,11 @@ def emu():
                                "-I/usr/local/cuda/include", src, "-o", SO])
     lib = C.CDLL(SO)
     dpp, ip = C.POINTER(C.POINTER(C.c_double)), C.POINTER(C.c_int)
-    lib.emu_sweep_mr.argtypes = [C.c_int, C.c_int, ip, C.c_int, C.c_int, dpp, dpp, dpp, C.c_double, C.c_double, C.c_double,
-                                 C.c_double, C.POINTER(EmuHalo), C.c_int, dpp, C.POINTER(C.POINTER(C.c_uint)), C.c_int]
+    dp_ = C.POINTER(C.c_double)
+    lib.emu_sweep_mr.argtypes = [C.c_int, C.c_int, C.c_int, ip, C.c_int, C.c_int, dpp, C.POINTER(EmuRecon), dpp, dpp, C.c_double,
+                                 C.c_double, C.c_double, C.c_double, C.POINTER(EmuHalo), C.c_int, dpp,
+                                 C.POINTER(C.POINTER(C.c_uint)), C.c_int]
+    lib.emu_compress.argtypes = [C.c_int, ip, dp_, dp_, dp_, C.POINTER(C.c_ushort), C.c_int, C.c_int, dp_]
     lib.emu_site.argtypes = [C.c_int, C.c_int, ip, ip]
     return lib
 
@@ -109,9 +116,47 @@ CASES = [
 
 @pytest.mark.parametrize("L,G,nlinks", CASES)
 def test_multi_rank_sweep_on_the_host_matches_the_oracle(emu, L, G, nlinks):
+    lat, g, (x, r0) = make_inputs(L, nlinks)
+    run_sweeps(emu, L, G, nlinks, lat, g, x, r0)
+
+
+def compress(emu, dl, X, nlinks, modes):
+    """compress_links (layout.cu) per rank on the host: returns (EmuRecon array, keep-alive list, rc bits) after the
+    library's own acceptance test (deviation <= 2e-14, |s|^2 spread <= 1e-13 for the 12-real form)."""
+    nl, Vh = nlinks // 4, int(np.prod(X)) // 2
+    rec = (EmuRecon * len(dl))()
+    keep, rcs = [], set()
+    dp = lambda a: a.ctypes.data_as(C.POINTER(C.c_double))
+    for r, links in enumerate(dl):
+        u12 = [np.zeros(4 * 2 * (7 if m == 14 else 6) * Vh * 2) if m else np.zeros(2) for m in (modes + [0])[:2]]
+        sgn = np.zeros(2 * Vh, dtype=np.uint16)
+        stats = np.zeros(6)
+        assert emu.emu_compress(nl, (C.c_int * 4)(*X), dp(links), dp(u12[0]), dp(u12[1]),
+                                sgn.ctypes.data_as(C.POINTER(C.c_ushort)), modes[0], (modes + [0])[1], dp(stats)) == 0
+        rc = 0
+        for j in range(nl):
+            if not modes[j]:
+                continue
+            dev, smin, smax = stats[j], stats[2 + j], stats[4 + j]
+            assert dev <= 2e-14 and smin > 0, (r, j, dev)
+            if modes[j] == 12:
+                assert smax - smin <= 1e-13 * smax
+                rec[r].inv[j] = 1.0 / np.sqrt(0.5 * (smin + smax))
+                rc |= 1 << j
+            else:
+                rec[r].inv[j] = 1.0
+                rc |= 4 << j
+            rec[r].u12[j] = dp(u12[j])
+        rec[r].sgn = sgn.ctypes.data_as(C.POINTER(C.c_ushort))
+        keep += [u12, sgn]
+        rcs.add(rc)
+    assert len(rcs) == 1
+    return rec, keep, rcs.pop()
+
+
+def run_sweeps(emu, L, G, nlinks, lat, g, x, r0, modes=None):
     import qex_b200 as qb
     world = int(np.prod(G))
-    lat, g, (x, r0) = make_inputs(L, nlinks)
     X = [L[d] // G[d] for d in range(4)]
     Vh = int(np.prod(X)) // 2
     blocks = [block_index(L, G, r) for r in range(world)]
@@ -130,6 +175,7 @@ def test_multi_rank_sweep_on_the_host_matches_the_oracle(emu, L, G, nlinks):
     arr = lambda xs: (C.POINTER(C.c_double) * world)(*[dp(a) for a in xs])
     Xc = (C.c_int * 4)(*X)
     ntiles = (Vh + 127) // 128
+    rec, keep, rc_bits = (None, None, 0) if modes is None else compress(emu, dl, X, nlinks, modes)
     for parity in (0, 1):
         tiles = []
         for r in range(world):
@@ -140,8 +186,8 @@ def test_multi_rank_sweep_on_the_host_matches_the_oracle(emu, L, G, nlinks):
         for a, b, sgn, post in ((0.0, 0.0, 1.0, 1.0), (0.7, -0.3, 1.0, 1.0), (0.0, 0.04, -1.0, 1.0)):
             dr = [vec_to_dev(r0[bk]) for bk in blocks]
             recv = [np.full(2 * cap, np.nan) for _ in range(world)]      # anything read but never packed shows as NaN
-            rc = emu.emu_sweep_mr(world, nlinks // 4, Xc, comm_mask, parity, arr(dl), arr(dx), arr(dr), a, b, sgn, post,
-                                  halo, ndir, arr(recv), tarr, ntiles)
+            rc = emu.emu_sweep_mr(world, nlinks // 4, rc_bits, Xc, comm_mask, parity, arr(dl), rec, arr(dx), arr(dr), a, b, sgn,
+                                  post, halo, ndir, arr(recv), tarr, ntiles)
             assert rc == 0
             want = r0.copy()
             if sgn > 0:
@@ -159,3 +205,31 @@ def test_multi_rank_sweep_on_the_host_matches_the_oracle(emu, L, G, nlinks):
                 assert np.isfinite(got).all()
                 assert rel_l2(got[sl], w[sl]) <= 1e-13, (r, parity, a, b)
                 assert np.array_equal(got[osl], r0[blocks[r]][osl])       # the other parity is untouched
+
+
+@pytest.mark.parametrize("L,G,nlinks,modes", [
+    ((8, 8, 8, 16), (1, 1, 1, 2), 4, [12]),
+    ((8, 8, 12, 8), (1, 1, 2, 1), 8, [12, 12]),
+    ((8, 8, 16, 16), (1, 1, 2, 2), 8, [0, 12]),      # fat 18, Naik 12: what a real HISQ set allows
+    ((16, 8, 8, 8), (4, 1, 1, 1), 4, [12]),
+    ((8, 8, 8, 16), (1, 1, 1, 2), 4, [14]),
+    ((8, 8, 16, 16), (1, 1, 2, 2), 8, [14, 14]),
+    ((8, 8, 16, 16), (1, 1, 2, 2), 8, [0, 14]),
+    ((8, 16, 16, 8), (1, 2, 2, 1), 8, [12, 14]),
+    ((8, 8, 8, 8), (1, 1, 1, 1), 8, [12, 12]),        # one rank: k_sweep's path (stencil_local only, local wrap of the sign bits)
+])
+def test_multi_rank_sweep_with_12_and_14_real_links(emu, L, G, nlinks, modes):
+    """The same with the compressed link forms: k_compress / k_sign_bwd's site functions build rows 0,1 (+ sign bits or
+    the factor phi) per rank, the sweep rebuilds the third row in `load_link_k` -- also in the pack items and for the
+    sign bits of backward hops next to a rank boundary.  12 reals: links SU(3) to machine precision with phases and
+    BC; 14 reals: U(3) links with a determinant phase that changes from site to site.  Bar: the 18-real oracle, 1e-13."""
+    from util import make_exact_inputs
+    lat, g, (x, r0) = make_exact_inputs(L, nlinks)
+    if 14 in modes:
+        th = np.random.default_rng(99).uniform(0, 2 * np.pi, g.shape[:2])
+        gc = (g[..., 0] + 1j * g[..., 1]) * np.exp(1j * th)[:, :, None, None]
+        if 12 in modes:       # keep the 12-real class SU(3): phases on the other class only
+            keep = [k for k in range(nlinks) if modes[k % 2 if nlinks == 8 else 0] == 12]
+            gc[keep] = (g[..., 0] + 1j * g[..., 1])[keep]
+        g = np.ascontiguousarray(np.stack([gc.real, gc.imag], axis=-1))
+    run_sweeps(emu, L, G, nlinks, lat, g, x, r0, modes)
