@@ -86,64 +86,6 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_sweep_t(const SweepArgs A) {
 // (region i: interior in split directions m_1..m_{i-1}, boundary in m_i, anything elsewhere),
 // one thread per site, which handles every split direction of its site in a fixed order:
 // no site is touched by two threads, so corners need no atomics and the sum is deterministic.
-struct ExtDir {
-  int mu, depth, faceh, nb;
-  const double2 *ghost_f, *ghost_b0, *ghost_b1;
-  const unsigned int *flag_f, *flag_b;   // p2p: set by the + / - neighbour's pack kernel
-};
-struct ExtRegion {
-  int n[4];      // index counts per direction (n[0] even)
-  int type[4];   // 0: whole extent, 1: boundary layers, 2: interior layers
-  int end;       // prefix end in threads (sites of one parity)
-};
-struct ExtArgs {
-  Links L;
-  double2* r;
-  double scale;  // post*sgn
-  int X[4], dep[4], nbv[4];
-  int Vh, parity, ndir, nreg;
-  ExtDir d[4];
-  ExtRegion reg[4];
-  unsigned int seq;
-  int wait;      // p2p: spin on the neighbours' flags before touching the ghosts
-  int* err;
-  unsigned long long timeout_ns;
-  // DOT epilogue: *result = sum over ranks of (*interior + sum over my sites Re<bx, r_new>)
-  const double2* bx;
-  double* partials;
-  unsigned int* ticket;
-  double* result;
-  const double* interior;
-  XRank* xr;
-  const double* skip;   // as SweepArgs::skip
-};
-
-// thread t of the boundary enumeration -> local coordinates of its site (parity A.parity)
-__device__ __forceinline__ void region_site(const ExtArgs& A, int t, int (&x)[4]) {
-  int ri = 0, base = 0;
-#pragma unroll
-  for (int i = 0; i < 3; i++)
-    if (i + 1 < A.nreg && t >= A.reg[i].end) { ri = i + 1; base = A.reg[i].end; }
-  const ExtRegion& R = A.reg[ri];
-  int tt = t - base;
-  int id[4];
-  const int n0h = R.n[0] >> 1;
-  const int i0h = tt % n0h; tt /= n0h;
-  id[1] = tt % R.n[1]; tt /= R.n[1];
-  id[2] = tt % R.n[2];
-  id[3] = tt / R.n[2];
-  int par = A.parity;
-#pragma unroll
-  for (int d = 1; d < 4; d++) par += id[d] + (R.type[d] == 2 ? A.dep[d] : 0);
-  par += (R.type[0] == 2 ? A.dep[0] : 0);
-  id[0] = 2 * i0h + (par & 1);
-#pragma unroll
-  for (int d = 0; d < 4; d++) {
-    const int i = id[d];
-    x[d] = (R.type[d] == 0) ? i : (R.type[d] == 2) ? A.dep[d] + i : (i < A.dep[d] ? i : A.X[d] - A.nbv[d] + i);
-  }
-}
-
 template <int NL, int RC, bool DOT>
 __global__ void __launch_bounds__(SWEEP_BLOCK) k_exterior(const ExtArgs A) {
   if (A.skip != nullptr && *A.skip != 0.0) return;
@@ -156,47 +98,7 @@ __global__ void __launch_bounds__(SWEEP_BLOCK) k_exterior(const ExtArgs A) {
   }
   const int t = blockIdx.x * SWEEP_BLOCK + threadIdx.x;
   double dot = 0.0;
-  if (t < A.reg[A.nreg - 1].end) {
-  int x[4];
-  region_site(A, t, x);
-  const int lex = ((x[3] * A.X[2] + x[2]) * A.X[1] + x[1]) * A.X[0] + x[0];
-  const int idx = lex >> 1, Vh = A.Vh;
-  double2 acc[3] = {{0, 0}, {0, 0}, {0, 0}};
-  const unsigned int sg = (RC & 3) ? A.L.sgn[(size_t)A.parity * Vh + idx] : 0u;
-  for (int di = 0; di < A.ndir; di++) {
-    const ExtDir& D = A.d[di];
-    const int mu = D.mu, Xm = A.X[mu], xmu = x[mu], d = D.depth;
-    if (xmu + d < Xm && xmu - d >= 0) continue;   // no off-rank hop in this direction
-    const int fidx = face_lex(x, mu, A.X) >> 1;
-#pragma unroll
-    for (int j = 0; j < NL; j++) {
-      const int h = (j == 0) ? 1 : 3;
-      if (xmu + h >= Xm) {
-        const int l = xmu + h - Xm;
-        double2 U[9], v[3];
-        load_link_k<NL, RC>(U, A.L, mu, j, A.parity, idx, Vh, (sg >> (2 * mu + j)) & 1u);
-#pragma unroll
-        for (int c = 0; c < 3; c++) v[c] = __ldcg(D.ghost_f + (size_t)c * d * D.faceh + (size_t)l * D.faceh + fidx);
-        mv_add(acc, U, v);
-      }
-      if (xmu - h < 0) {
-        const double2* gb = (j == 0) ? D.ghost_b0 : D.ghost_b1;
-#pragma unroll
-        for (int c = 0; c < 3; c++) {
-          const double2 w = __ldcg(gb + (size_t)c * h * D.faceh + (size_t)xmu * D.faceh + fidx);
-          acc[c].x -= w.x; acc[c].y -= w.y;
-        }
-      }
-    }
-  }
-#pragma unroll
-  for (int c = 0; c < 3; c++) {
-    double2 o = A.r[(size_t)c * Vh + idx];
-    o.x = fma(A.scale, acc[c].x, o.x); o.y = fma(A.scale, acc[c].y, o.y);
-    A.r[(size_t)c * Vh + idx] = o;
-    if (DOT) { const double2 bxv = A.bx[(size_t)c * Vh + idx]; dot += bxv.x * o.x + bxv.y * o.y; }
-  }
-  }
+  if (t < A.reg[A.nreg - 1].end) dot = exterior_site<NL, RC, DOT>(A, t);
   if (DOT) grid_reduce<SWEEP_BLOCK>(dot, A.partials, A.ticket, A.result, A.xr, A.interior);
 }
 
@@ -381,22 +283,7 @@ static int fill_ext(const Gauge& g, int parity, double2* r, double scale, const 
     D.flag_b = c.p2p ? win_flag(c.win, buf, hd.mu, 1) : nullptr;
     E.dep[hd.mu] = hd.depth; E.nbv[hd.mu] = D.nb;
   }
-  int end = 0, nreg = 0;
-  for (int i = 0; i < E.ndir; i++) {
-    ExtRegion R;
-    long long cnt = 1;
-    for (int d = 0; d < 4; d++) { R.type[d] = 0; R.n[d] = c.g.X[d]; }
-    for (int j = 0; j < i; j++) { const int m = c.halo[j].mu; R.type[m] = 2; R.n[m] = c.g.X[m] - E.nbv[m]; }
-    const int mi = c.halo[i].mu;
-    R.type[mi] = 1; R.n[mi] = E.nbv[mi];
-    for (int d = 0; d < 4; d++) cnt *= R.n[d];
-    if (cnt == 0) continue;
-    end += (int)(cnt / 2);
-    R.end = end;
-    E.reg[nreg++] = R;
-  }
-  E.nreg = nreg;
-  return end;
+  return plan_regions(E);
 }
 
 // NCCL path.  dot_out != nullptr: also completes Re<bx, r> (interior part already in *dot_interior).

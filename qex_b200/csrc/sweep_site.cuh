@@ -381,6 +381,137 @@ QB_HD unsigned int sign_bwd_site(const unsigned short* sgn, int Vh, int par, int
   return bits;
 }
 
+struct XRank;   // common.cuh
+
+// ---- exterior (NCCL path): one launch for all split directions ------------------------------
+struct ExtDir {
+  int mu, depth, faceh, nb;
+  const double2 *ghost_f, *ghost_b0, *ghost_b1;
+  const unsigned int *flag_f, *flag_b;   // p2p: set by the + / - neighbour's pack kernel
+};
+struct ExtRegion {
+  int n[4];      // index counts per direction (n[0] even)
+  int type[4];   // 0: whole extent, 1: boundary layers, 2: interior layers
+  int end;       // prefix end in threads (sites of one parity)
+};
+struct ExtArgs {
+  Links L;
+  double2* r;
+  double scale;  // post*sgn
+  int X[4], dep[4], nbv[4];
+  int Vh, parity, ndir, nreg;
+  ExtDir d[4];
+  ExtRegion reg[4];
+  unsigned int seq;
+  int wait;      // p2p: spin on the neighbours' flags before touching the ghosts
+  int* err;
+  unsigned long long timeout_ns;
+  // DOT epilogue: *result = sum over ranks of (*interior + sum over my sites Re<bx, r_new>)
+  const double2* bx;
+  double* partials;
+  unsigned int* ticket;
+  double* result;
+  const double* interior;
+  XRank* xr;
+  const double* skip;   // as SweepArgs::skip
+};
+
+// thread t of the boundary enumeration -> local coordinates of its site (parity A.parity)
+QB_HD void region_site(const ExtArgs& A, int t, int (&x)[4]) {
+  int ri = 0, base = 0;
+#pragma unroll
+  for (int i = 0; i < 3; i++)
+    if (i + 1 < A.nreg && t >= A.reg[i].end) { ri = i + 1; base = A.reg[i].end; }
+  const ExtRegion& R = A.reg[ri];
+  int tt = t - base;
+  int id[4];
+  const int n0h = R.n[0] >> 1;
+  const int i0h = tt % n0h; tt /= n0h;
+  id[1] = tt % R.n[1]; tt /= R.n[1];
+  id[2] = tt % R.n[2];
+  id[3] = tt / R.n[2];
+  int par = A.parity;
+#pragma unroll
+  for (int d = 1; d < 4; d++) par += id[d] + (R.type[d] == 2 ? A.dep[d] : 0);
+  par += (R.type[0] == 2 ? A.dep[0] : 0);
+  id[0] = 2 * i0h + (par & 1);
+#pragma unroll
+  for (int d = 0; d < 4; d++) {
+    const int i = id[d];
+    x[d] = (R.type[d] == 0) ? i : (R.type[d] == 2) ? A.dep[d] + i : (i < A.dep[d] ? i : A.X[d] - A.nbv[d] + i);
+  }
+}
+
+// One boundary site of the NCCL path's exterior kernel (boundarySB2 of stagD.nim:381-393): thread t of the region
+// enumeration adds, for every split direction of its site, the terms whose neighbour lives on another rank -- forward
+// hops from the + neighbour's psi layers, backward hops from the products the - neighbour formed.  Returns the site's
+// Re<bx, r_new> when DOT.
+template <int NL, int RC, bool DOT>
+QB_HD double exterior_site(const ExtArgs& A, int t) {
+  double dot = 0.0;
+  int x[4];
+  region_site(A, t, x);
+  const int lex = ((x[3] * A.X[2] + x[2]) * A.X[1] + x[1]) * A.X[0] + x[0];
+  const int idx = lex >> 1, Vh = A.Vh;
+  double2 acc[3] = {{0, 0}, {0, 0}, {0, 0}};
+  const unsigned int sg = (RC & 3) ? A.L.sgn[(size_t)A.parity * Vh + idx] : 0u;
+  for (int di = 0; di < A.ndir; di++) {
+    const ExtDir& D = A.d[di];
+    const int mu = D.mu, Xm = A.X[mu], xmu = x[mu], d = D.depth;
+    if (xmu + d < Xm && xmu - d >= 0) continue;   // no off-rank hop in this direction
+    const int fidx = face_lex(x, mu, A.X) >> 1;
+#pragma unroll
+    for (int j = 0; j < NL; j++) {
+      const int h = (j == 0) ? 1 : 3;
+      if (xmu + h >= Xm) {
+        const int l = xmu + h - Xm;
+        double2 U[9], v[3];
+        load_link_k<NL, RC>(U, A.L, mu, j, A.parity, idx, Vh, (sg >> (2 * mu + j)) & 1u);
+#pragma unroll
+        for (int c = 0; c < 3; c++) v[c] = ld_cg(D.ghost_f + (size_t)c * d * D.faceh + (size_t)l * D.faceh + fidx);
+        mv_add(acc, U, v);
+      }
+      if (xmu - h < 0) {
+        const double2* gb = (j == 0) ? D.ghost_b0 : D.ghost_b1;
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+          const double2 w = ld_cg(gb + (size_t)c * h * D.faceh + (size_t)xmu * D.faceh + fidx);
+          acc[c].x -= w.x; acc[c].y -= w.y;
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < 3; c++) {
+    double2 o = A.r[(size_t)c * Vh + idx];
+    o.x = fma(A.scale, acc[c].x, o.x); o.y = fma(A.scale, acc[c].y, o.y);
+    A.r[(size_t)c * Vh + idx] = o;
+    if (DOT) { const double2 bxv = A.bx[(size_t)c * Vh + idx]; dot += bxv.x * o.x + bxv.y * o.y; }
+  }
+  return dot;
+}
+
+// The disjoint boundary regions of fill_ext (dslash.cu): region i = interior in split directions m_1..m_{i-1}, boundary
+// layers in m_i, whole extent elsewhere.  Needs E.X, E.ndir, E.d[i].mu and E.nbv filled; returns the number of sites.
+inline int plan_regions(ExtArgs& E) {
+  int end = 0, nreg = 0;
+  for (int i = 0; i < E.ndir; i++) {
+    ExtRegion R;
+    long long cnt = 1;
+    for (int d = 0; d < 4; d++) { R.type[d] = 0; R.n[d] = E.X[d]; }
+    for (int j = 0; j < i; j++) { const int m = E.d[j].mu; R.type[m] = 2; R.n[m] = E.X[m] - E.nbv[m]; }
+    const int mi = E.d[i].mu;
+    R.type[mi] = 1; R.n[mi] = E.nbv[mi];
+    for (int d = 0; d < 4; d++) cnt *= R.n[d];
+    if (cnt == 0) continue;
+    end += (int)(cnt / 2);
+    R.end = end;
+    E.reg[nreg++] = R;
+  }
+  E.nreg = nreg;
+  return end;
+}
+
 // ---- face packing: one work item (see k_pack / k_sweep_mr in dslash.cu) ----------------------
 struct PackDir {
   int mu, depth, faceh, end;
@@ -435,7 +566,6 @@ QB_HD void pack_item(const PackArgs& A, int t) {
 }
 
 
-struct XRank;
 struct GhostDir {                        // indexed by mu; entries of unsplit directions stay null
   const double2 *gf, *gb0, *gb1;         // + neighbour's first layers of x ; - neighbour's U_k^+ x per link class
   const unsigned int *flag_f, *flag_b;   // raised by the + / - neighbour's pack blocks

@@ -89,6 +89,87 @@ static void sweep_all(int nranks, const int* X, int comm_mask, int parity, const
   }
 }
 
+// The NCCL transport's three phases (pack -> send/recv -> interior k_sweep -> k_exterior) with the same site functions:
+// pack_item into each rank's own send buffer, the exchange of comm.cu halo_start as plain copies (psi faces come from
+// the + neighbour, product faces from the - neighbour), stencil_local on every site (off-rank hops skipped), then
+// exterior_site over the disjoint boundary regions of plan_regions.
+template <int NL, int RC>
+static void sweep_nccl(int nranks, const int* X, int comm_mask, int parity, const double* const* links, const EmuRecon* rec,
+                       const double* const* x, double* const* r, double a, double b, double sgn, double post,
+                       const EmuHalo* halo, int ndir, double* const* send, double* const* recv) {
+  const int Vh = X[0] * X[1] * X[2] * X[3] / 2;
+  const int q = 1 - parity;
+  auto links_of = [&](int me) {
+    Links L = Links();
+    L.u = (const double2*)links[me];
+    for (int j = 0; j < 2; j++) { L.u12[j] = rec ? (const double2*)rec[me].u12[j] : nullptr; L.inv[j] = rec ? rec[me].inv[j] : 1.0; }
+    L.sgn = rec ? rec[me].sgn : nullptr;
+    return L;
+  };
+  for (int me = 0; me < nranks; me++) {
+    PackArgs P;
+    P.L = links_of(me);
+    P.x = (const double2*)x[me] + (size_t)q * 3 * Vh;
+    for (int d = 0; d < 4; d++) P.X[d] = X[d];
+    P.Vh = Vh; P.q = q; P.ndir = ndir; P.seq = 1; P.ticket = nullptr;
+    int end = 0;
+    for (int i = 0; i < ndir; i++) {
+      const EmuHalo& h = halo[me * 4 + i];
+      PackDir& D = P.d[i];
+      D.mu = h.mu; D.depth = h.depth; D.faceh = h.faceh;
+      end += (h.depth + (NL == 2 ? 4 : 1)) * h.faceh;
+      D.end = end;
+      D.out_f = (double2*)send[me] + h.off_f;
+      D.out_b0 = (double2*)send[me] + h.off_b;
+      D.out_b1 = D.out_b0 + (size_t)3 * h.faceh;
+      D.flag_f = D.flag_b = nullptr;
+    }
+    for (int t = 0; t < end; t++) pack_item<NL, RC>(P, t);
+  }
+  for (int me = 0; me < nranks; me++)       // ncclSend / ncclRecv pairs of halo_start
+    for (int i = 0; i < ndir; i++) {
+      const EmuHalo& h = halo[me * 4 + i];
+      const size_t nf = (size_t)3 * h.depth * h.faceh, nb = (size_t)3 * (NL == 2 ? 4 : 1) * h.faceh;
+      for (size_t k = 0; k < 2 * nf; k++) recv[me][2 * h.off_f + k] = send[h.rank_plus][2 * h.off_f + k];
+      for (size_t k = 0; k < 2 * nb; k++) recv[me][2 * h.off_b + k] = send[h.rank_minus][2 * h.off_b + k];
+    }
+  for (int me = 0; me < nranks; me++) {
+    SweepArgs A;
+    A.L = links_of(me);
+    A.x = (const double2*)x[me] + (size_t)q * 3 * Vh;
+    A.r = (double2*)r[me] + (size_t)parity * 3 * Vh;
+    A.bx = (const double2*)x[me] + (size_t)parity * 3 * Vh;
+    A.a = a; A.b = b; A.sgn = sgn; A.post = post;
+    for (int d = 0; d < 4; d++) A.X[d] = X[d];
+    A.Vh = Vh; A.parity = parity; A.comm_mask = comm_mask;
+    A.partials = nullptr; A.ticket = nullptr; A.result = nullptr; A.skip = nullptr;
+    for (int idx = 0; idx < Vh; idx++) {    // interior kernel: every site, hops that stay on the rank
+      const Site s = site_from_idx(idx, parity, A.X);
+      double2 acc[3] = {{0, 0}, {0, 0}, {0, 0}};
+      stencil_local<NL, RC>(A, s, idx, acc);
+      site_epilogue<false>(A, idx, acc);
+    }
+    ExtArgs E;                              // fill_ext of dslash.cu
+    E.L = A.L; E.r = A.r; E.scale = post * sgn; E.bx = A.bx;
+    E.partials = nullptr; E.ticket = nullptr; E.result = nullptr; E.interior = nullptr; E.xr = nullptr; E.skip = nullptr;
+    for (int d = 0; d < 4; d++) { E.X[d] = X[d]; E.dep[d] = 0; E.nbv[d] = 0; }
+    E.Vh = Vh; E.parity = parity; E.ndir = ndir; E.seq = 1; E.wait = 0; E.err = nullptr; E.timeout_ns = 0;
+    for (int i = 0; i < ndir; i++) {
+      const EmuHalo& h = halo[me * 4 + i];
+      ExtDir& D = E.d[i];
+      D.mu = h.mu; D.depth = h.depth; D.faceh = h.faceh;
+      D.nb = (2 * h.depth < X[h.mu]) ? 2 * h.depth : X[h.mu];
+      D.ghost_f = (const double2*)recv[me] + h.off_f;
+      D.ghost_b0 = (const double2*)recv[me] + h.off_b;
+      D.ghost_b1 = D.ghost_b0 + (size_t)3 * h.faceh;
+      D.flag_f = D.flag_b = nullptr;
+      E.dep[h.mu] = h.depth; E.nbv[h.mu] = D.nb;
+    }
+    const int end = plan_regions(E);
+    for (int t = 0; t < end; t++) exterior_site<NL, RC, false>(E, t);
+  }
+}
+
 extern "C" {
 // fields in the DEVICE layout: links[r] = double2[nlinks][2][9][Vh], x[r] / r[r] = double2[2][3][Vh];
 // recv[r] = the receive buffer of rank r; halo[r * 4 + i], i < ndir; tiles[r] = qexb200_plan_tiles of rank r;
@@ -101,6 +182,19 @@ int emu_sweep_mr(int nranks, int nl, int rc, const int* X, int comm_mask, int pa
     sweep_all<NLV, RCV>(nranks, X, comm_mask, parity, links, RCV ? rec : nullptr, x, r, a, b, sgn, post, halo, ndir, recv, \
                         tiles, ntiles);                                                                                 \
     return 0;                                                                                                           \
+  }
+  EMU_CASE(1, 0) EMU_CASE(1, 1) EMU_CASE(1, 4)
+  EMU_CASE(2, 0) EMU_CASE(2, 2) EMU_CASE(2, 3) EMU_CASE(2, 8) EMU_CASE(2, 12) EMU_CASE(2, 9) EMU_CASE(2, 6)
+#undef EMU_CASE
+  return 1;
+}
+int emu_sweep_nccl(int nranks, int nl, int rc, const int* X, int comm_mask, int parity, const double* const* links,
+                   const EmuRecon* rec, const double* const* x, double* const* r, double a, double b, double sgn, double post,
+                   const EmuHalo* halo, int ndir, double* const* send, double* const* recv) {
+#define EMU_CASE(NLV, RCV)                                                                                                     \
+  if (nl == NLV && rc == RCV) {                                                                                                \
+    sweep_nccl<NLV, RCV>(nranks, X, comm_mask, parity, links, RCV ? rec : nullptr, x, r, a, b, sgn, post, halo, ndir, send, recv); \
+    return 0;                                                                                                                  \
   }
   EMU_CASE(1, 0) EMU_CASE(1, 1) EMU_CASE(1, 4)
   EMU_CASE(2, 0) EMU_CASE(2, 2) EMU_CASE(2, 3) EMU_CASE(2, 8) EMU_CASE(2, 12) EMU_CASE(2, 9) EMU_CASE(2, 6)

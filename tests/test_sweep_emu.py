@@ -40,6 +40,8 @@ def emu():
     lib.emu_sweep_mr.argtypes = [C.c_int, C.c_int, C.c_int, ip, C.c_int, C.c_int, dpp, C.POINTER(EmuRecon), dpp, dpp, C.c_double,
                                  C.c_double, C.c_double, C.c_double, C.POINTER(EmuHalo), C.c_int, dpp,
                                  C.POINTER(C.POINTER(C.c_uint)), C.c_int]
+    lib.emu_sweep_nccl.argtypes = [C.c_int, C.c_int, C.c_int, ip, C.c_int, C.c_int, dpp, C.POINTER(EmuRecon), dpp, dpp, C.c_double,
+                                   C.c_double, C.c_double, C.c_double, C.POINTER(EmuHalo), C.c_int, dpp, dpp]
     lib.emu_compress.argtypes = [C.c_int, ip, dp_, dp_, dp_, C.POINTER(C.c_ushort), C.c_int, C.c_int, dp_]
     lib.emu_site.argtypes = [C.c_int, C.c_int, ip, ip]
     return lib
@@ -154,7 +156,7 @@ def compress(emu, dl, X, nlinks, modes):
     return rec, keep, rcs.pop()
 
 
-def run_sweeps(emu, L, G, nlinks, lat, g, x, r0, modes=None):
+def run_sweeps(emu, L, G, nlinks, lat, g, x, r0, modes=None, transport="p2p"):
     import qex_b200 as qb
     world = int(np.prod(G))
     X = [L[d] // G[d] for d in range(4)]
@@ -186,8 +188,13 @@ def run_sweeps(emu, L, G, nlinks, lat, g, x, r0, modes=None):
         for a, b, sgn, post in ((0.0, 0.0, 1.0, 1.0), (0.7, -0.3, 1.0, 1.0), (0.0, 0.04, -1.0, 1.0)):
             dr = [vec_to_dev(r0[bk]) for bk in blocks]
             recv = [np.full(2 * cap, np.nan) for _ in range(world)]      # anything read but never packed shows as NaN
-            rc = emu.emu_sweep_mr(world, nlinks // 4, rc_bits, Xc, comm_mask, parity, arr(dl), rec, arr(dx), arr(dr), a, b, sgn,
-                                  post, halo, ndir, arr(recv), tarr, ntiles)
+            if transport == "p2p":
+                rc = emu.emu_sweep_mr(world, nlinks // 4, rc_bits, Xc, comm_mask, parity, arr(dl), rec, arr(dx), arr(dr), a, b, sgn,
+                                      post, halo, ndir, arr(recv), tarr, ntiles)
+            else:
+                send = [np.full(2 * cap, np.nan) for _ in range(world)]
+                rc = emu.emu_sweep_nccl(world, nlinks // 4, rc_bits, Xc, comm_mask, parity, arr(dl), rec, arr(dx), arr(dr), a, b,
+                                        sgn, post, halo, ndir, arr(send), arr(recv))
             assert rc == 0
             want = r0.copy()
             if sgn > 0:
@@ -233,3 +240,29 @@ def test_multi_rank_sweep_with_12_and_14_real_links(emu, L, G, nlinks, modes):
             gc[keep] = (g[..., 0] + 1j * g[..., 1])[keep]
         g = np.ascontiguousarray(np.stack([gc.real, gc.imag], axis=-1))
     run_sweeps(emu, L, G, nlinks, lat, g, x, r0, modes)
+
+
+@pytest.mark.parametrize("L,G,nlinks,modes", [
+    ((8, 8, 8, 16), (1, 1, 1, 2), 4, None),
+    ((8, 8, 12, 8), (1, 1, 2, 1), 8, None),
+    ((8, 8, 8, 8), (1, 1, 1, 2), 8, None),           # local extent 4: region width = the whole extent
+    ((8, 8, 16, 16), (1, 1, 2, 2), 8, None),         # corners belong to exactly one region
+    ((16, 8, 8, 8), (4, 1, 1, 1), 4, None),
+    ((8, 16, 16, 8), (1, 2, 2, 1), 8, None),
+    ((8, 16, 16, 16), (1, 2, 2, 2), 8, None),        # three split directions: three regions
+    ((8, 8, 16, 32), (1, 1, 2, 4), 4, None),
+    ((8, 8, 16, 16), (1, 1, 2, 2), 8, [12, 12]),
+    ((8, 8, 8, 16), (1, 1, 1, 2), 4, [14]),
+])
+def test_nccl_transport_phases_on_the_host(emu, L, G, nlinks, modes):
+    """The second transport (pack -> ncclSend/ncclRecv -> interior k_sweep -> k_exterior, the 3-phase shape of
+    stagD.nim:355-393) with its site functions on the host: pack_item into send buffers, the message pairing of
+    comm.cu halo_start as copies, stencil_local with off-rank hops skipped, exterior_site over the disjoint boundary
+    regions (plan_regions) -- against the oracle."""
+    from util import make_exact_inputs
+    lat, g, (x, r0) = (make_inputs if modes is None else make_exact_inputs)(L, nlinks)
+    if modes and 14 in modes:
+        th = np.random.default_rng(7).uniform(0, 2 * np.pi, g.shape[:2])
+        gc = (g[..., 0] + 1j * g[..., 1]) * np.exp(1j * th)[:, :, None, None]
+        g = np.ascontiguousarray(np.stack([gc.real, gc.imag], axis=-1))
+    run_sweeps(emu, L, G, nlinks, lat, g, x, r0, modes, transport="nccl")
