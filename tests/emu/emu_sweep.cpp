@@ -201,6 +201,74 @@ int emu_sweep_nccl(int nranks, int nl, int rc, const int* X, int comm_mask, int 
 #undef EMU_CASE
   return 1;
 }
+// ---- one rank at a time: for the world_size-2/4 gloo runs of tests/multi_worker.py --cpu-sweep, where every process
+// is one rank and the send/recv buffers travel through torch.distributed (18-real links) --------------------------------
+static Links plain_links(const double* links) {
+  Links L = Links();
+  L.u = (const double2*)links; L.u12[0] = L.u12[1] = nullptr; L.sgn = nullptr; L.inv[0] = L.inv[1] = 1.0;
+  return L;
+}
+// phase 1 of the NCCL transport on this rank: pack the faces of x (parity 1 - parity) into `send`
+int emu_rank_pack(int nl, const int* X, int parity, const double* links, const double* x, const EmuHalo* halo, int ndir,
+                  double* send) {
+  const int Vh = X[0] * X[1] * X[2] * X[3] / 2, q = 1 - parity;
+  PackArgs P;
+  P.L = plain_links(links);
+  P.x = (const double2*)x + (size_t)q * 3 * Vh;
+  for (int d = 0; d < 4; d++) P.X[d] = X[d];
+  P.Vh = Vh; P.q = q; P.ndir = ndir; P.seq = 1; P.ticket = nullptr;
+  int end = 0;
+  for (int i = 0; i < ndir; i++) {
+    PackDir& D = P.d[i];
+    D.mu = halo[i].mu; D.depth = halo[i].depth; D.faceh = halo[i].faceh;
+    end += (halo[i].depth + (nl == 2 ? 4 : 1)) * halo[i].faceh;
+    D.end = end;
+    D.out_f = (double2*)send + halo[i].off_f;
+    D.out_b0 = (double2*)send + halo[i].off_b;
+    D.out_b1 = D.out_b0 + (size_t)3 * halo[i].faceh;
+    D.flag_f = D.flag_b = nullptr;
+  }
+  for (int t = 0; t < end; t++) { if (nl == 2) pack_item<2, 0>(P, t); else pack_item<1, 0>(P, t); }
+  return 0;
+}
+// phases 2 + 3 on this rank: interior sweep, then the boundary terms from the received buffer `recv`
+int emu_rank_sweep(int nl, const int* X, int comm_mask, int parity, const double* links, const double* x, double* r,
+                   double a, double b, double sgn, double post, const EmuHalo* halo, int ndir, const double* recv) {
+  const int Vh = X[0] * X[1] * X[2] * X[3] / 2, q = 1 - parity;
+  SweepArgs A;
+  A.L = plain_links(links);
+  A.x = (const double2*)x + (size_t)q * 3 * Vh;
+  A.r = (double2*)r + (size_t)parity * 3 * Vh;
+  A.bx = (const double2*)x + (size_t)parity * 3 * Vh;
+  A.a = a; A.b = b; A.sgn = sgn; A.post = post;
+  for (int d = 0; d < 4; d++) A.X[d] = X[d];
+  A.Vh = Vh; A.parity = parity; A.comm_mask = comm_mask;
+  A.partials = nullptr; A.ticket = nullptr; A.result = nullptr; A.skip = nullptr;
+  for (int idx = 0; idx < Vh; idx++) {
+    const Site s = site_from_idx(idx, parity, A.X);
+    double2 acc[3] = {{0, 0}, {0, 0}, {0, 0}};
+    if (nl == 2) stencil_local<2, 0>(A, s, idx, acc); else stencil_local<1, 0>(A, s, idx, acc);
+    site_epilogue<false>(A, idx, acc);
+  }
+  ExtArgs E;
+  E.L = A.L; E.r = A.r; E.scale = post * sgn; E.bx = A.bx;
+  E.partials = nullptr; E.ticket = nullptr; E.result = nullptr; E.interior = nullptr; E.xr = nullptr; E.skip = nullptr;
+  for (int d = 0; d < 4; d++) { E.X[d] = X[d]; E.dep[d] = 0; E.nbv[d] = 0; }
+  E.Vh = Vh; E.parity = parity; E.ndir = ndir; E.seq = 1; E.wait = 0; E.err = nullptr; E.timeout_ns = 0;
+  for (int i = 0; i < ndir; i++) {
+    ExtDir& D = E.d[i];
+    D.mu = halo[i].mu; D.depth = halo[i].depth; D.faceh = halo[i].faceh;
+    D.nb = (2 * halo[i].depth < X[halo[i].mu]) ? 2 * halo[i].depth : X[halo[i].mu];
+    D.ghost_f = (const double2*)recv + halo[i].off_f;
+    D.ghost_b0 = (const double2*)recv + halo[i].off_b;
+    D.ghost_b1 = D.ghost_b0 + (size_t)3 * halo[i].faceh;
+    D.flag_f = D.flag_b = nullptr;
+    E.dep[halo[i].mu] = halo[i].depth; E.nbv[halo[i].mu] = D.nb;
+  }
+  const int end = plan_regions(E);
+  for (int t = 0; t < end; t++) { if (nl == 2) exterior_site<2, 0, false>(E, t); else exterior_site<1, 0, false>(E, t); }
+  return 0;
+}
 // compress_links of layout.cu on the host: k_compress + k_sign_bwd site by site.  stats[6] = max deviation per class,
 // min |s|^2, max |s|^2 (what the host decides on); u12_j sized [4][2][6 or 7][Vh] double2, sgn [2][Vh].
 int emu_compress(int nl, const int* X, const double* links, double* u12_0, double* u12_1, unsigned short* sgn,

@@ -87,6 +87,61 @@ def cpu_plan_check(L, G, nlinks, rank, world, dist):
     return True
 
 
+def cpu_sweep_check(L, G, nlinks, rank, world, dist):
+    """One PROCESS per rank on the CPU (gloo): the site functions the CUDA kernels wrap (csrc/sweep_site.cuh, compiled
+    with g++ into tests/emu/_emu_sweep.so) pack this rank's faces, the send buffers travel through torch.distributed
+    with the library's own halo plan (same pairing and order as csrc/comm.cu halo_start), then the interior sweep and the
+    boundary terms run on the received data -- and every rank compares its block with the oracle's global stagD2."""
+    import ctypes as C
+    import torch
+    import oracle
+    import qex_b200 as qb
+    from util import make_inputs, rel_l2
+    from test_sweep_emu import EmuHalo, SO, block_index, links_to_dev, vec_to_dev, vec_from_dev
+    lib = C.CDLL(SO)     # built by the launching test (tests/test_dist_cpu.py) before the ranks start
+    dp_, ip = C.POINTER(C.c_double), C.POINTER(C.c_int)
+    lib.emu_rank_pack.argtypes = [C.c_int, ip, C.c_int, dp_, dp_, C.POINTER(EmuHalo), C.c_int, dp_]
+    lib.emu_rank_sweep.argtypes = [C.c_int, ip, C.c_int, C.c_int, dp_, dp_, dp_, C.c_double, C.c_double, C.c_double, C.c_double,
+                                   C.POINTER(EmuHalo), C.c_int, dp_]
+    lat, g, (x, r0) = make_inputs(L, nlinks)
+    X = [L[d] // G[d] for d in range(4)]
+    Vh = int(np.prod(X)) // 2
+    bk = block_index(L, G, rank)
+    plan, total = qb.plan_halo(L, G, rank, nlinks)
+    halo = (EmuHalo * 4)()
+    for i, h in enumerate(plan):
+        halo[i] = EmuHalo(h["mu"], h["depth"], h["faceh"], h["rank_plus"], h["rank_minus"], h["off_f"], h["off_b"])
+    comm_mask = sum(1 << d for d in range(4) if G[d] > 1)
+    dl, dx = links_to_dev(g[:, bk]), vec_to_dev(x[bk])
+    dp = lambda a: a.ctypes.data_as(dp_)
+    Xc = (C.c_int * 4)(*X)
+    worst = 0.0
+    for parity in (0, 1):
+        for a, b in ((0.0, 0.0), (0.7, -0.3)):
+            send = torch.full((2 * total,), float("nan"), dtype=torch.float64)
+            recv = torch.full((2 * total,), float("nan"), dtype=torch.float64)
+            assert lib.emu_rank_pack(nlinks // 4, Xc, parity, dp(dl), dp(dx), halo, len(plan), dp(send.numpy())) == 0
+            ops = []
+            for h in plan:      # csrc/comm.cu halo_start: psi faces to the - neighbour, products to the + neighbour
+                f0, f1, b0, b1 = 2 * h["off_f"], 2 * (h["off_f"] + h["n_f"]), 2 * h["off_b"], 2 * (h["off_b"] + h["n_b"])
+                ops += [dist.P2POp(dist.isend, send[f0:f1], h["rank_minus"]), dist.P2POp(dist.isend, send[b0:b1], h["rank_plus"]),
+                        dist.P2POp(dist.irecv, recv[f0:f1], h["rank_plus"]), dist.P2POp(dist.irecv, recv[b0:b1], h["rank_minus"])]
+            for w in dist.batch_isend_irecv(ops):
+                w.wait()
+            dr = vec_to_dev(r0[bk])
+            assert lib.emu_rank_sweep(nlinks // 4, Xc, comm_mask, parity, dp(dl), dp(dx), dp(dr), a, b, 1.0, 1.0, halo, len(plan),
+                                      dp(recv.numpy())) == 0
+            want = r0.copy()
+            lat.stagD2(g, want, x, a, b, parity)
+            got, w = vec_from_dev(dr), want[bk]
+            sl = slice(0, Vh) if parity == 0 else slice(Vh, 2 * Vh)
+            assert np.isfinite(got).all()
+            e = rel_l2(got[sl], w[sl])
+            assert e <= 1e-13, (rank, parity, a, b, e)
+            worst = max(worst, e)
+    return worst
+
+
 def gpu_case(L, G, nlinks, inner, rank, world, local_rank, dist, transport="nccl", recon=18):
     import torch
     import oracle
@@ -319,6 +374,7 @@ def links_case(L, G, inner, rank, world, local_rank, dist):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--cpu", action="store_true")
+    ap.add_argument("--cpu-sweep", action="store_true", help="with --cpu: also run the emulated multi-rank sweep over gloo")
     ap.add_argument("--lat", default="8,8,8,16")
     ap.add_argument("--rankgeom", default="1,1,1,2")
     ap.add_argument("--inner", default="1,1,1,1")
@@ -338,6 +394,8 @@ def main():
         dist.init_process_group("gloo")
         ok = cpu_plan_check(L, G, a.nlinks, rank, world, dist)
         out = {"ok": ok}
+        if a.cpu_sweep:
+            out["sweep_rel_l2"] = cpu_sweep_check(L, G, a.nlinks, rank, world, dist)
     else:
         import torch
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))

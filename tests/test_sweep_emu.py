@@ -27,14 +27,19 @@ class EmuRecon(C.Structure):
     _fields_ = [("u12", C.POINTER(C.c_double) * 2), ("sgn", C.POINTER(C.c_ushort)), ("inv", C.c_double * 2)]
 
 
-@pytest.fixture(scope="module")
-def emu():
+def build_emu():
+    """g++ of the harness + the library's host-device header (rebuilt when either changed); returns the .so path."""
     src = os.path.join(HERE, "emu", "emu_sweep.cpp")
     hdrs = [os.path.join(HERE, "..", "qex_b200", "csrc", h) for h in ("sweep_site.cuh", "linkops.cuh")]
     if not os.path.exists(SO) or os.path.getmtime(SO) < max(os.path.getmtime(p) for p in [src] + hdrs):
         subprocess.check_call(["/usr/bin/g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-x", "c++", "-w",
                                "-I/usr/local/cuda/include", src, "-o", SO])
-    lib = C.CDLL(SO)
+    return SO
+
+
+@pytest.fixture(scope="module")
+def emu():
+    lib = C.CDLL(build_emu())
     dpp, ip = C.POINTER(C.POINTER(C.c_double)), C.POINTER(C.c_int)
     dp_ = C.POINTER(C.c_double)
     lib.emu_sweep_mr.argtypes = [C.c_int, C.c_int, C.c_int, ip, C.c_int, C.c_int, dpp, C.POINTER(EmuRecon), dpp, dpp, C.c_double,
