@@ -55,3 +55,34 @@ def test_product_never_imports_oracle():
                     if re.search(r"import oracle|from oracle|oracle/|qex_oracle", txt):
                         bad.append(f)
     assert not bad, bad
+
+
+def test_header_is_plain_c_and_links(tmp_path):
+    """The boundary is a C ABI: include/qex_b200.h must compile as C99 (what Nim's importc / cgo / ctypes-style
+    bindings go through), and a C caller must link against libqex_b200.so and reach the entry points -- here the
+    ones that need no GPU: on a host without a device they must fail loudly, with a message, not crash."""
+    import subprocess
+    inc, libdir = os.path.join(ROOT, "include"), os.path.join(ROOT, "qex_b200")
+    src = tmp_path / "caller.c"
+    calls = "\n".join("  (void)(%s);" % s for s in declared_symbols())       # every declared symbol must resolve at link time
+    src.write_text('#include <stdio.h>\n#include <string.h>\n#include "qex_b200.h"\nint main(void) {\n' + calls + '''
+  qexb200_solver_params sp;
+  memset(&sp, 0, sizeof sp);
+  sp.r2req = 1e-8; sp.maxits = 10;
+  int lat[4] = {8, 8, 8, 8}, rg[4] = {1, 1, 1, 1};
+  qexb200_halo_dir dirs[4];
+  int nd = -1; long long tot = -1;
+  int rg2[4] = {1, 1, 1, 2};
+  if (qexb200_plan_halo(lat, rg2, 0, 8, dirs, &nd, &tot) != 0 || nd != 1 || dirs[0].mu != 3 || dirs[0].depth != 3) return 2;
+  int rc = qexb200_init(lat, rg, 0, 0, NULL);
+  printf("init rc=%d initialized=%d msg=%s\\n", rc, qexb200_is_initialized(), qexb200_last_error());
+  if (rc == 0) { qexb200_finalize(); return 0; }
+  return (qexb200_is_initialized() == 0 && strlen(qexb200_last_error()) > 0) ? 0 : 3;
+}
+''')
+    exe = tmp_path / "caller"
+    subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-I", inc, str(src), "-o", str(exe),
+                           "-L", libdir, "-lqex_b200", "-Wl,-rpath," + libdir])
+    r = subprocess.run([str(exe)], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "init rc=" in r.stdout
