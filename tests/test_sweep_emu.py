@@ -271,3 +271,26 @@ def test_nccl_transport_phases_on_the_host(emu, L, G, nlinks, modes):
         gc = (g[..., 0] + 1j * g[..., 1]) * np.exp(1j * th)[:, :, None, None]
         g = np.ascontiguousarray(np.stack([gc.real, gc.imag], axis=-1))
     run_sweeps(emu, L, G, nlinks, lat, g, x, r0, modes, transport="nccl")
+
+
+def _random_geometries(n, seed=20261105):
+    import random
+    rnd = random.Random(seed)
+    grids = [(1, 1, 1, 2), (1, 1, 2, 1), (1, 2, 1, 1), (2, 1, 1, 1), (1, 1, 2, 2), (2, 2, 1, 1), (1, 2, 1, 2), (2, 1, 2, 1),
+             (1, 1, 1, 4), (4, 1, 1, 1), (1, 4, 1, 1), (1, 1, 2, 4), (1, 2, 2, 2), (2, 2, 2, 1), (2, 1, 1, 4), (1, 1, 4, 2)]
+    out = []
+    while len(out) < n:
+        G, nlinks = rnd.choice(grids), rnd.choice([4, 8])
+        X = [rnd.choice([e for e in (2, 4, 6, 8) if e >= (4 if nlinks == 8 else 2)]) for _ in range(4)]
+        vol = int(np.prod(X)) * int(np.prod(G))
+        if 64 <= vol <= 20000:
+            out.append((tuple(X[d] * G[d] for d in range(4)), G, nlinks, rnd.choice(["p2p", "nccl"])))
+    return out
+
+
+@pytest.mark.parametrize("L,G,nlinks,transport", _random_geometries(14))
+def test_random_geometries(emu, L, G, nlinks, transport):
+    """Seeded random lattices, rank grids (up to 4 ranks in one direction, 8 in all), link sets and transports: local
+    extents down to 2 (naive) / 4 (fat+Naik, the library's own limit), every direction split in some case."""
+    lat, g, (x, r0) = make_inputs(L, nlinks)
+    run_sweeps(emu, L, G, nlinks, lat, g, x, r0, None, transport)
