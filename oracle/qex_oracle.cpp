@@ -6,13 +6,18 @@
 // only as the checker or the timed CPU baseline.  The product
 // (qex_b200/csrc) never links, imports or calls anything in oracle/.
 //
-// Parity pin: the input generator (RngMilc6 seeding + Box-Muller gaussian +
-// projectSU + plaq) is pinned against the reference's own known-answer test
-// tests/reprod/trandgauge.nim:14-17 (six plaquettes of g.random on 8^4, default
-// seed 17^7) -- see tests/test_oracle_golden.py.  The reference publishes no
-// golden Dslash vector or stand-alone CG iteration count, so the
-// operator/solver restatement is additionally pinned by analytic identities
-// (free-field eigenvalues, anti-Hermiticity, D^+D block identity, solve(Dx)=x).
+// Parity pins (numbers the reference itself holds):
+//  (1) inputs -- RngMilc6 seeding + Box-Muller gaussian + projectSU + plaq against the known-answer test
+//      tests/reprod/trandgauge.nim:14-17 (six plaquettes of g.random on 8^4, default seed 17^7);
+//  (2) operator and solver -- the first "Begin H" line of the golden logs tests/extra/staghmc_sh/ref.{0,1,2}
+//      (Sf per pseudofermion and T, the reference's own bar rel 2e-11, tests/extra/staghmc_sh/run:43), which is
+//      computed before any MD step from randomTAH, setBC/stagPhase, D with negative masses, `solve` at
+//      r2req = 1e-24 with its even-odd reconstruction and norm2: reproduced to a few ulp, iteration counts held
+//      to the Solver[action] statistics of the same logs -- tests/test_oracle_golden.py
+//      (test_trandgauge_golden_plaquettes, test_staghmc_sh_begin_H_golden, test_staghmc_sh_pin_discriminates).
+// The reference publishes no golden Dslash vector on a random gauge; there the restatement is
+// additionally held by analytic identities (free-field eigenvalues, anti-Hermiticity, D^+D block identity,
+// solve(Dx)=x).  "End H" of the golden logs needs the MD integrator of an external package and is not reproduced.
 // The reference itself (Nim + MPI + QMP) cannot be built in this image.
 //
 // Field memory layout used by the oracle == QEX's own layout for a single rank
