@@ -1,20 +1,25 @@
 #!/usr/bin/env python
 """Benchmark of the staggered Dslash + CG hot path (BASELINE.json metric), one process per GPU.
 
-  python bench.py [--gpus N --steps K --warmup W] [--impl reference]
+  python bench.py [--gpus N --steps K --warmup W] [--impl reference] [--config c2|c3|c4|c5] [--overlap off] [--transport nccl]
 
-Workload (BASELINE.json configs[1]): 32^4 naive staggered, random SU(3) links with antiperiodic-T
-BC + staggered phases, m = 0.1, even-even CG to r2req = 1e-8, fp64; weak scaling keeps 32^4 per GPU
-(32^4, 32^3x64, 32^2x64^2, 32x64^3 for 1/2/4/8 GPUs).
+Default workload c2 = BASELINE.json configs[1]: 32^4 naive staggered per GPU (weak series 32^4, 32^3x64 on 1.1.1.2,
+32^2x64^2 on 1.1.2.2, 32^2x64x128 on 1.1.2.4; --alt8: 32x64^3 on 1.2.2.2), inputs by the reference's own recipe
+generated on the device (per-site RngMilc6 seed 987654321, g.random = gaussian + projectSU, setBC + stagPhase, gaussian
+source), m = 0.1, even-even CG to r2req = 1e-8, fp64.  c3 / c5 = 48^3x96 / 64^3x128 fat+Naik (strong scaling),
+c4 = the solve sequence of one staghmc_spv trajectory at 64^4 on nHYP links.
 
 A "step" is one solveEE call (stagSolve.nim:57-138) = one CG solve on a device-resident source.
-value  = QEX's solver Gflop/s, (g.len*4*72+60)*nEven*iterations / seconds (stagSolve.nim:92), whole job.
-e2e    = the same through qexb200_solveXX with HOST (pinned) buffers: H2D of the source and D2H of
-         the solution inside the timed region.
-roofline = the dominant kernel (one parity sweep of the Dslash) timed live with CUDA events on the
-         library's stream over back-to-back launches, against the measured HBM peak.
-The reference arm (--impl reference) times the CPU oracle (the reference itself cannot be built in
-this image: no Nim/MPI/QMP) on all host cores, on a bounded sample of the same solve.
+value  = QEX's solver Gflop/s, (g.len*4*72+60)*nEven*iterations / seconds (stagSolve.nim:92), whole job, with the link
+         storage the library selects for these links (18-real); `variants` = after reunit with 12-real storage, fat+Naik.
+e2e    = the same through qexb200_solveXX with HOST (pinned) buffers: H2D of the source and D2H of the solution inside the
+         timed region (gauge handle resident); e2e_cold adds create + upload + re-layout of the links per step.
+roofline = the dominant kernel (one parity sweep of the Dslash) timed live with CUDA events on the library's stream over
+         back-to-back launches, against the measured HBM peak; roofline_target = the north_star config (fat+Naik 18/18).
+parity = preflight before anything is timed: a small lattice on the same rank grid against the oracle (checker only);
+true_residual = |b - A x|^2 / |b|^2 of the timed solve from two public stagD2 calls.
+The reference arm (--impl reference) times the CPU oracle (the reference itself cannot be built in this image: no
+Nim/MPI/QMP) with all host threads on the same global lattice and inputs the GPU arm uses at that N.
 """
 import argparse
 import json
@@ -33,8 +38,6 @@ MASS = 0.1
 R2REQ = 1e-8
 BYTES_PER_SITE = {4: 1248, 8: 2400}     # compulsory bytes per output site of one parity sweep
 FLOPS_PER_SITE = {4: 570, 8: 1146}      # algorithmic flops per output site of one sweep
-WEAK = {1: ((32, 32, 32, 32), (1, 1, 1, 1)), 2: ((32, 32, 32, 64), (1, 1, 1, 2)),
-        4: ((32, 32, 64, 64), (1, 1, 2, 2)), 8: ((32, 64, 64, 64), (1, 2, 2, 2))}
 
 
 def measured_peak():
