@@ -264,6 +264,38 @@ int qexb200_field_redot(qexb200_field_t f, qexb200_field_t g, int subset, double
  * templates (src/field/fieldET.nim:547-599) for callers that keep their vectors on the GPU. */
 int qexb200_field_axpby(qexb200_field_t y, double a, qexb200_field_t x, double b, int subset);
 
+/* |x|^2 of a device array the CALLER owns, computed without allocating anything: no cudaMalloc / cudaFree, no
+ * library context (qexb200_init is not needed), no torch.  It has no counterpart in the reference; it is the norm2
+ * kernel above (qexb200_field_norm2) with its reduction scratch -- per-block partial sums and a completion counter --
+ * moved from the context's cudaMalloc'd buffers into a static device array inside the library: 128.25 KB that every
+ * GPU on which the library is loaded holds until the process exits.
+ *
+ * It is meant for callers that cannot allocate device memory when they need the number: runs sized to fill the GPU
+ * (resident link sets of the largest lattices, or a device whose free memory belongs to another backend's pool or
+ * another process), where a late cudaMalloc fails mid-trajectory; sections in which the allocator's implicit
+ * device-wide synchronisation would stall kernels in flight on other streams; and monitoring code that only holds
+ * raw device pointers from its own allocator and never creates a qexb200 context.
+ *
+ *   d_x     device pointer, 16-byte aligned, nreals doubles (a colour-vector field or any part of one)
+ *   nreals  0 .. QEXB200_NOALLOC_MAX_REALS (1 GiB of doubles: one full-lattice vector at 64^4, one parity at
+ *           64^3 x 128).  More is refused with an error -- split the array and add the pieces.
+ *   d_out   device pointer to ONE double, written by the kernel
+ *   stream  the caller's cudaStream_t (NULL = the default stream).  The call only enqueues (a 256-byte memset of the
+ *           scratch's counter, then the kernel); *d_out is valid once the stream has reached that point.
+ *
+ * The sum is formed in a fixed order that depends on nreals alone (fixed 8192-real tiles, partials added in index
+ * order), so it is reproducible bit for bit from call to call and from GPU to GPU; it differs from
+ * qexb200_field_norm2 only by the rounding of a different summation order.
+ *
+ * Set-up: the FIRST call on each device resolves the device address of the static array (cudaGetSymbolAddress, with
+ * that device current) and remembers it; make that first call on every device before starting any stream capture.
+ * The device that is current at the call must be the one d_x, d_out and stream belong to.
+ * Sharing: all calls on one GPU use the same scratch.  Calls ordered on one stream are safe; two calls that can
+ * overlap on the GPU (different streams, or different host threads, of one process without ordering between them)
+ * race on it and return garbage -- serialise them. */
+#define QEXB200_NOALLOC_MAX_REALS 134217728LL
+int qexb200_norm2_noalloc(const double* d_x, long long nreals, double* d_out, void* stream);
+
 int qexb200_dev_stagD2(qexb200_gauge_t g, int parity, qexb200_field_t r, qexb200_field_t x,
                        double a, double b);
 int qexb200_dev_stagD(qexb200_gauge_t g, int parity, qexb200_field_t r, qexb200_field_t x,

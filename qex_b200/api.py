@@ -195,6 +195,7 @@ def lib():
         L.qexb200_debug_role_times.argtypes = [C.c_int, C.POINTER(C.c_ulonglong), C.c_int]
         L.qexb200_plan_halo.argtypes = [ip, ip, C.c_int, C.c_int, C.POINTER(HaloDir), ip, C.POINTER(C.c_longlong)]
         L.qexb200_timer_stop.argtypes = [C.POINTER(C.c_float)]
+        L.qexb200_norm2_noalloc.argtypes = [C.c_void_p, C.c_longlong, C.c_void_p, C.c_void_p]
         L.qexb200_launch_count.restype = C.c_longlong
         L.qexb200_launch_count.argtypes = [C.c_int]
         _lib = L
