@@ -65,9 +65,13 @@ struct SweepArgs {
   double* partials;
   unsigned int* ticket;
   double* result;
-  // != nullptr: the whole launch is a no-op once *skip != 0 -- the CG's "done" scalar: the host runs a few
-  // iterations ahead of the device, and the sweeps it queued past convergence must cost nothing (all ranks hold the
-  // same value, so on a split lattice every rank skips the same launches)
+  // != nullptr: the kernel returns at once when *skip != 0 -- the CG's "done" scalar: the host runs a few
+  // iterations ahead of the device, and the sweeps it queued past convergence then cost a launch and nothing else
+  // on one GPU and on the peer-memory transport (all ranks hold the same value, so every rank skips the same
+  // launches).  NOT on the NCCL transport: halo_start has no skip argument, so each of the up to 2 * LAG queued
+  // sweeps still runs k_pack and its ncclSend/ncclRecv group before k_sweep / k_exterior return early -- results
+  // are unaffected (every rank queues the same exchanges), but an NCCL-transport solve carries those few extra
+  // exchanges.
   const double* skip;
 };
 
