@@ -109,9 +109,19 @@ int qexb200_gauge_destroy(qexb200_gauge_t g);
  * destroyed.  `version` is the caller's update counter of these links -- QEX rewrites fermion links only through
  * smear -> setBC -> stagPhase (src/stagg_pv_hmc/staghmc_spv.nim:367-386, src/physics/stagD.nim:72-80), the glue bumps
  * its counter there.  What qudaSolveXX re-does on every call (src/quda/qudaWrapperImpl.nim:198-261) is paid once per
- * link update.  Handles obtained here are owned by the cache: do not pass them to qexb200_gauge_destroy. */
+ * link update.  Handles obtained here are owned by the cache: do not pass them to qexb200_gauge_destroy.
+ * Guard against a forgotten bump: on every call the library also fingerprints a strided sample of the host links
+ * (1024 doubles per field, a few KB) and uploads again when it differs from the one taken at upload time, even if
+ * the version is unchanged -- this catches whole-field rewrites (smear, rephase, a new configuration, a freed set
+ * whose addresses were reused), not a change confined to sites between the samples, so the counter remains the
+ * contract.  When link arrays are freed, call qexb200_gauge_invalidate with their pointers (or use a version that
+ * is never repeated across distinct link objects). */
 int qexb200_gauge_cached(const double* const* links, int nlinks, unsigned long long version,
                          qexb200_gauge_t* g, int* cached);
+/* Drops the cached device copy keyed on these host pointers, if any (no error when there is none).  For the glue's
+ * finaliser of a Staggered object: qudaSolveXX needs nothing like it because it uploads on every call
+ * (src/quda/qudaWrapperImpl.nim:198-261). */
+int qexb200_gauge_invalidate(const double* const* links, int nlinks);
 /* Link storage the sweeps read.  want = 18: all 18 reals of every link (default).  want = 12: each
  * link class (one-hop, three-hop) whose matrices are s*SU(3) with a single |s| -- naive links with
  * staggered phases and BC (+-SU(3)), Naik links -- is additionally held as rows 0,1 and the third

@@ -12,7 +12,7 @@ library is missing or no CUDA device is present.
 """
 from .api import (  # noqa: F401
     QexB200Error, SolverParams, Staggered, CgState, DeviceField, DeviceGauge, RngField, newRNGField, Fat7lCoefs, HisqCoefs, HypCoefs, makeImpLinks, fat7lDeriv, getFileLattice, stagDeriv, stagD2deriv, init, finalize, is_initialized,
-    newStag, newStag3, cachedStag, stagD2, stagD, stagD2ee, stagD2oo, stagDb, stagD1, stagD1x, set_host_layout, local_sites,
+    newStag, newStag3, cachedStag, invalidateStag, stagD2, stagD, stagD2ee, stagD2oo, stagDb, stagD1, stagD1x, set_host_layout, local_sites,
     nccl_unique_id, plan_halo, plan_peers, plan_tiles, role_times, p2p_export, p2p_attach, p2p_active, p2p_attach_torch, sync, timer_start, timer_stop, launch_count, lib, lib_path,
     EVEN, ODD, ALL,
 )

@@ -184,6 +184,7 @@ def lib():
         L.qexb200_dev_solve.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, spp]
         L.qexb200_plan_peers.argtypes = [ip, ip, C.c_int, C.POINTER(C.c_ubyte)]
         L.qexb200_gauge_cached.argtypes = [C.POINTER(C.POINTER(C.c_double)), C.c_int, C.c_ulonglong, ip, ip]
+        L.qexb200_gauge_invalidate.argtypes = [C.POINTER(C.POINTER(C.c_double)), C.c_int]
         L.qexb200_field_axpby.argtypes = [C.c_int, C.c_double, C.c_int, C.c_double, C.c_int]
         L.qexb200_solveEO.argtypes = [C.c_int, dp, dp, C.c_double, spp]
         L.qexb200_dev_solveEO.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, spp]
@@ -712,6 +713,13 @@ def cachedStag(links, version):
     g = DeviceGauge.__new__(DeviceGauge)
     g.nlinks, g.h, g._owner = n, h.value, False
     return Staggered(g), bool(hit.value)
+
+
+def invalidateStag(links):
+    """qexb200_gauge_invalidate: forget the device copy cached against these host link arrays (call before freeing them)."""
+    n = len(links)
+    arr = (C.POINTER(C.c_double) * n)(*[_dp(l) for l in links])
+    _ck(lib().qexb200_gauge_invalidate(arr, n))
 
 
 def newStag(g):

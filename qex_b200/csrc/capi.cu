@@ -62,7 +62,8 @@ struct CgObj { CgKeep k; int gauge, parity, x, b; };   // a CgState bound to its
 static std::map<int, CgObj> g_cgs;
 static int g_next_handle = 1;
 // device copies cached against the caller's host link pointers (qexb200_gauge_cached)
-struct CacheEntry { std::vector<const double*> ptrs; unsigned long long version; int handle; unsigned long long used; };
+struct CacheEntry { std::vector<const double*> ptrs; unsigned long long version; int handle; unsigned long long used;
+                    unsigned long long print; };   // print: fingerprint of a strided sample of the host links at upload
 static std::vector<CacheEntry> g_cache;
 static unsigned long long g_cache_clock = 0;
 constexpr size_t CACHE_MAX = 8;
@@ -572,20 +573,43 @@ static void cache_forget(int h) {
   for (size_t i = 0; i < g_cache.size(); i++)
     if (g_cache[i].handle == h) { g_cache.erase(g_cache.begin() + (long)i); return; }
 }
+// FNV-1a over CACHE_SAMPLES evenly spaced doubles (plus the last one) of every host link field: a few KB read per
+// call.  It catches what a version counter alone cannot -- links rewritten in place without a bump, or a freed set
+// whose addresses were handed to a new one -- whenever the rewrite touches the whole field (smearing, rephasing, a new
+// configuration all do).  A rewrite confined to sites between the samples is NOT seen: the counter stays the contract.
+constexpr size_t CACHE_SAMPLES = 1024;
+static unsigned long long links_fingerprint(const double* const* links, int nlinks) {
+  const size_t n = (size_t)18 * (size_t)g_ctx.g.V;
+  const size_t step = n > CACHE_SAMPLES ? n / CACHE_SAMPLES : 1;
+  unsigned long long h = 1469598103934665603ull;
+  auto mix = [&h](double v) {
+    unsigned long long b;
+    memcpy(&b, &v, sizeof b);
+    for (int i = 0; i < 8; i++) { h ^= (b >> (8 * i)) & 0xffull; h *= 1099511628211ull; }
+  };
+  for (int k = 0; k < nlinks; k++) {
+    if (!links[k]) continue;                     // upload_links reports the NULL
+    for (size_t i = 0; i < n; i += step) mix(links[k][i]);
+    mix(links[k][n - 1]);
+  }
+  return h;
+}
 int qexb200_gauge_cached(const double* const* links, int nlinks, unsigned long long version,
                          qexb200_gauge_t* out, int* cached) {
   QB_CHECK(need_ctx());
   if (!links || !out) return fail("gauge_cached: null argument");
   if (nlinks != 4 && nlinks != 8) return fail("gauge_cached: nlinks must be 4 or 8, got %d", nlinks);
   std::vector<const double*> key(links, links + nlinks);
+  const unsigned long long print = links_fingerprint(links, nlinks);
   for (CacheEntry& e : g_cache) {
     if (e.ptrs != key) continue;
     e.used = ++g_cache_clock;
     *out = e.handle;
-    if (e.version == version) { if (cached) *cached = 1; return 0; }
+    if (e.version == version && e.print == print) { if (cached) *cached = 1; return 0; }
     Gauge* g; QB_CHECK(get_gauge(e.handle, &g));
     QB_CHECK(upload_links(*g, links));          // same storage, new content (sticky recon request re-applied)
     e.version = version;
+    e.print = print;
     if (cached) *cached = 0;
     return 0;
   }
@@ -599,10 +623,23 @@ int qexb200_gauge_cached(const double* const* links, int nlinks, unsigned long l
   int h = 0;
   QB_CHECK(qexb200_gauge_create(nlinks, &h));
   if (qexb200_gauge_load(h, links) != 0) { const std::string keep = g_err; qexb200_gauge_destroy(h); g_err = keep; return 1; }
-  g_cache.push_back(CacheEntry{key, version, h, ++g_cache_clock});
+  g_cache.push_back(CacheEntry{key, version, h, ++g_cache_clock, print});
   *out = h;
   if (cached) *cached = 0;
   return 0;
+}
+
+int qexb200_gauge_invalidate(const double* const* links, int nlinks) {
+  QB_CHECK(need_ctx());
+  if (!links) return fail("gauge_invalidate: null argument");
+  if (nlinks != 4 && nlinks != 8) return fail("gauge_invalidate: nlinks must be 4 or 8, got %d", nlinks);
+  const std::vector<const double*> key(links, links + nlinks);
+  for (size_t i = 0; i < g_cache.size(); i++) {
+    if (g_cache[i].ptrs != key) continue;
+    const int victim = g_cache[i].handle;
+    return qexb200_gauge_destroy(victim);       // also drops the cache entry (cache_forget)
+  }
+  return 0;                                      // nothing cached for these pointers: not an error
 }
 
 int qexb200_gauge_destroy(qexb200_gauge_t h) {

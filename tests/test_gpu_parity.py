@@ -617,12 +617,18 @@ def test_gauge_handle_cache_of_the_glue(orc, ctx_factory):
         l *= -1.0
     s3, hit = qb.cachedStag(links, 1)
     s3.D(got, x, 0.1)
-    assert hit and rel_l2(got, want) <= DSLASH_TOL                    # ... same counter: the stale copy is used (by contract)
+    lat.D(-g, want, x, 0.1)
+    # ... same counter: the sampled fingerprint of the host links sees a whole-field rewrite and uploads again
+    # (qudaSolveXX uploads every call, qudaWrapperImpl.nim:198-261: a forgotten bump must not solve on stale links)
+    assert not hit and s3.h == s1.h and rel_l2(got, want) <= DSLASH_TOL
     s4, hit = qb.cachedStag(links, 2)                                 # ... bumped counter: uploaded again, same handle
     assert not hit and s4.h == s1.h
-    lat.D(-g, want, x, 0.1)
     s4.D(got, x, 0.1)
     assert rel_l2(got, want) <= DSLASH_TOL
+    links[0][5, 1, 1, 0] += 1.0                                       # a change between the samples is NOT seen: the
+    _, hit = qb.cachedStag(links, 2)                                  # counter stays the contract (documented limit)
+    assert hit
+    links[0][5, 1, 1, 0] -= 1.0
     others = [[g[k].copy() for k in range(4)] for _ in range(8)]
     hs = [qb.cachedStag(o, 1)[0].h for o in others]
     assert len(set(hs)) == 8 and s1.h not in hs
@@ -630,3 +636,7 @@ def test_gauge_handle_cache_of_the_glue(orc, ctx_factory):
     assert not hit
     _, hit = qb.cachedStag(others[-1], 1)
     assert hit
+    qb.invalidateStag(others[-1])                                     # the glue's finaliser: entry and handle are gone
+    _, hit = qb.cachedStag(others[-1], 1)
+    assert not hit
+    qb.invalidateStag([g[k].copy() for k in range(4)])                # unknown pointers: not an error
