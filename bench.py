@@ -221,7 +221,10 @@ def run_reference(args):
             "solve": {"cg_iterations": res["iterations"] // nsteps, "time_to_solution_ms": res["ms_per_solve"], "solves_timed": nsteps},
             "cpu_baseline": res,
             "e2e": {"value": v, "unit": "GFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "gpu_launches": 0}
+            "gpu_launches": 0,
+            # what was actually timed: on the large lattices `steps` is the requested label, the
+            # sample is `solves_timed` solves each capped at `capped_at` iterations (GFLOP/s per iteration compares)
+            "solves_timed": nsteps, "capped_at": (cap if cap < 20000 else None)}
     print(json.dumps(line))
 
 
@@ -349,7 +352,11 @@ def run_ours(args):
         if world > 1:
             dist.destroy_process_group()
         if rank == 0:
-            print(json.dumps(line))
+            print(json.dumps(line), flush=True)
+        bad = verdict_of_checks(parity, [], args.no_parity)
+        if bad:
+            sys.stderr.write("bench.py: FAILED checks: %s\n" % "; ".join(bad))
+            sys.exit(3)
         return
 
     # ---- inputs by the reference's recipe, generated on the device: per-site RngMilc6 seeded with the
@@ -549,6 +556,18 @@ def run_ours(args):
             "cg_gflops": rr["gflops"], "time_to_solution_ms": rr["ms_per_step"], "cg_iterations": rr["iterations"],
             "true_residual": rr["true_r2"], "e2e_gflops": rr["e2e_gflops"], "roofline": roof(rr, nlinks)}
     line["variants"] = variants
+    # the driver keeps `roofline` whole: the parity summary, the north_star target sweep and the
+    # fat+Naik solve of this lattice ride inside it
+    line["roofline"]["parity"] = parity_summary(parity)
+    line["roofline"]["true_residual"] = r["true_r2"]
+    if "roofline_target" in line:
+        t = line["roofline_target"]
+        line["roofline"]["target"] = {"kernel": t["kernel"], "ms_per_launch": t["ms_per_launch"], "frac": t["frac"],
+                                      "achieved": t["achieved"], "traffic": t["traffic"], "target_frac": 0.70}
+    if (8, "links18_18") in results and not big:
+        hr = results[(8, "links18_18")]
+        line["roofline"]["hisq_weak"] = {"solve_ms": hr["ms_per_step"], "iterations": hr["iterations"],
+                                         "true_residual": hr["true_r2"], "cg_iteration_frac": hr["cg_iter_gbs"] / peak}
     if cfg == "c2" and not args.no_links and (world == 1 or args.transport == "p2p"):
         # on several GPUs: link-shaped fields in the peer-mapped arena, neighbours read over NVLink (csrc/smear.cu)
         try:
@@ -574,7 +593,38 @@ def run_ours(args):
     if world > 1:
         dist.destroy_process_group()
     if rank == 0:
-        print(json.dumps(line))
+        print(json.dumps(line), flush=True)
+    # a line whose preflight parity or true residual failed is printed (for the record) and the run FAILS: rc 0 at
+    # every N then means Dslash <= 1e-13 and CG iterations within +-1 of the oracle on that rank grid
+    bad = verdict_of_checks(parity, [rr["true_r2"] for rr in results.values()], args.no_parity)
+    if bad:
+        sys.stderr.write("bench.py: FAILED checks: %s\n" % "; ".join(bad))
+        sys.exit(3)
+
+
+TRUE_RESIDUAL_SLACK = 1.01   # the CG stops on the RECURSIVE r2 <= r2req b2; the true one agrees to rounding
+
+
+def parity_summary(parity):
+    if parity is None:
+        return None
+    return {"ok": parity["ok"], "dslash_rel_l2": parity["dslash_rel_l2"], "cg_iters": parity["cg_iters"],
+            "cg_iters_fat_naik": parity["fat_naik"]["cg_iters"], "lattice": parity["lattice"], "rankgeom": parity["rankgeom"]}
+
+
+def verdict_of_checks(parity, true_residuals, no_parity=False):
+    """Reasons this run must exit non-zero (empty list = pass).  Pure host logic (tests/test_bench_host.py)."""
+    bad = []
+    if parity is None:
+        if not no_parity:
+            bad.append("preflight parity did not run")
+    elif not parity.get("ok", False):
+        bad.append("preflight parity against the oracle failed: dslash rel-L2 %.3e, cg iters %s"
+                   % (parity.get("dslash_rel_l2", float("nan")), parity.get("cg_iters")))
+    for t in true_residuals:
+        if not (t <= TRUE_RESIDUAL_SLACK * R2REQ):
+            bad.append("true residual %.3e of a timed solve exceeds r2req = %.1e" % (t, R2REQ))
+    return bad
 
 
 def trajectory_leg(args, qb, wl, lat_shape, rankgeom, world, rank, local_rank, nsites, neven, peak, peak_src, barrier, maxreduce):

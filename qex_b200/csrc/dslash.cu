@@ -11,6 +11,7 @@
 // coalesced along the site index.  Links are streamed with ld.global.cs, vectors
 // go through the read-only path so the 8/16 neighbour re-reads hit L1/L2.
 #include "stencil.cuh"
+#include <utility>
 #include <algorithm>
 #include <cstdlib>
 
@@ -242,6 +243,9 @@ static int fill_pack(const Gauge& g, int q, const double2* x, unsigned int seq, 
       D.out_b1 = c.sendbuf + hd.off_b + (size_t)3 * hd.faceh;
       D.flag_f = D.flag_b = nullptr;
     }
+#ifdef QEXB200_FAULT_INJECT   // never in the product binary: a deliberately wrong halo (the x layers land in the U^+ x slots and
+    std::swap(D.out_f, D.out_b0);   // vice versa) to show that bench.py's preflight turns a broken exchange into exit code 3
+#endif
   }
   return end;   // work items
 }

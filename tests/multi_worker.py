@@ -313,7 +313,15 @@ def links_case(L, G, inner, rank, world, local_rank, dist):
     for mu in range(4):   # site by site the typical deviation is at rounding level
         w = mine(wfl[mu])
         site = np.linalg.norm((gfl[mu] - w).reshape(w.shape[0], -1), axis=1) / np.linalg.norm(w.reshape(w.shape[0], -1), axis=1)
-        assert np.median(site) < 2e-14, (mu, float(np.median(site)))   # rounding level (observed 0.6-1.01e-14)
+        # bar from an independent quantity: the ORACLE's own median per-site distance from the
+        # exact-projection chain (numpy SVD polar factor) on this rank's block, 4.6-4.8e-15 at these sizes.  Two correct
+        # implementations of QEX's closed-form projectU, each that far from the exact result, differ by up to twice it;
+        # another factor 2 covers the block-to-block spread.  Observed device-vs-oracle medians: 0.6-1.01e-14.
+        e = mine(efl[mu])
+        own = np.linalg.norm((w - e).reshape(w.shape[0], -1), axis=1) / np.linalg.norm(e.reshape(e.shape[0], -1), axis=1)
+        bar_site = 4.0 * float(np.median(own))
+        res.setdefault("hisq_site_median", []).append([float(np.median(site)), bar_site])
+        assert np.median(site) < bar_site, (mu, float(np.median(site)), bar_site)
     if int(os.environ.get("QEXB200_ARENA_FIELDS", "64")) >= 100:
         # fat7lDeriv and the HISQ smearedForce on the split lattice (fat7lderiv.nim:122-335, hisqsmear.nim:51-84), on
         # links near the unit gauge so that the chain is well conditioned and the bar can be tight

@@ -60,3 +60,19 @@ def test_reference_arm_has_no_line_for_the_trajectory_config():
                        capture_output=True, text=True, timeout=120)
     line = json.loads(r.stdout.strip().splitlines()[-1])
     assert r.returncode == 0 and line["impl"] == "reference" and "unavailable" in line
+
+
+def test_failed_checks_turn_into_a_non_zero_exit():
+    """rc 0 of bench.py must MEAN parity: a failed preflight, a missing preflight or a true residual above r2req each
+    give a reason (run_ours prints the line, then exits 3 when the list is not empty)."""
+    good = {"ok": True, "dslash_rel_l2": 3.7e-16, "cg_iters": [161, 161], "lattice": [8, 8, 8, 16], "rankgeom": [1, 1, 1, 2],
+            "fat_naik": {"cg_iters": [160, 160]}}
+    assert bench.verdict_of_checks(good, [8.8e-9, 9.98e-9]) == []
+    assert bench.verdict_of_checks(None, [8.8e-9], no_parity=True) == []          # --no-parity is an explicit choice
+    assert len(bench.verdict_of_checks(None, [8.8e-9])) == 1
+    assert len(bench.verdict_of_checks(dict(good, ok=False, dslash_rel_l2=0.3), [8.8e-9])) == 1
+    assert len(bench.verdict_of_checks(good, [8.8e-9, 1.2e-8])) == 1
+    assert len(bench.verdict_of_checks(good, [float("nan")])) == 1
+    s = bench.parity_summary(good)
+    assert s["ok"] and s["cg_iters"] == [161, 161] and s["cg_iters_fat_naik"] == [160, 160] and s["rankgeom"] == [1, 1, 1, 2]
+    assert bench.parity_summary(None) is None
