@@ -381,7 +381,10 @@ int qexb200_cg_destroy(qexb200_cg_t cg);
 
 /* newRNGField(RngMilc6, lo, seed) (src/rng/distributionUtils.nim:306-331): one RngMilc6 (src/rng/milcrng.nim:92-154)
  * per site, seeded with the GLOBAL lexicographic site index, so the fields do not depend on the rank geometry.  The
- * integer streams are bit-identical with QEX's; a deviate (milcrng.nim:158-188) is float32, as in QEX. */
+ * integer streams are bit-identical with QEX's; a deviate (milcrng.nim:158-188) is float32, as in QEX, but is formed
+ * with the device's log/cos: about one deviate in 1e8 differs from QEX's by one float32 ulp (the double result sits on
+ * a float32 rounding boundary and the two libms disagree in its last bit).  The 8^4 plaquettes of
+ * tests/reprod/trandgauge.nim:17 are reproduced to sum diff^2 = 9e-32 (reference bar 1e-30). */
 int qexb200_rng_create(unsigned long long seed, qexb200_rng_t* r);
 int qexb200_rng_destroy(qexb200_rng_t r);
 /* g.random r (src/gauge/gaugeUtils.nim:1348-1355,1424-1429): field by field, 18 deviates per site, projectSU. */

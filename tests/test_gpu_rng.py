@@ -83,7 +83,11 @@ def test_device_random_gauge_reproduces_the_reference_plaquettes(orc, ctx):
     pl = dg.plaq()
     obs = float(((pl - P) ** 2).sum())
     print("device g.random plaquettes vs trandgauge.nim:17: sum diff^2 = %.3e" % obs)
-    assert obs <= 1e-26, (obs, pl - P)
+    # the reference's own bar (trandgauge.nim:26: 1e-30).  Observed on a B200: 9.2e-32 (profiles/r03_cache_rng.log; the
+    # oracle reaches 1.4e-31).  Device deviates are float32 like QEX's but come from libdevice log/cos, which can differ
+    # from glibc in the last double bit and then flip the float32 rounding (rate ~1e-8 per draw, csrc/rng.cu): none of the
+    # 8^4 * 72 draws of this test is affected, a different lattice or seed may see one link change by one float32 ulp.
+    assert obs <= 1e-30, (obs, pl - P)
     dg.free(); rd.free()
 
 
