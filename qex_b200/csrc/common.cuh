@@ -60,8 +60,30 @@ struct XRank {
   unsigned long long* stamps;   // diagnostic: [0] ns spent inside xrank_sum, [1] calls, [2] longest (or nullptr)
 };
 
+// Programmatic dependent launch (sm_90+): a kernel launched with pdl = true may become resident while the kernel before
+// it in the stream is still draining its last wave.  Contract of every kernel that can be launched so: it calls
+// pdl_wait() before it touches ANY memory an earlier kernel of the stream writes (the wait returns once the previous
+// grid has completed and its writes are visible), and pdl_trigger() only AFTER its own pdl_wait() -- so kernel K+1 can
+// overlap kernel K only, never K-1, and what K+1 does before its wait need only be independent of K.  Without the launch
+// attribute both calls are no-ops.
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, cudaStream_t st, bool pdl, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = 0; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+#endif
+
 struct Context {
   bool live = false;
+  bool pdl_loop = false;   // set by the CG loop on one GPU: its sweeps and BLAS-1 kernels are launched with the PDL attribute
   int device = 0;
   Geom g;
   cudaStream_t stream = nullptr, comm_stream = nullptr;

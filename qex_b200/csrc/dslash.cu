@@ -45,6 +45,10 @@ constexpr int SWEEP_MINB = 6;
 
 template <int NL, int RC, bool DOT>
 __global__ void __launch_bounds__(SWEEP_BLOCK, SWEEP_MINB) k_sweep(const SweepArgs A) {
+  // Nothing is done before the wait: an L2 prefetch of the first wave's forward links there (they do not depend on the
+  // previous kernel) was measured SLOWER than the plain wait (32^4: 32.25 vs 31.59 ms per solve, profiles/r03_pdl_ab.log).
+  pdl_wait();      // x, the done flag and the reduction scratch belong to the kernels before this one
+  pdl_trigger();
   if (A.skip != nullptr && *A.skip != 0.0) return;
   const int idx = blockIdx.x * SWEEP_BLOCK + threadIdx.x;
   double dot = 0.0;
@@ -432,7 +436,8 @@ int sweep(const Gauge& g, int parity, double2* r, const double2* x, const double
   double* dot_interior = c.d_scal + 48;
   if (multi) A.result = dot_interior;
   if (multi && !overlap_on()) QB_CHECK(halo_wait());   // measurement switch: exchange first, then the interior
-  QB_DISPATCH(g, fused_dot, k_sweep<NL, RC, DOT><<<grid, SWEEP_BLOCK, 0, c.stream>>>(A));
+  const bool pdl = c.pdl_loop && !multi;
+  QB_DISPATCH(g, fused_dot, QB_CUDA(launch_k(k_sweep<NL, RC, DOT>, dim3(grid), dim3(SWEEP_BLOCK), c.stream, pdl, A)));
   count_launch();
   QB_CUDA(cudaGetLastError());
   if (multi) {

@@ -13,6 +13,7 @@
 // no-ops, so the iteration count and x are exactly those of the textbook loop.
 #include "stencil.cuh"
 #include <chrono>
+#include <cstdlib>
 
 namespace qb {
 
@@ -41,6 +42,8 @@ constexpr int CB = 256;
 // p = r + beta p   (cg.nim:186-193; itn==0: p := r)
 __global__ void __launch_bounds__(CB) k_cg_p(double2* __restrict__ p, const double2* __restrict__ r,
                                               const double* __restrict__ S, size_t n) {
+  pdl_wait();
+  pdl_trigger();
   if (S[S_DONE] != 0.0) return;
   const bool first = (S[S_ITN] == 0.0);
   const double beta = first ? 0.0 : S[S_R2] / S[S_R2OLD];
@@ -69,6 +72,8 @@ __global__ void __launch_bounds__(CB) k_cg_xr(double2* __restrict__ x, double2* 
                                                const double2* __restrict__ p, const double2* __restrict__ Ap,
                                                double* S, size_t n, double* partials, unsigned int* ticket,
                                                XRank* xr, CgStatus* st) {
+  pdl_wait();
+  pdl_trigger();
   if (S[S_DONE] != 0.0) {
     if (blockIdx.x == 0 && threadIdx.x == 0) cg_publish(S, st);
     return;
@@ -173,6 +178,12 @@ int apply_xx_public(const Gauge& g, int parity, double2* out, const double2* x, 
   return apply_xx(g, parity, out, x, m2, nullptr);
 }
 
+// QEXB200_PDL=0: plain stream order (A/B runs); anything else, or unset: programmatic dependent launch
+static bool pdl_enabled() {
+  static const bool on = [] { const char* e = getenv("QEXB200_PDL"); return !(e && e[0] == '0'); }();
+  return on;
+}
+
 static inline int cg_grid(size_t n) {
   size_t gsz = (n + CB - 1) / CB;
   const size_t cap = 148 * 8;
@@ -228,8 +239,13 @@ int cg_xx(const Gauge& g, int parity, double2* x, const double2* b, double m2, d
   const int LAG = 3;  // iterations the host may run ahead of the device
   int launched = 0;
   bool done = h_status[0].done != 0;  // slot 0 = state after k_cg_init (fetch_scalars synchronised)
+  // one GPU: the four kernels of an iteration are launched with the programmatic-dependent-launch attribute, so each
+  // becomes resident while its predecessor drains (common.cuh pdl_wait / pdl_trigger).  QEXB200_PDL=0 turns it off (A/B).
+  const bool pdl = (c.g.nranks == 1) && pdl_enabled();
+  c.pdl_loop = pdl;
+  struct PdlOff { Context& c; ~PdlOff() { c.pdl_loop = false; } } pdl_off{c};
   while (!done && launched < maxits - itn0) {
-    k_cg_p<<<grid, CB, 0, c.stream>>>(w_p, w_r, S, n);
+    QB_CUDA(launch_k(k_cg_p, dim3(grid), dim3(CB), c.stream, pdl, w_p, w_r, S, n));
     count_launch();
     QB_CHECK(apply_xx(g, parity, w_Ap, w_p, m2, S + S_PAP, S + S_DONE));
     QB_CHECK(allreduce_scalars(S + S_PAP, 1));
@@ -241,7 +257,8 @@ int cg_xx(const Gauge& g, int parity, double2* x, const double2* b, double m2, d
       k_cg_step<<<1, 1, 0, c.stream>>>(S, d_status);
       count_launch();
     } else {
-      k_cg_xr<<<grid, CB, 0, c.stream>>>(x, w_r, w_p, w_Ap, S, n, c.d_partials, c.d_ticket, xrank(), d_status);
+      QB_CUDA(launch_k(k_cg_xr, dim3(grid), dim3(CB), c.stream, pdl, x, w_r, w_p, w_Ap, S, n, c.d_partials, c.d_ticket,
+                       xrank(), d_status));
       count_launch();
     }
     launched++;
