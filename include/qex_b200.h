@@ -50,6 +50,10 @@ typedef struct {
   int maxits;
   int use_prev_soln; /* usePrevSoln: x on entry is the initial guess (qexb200_solve only) */
   int verbosity;
+  int sloppy_solve;  /* sloppySolve: 0 SloppyNone, 1 SloppySingle, 2 SloppyHalf (solverBase.nim:8-9,15).  ACCEPTED BUT NOT
+                        USED YET: this library has fp64 kernels only and solves in full fp64 whatever is asked -- what
+                        QEX's own backend does too (only its QUDA backend maps the field to mixed precision,
+                        src/quda/qudaWrapperImpl.nim:194-197).  sloppy_used (below) tells the caller. */
   /* outputs of THIS call (the Nim glue folds them into sp0 with addStats, solverBase.nim:75-83) */
   int calls;
   int iterations;
@@ -57,6 +61,7 @@ typedef struct {
   double seconds;
   double flops;      /* QEX flop model (g.len*4*72+60)*nEven*iterations, stagSolve.nim:92 */
   double r2;         /* solveXX: final recursive r2/b2; solve: true |b-Dx|^2/|b|^2 */
+  int sloppy_used;   /* precision the inner solve actually ran in: always 0 (fp64) in this version */
 } qexb200_solver_params;
 
 /* ---- lifetime ---------------------------------------------------------- */

@@ -22,9 +22,9 @@ class QexB200Error(RuntimeError):
 
 class _CSolverParams(C.Structure):
     _fields_ = [("r2req", C.c_double), ("maxits", C.c_int), ("use_prev_soln", C.c_int),
-                ("verbosity", C.c_int), ("calls", C.c_int), ("iterations", C.c_int),
+                ("verbosity", C.c_int), ("sloppy_solve", C.c_int), ("calls", C.c_int), ("iterations", C.c_int),
                 ("iterations_max", C.c_int), ("seconds", C.c_double), ("flops", C.c_double),
-                ("r2", C.c_double)]
+                ("r2", C.c_double), ("sloppy_used", C.c_int)]
 
 
 class HaloDir(C.Structure):
@@ -353,7 +353,9 @@ def launch_count(reset=False):
 
 # ---- SolverParams (src/solvers/solverBase.nim:10-58) ----------------------------
 class SolverParams:
-    def __init__(self, r2req=1e-6, maxits=50000, usePrevSoln=False, verbosity=1):
+    def __init__(self, r2req=1e-6, maxits=50000, usePrevSoln=False, verbosity=1, sloppySolve=0):
+        self.sloppySolve = sloppySolve   # SloppyNone/Single/Half = 0/1/2; accepted, the solve is fp64 (sloppyUsed == 0)
+        self.sloppyUsed = 0
         self.r2req = r2req
         self.maxits = maxits
         self.usePrevSoln = usePrevSoln
@@ -371,6 +373,7 @@ class SolverParams:
     def _c(self):
         c = _CSolverParams()
         c.r2req, c.maxits, c.use_prev_soln, c.verbosity = self.r2req, int(self.maxits), int(self.usePrevSoln), self.verbosity
+        c.sloppy_solve = int(self.sloppySolve)
         return c
 
     def _addStats(self, c):  # addStats, solverBase.nim:75-83
@@ -380,6 +383,7 @@ class SolverParams:
         self.seconds += c.seconds
         self.flops += c.flops
         self.r2 = c.r2
+        self.sloppyUsed = c.sloppy_used
 
     def getStats(self):  # getStats typ 3, solverBase.nim:84-112
         s = max(1e-12, self.seconds)

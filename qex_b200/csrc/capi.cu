@@ -129,8 +129,19 @@ static double now_s() {
   return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
 
+// SolverParams.sloppySolve (solverBase.nim:8-9,15).  QEX's own backend ignores it; its QUDA backend maps it to mixed
+// precision (qudaWrapperImpl.nim:194-197).  This library has fp64 kernels only: the request is accepted, the solve runs in
+// full fp64 (the returned residuals hold in fp64 either way) and sloppy_used reports that nothing narrower ran.
+static int sloppy_ok(qexb200_solver_params* sp) {
+  if (sp->sloppy_solve < 0 || sp->sloppy_solve > 2)
+    return fail("solver_params: sloppy_solve = %d, must be 0 (SloppyNone), 1 (SloppySingle) or 2 (SloppyHalf)", sp->sloppy_solve);
+  sp->sloppy_used = 0;
+  return 0;
+}
+
 // solveXX with the device backend, stagSolve.nim:57-132
 static int op_solveXX(const Gauge& g, int parity, Field& r, const Field& x, double m, qexb200_solver_params* sp) {
+  QB_CHECK(sloppy_ok(sp));
   const double t0 = now_s();
   QB_CHECK(blas_zero(r.d, 2 * nhalf()));                      // threads: r := 0   (stagSolve.nim:63-64)
   CgResult res;
@@ -205,6 +216,7 @@ static int solveInner(const Gauge& g, Field& x, const Field& b, double m, qexb20
 }
 // solve, stagSolve.nim:224-294
 static int op_solve(const Gauge& g, Field& x, const Field& b, double m, qexb200_solver_params* sp0) {
+  QB_CHECK(sloppy_ok(sp0));
   const double t0 = now_s();
   QB_CHECK(solve_work());
   Field &r = g_sw.r, &y = g_sw.y;
@@ -255,6 +267,7 @@ static int op_solve(const Gauge& g, Field& x, const Field& b, double m, qexb200_
 // (cgm.nim:169).
 static int op_solveXX_multi(const Gauge& g, int parity, Field* const* xs, const Field& b, const double* shifts,
                             int nmass, qexb200_solver_params* sp) {
+  QB_CHECK(sloppy_ok(sp));
   const double t0 = now_s();
   std::vector<double2*> xp(nmass);
   for (int m = 0; m < nmass; m++) xp[m] = hf(*xs[m], parity);
@@ -288,6 +301,7 @@ static int multi_work(int nmass, bool host) {
 // solve(s, xs, b, ms, sp0), stagSolve.nim:347-446: xs[k] = Ddag(m_k) y_k with (D Ddag)(m_k) y_k = b
 static int op_solve_multi(const Gauge& g, Field* const* xs, const Field& b, const double* ms, int nmass,
                           qexb200_solver_params* sp0) {
+  QB_CHECK(sloppy_ok(sp0));
   const double t0 = now_s();
   QB_CHECK(solve_work());
   QB_CHECK(multi_work(nmass, false));
@@ -1103,6 +1117,7 @@ int qexb200_dev_solve(qexb200_gauge_t hg, qexb200_field_t x, qexb200_field_t b, 
 // solveEO, stagSolve.nim:17-38: cgSolve(r, x, stagD2ee(m^2)) on the even subset -- r is NOT zeroed, its content is
 // the initial guess (CgState.solve forms r0 = b - A x on its first call, cg.nim:146-149)
 static int op_solveEO(const Gauge& g, Field& r, const Field& x, double m, qexb200_solver_params* sp) {
+  QB_CHECK(sloppy_ok(sp));
   const double t0 = now_s();
   CgResult res;
   QB_CHECK(cg_xx(g, 0, hf(r, 0), hf(x, 0), m * m, sp->r2req, sp->maxits, false, &res));
@@ -1147,6 +1162,7 @@ int qexb200_cg_reset(qexb200_cg_t h) {     // CgState.reset, cg.nim:21-27
   return 0;
 }
 int qexb200_cg_solve(qexb200_cg_t h, double m, qexb200_solver_params* sp) {   // CgState.solve(op, sp), cg.nim:55-254
+  QB_CHECK(sloppy_ok(sp));
   QB_CHECK(need_ctx());
   CgObj* o; QB_CHECK(get_cg(h, &o));
   Gauge* g; QB_CHECK(get_gauge(o->gauge, &g));

@@ -640,3 +640,25 @@ def test_gauge_handle_cache_of_the_glue(orc, ctx_factory):
     _, hit = qb.cachedStag(others[-1], 1)
     assert not hit
     qb.invalidateStag([g[k].copy() for k in range(4)])                # unknown pointers: not an error
+
+
+def test_sloppySolve_is_accepted_and_reported_as_fp64(orc, ctx_factory):
+    """SolverParams.sloppySolve (solverBase.nim:8-9,15; qudaWrapperImpl.nim:194-197) crosses the boundary.  There are no
+    mixed-precision kernels: SloppySingle / SloppyHalf run the same fp64 solve (bit-identical solution, same iteration
+    count) and the library says so in sloppy_used; an out-of-range value is an error, not a silent default."""
+    L = (8, 8, 8, 8)
+    qb = ctx_factory(L)
+    lat, g, (x, _) = make_inputs(L, 4)
+    s = qb.Staggered([g[k] for k in range(4)])
+    sols, its = [], []
+    for sloppy in (0, 1, 2):
+        sp = qb.SolverParams(r2req=1e-10, sloppySolve=sloppy)
+        sol = lat.vector()
+        s.solve(sol, x, 0.1, sp)
+        assert sp.sloppyUsed == 0
+        sols.append(sol); its.append(sp.iterations)
+    assert its[0] == its[1] == its[2]
+    assert np.array_equal(sols[0], sols[1]) and np.array_equal(sols[0], sols[2])
+    with pytest.raises(qb.QexB200Error, match="sloppy_solve"):
+        s.solve(lat.vector(), x, 0.1, qb.SolverParams(r2req=1e-10, sloppySolve=7))
+    s.free()
